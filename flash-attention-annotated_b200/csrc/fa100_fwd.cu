@@ -1,0 +1,146 @@
+// fa100_fwd.cu -- validation, tensor maps and launch of the forward kernel.
+// Role of set_params_fprop + run_mha_fwd + run_flash_fwd (hopper/flash_api.cpp:50-168,367-385,
+// hopper/flash_fwd_launch_template.h:30-198) for the sm_100a kernel in fa100_fwd_softmax.cuh.
+#include "fa100_host.h"
+#include "fa100_fwd_softmax.cuh"
+
+#include <algorithm>
+#include <cstring>
+
+namespace fa100 {
+
+template <int HD, int ELT, bool FP8>
+static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK,
+                           const CUtensorMap& tmV, uint32_t fmt, int grid, cudaStream_t stream) {
+  using L = FwdSmem<HD, ELT>;
+  auto kernel = fa100_fwd_kernel<HD, ELT, FP8>;
+  static bool attr_set = false;  // benign race: the call is idempotent
+  if (!attr_set) {
+    FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes));
+    attr_set = true;
+  }
+  kernel<<<grid, kThreads, L::kTotalBytes, stream>>>(kp, tmQ, tmK, tmV, fmt);
+  FA_CUDA(cudaGetLastError());
+  return FA100_OK;
+}
+
+int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stream) {
+  // ---- validation (hopper/flash_api.cpp:710-856)
+  FA_CHECK_ARG(p->q && p->k && p->v && p->o && p->lse, "q, k, v, o and lse must be non-null");
+  FA_CHECK_ARG(p->dtype == FA100_BF16 || p->dtype == FA100_FP16 || p->dtype == FA100_E4M3, "unsupported dtype %d", p->dtype);
+  FA_CHECK_ARG(p->b > 0 && p->h > 0 && p->h_k > 0 && p->h % p->h_k == 0, "bad batch/head counts b=%d h=%d h_k=%d", p->b, p->h, p->h_k);
+  FA_CHECK_ARG(p->d > 0 && p->dv > 0 && p->d % 8 == 0 && p->dv % 8 == 0, "head dims must be multiples of 8 (d=%d dv=%d)", p->d, p->dv);
+  const bool fp8 = p->dtype == FA100_E4M3;
+  const int elt = fp8 ? 1 : 2;
+  if (fp8) FA_CHECK_ARG(p->d % 16 == 0 && p->dv % 16 == 0, "fp8 head dims must be multiples of 16");
+  FA_UNSUPPORTED(p->d > 128 || p->dv > 128, "head dim > 128 not built yet (d=%d dv=%d)", p->d, p->dv);
+  FA_UNSUPPORTED(p->k_new || p->v_new || p->rotary_cos, "append-KV / rotary handled by the caller-side kernel, not fa100_fwd");
+  FA_UNSUPPORTED(fp8 && p->softcap > 0.f, "softcap with fp8 not supported");
+  const bool varlen_q = p->cu_seqlens_q != nullptr;
+  const bool varlen_k = p->cu_seqlens_k != nullptr;
+  const bool paged = p->page_table != nullptr;
+  FA_CHECK_ARG(!(paged && varlen_k), "page_table and cu_seqlens_k are exclusive");
+  if (paged) {
+    FA_CHECK_ARG(p->page_size > 0 && p->num_pages > 0, "paged KV needs page_size and num_pages");
+    FA_UNSUPPORTED(!(p->page_size % 128 == 0 || (p->page_size >= 8 && 128 % p->page_size == 0)),
+                   "page_size %d: TMA path needs a multiple of 128 or a divisor of 128 that is >= 8", p->page_size);
+    FA_UNSUPPORTED(p->leftpad_k != nullptr, "leftpad_k with paged KV not supported");
+  }
+  const int splits = plan->num_splits;
+  if (splits > 1) FA_CHECK_ARG(p->o_accum && p->lse_accum, "num_splits > 1 needs o_accum and lse_accum");
+
+  // ---- kernel parameters
+  FwdKernelParams kp;
+  std::memset(&kp, 0, sizeof(kp));
+  kp.o = p->o; kp.lse = p->lse; kp.o_accum = p->o_accum; kp.lse_accum = p->lse_accum;
+  kp.o_batch_stride = p->o_batch_stride; kp.o_row_stride = p->o_row_stride; kp.o_head_stride = p->o_head_stride;
+  const int64_t rows_q = varlen_q ? p->total_q : p->seqlen_q;
+  kp.lse_head_stride = rows_q;
+  kp.lse_batch_stride = varlen_q ? 0 : int64_t(p->h) * rows_q;
+  kp.lseacc_split_stride = (varlen_q ? 1 : int64_t(p->b)) * p->h * rows_q;
+  kp.oacc_head_stride = rows_q * p->dv;
+  kp.oacc_batch_stride = varlen_q ? 0 : int64_t(p->h) * rows_q * p->dv;
+  kp.oacc_split_stride = kp.lseacc_split_stride * p->dv;
+  kp.cu_seqlens_q = p->cu_seqlens_q; kp.cu_seqlens_k = p->cu_seqlens_k;
+  kp.seqused_q = p->seqused_q; kp.seqused_k = p->seqused_k;
+  kp.leftpad_k = p->leftpad_k; kp.kv_batch_idx = p->kv_batch_idx;
+  kp.page_table = p->page_table; kp.page_table_batch_stride = p->page_table_batch_stride;
+  kp.q_descale = p->q_descale; kp.k_descale = p->k_descale; kp.v_descale = p->v_descale;
+  kp.q_descale_batch_stride = p->q_descale_batch_stride; kp.q_descale_head_stride = p->q_descale_head_stride;
+  kp.k_descale_batch_stride = p->k_descale_batch_stride; kp.k_descale_head_stride = p->k_descale_head_stride;
+  kp.v_descale_batch_stride = p->v_descale_batch_stride; kp.v_descale_head_stride = p->v_descale_head_stride;
+  kp.b = p->b; kp.h = p->h; kp.h_k = p->h_k; kp.seqlen_q = p->seqlen_q; kp.seqlen_k = p->seqlen_k; kp.d = p->d; kp.dv = p->dv;
+  kp.page_size = paged ? p->page_size : 0;
+  kp.kv_box_rows = paged ? std::min(128, p->page_size) : 128;
+  const int G = p->h / p->h_k;
+  kp.qheads_per_kv = G;
+  kp.pack = plan->pack_gqa ? G : 1;
+  kp.pos_per_tile = 128 / kp.pack;
+  kp.num_m_blocks = std::max(1, (p->seqlen_q + 2 * kp.pos_per_tile - 1) / (2 * kp.pos_per_tile));
+  kp.heads_work = plan->pack_gqa ? p->h_k : p->h;
+  kp.num_splits = splits;
+  kp.num_work = kp.num_m_blocks * p->b * kp.heads_work * splits;
+  // causal / local normalisation (hopper/flash_api.cpp:148-160, 796-805)
+  int wl = p->window_left, wr = p->window_right;
+  bool causal = p->is_causal != 0;
+  if (causal) wr = 0;
+  const bool fixed_len = !varlen_q && !varlen_k && !p->seqused_q && !p->seqused_k && !p->leftpad_k;
+  if (fixed_len && wl >= p->seqlen_k - 1) wl = -1;
+  if (fixed_len && wr >= p->seqlen_q - 1) wr = -1;
+  kp.is_causal = (wl < 0 && wr == 0 && p->attention_chunk == 0) ? 1 : 0;
+  kp.is_local = ((wl >= 0 || wr >= 0 || p->attention_chunk > 0) && !kp.is_causal) ? 1 : 0;
+  kp.window_left = wl; kp.window_right = wr; kp.attention_chunk = p->attention_chunk;
+  kp.out_fp16 = p->dtype == FA100_FP16;
+  kp.softmax_scale = p->softmax_scale;
+  if (p->softcap > 0.f) { kp.softcap_pre = p->softmax_scale / p->softcap; kp.scale_log2 = p->softcap * kLog2e; }
+  else { kp.softcap_pre = 0.f; kp.scale_log2 = p->softmax_scale * kLog2e; }
+
+  // ---- tensor maps
+  const int cols_per_box = 128 / elt;
+  CUtensorMap tmQ, tmK, tmV;
+  {
+    const uint64_t heads3 = plan->pack_gqa ? p->h_k : p->h;
+    uint64_t dims[5] = {uint64_t(p->d), uint64_t(kp.pack), uint64_t(rows_q), heads3, uint64_t(varlen_q ? 1 : p->b)};
+    uint64_t str[5] = {0, uint64_t(p->q_head_stride) * elt, uint64_t(p->q_row_stride) * elt,
+                       uint64_t(p->q_head_stride) * kp.pack * elt, uint64_t(p->q_batch_stride) * elt};
+    uint32_t box[5] = {uint32_t(cols_per_box), uint32_t(kp.pack), uint32_t(kp.pos_per_tile), 1, 1};
+    int rc = encode_tensor_map(&tmQ, p->dtype, 5, p->q, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t rows_k = paged ? uint64_t(p->page_size) : uint64_t(varlen_k ? p->total_k : p->seqlen_k);
+    const uint64_t nb = paged ? uint64_t(p->num_pages) : uint64_t(varlen_k ? 1 : p->b_k);
+    uint32_t box[4] = {uint32_t(cols_per_box), uint32_t(kp.kv_box_rows), 1, 1};
+    uint64_t dimsK[4] = {uint64_t(p->d), rows_k, uint64_t(p->h_k), nb};
+    uint64_t strK[4] = {0, uint64_t(p->k_row_stride) * elt, uint64_t(p->k_head_stride) * elt, uint64_t(p->k_batch_stride) * elt};
+    int rc = encode_tensor_map(&tmK, p->dtype, 4, p->k, dimsK, strK, box);
+    if (rc) return rc;
+    uint64_t dimsV[4] = {uint64_t(p->dv), rows_k, uint64_t(p->h_k), nb};
+    uint64_t strV[4] = {0, uint64_t(p->v_row_stride) * elt, uint64_t(p->v_head_stride) * elt, uint64_t(p->v_batch_stride) * elt};
+    rc = encode_tensor_map(&tmV, p->dtype, 4, p->v, dimsV, strV, box);
+    if (rc) return rc;
+  }
+  FA_CHECK_ARG((p->o_row_stride % 8 == 0) && (p->o_head_stride % 8 == 0) && (p->o_batch_stride % 8 == 0) &&
+                   (reinterpret_cast<uintptr_t>(p->o) % 16 == 0),
+               "o must be 16-byte aligned with strides that are multiples of 8 elements");
+
+  int num_sm = plan->num_sm;
+  const int grid = std::max(1, std::min(kp.num_work, num_sm));
+  const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : (p->dtype == FA100_FP16 ? kFmtF16 : kFmtE4M3);
+  const int hd = (p->d <= 64 && p->dv <= 64 && !fp8) ? 64 : 128;
+  if (fp8) return launch_instance<128, 1, true>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+  if (hd == 64) return launch_instance<64, 2, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+  return launch_instance<128, 2, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+}
+
+}  // namespace fa100
+
+extern "C" int fa100_debug_hang_info(uint32_t out[4]) {
+  // reads and clears the watchdog record of this library's forward kernels
+  unsigned int h[4] = {0, 0, 0, 0}, zero[4] = {0, 0, 0, 0}, z = 0;
+  cudaError_t e = cudaMemcpyFromSymbol(h, fa100::g_fa100_hang_info, sizeof(h));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(fa100::g_fa100_hang_info, zero, sizeof(zero));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(fa100::g_fa100_abort, &z, sizeof(z));
+  for (int i = 0; i < 4; ++i) out[i] = h[i];
+  return e == cudaSuccess ? 0 : fa100::set_error(FA100_ERR_CUDA, "hang info: %s", cudaGetErrorString(e));
+}

@@ -1,0 +1,166 @@
+// fa100_fwd_kernel.cuh -- warp-specialised FlashAttention forward for sm_100a.
+//
+// Role of the reference's mainloop + softmax + mask + epilogue + tile scheduler
+// (hopper/mainloop_fwd_sm90_tma_gmma_ws.hpp:591-1352, softmax.h:92-168, mask.h:47-162, block.h:14-60,
+// epilogue_fwd.hpp:215-481, tile_scheduler.hpp), re-designed for Blackwell:
+//
+//   warps 0-3   softmax warpgroup for Q tile 0   (1 thread == 1 query row == 1 TMEM lane)
+//   warps 4-7   softmax warpgroup for Q tile 1
+//   warp  8     MMA issuer (one thread): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
+//   warp  9     TMA producer (one thread): Q tiles once per work item, K/V tiles through an mbarrier ring
+//   warps 10-11 idle (pad the third warpgroup so setmaxnreg can hand its registers to the softmax WGs)
+//
+// TMEM (512 columns): S0 @0, S1 @128, O0 @256, O1 @384; P_t (16-bit) overwrites columns [0,64) of S_t.
+// Two 128-row Q tiles per CTA ping-pong through the single MMA thread so that softmax(S_t) overlaps the
+// tensor-core work of the other tile.  O is only rescaled when the running row max grew by more than 2^8
+// (exact: the final 1/rowsum and LSE use the same stale max), and the rescale is done in place in TMEM by
+// the softmax warps, which also run the epilogue (normalise, convert, store O and LSE).
+#pragma once
+#include "fa100_ptx.cuh"
+
+namespace fa100 {
+
+constexpr int kBlockM = 128;   // query rows per Q tile
+constexpr int kBlockN = 128;   // keys per main-loop step
+constexpr int kQTiles = 2;     // Q tiles per CTA
+constexpr int kThreads = 384;
+constexpr int kMmaWarp = 8;
+constexpr int kLoadWarp = 9;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr float kRescaleThreshold = 8.0f;  // log2 units
+
+struct FwdKernelParams {
+  void* o;
+  float* lse;
+  float* o_accum;
+  float* lse_accum;
+  int64_t o_batch_stride, o_row_stride, o_head_stride;            // elements
+  int64_t oacc_split_stride, oacc_batch_stride, oacc_head_stride; // fp32 elements; row stride == dv
+  int64_t lse_batch_stride, lse_head_stride;                      // fp32 elements; row stride == 1
+  int64_t lseacc_split_stride;
+  const int32_t* cu_seqlens_q;
+  const int32_t* cu_seqlens_k;
+  const int32_t* seqused_q;
+  const int32_t* seqused_k;
+  const int32_t* leftpad_k;
+  const int32_t* kv_batch_idx;
+  const int32_t* page_table;
+  int64_t page_table_batch_stride;
+  const float* q_descale;
+  const float* k_descale;
+  const float* v_descale;
+  int64_t q_descale_batch_stride, q_descale_head_stride;
+  int64_t k_descale_batch_stride, k_descale_head_stride;
+  int64_t v_descale_batch_stride, v_descale_head_stride;
+  int32_t b, h, h_k, seqlen_q, seqlen_k, d, dv;
+  int32_t page_size;      // 0 = not paged
+  int32_t kv_box_rows;    // rows per K/V TMA box: min(128, page_size)
+  int32_t qheads_per_kv;  // G
+  int32_t pack;           // Gp: G when pack_gqa else 1
+  int32_t pos_per_tile;   // 128 / Gp query positions per Q tile
+  int32_t num_m_blocks;   // ceil(max_seqlen_q / (2 * pos_per_tile))
+  int32_t heads_work;     // h_k when packed else h
+  int32_t num_splits;
+  int32_t num_work;
+  int32_t is_causal, is_local, window_left, window_right, attention_chunk;
+  int32_t out_fp16;       // 1: fp16 output, 0: bf16 output
+  float scale_log2;       // softmax_scale * log2(e)   (softcap: softcap * log2(e))
+  float softcap_pre;      // softmax_scale / softcap, 0 when softcap is off
+  float softmax_scale;
+};
+
+// ----------------------------------------------------------------------------- geometry shared by all roles
+struct WorkItem { int m_blk, head, bi, split; };
+
+struct SeqInfo {
+  int sq, sk;      // this batch element's lengths
+  int q_off;       // row offset of the sequence inside a packed q / o / lse
+  int k_off;       // row offset inside k/v (packed offset + left pad)
+  int bq, bk;      // batch coordinates for TMA (0 when packed)
+};
+
+struct TileRange { int n_min, n_max; bool has_rows; };
+
+FA_DEVICE WorkItem decode_work(const FwdKernelParams& p, int w) {
+  // w = ((m_rev * b + bi) * heads + head) * splits + split : heads of one KV group and the splits of one
+  // row block are neighbours (run at the same time on different SMs -> share K/V in L2); long (late) causal
+  // row blocks come first (LPT).
+  WorkItem it;
+  it.split = w % p.num_splits; w /= p.num_splits;
+  it.head = w % p.heads_work;  w /= p.heads_work;
+  it.bi = w % p.b;             w /= p.b;
+  it.m_blk = p.num_m_blocks - 1 - w;
+  return it;
+}
+
+FA_DEVICE SeqInfo load_seq(const FwdKernelParams& p, int bi) {
+  SeqInfo s;
+  const int leftpad = p.leftpad_k ? p.leftpad_k[bi] : 0;
+  s.q_off = p.cu_seqlens_q ? p.cu_seqlens_q[bi] : 0;
+  s.k_off = (p.cu_seqlens_k ? p.cu_seqlens_k[bi] : 0) + leftpad;
+  s.sq = p.seqused_q ? p.seqused_q[bi] : (p.cu_seqlens_q ? p.cu_seqlens_q[bi + 1] - p.cu_seqlens_q[bi] : p.seqlen_q);
+  s.sk = (p.seqused_k ? p.seqused_k[bi] : (p.cu_seqlens_k ? p.cu_seqlens_k[bi + 1] - p.cu_seqlens_k[bi] : p.seqlen_k)) - leftpad;
+  s.bq = p.cu_seqlens_q ? 0 : bi;
+  s.bk = p.cu_seqlens_k ? 0 : (p.kv_batch_idx ? p.kv_batch_idx[bi] : bi);
+  return s;
+}
+
+FA_DEVICE int floor_mod(int x, int m) { int r = x % m; return r < 0 ? r + m : r; }
+
+// Key-block range of one Q tile (arithmetic of hopper/block.h:14-60, on 128-row tiles; -1 windows = unbounded).
+FA_DEVICE TileRange tile_range(const FwdKernelParams& p, const SeqInfo& s, int pos0, int split) {
+  TileRange r;
+  r.has_rows = pos0 < s.sq;
+  r.n_min = 0; r.n_max = 0;
+  if (!r.has_rows) return r;
+  const int pos_end = min(pos0 + p.pos_per_tile, s.sq);
+  const int shift = s.sk - s.sq;
+  int n_max = (s.sk + kBlockN - 1) / kBlockN;
+  int n_min = 0;
+  if (p.is_causal || p.is_local) {
+    if (p.is_causal || p.window_right >= 0 || p.attention_chunk > 0) {
+      int right = pos_end + shift + ((p.is_local && p.window_right >= 0) ? p.window_right : 0);
+      if (p.is_local && p.window_right < 0) right = s.sk;
+      if (p.is_local && p.attention_chunk > 0) {
+        const int x = pos_end - 1 + shift;  // last row's absolute position
+        right = min(right, x - floor_mod(x, p.attention_chunk) + p.attention_chunk);
+      }
+      n_max = min(n_max, right <= 0 ? 0 : (right + kBlockN - 1) / kBlockN);
+    }
+    if (p.is_local) {
+      int left = (p.window_left >= 0) ? pos0 + shift - p.window_left : 0;
+      if (p.attention_chunk > 0) { const int x = pos0 + shift; left = max(left, x - floor_mod(x, p.attention_chunk)); }
+      n_min = max(0, left / kBlockN);
+    }
+  }
+  if (p.num_splits > 1) {
+    const int per = n_max <= n_min ? 0 : (n_max - n_min + p.num_splits - 1) / p.num_splits;
+    n_min = n_min + split * per;
+    n_max = min(n_min + per, n_max);
+  }
+  r.n_min = n_min; r.n_max = max(n_max, n_min);
+  return r;
+}
+
+// ----------------------------------------------------------------------------- shared memory
+template <int HD, int ELT>
+struct FwdSmem {
+  static constexpr int kQBytes = kBlockM * HD * ELT;   // one Q tile
+  static constexpr int kKVBytes = kBlockN * HD * ELT;  // one K or V tile
+  static constexpr int kBudget = 227 * 1024 - 2048;    // barriers + 1 KB alignment slack
+  static constexpr int kStagesRaw = (kBudget - kQTiles * kQBytes) / kKVBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kDataBytes = kQTiles * kQBytes + kStages * kKVBytes;
+  static constexpr int kTotalBytes = kDataBytes + 1024 /*align*/ + 512 /*barriers*/;
+};
+
+struct FwdBarriers {
+  uint64_t q_full[kQTiles], q_empty[kQTiles];
+  uint64_t s_full[kQTiles], p_full[kQTiles];
+  uint64_t o_full[kQTiles], o_empty[kQTiles];
+  uint64_t kv_full[8], kv_empty[8];
+  uint32_t tmem_base;
+};
+
+}  // namespace fa100

@@ -1,0 +1,297 @@
+"""Host layer of the forward path: validation, allocation, normalisation and the calls into libfa100.so.
+
+Python counterpart of the reference's ``mha_fwd`` / ``mha_combine`` / ``mha_fwd_get_scheduler_metadata``
+(hopper/flash_api.cpp:672-1198, :1569-1670, :521-662).  Registered below as
+``torch.ops.flash_attn_3.{fwd,fwd_combine,get_scheduler_metadata,bwd}`` with the reference's frozen schemas
+(hopper/flash_api.cpp:1672-1761, pinned by hopper/test_flash_attn.py:1163-1201).  PyTorch is plumbing here:
+device memory, the current stream, nothing else -- all arithmetic runs in the CUDA library.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+import fa100_native as N
+
+_DT = {torch.bfloat16: N.BF16, torch.float16: N.FP16, torch.float8_e4m3fn: N.E4M3, torch.float32: N.FP32}
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _chk(cond, msg):
+    if not cond:
+        raise RuntimeError(msg)
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _i32(t, name, n=None):
+    _chk(t.dtype == torch.int32, f"{name} must have dtype torch.int32")
+    _chk(t.is_cuda and t.is_contiguous(), f"{name} must be a contiguous CUDA tensor")
+    if n is not None:
+        _chk(t.numel() == n, f"{name} must have shape ({n},)")
+
+
+def plan(b, seqlen_q, seqlen_k, h, h_k, d, dv, dtype, causal, local, num_splits, pack_gqa, sm_margin, device=None):
+    """Sizes-only policy (num_splits, pack_gqa, #work items); the role of get_num_splits/get_pack_gqa."""
+    num_sm = torch.cuda.get_device_properties(device if device is not None else torch.cuda.current_device()).multi_processor_count
+    s = N.Shape(b=b, seqlen_q=seqlen_q, seqlen_k=seqlen_k, h=h, h_k=h_k, d=d, dv=dv, dtype=_DT[dtype],
+                is_causal=int(causal), is_local=int(local), num_splits=int(num_splits),
+                pack_gqa=-1 if pack_gqa is None else int(bool(pack_gqa)), num_sm=max(1, num_sm - sm_margin))
+    p = N.Plan()
+    N.check(N.lib().fa100_plan(C.byref(s), C.byref(p)))
+    return p
+
+
+def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=None, cu_seqlens_k=None,
+            cu_seqlens_k_new=None, seqused_q=None, seqused_k=None, max_seqlen_q=None, max_seqlen_k=None,
+            page_table=None, kv_batch_idx=None, leftpad_k=None, rotary_cos=None, rotary_sin=None,
+            seqlens_rotary=None, q_descale=None, k_descale=None, v_descale=None, softmax_scale=None,
+            is_causal=False, window_size_left=-1, window_size_right=-1, attention_chunk=0, softcap=0.0,
+            is_rotary_interleaved=False, scheduler_metadata=None, num_splits=0, pack_gqa=None, sm_margin=0):
+    _chk(q.is_cuda and k.is_cuda and v.is_cuda, "q, k, v must be CUDA tensors (there is no CPU path)")
+    qt = q.dtype
+    _chk(qt in (torch.bfloat16, torch.float16, torch.float8_e4m3fn), "FlashAttention only supports fp16, bf16, and fp8_e4m3 data type")
+    _chk(k.dtype == qt and v.dtype == qt, "query, key and value must have the same dtype")
+    _chk(q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Input tensor must have contiguous last dimension")
+    if q_v is not None:
+        raise NotImplementedError("fa100: qv (MLA-style absorbed heads) is not built yet")
+    paged = page_table is not None
+    varlen_q = cu_seqlens_q is not None
+    varlen_k = cu_seqlens_k is not None
+    _chk(not (paged and varlen_k), "If cu_seqlens_k is passed in, then page table is not supported")
+    if varlen_q:
+        _i32(cu_seqlens_q, "cu_seqlens_q")
+        _chk(max_seqlen_q is not None, "max_seqlen_q must be provided if cu_seqlens_q is provided")
+        _chk(q.dim() == 3, "q must be (total_q, nheads, headdim) when cu_seqlens_q is given")
+    if varlen_k:
+        _i32(cu_seqlens_k, "cu_seqlens_k")
+        _chk(max_seqlen_k is not None, "max_seqlen_k must be provided if cu_seqlens_k is provided")
+        _chk(k.dim() == 3, "k must be (total_k, nheads_k, headdim) when cu_seqlens_k is given")
+    b = (cu_seqlens_q.numel() - 1) if varlen_q else q.shape[0]
+    seqlen_q = max_seqlen_q if varlen_q else q.shape[1]
+    total_q = q.shape[0] if varlen_q else 0
+    h, d = q.shape[-2], q.shape[-1]
+    h_k, dv = k.shape[-2], v.shape[-1]
+    if paged:
+        _i32(page_table, "page_table")
+        _chk(page_table.dim() == 2 and page_table.shape[0] == b, "page_table must have shape (batch_size, max_num_pages_per_seq)")
+        num_pages, page_size = k.shape[0], k.shape[1]
+        seqlen_k = page_table.shape[1] * page_size
+        b_k = num_pages
+        _chk(tuple(v.shape) == (num_pages, page_size, h_k, dv), "v has the wrong paged shape")
+    else:
+        num_pages = page_size = 0
+        seqlen_k = max_seqlen_k if varlen_k else k.shape[1]
+        b_k = (cu_seqlens_k.numel() - 1) if varlen_k else k.shape[0]
+        if not varlen_k:
+            _chk(tuple(v.shape) == (b_k, seqlen_k, h_k, dv), "v has the wrong shape")
+    total_k = k.shape[0] if varlen_k else 0
+    _chk(k.shape[-1] == d, "k must have the same head dim as q")
+    _chk(h % h_k == 0, "Number of heads in key/value must divide number of heads in query")
+    if kv_batch_idx is None and not varlen_k and not paged:
+        _chk(b_k == b, "batch_size must be equal to batch_size_k")
+    for t, nm in ((seqused_q, "seqused_q"), (seqused_k, "seqused_k"), (leftpad_k, "leftpad_k"), (kv_batch_idx, "kv_batch_idx")):
+        if t is not None:
+            _i32(t, nm, b)
+    if leftpad_k is not None:
+        _chk(not paged, "leftpad_k is not supported with paged KV")
+    align = 16 if qt == torch.float8_e4m3fn else 8
+    _chk(d % align == 0 and dv % align == 0, f"head dims must be multiples of {align} for {qt}")
+    if k_new is not None or v_new is not None or rotary_cos is not None:
+        raise NotImplementedError("fa100: append-KV / rotary (k, v, rotary_cos of flash_attn_with_kvcache) is not built yet")
+    if softmax_scale is None:
+        softmax_scale = d ** -0.5
+    if is_causal:
+        window_size_right = 0
+    is_local = (window_size_left >= 0 or window_size_right >= 0 or attention_chunk > 0) and not (
+        window_size_left < 0 and window_size_right == 0 and attention_chunk == 0)
+
+    out_dtype = torch.bfloat16 if qt == torch.float8_e4m3fn else qt
+    out_shape = (total_q, h, dv) if varlen_q else (b, seqlen_q, h, dv)
+    if out is None:
+        out = torch.empty(out_shape, dtype=out_dtype, device=q.device)
+    else:
+        _chk(out.dtype == out_dtype and tuple(out.shape) == out_shape and out.stride(-1) == 1 and out.device == q.device,
+             "out has the wrong dtype / shape / layout")
+    lse = torch.empty((h, total_q) if varlen_q else (b, h, seqlen_q), dtype=torch.float32, device=q.device)
+    empty = torch.empty(0, dtype=torch.float32, device=q.device)
+    if seqlen_k == 0 or out.numel() == 0:  # hopper/flash_api.cpp:1190-1194
+        out.zero_()
+        lse.fill_(float("inf"))
+        return out, lse, empty, empty
+    if scheduler_metadata is not None:
+        _chk(scheduler_metadata.dtype == torch.int32 and scheduler_metadata.is_cuda and scheduler_metadata.is_contiguous(),
+             "scheduler_metadata must be a contiguous int32 CUDA tensor")
+
+    pl = plan(b, seqlen_q, seqlen_k, h, h_k, d, dv, qt, is_causal, is_local, num_splits, pack_gqa, sm_margin, q.device)
+    splits = pl.num_splits
+    out_accum = lse_accum = None
+    if splits > 1:
+        if varlen_q:
+            out_accum = torch.empty((splits, h, total_q, dv), dtype=torch.float32, device=q.device)
+            lse_accum = torch.empty((splits, h, total_q), dtype=torch.float32, device=q.device)
+        else:
+            out_accum = torch.empty((splits, b, h, seqlen_q, dv), dtype=torch.float32, device=q.device)
+            lse_accum = torch.empty((splits, b, h, seqlen_q), dtype=torch.float32, device=q.device)
+
+    p = N.FwdParams()
+    p.q, p.k, p.v, p.o, p.lse = _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(lse)
+    if varlen_q:
+        p.q_batch_stride, p.q_row_stride, p.q_head_stride = 0, q.stride(0), q.stride(1)
+        p.o_batch_stride, p.o_row_stride, p.o_head_stride = 0, out.stride(0), out.stride(1)
+    else:
+        p.q_batch_stride, p.q_row_stride, p.q_head_stride = q.stride(0), q.stride(1), q.stride(2)
+        p.o_batch_stride, p.o_row_stride, p.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
+    if varlen_k:
+        p.k_batch_stride, p.k_row_stride, p.k_head_stride = 0, k.stride(0), k.stride(1)
+        p.v_batch_stride, p.v_row_stride, p.v_head_stride = 0, v.stride(0), v.stride(1)
+    else:
+        p.k_batch_stride, p.k_row_stride, p.k_head_stride = k.stride(0), k.stride(1), k.stride(2)
+        p.v_batch_stride, p.v_row_stride, p.v_head_stride = v.stride(0), v.stride(1), v.stride(2)
+    p.o_accum, p.lse_accum = _ptr(out_accum), _ptr(lse_accum)
+    p.b, p.b_k, p.seqlen_q, p.seqlen_k, p.total_q, p.total_k = b, b_k, seqlen_q, seqlen_k, total_q, total_k
+    p.h, p.h_k, p.d, p.dv, p.dtype = h, h_k, d, dv, _DT[qt]
+    p.cu_seqlens_q, p.cu_seqlens_k = _ptr(cu_seqlens_q), _ptr(cu_seqlens_k)
+    p.seqused_q, p.seqused_k, p.leftpad_k, p.kv_batch_idx = _ptr(seqused_q), _ptr(seqused_k), _ptr(leftpad_k), _ptr(kv_batch_idx)
+    if paged:
+        p.page_table, p.page_table_batch_stride = _ptr(page_table), page_table.stride(0)
+        p.page_size, p.num_pages = page_size, num_pages
+    for nm, t in (("q", q_descale), ("k", k_descale), ("v", v_descale)):
+        if t is not None:
+            _chk(qt == torch.float8_e4m3fn or True, "")
+            _chk(t.dtype == torch.float32 and t.is_cuda and tuple(t.shape) == (b, h_k), f"{nm}_descale must be fp32 (batch, nheads_k)")
+            setattr(p, f"{nm}_descale", _ptr(t))
+            setattr(p, f"{nm}_descale_batch_stride", t.stride(0))
+            setattr(p, f"{nm}_descale_head_stride", t.stride(1))
+    p.softmax_scale, p.softcap = float(softmax_scale), float(softcap)
+    p.is_causal, p.window_left, p.window_right, p.attention_chunk = int(is_causal), window_size_left, window_size_right, attention_chunk
+    p.num_splits, p.pack_gqa, p.num_sm = splits, pl.pack_gqa, pl.num_sm
+    with torch.cuda.device(q.device):
+        N.check(N.lib().fa100_fwd(C.byref(p), _stream()))
+        if splits > 1:
+            if varlen_q:  # (splits, h, total_q, dv) viewed as (splits, b=1, s=total_q, h, dv)
+                op = out_accum.permute(0, 2, 1, 3).unsqueeze(1)
+                lp = lse_accum.permute(0, 2, 1).unsqueeze(1)
+                _combine_into(op, lp, out.unsqueeze(0), lse.t().unsqueeze(0))
+            else:
+                _combine_into(out_accum.permute(0, 1, 3, 2, 4), lse_accum.permute(0, 1, 3, 2), out, lse.permute(0, 2, 1))
+    return out, lse, (out_accum if out_accum is not None else empty), (lse_accum if lse_accum is not None else empty)
+
+
+def _combine_into(op, lp, out, lse):
+    """op (splits,b,s,h,d) fp32, lp (splits,b,s,h) fp32, out (b,s,h,d), lse (b,s,h) -- any strides, d stride 1."""
+    splits, b, s, h, d = op.shape
+    c = N.CombineParams()
+    c.o_partial, c.lse_partial, c.o, c.lse = _ptr(op), _ptr(lp), _ptr(out), _ptr(lse)
+    c.op_split_stride, c.op_batch_stride, c.op_row_stride, c.op_head_stride = op.stride(0), op.stride(1), op.stride(2), op.stride(3)
+    c.lp_split_stride, c.lp_batch_stride, c.lp_row_stride, c.lp_head_stride = lp.stride(0), lp.stride(1), lp.stride(2), lp.stride(3)
+    c.o_batch_stride, c.o_row_stride, c.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
+    c.lse_batch_stride, c.lse_row_stride, c.lse_head_stride = lse.stride(0), lse.stride(1), lse.stride(2)
+    c.num_splits, c.b, c.s, c.h, c.d, c.out_dtype = splits, b, s, h, d, _DT[out.dtype]
+    N.check(N.lib().fa100_combine(C.byref(c), _stream()))
+
+
+def mha_combine(out_partial, lse_partial, out=None, out_dtype=None):
+    """hopper/flash_api.cpp:1569-1670: out_partial (splits,b,s,h,d) fp32, lse_partial (splits,b,s,h) fp32."""
+    _chk(out_partial.is_cuda and lse_partial.is_cuda, "inputs must be CUDA tensors")
+    _chk(out_partial.dtype == torch.float32 and lse_partial.dtype == torch.float32, "FlashAttention combine only supports fp32 partials")
+    _chk(out_partial.dim() == 5 and lse_partial.dim() == 4, "out_partial must be 5-D and lse_partial 4-D")
+    _chk(out_partial.stride(-1) == 1, "Input tensor must have contiguous last dimension")
+    splits, b, s, h, d = out_partial.shape
+    _chk(tuple(lse_partial.shape) == (splits, b, s, h), "lse_partial has the wrong shape")
+    _chk(1 <= splits <= 256, "FlashAttention combine only supports num_splits at most 256")
+    if out_dtype is None:
+        out_dtype = out.dtype if out is not None else torch.float32
+    _chk(out_dtype in (torch.float32, torch.float16, torch.bfloat16), "out_dtype must be fp32, fp16 or bf16")
+    d4 = (d + 3) // 4 * 4
+    op = out_partial
+    if d4 != d or any(st % 4 for st in op.stride()[:-1]) or op.data_ptr() % 16:
+        op = torch.nn.functional.pad(out_partial, (0, d4 - d)).contiguous()
+    if out is None:
+        out_p = torch.empty((b, s, h, d4), dtype=out_dtype, device=op.device)
+    else:
+        _chk(tuple(out.shape) == (b, s, h, d) and out.dtype == out_dtype and out.stride(-1) == 1, "out has the wrong shape/dtype")
+        out_p = out if d4 == d and all(st % 4 == 0 for st in out.stride()[:-1]) else torch.empty((b, s, h, d4), dtype=out_dtype, device=op.device)
+    lse = torch.empty((b, h, s), dtype=torch.float32, device=op.device).transpose(1, 2)  # (b, s, h) view, s contiguous
+    with torch.cuda.device(op.device):
+        _combine_into(op, lse_partial, out_p, lse)
+    if out is None:
+        out = out_p[..., :d] if d4 != d else out_p
+    elif out_p is not out:
+        out.copy_(out_p[..., :d])
+    return out, lse
+
+
+def mha_fwd_get_scheduler_metadata(batch_size, max_seqlen_q, max_seqlen_k, num_heads, num_heads_k, headdim, headdim_v,
+                                   qkv_dtype, seqused_k, cu_seqlens_q=None, cu_seqlens_k=None, cu_seqlens_k_new=None,
+                                   seqused_q=None, leftpad_k=None, page_size=None, max_seqlen_k_new=0, is_causal=False,
+                                   window_size_left=-1, window_size_right=-1, attention_chunk=0, has_softcap=False,
+                                   num_splits=0, pack_gqa=None, sm_margin=0):
+    """Ahead-of-time plan for CUDA-graphed decode (hopper/flash_api.cpp:521-662).  The fa100 schedule is a pure
+    function of sizes, so the tensor only records it: [magic, num_splits, pack_gqa, num_sm, num_work, 0, 0, 0]."""
+    if is_causal:
+        window_size_right = 0
+    is_local = (window_size_left >= 0 or window_size_right >= 0 or attention_chunk > 0) and not (
+        window_size_left < 0 and window_size_right == 0 and attention_chunk == 0)
+    pl = plan(batch_size, max_seqlen_q, max_seqlen_k + max_seqlen_k_new, num_heads, num_heads_k, headdim, headdim_v, qkv_dtype,
+              is_causal, is_local, num_splits, pack_gqa, sm_margin, seqused_k.device)
+    return torch.tensor([0xFA100, pl.num_splits, pl.pack_gqa, pl.num_sm, pl.num_work, 0, 0, 0], dtype=torch.int32,
+                        device=seqused_k.device)
+
+
+def mha_bwd(*args, **kwargs):
+    raise NotImplementedError("fa100 is a forward-only build: flash_attn_3::bwd is out of scope (SURVEY.md 8f rank 2)")
+
+
+# ----------------------------------------------------------------------------- torch.library registration
+_FWD_SCHEMA = (
+    "(Tensor q, Tensor k, Tensor v, Tensor(k_new!)? k_new = None, Tensor(v_new!)? v_new = None, Tensor? q_v = None, "
+    "Tensor(out!)? out = None, Tensor? cu_seqlens_q = None, Tensor? cu_seqlens_k = None, Tensor? cu_seqlens_k_new = None, "
+    "Tensor? seqused_q = None, Tensor? seqused_k = None, int? max_seqlen_q = None, int? max_seqlen_k = None, "
+    "Tensor? page_table = None, Tensor? kv_batch_idx = None, Tensor? leftpad_k = None, Tensor? rotary_cos = None, "
+    "Tensor? rotary_sin = None, Tensor? seqlens_rotary = None, Tensor? q_descale = None, Tensor? k_descale = None, "
+    "Tensor? v_descale = None, float? softmax_scale = None, bool is_causal = False, int window_size_left = -1, "
+    "int window_size_right = -1, int attention_chunk = 0, float softcap = 0.0, bool is_rotary_interleaved = False, "
+    "Tensor? scheduler_metadata = None, int num_splits = 0, bool? pack_gqa = None, int sm_margin = 0) "
+    "-> (Tensor(out!), Tensor, Tensor, Tensor)")
+_BWD_SCHEMA = (
+    "(Tensor dout, Tensor q, Tensor k, Tensor v, Tensor out, Tensor softmax_lse, Tensor(dq!)? dq = None, "
+    "Tensor(dk!)? dk = None, Tensor(dv!)? dv = None, Tensor? cu_seqlens_q = None, Tensor? cu_seqlens_k = None, "
+    "Tensor? seqused_q = None, Tensor? seqused_k = None, int? max_seqlen_q = None, int? max_seqlen_k = None, "
+    "float? softmax_scale = None, bool is_causal = False, int window_size_left = -1, int window_size_right = -1, "
+    "float softcap = 0.0, bool deterministic = False, int sm_margin = 0) "
+    "-> (Tensor(dq!), Tensor(dk!), Tensor(dv!), Tensor, Tensor, Tensor, Tensor, Tensor)")
+_COMBINE_SCHEMA = "(Tensor out_partial, Tensor lse_partial, Tensor(out!)? out = None, ScalarType? out_dtype = None) -> (Tensor(out!), Tensor)"
+_META_SCHEMA = (
+    "(int batch_size, int max_seqlen_q, int max_seqlen_k, int num_heads, int num_heads_k, int headdim, int headdim_v, "
+    "ScalarType qkv_dtype, Tensor seqused_k, Tensor? cu_seqlens_q = None, Tensor? cu_seqlens_k = None, "
+    "Tensor? cu_seqlens_k_new = None, Tensor? seqused_q = None, Tensor? leftpad_k = None, int? page_size = None, "
+    "int max_seqlen_k_new = 0, bool is_causal = False, int window_size_left = -1, int window_size_right = -1, "
+    "int attention_chunk = 0, bool has_softcap = False, int num_splits = 0, bool? pack_gqa = None, int sm_margin = 0) -> Tensor")
+
+_lib_def = None
+
+
+def register_ops():
+    """Define flash_attn_3::* once per process; CUDA dispatch key only, like the reference (no CPU/Meta kernels)."""
+    global _lib_def
+    if _lib_def is not None:
+        return
+    if hasattr(torch.ops, "flash_attn_3") and hasattr(torch.ops.flash_attn_3, "fwd"):
+        raise RuntimeError("torch.ops.flash_attn_3 is already defined by another extension in this process")
+    _lib_def = torch.library.Library("flash_attn_3", "DEF")
+    _lib_def.define("fwd" + _FWD_SCHEMA)
+    _lib_def.define("bwd" + _BWD_SCHEMA)
+    _lib_def.define("fwd_combine" + _COMBINE_SCHEMA)
+    _lib_def.define("get_scheduler_metadata" + _META_SCHEMA)
+    _lib_def.impl("fwd", mha_fwd, "CUDA")
+    _lib_def.impl("bwd", mha_bwd, "CUDA")
+    _lib_def.impl("fwd_combine", mha_combine, "CUDA")
+    _lib_def.impl("get_scheduler_metadata", mha_fwd_get_scheduler_metadata, "CUDA")

@@ -1,0 +1,176 @@
+/* fa100.h -- C ABI of the B200-native FlashAttention forward (libfa100.so).
+ *
+ * This is the drop-in boundary for the reference's forward path.  In the reference the same
+ * boundary is in-process C++ (all paths relative to the reference tree):
+ *   run_mha_fwd(Flash_fwd_params&, cudaStream_t)                    hopper/flash_api.cpp:367
+ *   run_mha_fwd_combine(Flash_fwd_params&, cudaStream_t, bool)      hopper/flash_api.cpp:387
+ *   prepare_varlen_num_blocks(params, stream, ...)                  hopper/flash.h:220
+ *   get_num_splits / get_pack_gqa heuristics                        hopper/flash_api.cpp:426-470
+ * and its torch-free precedent is
+ *   int flash::flash_attention_forward(FlashAttentionParams&, cudaStream_t)
+ *                                                                    standalone/include/flash_api.h:222-247
+ * The struct below is the subset of Flash_fwd_params (hopper/flash.h:12-168) this path needs.
+ *
+ * Rules: plain pointers and sizes only (no torch types); the library allocates nothing, keeps no
+ * pointer after a call returns, launches on the caller's stream and never synchronises, so every
+ * call is re-entrant and CUDA-graph capturable.  Every function returns 0 on success or a negative
+ * FA100_ERR_* code; fa100_last_error() gives the thread-local message.  Nothing ever calls exit().
+ */
+#ifndef FA100_H_
+#define FA100_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FA100_ABI_VERSION 1
+
+enum {
+  FA100_OK = 0,
+  FA100_ERR_INVALID = -1,     /* bad argument (shape, stride, alignment, null pointer) */
+  FA100_ERR_UNSUPPORTED = -2, /* valid request this build has no kernel for (raise NotImplementedError) */
+  FA100_ERR_CUDA = -3         /* CUDA driver/runtime error, text in fa100_last_error() */
+};
+
+enum { FA100_BF16 = 0, FA100_FP16 = 1, FA100_E4M3 = 2, FA100_FP32 = 3 };
+
+typedef void* fa100_stream_t; /* cudaStream_t */
+
+/* All strides are in ELEMENTS of the tensor's dtype; the last (head-dim) stride is always 1.
+ * Layouts: q (b, sq, h, d) or packed (total_q, h, d) with cu_seqlens_q;
+ * k/v (b_k, sk, h_k, d|dv), packed (total_k, h_k, d), or paged (num_pages, page_size, h_k, d);
+ * o like q with dv; lse fp32 (b, h, sq) or (h, total_q). */
+typedef struct Fa100FwdParams {
+  /* tensors */
+  const void* q;
+  const void* k;
+  const void* v;
+  void* o;             /* out dtype: same as q for bf16/fp16, bf16 for e4m3 */
+  float* lse;          /* (b, h, sq) contiguous, or (h, total_q) when cu_seqlens_q is set */
+  int64_t q_batch_stride, q_row_stride, q_head_stride;
+  int64_t k_batch_stride, k_row_stride, k_head_stride; /* batch stride == page stride when paged */
+  int64_t v_batch_stride, v_row_stride, v_head_stride;
+  int64_t o_batch_stride, o_row_stride, o_head_stride;
+
+  /* split-KV partials, required when num_splits > 1 (hopper/flash_api.cpp:1094-1113):
+   * o_accum fp32 (splits, b, h, sq, dv) / (splits, h, total_q, dv); lse_accum fp32 (splits, b, h, sq) / (splits, h, total_q) */
+  float* o_accum;
+  float* lse_accum;
+
+  /* sizes */
+  int32_t b;           /* batch of q */
+  int32_t b_k;         /* batch of the k/v tensor (cache batch; num_pages when paged) */
+  int32_t seqlen_q;    /* max seqlen_q when varlen */
+  int32_t seqlen_k;    /* max seqlen_k (cache capacity for a kv-cache; page_size*max_pages when paged) */
+  int32_t total_q;     /* rows of q when cu_seqlens_q is set, else 0 */
+  int32_t total_k;     /* rows of k when cu_seqlens_k is set, else 0 */
+  int32_t h, h_k;
+  int32_t d, dv;
+  int32_t dtype;       /* FA100_BF16 / FA100_FP16 / FA100_E4M3 */
+
+  /* variable length (all int32 device pointers, may be null) */
+  const int32_t* cu_seqlens_q; /* (b+1) */
+  const int32_t* cu_seqlens_k; /* (b+1) */
+  const int32_t* seqused_q;    /* (b)   */
+  const int32_t* seqused_k;    /* (b)   cache_seqlens */
+  const int32_t* leftpad_k;    /* (b)   */
+  const int32_t* kv_batch_idx; /* (b)   cache_batch_idx */
+
+  /* paged KV */
+  const int32_t* page_table;   /* (b, max_pages_per_seq) */
+  int64_t page_table_batch_stride;
+  int32_t page_size;
+  int32_t num_pages;
+
+  /* append-KV + rotary (hopper/flash_api.cpp:1036-1092) */
+  const void* k_new;           /* (b, s_new, h_k, d) or (total_k_new, h_k, d) */
+  const void* v_new;
+  int64_t knew_batch_stride, knew_row_stride, knew_head_stride;
+  int64_t vnew_batch_stride, vnew_row_stride, vnew_head_stride;
+  int32_t seqlen_knew;
+  int32_t total_knew;
+  const int32_t* cu_seqlens_knew;
+  const void* rotary_cos;      /* (seqlen_ro, rotary_dim/2) in q dtype */
+  const void* rotary_sin;
+  const int32_t* seqlens_rotary;
+  int32_t rotary_dim;
+  int32_t is_rotary_interleaved;
+
+  /* FP8 descale, fp32 (b, h_k) with element strides (hopper/flash_api.cpp:1115-1146); may be null */
+  const float* q_descale;
+  const float* k_descale;
+  const float* v_descale;
+  int64_t q_descale_batch_stride, q_descale_head_stride;
+  int64_t k_descale_batch_stride, k_descale_head_stride;
+  int64_t v_descale_batch_stride, v_descale_head_stride;
+
+  /* math */
+  float softmax_scale;
+  float softcap;               /* 0 = off */
+  int32_t is_causal;
+  int32_t window_left;         /* -1 = unbounded */
+  int32_t window_right;        /* -1 = unbounded */
+  int32_t attention_chunk;     /* 0 = off */
+
+  /* scheduling */
+  int32_t num_splits;          /* >= 1 (resolved by the caller, e.g. through fa100_plan) */
+  int32_t pack_gqa;            /* 0/1 (resolved by the caller) */
+  int32_t num_sm;              /* SMs this call may use (multiProcessorCount - sm_margin); 0 = all */
+  int32_t* tile_counter;       /* optional int32[1] zeroed by the caller: dynamic tile scheduler */
+  int32_t reserved[8];
+} Fa100FwdParams;
+
+/* LSE-weighted merge of split partials (hopper/flash_fwd_combine_kernel.h:200-483,
+ * mha_combine hopper/flash_api.cpp:1569-1670).  Element strides; d stride is 1. */
+typedef struct Fa100CombineParams {
+  const float* o_partial;   /* (splits, b, s, h, d) logical */
+  const float* lse_partial; /* (splits, b, s, h)   logical */
+  void* o;                  /* (b, s, h, d) in out_dtype */
+  float* lse;               /* (b, s, h) logical */
+  int64_t op_split_stride, op_batch_stride, op_row_stride, op_head_stride;
+  int64_t lp_split_stride, lp_batch_stride, lp_row_stride, lp_head_stride;
+  int64_t o_batch_stride, o_row_stride, o_head_stride;
+  int64_t lse_batch_stride, lse_row_stride, lse_head_stride;
+  int32_t num_splits, b, s, h, d;
+  int32_t out_dtype;        /* FA100_BF16 / FA100_FP16 / FA100_FP32 */
+  /* per-batch row counts for packed (varlen) layouts; null = all s rows valid */
+  const int32_t* cu_seqlens;
+  const int32_t* seqused;
+  int32_t reserved[8];
+} Fa100CombineParams;
+
+/* Sizes-only planning (the role of get_num_splits / get_pack_gqa / tile_size_fwd_*,
+ * hopper/flash_api.cpp:415-470, hopper/heuristics.h:9-59).  Needs no device buffer. */
+typedef struct Fa100Shape {
+  int32_t b, seqlen_q, seqlen_k, h, h_k, d, dv, dtype;
+  int32_t is_causal, is_local, is_varlen, is_paged, page_size, has_new_kv;
+  int32_t num_splits;   /* 0 = choose; >= 1 = forced */
+  int32_t pack_gqa;     /* -1 = choose; 0/1 = forced */
+  int32_t num_sm;       /* 0 = query the current device */
+} Fa100Shape;
+
+typedef struct Fa100Plan {
+  int32_t block_m;      /* query rows per CTA tile */
+  int32_t block_n;      /* keys per main-loop step */
+  int32_t num_splits;
+  int32_t pack_gqa;
+  int32_t num_sm;
+  int32_t num_work;     /* CTA work items the forward kernel will iterate */
+  int32_t smem_bytes;
+  int32_t reserved[9];
+} Fa100Plan;
+
+int fa100_abi_version(void);
+const char* fa100_last_error(void);
+int fa100_plan(const Fa100Shape* shape, Fa100Plan* out);
+int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream);
+int fa100_combine(const Fa100CombineParams* p, fa100_stream_t stream);
+/* self-test hook used by the GPU tests: returns the hang-watchdog record of the last trapped kernel */
+int fa100_debug_hang_info(uint32_t out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FA100_H_ */
