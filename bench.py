@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native FlashAttention forward (driver contract).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c3nc|c4] [--impl reference]
+
+Default workload = BASELINE.json configs[1] (C2): bf16, batch 8, 32 Q / 8 KV heads, seqlen 8192, hdim 128, causal.
+A step is one forward over that batch.  `value` times the kernel with inputs resident in HBM (CUDA events on the
+launching stream); `e2e` times the public flash_attn_func call with HOST (pinned) q/k/v copied in and the output
+copied back every step.  `roofline` relates the kernel to the measured tensor peak (MEASURED_PEAKS.json);
+`cpu_baseline` is the CPU oracle (a restatement of the reference's attention_ref) on a bounded sample.
+With N > 1 (torchrun) every rank runs the same per-GPU workload (batch x heads shard with no communication:
+weak scaling) and `value` is the aggregate.  `--impl reference` times the reference's CPU path (oracle port).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path[:0] = [os.path.join(ROOT, "flash-attention-annotated_b200"), os.path.join(ROOT, "oracle")]
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: (dtype, b, sq, sk, h, hk, d, causal, metric, unit, description)
+    "c2": dict(dtype="bf16", b=8, sq=8192, sk=8192, h=32, hk=8, d=128, causal=True,
+               desc="FA fwd bf16 Llama-3-8B shape: b8 32q/8kv s8192 d128 causal"),
+    "c3": dict(dtype="e4m3", b=4, sq=16384, sk=16384, h=16, hk=16, d=128, causal=True,
+               desc="FA fwd FP8 e4m3 per-tensor descale: b4 h16 s16384 d128 causal"),
+    "c3nc": dict(dtype="e4m3", b=4, sq=16384, sk=16384, h=16, hk=16, d=128, causal=False,
+                 desc="FA fwd FP8 e4m3 per-tensor descale: b4 h16 s16384 d128 non-causal"),
+    "c4": dict(dtype="bf16", b=64, sq=1, sk=32768, h=32, hk=8, d=128, causal=False, page=256,
+               desc="split-KV decode, paged KV (page 256): b64 32q/8kv sq1 sk32768 d128"),
+}
+
+
+def flops(w):
+    avg_k = (max(0, w["sk"] - w["sq"]) + w["sk"]) / 2 if w["causal"] else w["sk"]
+    return w["b"] * w["h"] * 2 * w["sq"] * avg_k * (w["d"] + w["d"])
+
+
+def decode_bytes(w):
+    elt = 2
+    kv = w["b"] * w["sk"] * w["hk"] * (w["d"] + w["d"]) * elt
+    qo = 2 * w["b"] * w["sq"] * w["h"] * w["d"] * elt
+    return kv + qo + w["b"] * (w["sk"] // w.get("page", 256)) * 4
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            m = json.load(f)
+        return dict(hbm=m["hbm_gbs"], tensor=m["bf16_tflops"], tensor_sustained=m.get("bf16_tflops_sustained"), source="measured")
+    except Exception:  # noqa: BLE001
+        return dict(hbm=6650.0, tensor=1590.0, tensor_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=max(mx) if mx else None, reasons=reasons,
+                    samples=len(sm))
+
+
+def make_inputs(w, device, seed):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    dt = torch.bfloat16
+    b, sq, sk, h, hk, d = w["b"], w["sq"], w["sk"], w["h"], w["hk"], w["d"]
+    t = dict()
+    if "page" in w:
+        ps = w["page"]
+        npages = b * sk // ps
+        t["q"] = torch.randn(b, sq, h, d, generator=g).to(dt)
+        t["k"] = torch.randn(npages, ps, hk, d, dtype=torch.bfloat16, device=device)
+        t["v"] = torch.randn(npages, ps, hk, d, dtype=torch.bfloat16, device=device)
+        t["page_table"] = torch.randperm(npages, generator=g).to(torch.int32).view(b, sk // ps).to(device)
+        t["cache_seqlens"] = torch.full((b,), sk, dtype=torch.int32, device=device)
+        return t
+    if w["dtype"] == "e4m3":
+        mk = lambda *s: torch.randn(*s, dtype=torch.bfloat16, device=device).to(torch.float8_e4m3fn).cpu()  # noqa: E731
+        t["q"], t["k"], t["v"] = mk(b, sq, h, d), mk(b, sk, hk, d), mk(b, sk, hk, d)
+        for nm, val in (("q_descale", 0.5), ("k_descale", 0.75), ("v_descale", 1.25)):
+            t[nm] = torch.full((b, hk), val, dtype=torch.float32, device=device)
+    else:
+        mk = lambda *s: torch.randn(*s, dtype=dt, device=device).cpu()  # noqa: E731
+        t["q"], t["k"], t["v"] = mk(b, sq, h, d), mk(b, sk, hk, d), mk(b, sk, hk, d)
+    return t
+
+
+def cpu_sample(w, threads, slices):
+    """CPU oracle on `slices` (batch, kv-group) slices of the workload; returns (seconds, flops done)."""
+    import attention_oracle as A
+
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(0)
+    G = w["h"] // w["hk"]
+    sq, sk = min(w["sq"], 8192), min(w["sk"], 8192)
+    t0 = time.perf_counter()
+    for _ in range(slices):
+        q = torch.randn(1, sq, G, w["d"], generator=g).to(torch.bfloat16)
+        k = torch.randn(1, sk, 1, w["d"], generator=g).to(torch.bfloat16)
+        v = torch.randn(1, sk, 1, w["d"], generator=g).to(torch.bfloat16)
+        A.attention_oracle_sliced(q, k, v, rows_per_call=1024, causal=w["causal"])
+    dt = time.perf_counter() - t0
+    return dt, slices * A.flops(1, G, sq, sk, w["d"], w["d"], w["causal"])
+
+
+def run_reference(args, w, rank):
+    """--impl reference: the reference's CPU path (oracle port of attention_ref) on all host threads."""
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    slices = 2
+    for _ in range(min(args.warmup, 1)):
+        cpu_sample(w, threads, 1)
+    tot_t, tot_f = 0.0, 0.0
+    for _ in range(args.steps):
+        dt, fl = cpu_sample(w, threads, slices)
+        tot_t += dt
+        tot_f += fl
+    val = tot_f / tot_t / 1e12
+    sample = f"{slices} (batch, kv-group) slices of {w['h'] // w['hk']} q-heads per step, seq capped at 8192, q-row-blocked"
+    line = dict(impl="reference", metric=metric_name(w), value=val, unit="TFLOP/s", n_gpus=args.gpus, steps=args.steps,
+                warmup=args.warmup, ms_per_step=tot_t / args.steps * 1e3, higher_is_better=True, scaling="weak",
+                vs_baseline=None, dtype="f32", data="synthetic", config=dict(workload=w["desc"]),
+                cpu_baseline=dict(value=val, unit="TFLOP/s", cores=threads, kind="port", sample=sample),
+                e2e=dict(value=val, unit="TFLOP/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line), flush=True)
+
+
+def metric_name(w):
+    if "page" in w:
+        return "decode HBM GB/s (split-KV paged decode)"
+    return f"fwd TFLOPS/GPU {w['dtype']} hdim128 {'causal' if w['causal'] else 'non-causal'}"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="fa100", choices=["fa100", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "fa100" else args.warmup
+    w = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, w, rank)
+        return
+
+    import fa100_native as N
+    from flash_attn_interface import flash_attn_func, flash_attn_with_kvcache
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    host = make_inputs(w, dev, seed=1234 + rank)
+    pin = {k_: (v_.pin_memory() if v_.device.type == "cpu" else v_) for k_, v_ in host.items()}
+    devt = {k_: v_.to(dev, non_blocking=True) for k_, v_ in pin.items()}
+    torch.cuda.synchronize()
+    decode = "page" in w
+
+    def step(t):
+        if decode:
+            return flash_attn_with_kvcache(t["q"], t["k"], t["v"], cache_seqlens=t["cache_seqlens"], page_table=t["page_table"],
+                                           causal=False)
+        kw = {n: t[n] for n in ("q_descale", "k_descale", "v_descale") if n in t}
+        return flash_attn_func(t["q"], t["k"], t["v"], causal=w["causal"], **kw)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        out = step(devt)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        out = step(devt)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    hang = N.hang_info()
+    assert hang[0] == 0, f"kernel watchdog fired: {hang}"
+
+    # e2e: host buffers in, host result out, every step (pinned memory, same stream)
+    e2e_ms, h2d, d2h = None, 0, 0
+    if not args.no_e2e:
+        host_keys = [k_ for k_, v_ in pin.items() if v_.device.type == "cpu"]
+        out_host = torch.empty(out.shape, dtype=out.dtype).pin_memory()
+        h2d = sum(pin[k_].numel() * pin[k_].element_size() for k_ in host_keys)
+        d2h = out_host.numel() * out_host.element_size()
+
+        def e2e_step():
+            t = dict(devt)
+            for k_ in host_keys:
+                t[k_] = pin[k_].to(dev, non_blocking=True)
+            out_host.copy_(step(t), non_blocking=True)
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        n_e2e = max(3, min(args.steps, 10))
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(n_e2e):
+            e2e_step()
+        e1.record()
+        barrier()
+        e2e_ms = e0.elapsed_time(e1) / n_e2e
+        _ = time.perf_counter() - t0
+    vals = torch.tensor([ms, e2e_ms or 0.0], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = vals[0].item(), (vals[1].item() if e2e_ms is not None else None)
+
+    if rank == 0:
+        peaks = measured_peaks()
+        if decode:
+            per_gpu = decode_bytes(w) / (ms * 1e-3) / 1e9
+            unit, bound, peak = "GB/s", "hbm", peaks["hbm"]
+            e2e_val = decode_bytes(w) * world / (e2e_ms * 1e-3) / 1e9 if e2e_ms else None
+        else:
+            per_gpu = flops(w) / (ms * 1e-3) / 1e12
+            unit, bound, peak = "TFLOP/s", "tensor", peaks["tensor"] * (2.0 if w["dtype"] == "e4m3" else 1.0)
+            e2e_val = flops(w) * world / (e2e_ms * 1e-3) / 1e12 if e2e_ms else None
+        line = dict(metric=metric_name(w), value=per_gpu * world, unit=unit, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=ms, higher_is_better=True, scaling="weak", vs_baseline=None,
+                    dtype={"bf16": "bf16", "e4m3": "fp8_e4m3"}[w["dtype"]], data="synthetic",
+                    config=dict(workload=w["desc"], per_gpu="full workload on every GPU (batch x heads sharding, no communication)",
+                                l2="inputs (>= 0.67 GB) exceed the 126 MB L2; no flush between steps"),
+                    clocks=clocks, gpu_launches=args.steps * (2 if decode else 1),
+                    e2e=dict(value=e2e_val, unit=unit, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h),
+                    roofline=dict(bound=bound, achieved=per_gpu, peak=peak, unit=unit, frac=per_gpu / peak, traffic=None,
+                                  peak_source=peaks["source"] + (" (bf16 burst x2 for fp8)" if w["dtype"] == "e4m3" and not decode else ""),
+                                  frac_of_sustained=(per_gpu / (peaks["tensor_sustained"] * (2.0 if w["dtype"] == "e4m3" else 1.0))
+                                                     if bound == "tensor" and peaks["tensor_sustained"] else None),
+                                  kernel="fa100_fwd_kernel"))
+        if not args.no_cpu_baseline and world == 1:
+            threads = os.cpu_count() or 1
+            slices = 4
+            dt, fl = cpu_sample(w, threads, slices)
+            line["cpu_baseline"] = dict(value=fl / dt / 1e12, unit="TFLOP/s", cores=threads, kind="port",
+                                        sample=f"{slices} (batch, kv-group) slices ({slices * (w['h'] // w['hk'])} of "
+                                               f"{w['b'] * w['h']} q-head rows), seq capped at 8192, {dt:.1f} s")
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

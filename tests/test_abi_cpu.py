@@ -1,0 +1,122 @@
+"""CPU: the C-ABI library builds, loads and exports every symbol include/fa100.h declares; ctypes mirrors of the
+structs have the C sizes; the sizes-only planner and argument validation work without a GPU; the op schemas match
+the reference's frozen ones (hopper/test_flash_attn.py:1163-1201)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def native():
+    import __graft_entry__ as G
+
+    G.build()
+    import fa100_native as N
+
+    return N
+
+
+def test_exports_match_header(native):
+    hdr = open(os.path.join(ROOT, "include", "fa100.h")).read()
+    declared = set(re.findall(r"^(?:int|const char\*)\s+(fa100_\w+)\s*\(", hdr, flags=re.M))
+    assert declared == set(native.EXPORTS)
+    lib = native.lib()
+    for name in declared:
+        assert getattr(lib, name) is not None
+    assert lib.fa100_abi_version() == 1
+
+
+def test_struct_sizes_match_c(native, tmp_path):
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include "fa100.h"\nint main(){printf("%zu %zu %zu %zu\\n", sizeof(Fa100FwdParams),'
+                   'sizeof(Fa100CombineParams), sizeof(Fa100Shape), sizeof(Fa100Plan));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    sizes = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert sizes == [C.sizeof(native.FwdParams), C.sizeof(native.CombineParams), C.sizeof(native.Shape), C.sizeof(native.Plan)]
+
+
+def _plan(native, **kw):
+    base = dict(b=1, seqlen_q=1, seqlen_k=1, h=1, h_k=1, d=128, dv=128, dtype=0, num_splits=0, pack_gqa=-1, num_sm=148)
+    base.update(kw)
+    s, p = native.Shape(**base), native.Plan()
+    rc = native.lib().fa100_plan(C.byref(s), C.byref(p))
+    return rc, p
+
+
+def test_plan_policy(native):
+    rc, p = _plan(native, b=8, seqlen_q=8192, seqlen_k=8192, h=32, h_k=8, is_causal=1)
+    assert rc == 0 and p.num_splits == 1 and p.pack_gqa == 0 and p.num_work == 8 * 32 * 32
+    rc, p = _plan(native, b=64, seqlen_q=1, seqlen_k=32768, h=32, h_k=8)          # C4: decode packs the 4 group heads
+    assert rc == 0 and p.pack_gqa == 1 and p.num_work == 64 * 8 * p.num_splits
+    rc, p = _plan(native, b=1, seqlen_q=1, seqlen_k=32768, h=8, h_k=8)             # tiny batch: split to fill the SMs
+    assert rc == 0 and p.num_splits > 8 and p.num_work <= 148
+    rc, p = _plan(native, b=2, seqlen_q=64, seqlen_k=100, h=4, h_k=4)              # one key block: never split
+    assert rc == 0 and p.num_splits == 1
+    rc, p = _plan(native, b=2, seqlen_q=64, seqlen_k=4096, h=4, h_k=4, num_splits=7, pack_gqa=0)  # forced values are kept
+    assert rc == 0 and p.num_splits == 7 and p.pack_gqa == 0
+    rc, _ = _plan(native, h=6, h_k=4)
+    assert rc == native.ERR_INVALID and b"multiple" in native.lib().fa100_last_error()
+
+
+def test_argument_validation_without_gpu(native):
+    p = native.FwdParams()
+    assert native.lib().fa100_fwd(C.byref(p), None) != 0          # null tensors / zero sizes are rejected before any launch
+    c = native.CombineParams()
+    assert native.lib().fa100_combine(C.byref(c), None) == native.ERR_INVALID
+    assert native.lib().fa100_fwd(None, None) == native.ERR_INVALID
+    with pytest.raises(RuntimeError):
+        native.check(native.ERR_INVALID)
+    with pytest.raises(NotImplementedError):
+        native.check(native.ERR_UNSUPPORTED)
+
+
+def test_op_schemas_match_reference(native):
+    import flash_attn_interface  # noqa: F401
+
+    fwd = str(torch.ops.flash_attn_3.fwd.default._schema)
+    assert fwd.startswith("flash_attn_3::fwd(Tensor q, Tensor k, Tensor v, Tensor(k_new!)? k_new=None, Tensor(v_new!)? v_new=None, Tensor? q_v=None, Tensor(out!)? out=None")
+    assert "int num_splits=0, bool? pack_gqa=None, int sm_margin=0) -> (Tensor(out!), Tensor, Tensor, Tensor)" in fwd
+    comb = str(torch.ops.flash_attn_3.fwd_combine.default._schema)
+    assert comb == ("flash_attn_3::fwd_combine(Tensor out_partial, Tensor lse_partial, Tensor(out!)? out=None, "
+                    "ScalarType? out_dtype=None) -> (Tensor(out!), Tensor)")
+    meta = str(torch.ops.flash_attn_3.get_scheduler_metadata.default._schema)
+    assert meta.startswith("flash_attn_3::get_scheduler_metadata(int batch_size, int max_seqlen_q, int max_seqlen_k, int num_heads, "
+                           "int num_heads_k, int headdim, int headdim_v, ScalarType qkv_dtype, Tensor seqused_k")
+    assert "flash_attn_3::bwd(Tensor dout" in str(torch.ops.flash_attn_3.bwd.default._schema)
+
+
+def test_public_signatures_match_reference(native):
+    """argument names and defaults of the public functions (hopper/flash_attn_interface.py:507-523,588-610,640-671,803-820)."""
+    import inspect
+
+    import flash_attn_interface as F
+
+    sig = lambda f: [(n, p.default) for n, p in inspect.signature(f).parameters.items()]  # noqa: E731
+    E = inspect.Parameter.empty
+    assert sig(F.flash_attn_func) == [("q", E), ("k", E), ("v", E), ("softmax_scale", None), ("causal", False), ("qv", None),
+                                      ("q_descale", None), ("k_descale", None), ("v_descale", None), ("window_size", (-1, -1)),
+                                      ("attention_chunk", 0), ("softcap", 0.0), ("num_splits", 1), ("pack_gqa", None),
+                                      ("deterministic", False), ("sm_margin", 0), ("return_attn_probs", False)]
+    names = [n for n, _ in sig(F.flash_attn_varlen_func)]
+    assert names[:9] == ["q", "k", "v", "cu_seqlens_q", "cu_seqlens_k", "max_seqlen_q", "max_seqlen_k", "seqused_q", "seqused_k"]
+    kv = dict(sig(F.flash_attn_with_kvcache))
+    assert list(kv)[:9] == ["q", "k_cache", "v_cache", "k", "v", "qv", "rotary_cos", "rotary_sin", "cache_seqlens"]
+    assert kv["num_splits"] == 0 and kv["rotary_interleaved"] is True and kv["return_softmax_lse"] is False
+    assert [n for n, _ in sig(F.flash_attn_combine)] == ["out_partial", "lse_partial", "out", "out_dtype"]
+    assert [n for n, _ in sig(F.get_scheduler_metadata)][:7] == ["batch_size", "max_seqlen_q", "max_seqlen_k", "num_heads_q",
+                                                                 "num_heads_kv", "headdim", "cache_seqlens"]
+
+
+def test_no_cpu_fallback(native):
+    import flash_attn_interface as F
+
+    q = torch.randn(1, 8, 2, 64, dtype=torch.bfloat16)
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        F.flash_attn_func(q, q, q)

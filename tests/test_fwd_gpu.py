@@ -1,0 +1,269 @@
+"""GPU parity tests: the CUDA path (flash_attn_interface -> torch.ops.flash_attn_3 -> libfa100.so C ABI) against the
+CPU oracle on the same seeded inputs.  Shapes and tolerance rule follow hopper/test_flash_attn.py:53-286 (output),
+:290-598 (varlen), :601-989 (kvcache), :1043-1102 (bitwise repeatability).
+
+Tolerances (written here as north_star requires):
+  bf16/fp16: max|out - ref_fp32| <= 2 * max|ref_lowprec - ref_fp32| + fwd_atol   (3x with softcap)
+  fp8:       same rule with the e4m3-intermediate low-precision arm and multiplier 4
+  LSE:       |lse - lse_ref| <= 1e-3 * max(1, |lse_ref|), and -inf exactly where the oracle has -inf
+"""
+import pytest
+import torch
+
+import attention_oracle as A
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _iface():
+    import flash_attn_interface as F
+
+    return F
+
+
+def _check(out, lse, ref, low, lse_ref, rtol=2.0):
+    import fa100_native as N
+
+    torch.cuda.synchronize()
+    hang = N.hang_info()
+    assert hang[0] == 0, f"kernel watchdog fired: {[hex(x) for x in hang]}"
+    assert torch.isfinite(out.float()).all()
+    err = (out.float().cpu() - ref.float()).abs().max().item()
+    tol = A.fwd_tolerance(ref, low, rtol)
+    assert err <= tol, f"max err {err:.3e} > tol {tol:.3e}"
+    if lse is not None:
+        lse = lse.cpu()
+        assert torch.equal(torch.isneginf(lse), torch.isneginf(lse_ref))
+        fin = torch.isfinite(lse_ref)
+        rel = ((lse[fin] - lse_ref[fin]).abs() / lse_ref[fin].abs().clamp_min(1.0)).max().item() if fin.any() else 0.0
+        assert rel <= 1e-3, f"lse rel err {rel:.3e}"
+
+
+def _qkv(b, sq, sk, h, hk, d, dtype, seed=0, dv=None):
+    g = torch.Generator().manual_seed(seed)
+    dv = dv or d
+    return (torch.randn(b, sq, h, d, generator=g).to(dtype), torch.randn(b, sk, hk, d, generator=g).to(dtype),
+            torch.randn(b, sk, hk, dv, generator=g).to(dtype))
+
+
+SHAPES = [(1, 1), (64, 128), (128, 128), (256, 256), (113, 203), (128, 217), (113, 211), (108, 256), (256, 512), (239, 1),
+          (384, 256), (640, 128), (512, 256), (1024, 1024), (1023, 1024), (799, 3), (1, 1024)]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("mha_type", ["mha", "mqa", "gqa"])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d", [64, 128])
+@pytest.mark.parametrize("sq,sk", SHAPES)
+def test_output(sq, sk, d, causal, mha_type, dtype):
+    F = _iface()
+    h = 6
+    hk = {"mha": 6, "mqa": 1, "gqa": 2}[mha_type]
+    q, k, v = _qkv(3, sq, sk, h, hk, d, dtype)
+    ref, lse_ref = A.attention_oracle(q, k, v, causal=causal)
+    low, _ = A.attention_oracle(q, k, v, causal=causal, upcast=False, reorder_ops=True)
+    for pack_gqa, num_splits in ((False, 1), (True, 1), (False, 3), (True, 3)):
+        out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), causal=causal, pack_gqa=pack_gqa, num_splits=num_splits,
+                                     return_attn_probs=True)
+        _check(out, lse, ref, low, lse_ref)
+
+
+@pytest.mark.parametrize("kw", [dict(window_size=(100, 50)), dict(window_size=(300, 0)), dict(window_size=(0, 0)),
+                                dict(window_size=(-1, 30)), dict(attention_chunk=128), dict(attention_chunk=77, window_size=(200, 10)),
+                                dict(softcap=15.0), dict(softcap=15.0, causal=True), dict(softmax_scale=0.3, causal=True)])
+@pytest.mark.parametrize("sq,sk", [(500, 700), (700, 500), (64, 1500), (1, 333)])
+def test_masks_and_softcap(sq, sk, kw):
+    F = _iface()
+    q, k, v = _qkv(2, sq, sk, 4, 2, 128, torch.bfloat16, seed=1)
+    okw = dict(kw)
+    ref, lse_ref = A.attention_oracle(q, k, v, **okw)
+    low, _ = A.attention_oracle(q, k, v, upcast=False, reorder_ops=True, **okw)
+    for num_splits in (1, 2):
+        out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), return_attn_probs=True, num_splits=num_splits, **kw)
+        _check(out, lse, ref, low, lse_ref, rtol=3.0 if kw.get("softcap") else 2.0)
+
+
+@pytest.mark.parametrize("d,dv", [(96, 96), (80, 80), (128, 64), (64, 128), (40, 40)])
+def test_odd_head_dims(d, dv):
+    F = _iface()
+    q, k, v = _qkv(2, 300, 411, 4, 2, d, torch.bfloat16, seed=2, dv=dv)
+    ref, lse_ref = A.attention_oracle(q, k, v, causal=True)
+    low, _ = A.attention_oracle(q, k, v, causal=True, upcast=False, reorder_ops=True)
+    out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), causal=True, return_attn_probs=True)
+    _check(out, lse, ref, low, lse_ref)
+
+
+def test_noncontiguous_inputs():
+    """only last-dim contiguity is required (hopper/flash_api.cpp:726-728)."""
+    F = _iface()
+    q, k, v = _qkv(2, 200, 200, 4, 4, 128, torch.bfloat16, seed=3)
+    qkv = torch.stack([q, k, v], dim=2).to(DEV)  # (b, s, 3, h, d): packed QKV views
+    out = F.flash_attn_qkvpacked_func(qkv, causal=True)
+    ref, _ = A.attention_oracle(q, k, v, causal=True)
+    low, _ = A.attention_oracle(q, k, v, causal=True, upcast=False, reorder_ops=True)
+    _check(out, None, ref, low, None)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("lens_q,lens_k", [([100, 257, 31], [100, 300, 77]), ([128, 5, 300, 1], [128, 0, 511, 1000]),
+                                           ([1, 1, 1, 1, 1], [7, 130, 250, 1, 600])])
+def test_varlen(lens_q, lens_k, causal):
+    F = _iface()
+    g = torch.Generator().manual_seed(4)
+    h, hk, d = 4, 2, 128
+    cq = torch.tensor([0] + torch.tensor(lens_q).cumsum(0).tolist(), dtype=torch.int32)
+    ck = torch.tensor([0] + torch.tensor(lens_k).cumsum(0).tolist(), dtype=torch.int32)
+    q = torch.randn(int(cq[-1]), h, d, generator=g).to(torch.bfloat16)
+    k = torch.randn(int(ck[-1]), hk, d, generator=g).to(torch.bfloat16)
+    v = torch.randn(int(ck[-1]), hk, d, generator=g).to(torch.bfloat16)
+    refs, lows, lses = [], [], []
+    for i in range(len(lens_q)):
+        qi, ki, vi = q[cq[i]:cq[i + 1]][None], k[ck[i]:ck[i + 1]][None], v[ck[i]:ck[i + 1]][None]
+        if lens_k[i] == 0:
+            refs.append(torch.zeros_like(qi[0])); lows.append(torch.zeros_like(qi[0]))
+            lses.append(torch.full((h, lens_q[i]), float("-inf")))
+            continue
+        r, l = A.attention_oracle(qi, ki, vi, causal=causal)
+        lo, _ = A.attention_oracle(qi, ki, vi, causal=causal, upcast=False, reorder_ops=True)
+        refs.append(r[0]); lows.append(lo[0]); lses.append(l[0])
+    for pack_gqa, num_splits in ((False, 1), (True, 2)):
+        out, lse = F.flash_attn_varlen_func(q.to(DEV), k.to(DEV), v.to(DEV), cq.to(DEV), ck.to(DEV), max(lens_q), max(lens_k),
+                                            causal=causal, pack_gqa=pack_gqa, num_splits=num_splits, return_attn_probs=True)
+        _check(out, lse, torch.cat(refs), torch.cat(lows), torch.cat(lses, dim=1))
+
+
+def test_varlen_seqused():
+    """seqused_q / seqused_k shorter than the cu_seqlens slots (hopper/test_flash_attn.py add_unused_qkv)."""
+    F = _iface()
+    g = torch.Generator().manual_seed(5)
+    b, sq, sk, h, hk, d = 3, 160, 300, 4, 1, 128
+    q, k, v = _qkv(b, sq, sk, h, hk, d, torch.bfloat16, seed=5)
+    uq = torch.tensor([160, 17, 100], dtype=torch.int32)
+    uk = torch.tensor([300, 129, 5], dtype=torch.int32)
+    cq = torch.arange(0, (b + 1) * sq, sq, dtype=torch.int32)
+    ck = torch.arange(0, (b + 1) * sk, sk, dtype=torch.int32)
+    out, lse = F.flash_attn_varlen_func(q.reshape(-1, h, d).to(DEV), k.reshape(-1, hk, d).to(DEV), v.reshape(-1, hk, d).to(DEV),
+                                        cq.to(DEV), ck.to(DEV), sq, sk, seqused_q=uq.to(DEV), seqused_k=uk.to(DEV), causal=True,
+                                        return_attn_probs=True)
+    ref, lse_ref = A.attention_oracle(q, k, v, q_lens=uq, k_lens=uk, causal=True)
+    low, _ = A.attention_oracle(q, k, v, q_lens=uq, k_lens=uk, causal=True, upcast=False, reorder_ops=True)
+    valid = (torch.arange(sq).view(1, -1) < uq.view(-1, 1))
+    out = torch.where(valid.view(b, sq, 1, 1), out.view(b, sq, h, d).cpu(), torch.zeros((), dtype=out.dtype))  # rows past seqused_q are not written
+    lse = lse.view(h, b, sq).permute(1, 0, 2).cpu().masked_fill(~valid.view(b, 1, sq), float("-inf"))
+    _check(out, lse, ref, low, lse_ref)
+
+
+@pytest.mark.parametrize("page_size", [None, 16, 64, 128, 256])
+@pytest.mark.parametrize("sq,sk", [(1, 128), (1, 339), (3, 1024), (64, 800), (16, 3000), (128, 128)])
+@pytest.mark.parametrize("causal", [False, True])
+def test_kvcache(sq, sk, page_size, causal):
+    F = _iface()
+    g = torch.Generator().manual_seed(6)
+    b, h, hk, d = 4, 8, 2, 128
+    q = torch.randn(b, sq, h, d, generator=g).to(torch.bfloat16)
+    lens = torch.randint(max(1, sk // 2), sk + 1, (b,), generator=g, dtype=torch.int32)
+    if causal:
+        lens = lens.clamp_min(sq)
+    if page_size is None:
+        kd = torch.randn(b, sk, hk, d, generator=g).to(torch.bfloat16)
+        vd = torch.randn(b, sk, hk, d, generator=g).to(torch.bfloat16)
+        kin, vin, table = kd, vd, None
+    else:
+        kd, vd, table, kin, vin = A.paged_kvcache(sk, page_size, b, hk, d, d, torch.bfloat16, generator=g)
+    ref, lse_ref = A.attention_oracle(q, kd, vd, k_lens=lens, causal=causal)
+    low, _ = A.attention_oracle(q, kd, vd, k_lens=lens, causal=causal, upcast=False, reorder_ops=True)
+    for num_splits in (0, 1, 3):
+        out, lse, *_ = F.flash_attn_with_kvcache(q.to(DEV), kin.to(DEV), vin.to(DEV), cache_seqlens=lens.to(DEV),
+                                                 page_table=None if table is None else table.to(DEV), causal=causal,
+                                                 num_splits=num_splits, return_softmax_lse=True)
+        _check(out, lse, ref, low, lse_ref)
+
+
+def test_kvcache_batch_idx_and_leftpad():
+    F = _iface()
+    g = torch.Generator().manual_seed(7)
+    b, bc, sq, sk, h, hk, d = 3, 7, 2, 600, 4, 2, 128
+    q = torch.randn(b, sq, h, d, generator=g).to(torch.bfloat16)
+    kc = torch.randn(bc, sk, hk, d, generator=g).to(torch.bfloat16)
+    vc = torch.randn(bc, sk, hk, d, generator=g).to(torch.bfloat16)
+    idx = torch.tensor([5, 0, 3], dtype=torch.int32)
+    lens = torch.tensor([600, 257, 400], dtype=torch.int32)   # cache_seqlens counts from the start of the buffer
+    pad = torch.tensor([0, 100, 37], dtype=torch.int32)
+    out, lse, *_ = F.flash_attn_with_kvcache(q.to(DEV), kc.to(DEV), vc.to(DEV), cache_seqlens=lens.to(DEV), cache_batch_idx=idx.to(DEV),
+                                             cache_leftpad=pad.to(DEV), causal=True, return_softmax_lse=True)
+    kd, vd = kc[idx.long()], vc[idx.long()]
+    ref, lse_ref = A.attention_oracle(q, kd, vd, k_lens=lens - pad, key_leftpad=pad, causal=True)
+    low, _ = A.attention_oracle(q, kd, vd, k_lens=lens - pad, key_leftpad=pad, causal=True, upcast=False, reorder_ops=True)
+    _check(out, lse, ref, low, lse_ref)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("sq,sk", [(128, 128), (700, 700), (113, 203), (1, 900)])
+def test_fp8(sq, sk, causal):
+    """e4m3 inputs, fp32 (b, h_k) descales, bf16 output (hopper/test_flash_attn.py:118-149, multipliers :986-989)."""
+    F = _iface()
+    g = torch.Generator().manual_seed(8)
+    b, h, hk, d = 2, 4, 2, 128
+    q = torch.randn(b, sq, h, d, generator=g).to(torch.float8_e4m3fn)
+    k = torch.randn(b, sk, hk, d, generator=g).to(torch.float8_e4m3fn)
+    v = torch.randn(b, sk, hk, d, generator=g).to(torch.float8_e4m3fn)
+    ds = [torch.rand(b, hk, generator=g) * 2 for _ in range(3)]
+    qr, kr, vr = (x.to(torch.bfloat16) for x in (q, k, v))
+    kw = dict(causal=causal, q_descale=ds[0], k_descale=ds[1], v_descale=ds[2])
+    ref, lse_ref = A.attention_oracle(qr, kr, vr, **kw)
+    low, _ = A.attention_oracle(qr, kr, vr, upcast=False, reorder_ops=True, intermediate_dtype=torch.float8_e4m3fn, **kw)
+    out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), causal=causal, q_descale=ds[0].to(DEV), k_descale=ds[1].to(DEV),
+                                 v_descale=ds[2].to(DEV), return_attn_probs=True)
+    assert out.dtype == torch.bfloat16
+    _check(out, lse, ref, low, lse_ref, rtol=4.0)
+
+
+@pytest.mark.parametrize("num_splits", [1, 2, 3, 5, 17, 32, 55, 97, 133])
+@pytest.mark.parametrize("seqlen", [1, 3, 113, 640])
+@pytest.mark.parametrize("d,dtype", [(64, torch.float32), (128, torch.bfloat16), (96, torch.float16), (256, torch.float32)])
+def test_combine(num_splits, seqlen, d, dtype):
+    """hopper/test_flash_attn.py:1117-1156: non-contiguous inputs, -inf splits, lse to 1e-5."""
+    F = _iface()
+    torch.manual_seed(1)
+    b, h = 5, 16
+    op = torch.randn(num_splits * 2, b, h, seqlen, d, device=DEV).transpose(2, 3)[:num_splits]
+    lp = torch.randn(num_splits, b, h * 2, seqlen, device=DEV).transpose(-1, -2)[:, :, :, :h]
+    lp[num_splits // 2:, : b // 3] = float("-inf")
+    out, lse = F.flash_attn_combine(op, lp, out_dtype=dtype)
+    oref, lref = A.combine_oracle(op.cpu(), lp.cpu())
+    assert torch.allclose(lse.cpu(), lref, atol=1e-5, rtol=1e-5)
+    opt = oref.to(dtype)
+    err = (out.cpu().float() - oref).abs().max().item()
+    assert err <= 2 * (opt.float() - oref).abs().max().item() or torch.allclose(out.cpu().float(), opt.float(), atol=1e-5, rtol=1e-5)
+
+
+def test_bitwise_repeatable():
+    """hopper/test_flash_attn.py:1043-1102: the forward must be bitwise deterministic run to run."""
+    F = _iface()
+    q, k, v = (x.to(DEV) for x in _qkv(2, 1024, 1024, 8, 2, 128, torch.bfloat16, seed=9))
+    for kw in (dict(causal=True), dict(causal=True, num_splits=4), dict(causal=False, pack_gqa=True)):
+        o0, l0 = F.flash_attn_func(q, k, v, return_attn_probs=True, **kw)
+        for _ in range(50):
+            o, l = F.flash_attn_func(q, k, v, return_attn_probs=True, **kw)
+            assert torch.equal(o, o0) and torch.equal(l, l0)
+
+
+def test_split_combine_identity_full_size():
+    """size-independent property at a large size: split-KV partials merged by the combine kernel == unsplit result."""
+    F = _iface()
+    q, k, v = (x.to(DEV) for x in _qkv(1, 2048, 8192, 8, 2, 128, torch.bfloat16, seed=10))
+    o1, l1 = F.flash_attn_func(q, k, v, causal=True, num_splits=1, return_attn_probs=True)
+    o8, l8 = F.flash_attn_func(q, k, v, causal=True, num_splits=8, return_attn_probs=True)
+    assert (o1.float() - o8.float()).abs().max().item() <= 2e-2
+    assert torch.allclose(l1, l8, atol=1e-4, rtol=1e-4)
+
+
+def test_unsupported_raises():
+    F = _iface()
+    q, k, v = (x.to(DEV) for x in _qkv(1, 64, 64, 2, 2, 256, torch.bfloat16))
+    with pytest.raises(NotImplementedError):
+        F.flash_attn_func(q, k, v)
+    q, k, v = _qkv(1, 64, 64, 2, 2, 64, torch.bfloat16)
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        F.flash_attn_func(q, k, v)  # CPU tensors: no fallback
