@@ -144,3 +144,23 @@ extern "C" int fa100_debug_hang_info(uint32_t out[4]) {
   for (int i = 0; i < 4; ++i) out[i] = h[i];
   return e == cudaSuccess ? 0 : fa100::set_error(FA100_ERR_CUDA, "hang info: %s", cudaGetErrorString(e));
 }
+
+extern "C" int fa100_debug_trace(uint32_t* out, int max_events) {
+  // copies up to max_events {tag|warp<<16, begin, end} triples of the opt-in timeline and clears it;
+  // returns the number of events (0 in the product build, which carries no trace code)
+#ifdef FA100_TRACE
+  static unsigned int host_buf[fa100::kTraceWarps * fa100::kTracePerWarp * 3];
+  unsigned int cnt[fa100::kTraceWarps], zero[fa100::kTraceWarps] = {};
+  if (cudaMemcpyFromSymbol(cnt, fa100::g_fa100_trace_cnt, sizeof(cnt)) != cudaSuccess) return -3;
+  if (cudaMemcpyFromSymbol(host_buf, fa100::g_fa100_trace, sizeof(host_buf)) != cudaSuccess) return -3;
+  cudaMemcpyToSymbol(fa100::g_fa100_trace_cnt, zero, sizeof(zero));
+  int n = 0;
+  for (int w = 0; w < fa100::kTraceWarps; ++w)
+    for (unsigned int i = 0; i < cnt[w] && n < max_events; ++i, ++n)
+      for (int j = 0; j < 3; ++j) out[n * 3 + j] = host_buf[(w * fa100::kTracePerWarp + i) * 3 + j];
+  return n;
+#else
+  (void)out; (void)max_events;
+  return 0;
+#endif
+}

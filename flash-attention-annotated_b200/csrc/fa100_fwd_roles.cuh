@@ -32,7 +32,9 @@ FA_DEVICE bool tile_uses(const WorkGeom& g, int t, int nb) { return nb >= g.tr[t
 struct RingState { int stage = 0; uint32_t phase = 0; };
 template <int STAGES> FA_DEVICE void ring_advance(RingState& r) { if (++r.stage == STAGES) { r.stage = 0; r.phase ^= 1; } }
 
-// ----------------------------------------------------------------------------- TMA producer (one thread)
+// ----------------------------------------------------------------------------- TMA producer
+// The whole warp walks the schedule (warp-uniform control flow keeps descriptors and coordinates in uniform
+// registers); one elected lane issues the bulk copies.
 template <int HD, int ELT>
 FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, const CUtensorMap* tmK,
                              const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar) {
@@ -51,12 +53,15 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
     for (int t = 0; t < kQTiles; ++t) {
       if (!tile_live(g, t)) continue;
       mbar_wait(&bar->q_empty[t], (q_it[t] & 1) ^ 1, 0x10 + t);
-      mbar_arrive_expect_tx(&bar->q_full[t], q_tx);
       const int pos0 = (g.it.m_blk * kQTiles + t) * p.pos_per_tile;
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&bar->q_full[t], q_tx);
 #pragma unroll
-      for (int hb = 0; hb < kBoxesD; ++hb)
-        tma_load_5d(sQ + t * L::kQBytes + hb * kHalfBytes, tmQ, &bar->q_full[t], hb * kColsPerBox, 0,
-                    g.seq.q_off + pos0, p.pack > 1 ? g.it.head : g.it.head, g.seq.bq);
+        for (int hb = 0; hb < kBoxesD; ++hb)
+          tma_load_5d(sQ + t * L::kQBytes + hb * kHalfBytes, tmQ, &bar->q_full[t], hb * kColsPerBox, 0,
+                      g.seq.q_off + pos0, g.it.head, g.seq.bq);
+      }
+      __syncwarp();
       ++q_it[t];
     }
     for (int nb = g.n_hi - 1; nb >= g.n_lo; --nb) {
@@ -64,32 +69,39 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
       for (int kv = 0; kv < 2; ++kv) {  // K tile then V tile of this key block
         const CUtensorMap* tm = kv == 0 ? tmK : tmV;
         mbar_wait(&bar->kv_empty[ring.stage], ring.phase ^ 1, 0x20 + kv);
-        mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
         uint8_t* dst = sKV + ring.stage * L::kKVBytes;
         if (p.page_size == 0) {
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
 #pragma unroll
-          for (int hb = 0; hb < kBoxesD; ++hb)
-            tma_load_4d(dst + hb * kHalfBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
-                        g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
+            for (int hb = 0; hb < kBoxesD; ++hb)
+              tma_load_4d(dst + hb * kHalfBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
+                          g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
+          }
         } else {
           // paged: kv_box_rows = min(128, page_size) rows per box; page ids come from the table
           const int32_t* tbl = p.page_table + int64_t(g.it.bi) * p.page_table_batch_stride;
+          if (elect_one()) mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
           for (int r0 = 0; r0 < kBlockN; r0 += p.kv_box_rows) {
             const int row = nb * kBlockN + r0;
             const int page = tbl[row / p.page_size];
+            if (elect_one()) {
 #pragma unroll
-            for (int hb = 0; hb < kBoxesD; ++hb)
-              tma_load_4d(dst + hb * kHalfBytes + r0 * kRowBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
-                          row % p.page_size, g.hk, page);
+              for (int hb = 0; hb < kBoxesD; ++hb)
+                tma_load_4d(dst + hb * kHalfBytes + r0 * kRowBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
+                            row % p.page_size, g.hk, page);
+            }
           }
         }
+        __syncwarp();
         ring_advance<L::kStages>(ring);
       }
     }
   }
 }
 
-// ----------------------------------------------------------------------------- MMA issuer (one thread)
+// ----------------------------------------------------------------------------- MMA issuer
+// All 32 lanes run the loop and the barrier waits (warp-uniform), one elected lane issues tcgen05.mma / commit.
 // TMEM columns: S_t = t*128, P_t = S_t (16-bit, 64 columns), O_t = 256 + t*128.
 template <int HD, int ELT, bool FP8>
 FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar,
@@ -115,24 +127,31 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
 
   auto issue_qk = [&](int t, int stage) {
     const uint32_t a0 = sQ_addr + t * L::kQBytes, b0 = sKV_addr + stage * L::kKVBytes;
+    if (elect_one()) {
 #pragma unroll
-    for (int ks = 0; ks < kQKSlices; ++ks) {
-      const uint32_t off = (ks / kSlicesPerBox) * kHalfBytes + (ks % kSlicesPerBox) * 32;
-      const uint64_t ad = sdesc_at(kDescK, a0 + off), bd = sdesc_at(kDescK, b0 + off);
-      if (FP8) mma_f8_ss(tmem + t * 128, ad, bd, idesc_qk, ks > 0);
-      else     mma_f16_ss(tmem + t * 128, ad, bd, idesc_qk, ks > 0);
+      for (int ks = 0; ks < kQKSlices; ++ks) {
+        const uint32_t off = (ks / kSlicesPerBox) * kHalfBytes + (ks % kSlicesPerBox) * 32;
+        const uint64_t ad = sdesc_at(kDescK, a0 + off), bd = sdesc_at(kDescK, b0 + off);
+        if (FP8) mma_f8_ss(tmem + t * 128, ad, bd, idesc_qk, ks > 0);
+        else     mma_f16_ss(tmem + t * 128, ad, bd, idesc_qk, ks > 0);
+      }
+      tc_commit(&bar->s_full[t]);
     }
-    tc_commit(&bar->s_full[t]);
+    __syncwarp();
   };
+  auto commit = [&](uint64_t* b) { if (elect_one()) tc_commit(b); __syncwarp(); };
   auto issue_pv = [&](int t, int stage, bool accumulate) {
     const uint32_t b0 = sKV_addr + stage * L::kKVBytes;
+    if (elect_one()) {
 #pragma unroll
-    for (int ks = 0; ks < kPVSlices; ++ks) {
-      const uint64_t bd = sdesc_at(kDescV, b0 + ks * kKPerMma * 128);
-      const uint32_t a_tmem = tmem + t * 128 + ks * 8;  // 8 columns (32 B of P) per K slice
-      if (FP8) mma_f8_ts(tmem + 256 + t * 128, a_tmem, bd, idesc_pv, (accumulate || ks > 0));
-      else     mma_f16_ts(tmem + 256 + t * 128, a_tmem, bd, idesc_pv, (accumulate || ks > 0));
+      for (int ks = 0; ks < kPVSlices; ++ks) {
+        const uint64_t bd = sdesc_at(kDescV, b0 + ks * kKPerMma * 128);
+        const uint32_t a_tmem = tmem + t * 128 + ks * 8;  // 8 columns (32 B of P) per K slice
+        if (FP8) mma_f8_ts(tmem + 256 + t * 128, a_tmem, bd, idesc_pv, (accumulate || ks > 0));
+        else     mma_f16_ts(tmem + 256 + t * 128, a_tmem, bd, idesc_pv, (accumulate || ks > 0));
+      }
     }
+    __syncwarp();
   };
 
   for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
@@ -150,9 +169,9 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
       for (int t = 0; t < kQTiles; ++t)
         if (tile_uses(g, t, g.n_hi - 1)) {
           issue_qk(t, ring.stage);
-          if (g.tr[t].n_min == g.n_hi - 1) { tc_commit(&bar->q_empty[t]); ++q_it[t]; }
+          if (g.tr[t].n_min == g.n_hi - 1) { commit(&bar->q_empty[t]); ++q_it[t]; }
         }
-      tc_commit(&bar->kv_empty[ring.stage]);
+      commit(&bar->kv_empty[ring.stage]);
       ring_advance<L::kStages>(ring);
     }
     for (int nb = g.n_hi - 1; nb >= g.n_lo; --nb) {
@@ -172,15 +191,15 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
           ++p_it[t];
           tc_fence_after();
           issue_pv(t, rv.stage, !first);
-          if (nb == g.tr[t].n_min) { tc_commit(&bar->o_full[t]); ++o_it[t]; }
+          if (nb == g.tr[t].n_min) { commit(&bar->o_full[t]); ++o_it[t]; }
         }
         if (has_next && tile_uses(g, t, nb - 1)) {
           issue_qk(t, rk.stage);
-          if (g.tr[t].n_min == nb - 1) { tc_commit(&bar->q_empty[t]); ++q_it[t]; }
+          if (g.tr[t].n_min == nb - 1) { commit(&bar->q_empty[t]); ++q_it[t]; }
         }
       }
-      tc_commit(&bar->kv_empty[rv.stage]);
-      if (has_next) tc_commit(&bar->kv_empty[rk.stage]);
+      commit(&bar->kv_empty[rv.stage]);
+      if (has_next) commit(&bar->kv_empty[rk.stage]);
     }
   }
 }

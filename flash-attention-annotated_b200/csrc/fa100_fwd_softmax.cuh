@@ -89,6 +89,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
         mx3 = fmaxf(mx3, __uint_as_float(s[3][i]));
       }
       const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      FA_TRACE_POINT(0x90 + t);  // S loaded, row max known
       const float m_cand = fmaxf(m_run, m_blk);
       // lazy rescale: keep the stale max unless it grew by more than 2^8 (NaN from -inf - -inf compares false)
       const bool grow = (m_cand - m_run) * scale_log2 > (FP8 ? 0.0f : kRescaleThreshold);
@@ -143,6 +144,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar->p_full[t]);
+      FA_TRACE_POINT(0xA0 + t);  // P published
     }
 
     // ---- epilogue: O / rowsum, LSE (hopper/softmax.h:137-155, epilogue_fwd.hpp:215-481)
@@ -234,12 +236,12 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
   const uint32_t tmem = bar->tmem_base;
 
   if (warp < 8) {
-    setmaxnreg_inc<232>();
+    setmaxnreg_inc<224>();
     softmax_role<HD, ELT, FP8>(p, bar, tmem, warp / 4, threadIdx.x % 128, warp % 4, lane);
   } else {
-    setmaxnreg_dec<40>();
-    if (warp == kMmaWarp && lane == 0) mma_role<HD, ELT, FP8>(p, fmt, sQ, sKV, bar, tmem);
-    if (warp == kLoadWarp && lane == 0) producer_role<HD, ELT>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar);
+    setmaxnreg_dec<56>();  // pool = 384 x 168 regs at launch: 4 warps release 112 each, 8 warps take 56 each
+    if (warp == kMmaWarp) mma_role<HD, ELT, FP8>(p, fmt, sQ, sKV, bar, tmem);
+    if (warp == kLoadWarp) producer_role<HD, ELT>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar);
   }
   tc_fence_before();
   __syncthreads();

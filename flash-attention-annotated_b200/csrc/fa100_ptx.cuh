@@ -63,25 +63,57 @@ FA_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 static __device__ unsigned int g_fa100_hang_info[4];
 static __device__ volatile unsigned int g_fa100_abort;
 
+// Opt-in timeline (build with -DFA100_TRACE -> libfa100_trace.so): lane 0 of every warp of one CTA records
+// {tag | warp << 16, begin, end} (SM clock, low 32 bits) for each barrier wait and for explicit FA_TRACE_POINTs;
+// the host reads it with fa100_debug_trace().  Never compiled into the product library.
+#ifdef FA100_TRACE
+#ifndef FA100_TRACE_BLOCK
+#define FA100_TRACE_BLOCK 0
+#endif
+constexpr int kTraceWarps = 12, kTracePerWarp = 4096;
+static __device__ unsigned int g_fa100_trace[kTraceWarps * kTracePerWarp * 3];
+static __device__ unsigned int g_fa100_trace_cnt[kTraceWarps];
+FA_DEVICE bool trace_on() { return blockIdx.x == FA100_TRACE_BLOCK && (threadIdx.x & 31) == 0; }
+FA_DEVICE void trace_emit(int tag, long long tb, long long te) {
+  const int w = threadIdx.x >> 5;
+  const unsigned int n = g_fa100_trace_cnt[w];
+  if (n < kTracePerWarp) {
+    unsigned int* dst = g_fa100_trace + (w * kTracePerWarp + n) * 3;
+    dst[0] = unsigned(tag) | (unsigned(w) << 16); dst[1] = unsigned(tb); dst[2] = unsigned(te);
+    g_fa100_trace_cnt[w] = n + 1;
+  }
+}
+#define FA_TRACE_POINT(tag) do { if (trace_on()) { long long t_ = clock64(); trace_emit(tag, t_, t_); } } while (0)
+#else
+#define FA_TRACE_POINT(tag) do { } while (0)
+#endif
+
 FA_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  uint32_t polls = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if ((++polls & 63u) == 0) {
-      if (g_fa100_abort) return;
-      if (clock64() - t0 > FA100_WATCHDOG_CYCLES) {
-        if (atomicCAS(const_cast<unsigned int*>(&g_fa100_abort), 0u, 1u) == 0u) {
-          g_fa100_hang_info[0] = 0xDEAD0000u | (unsigned)tag;
-          g_fa100_hang_info[1] = blockIdx.x;
-          g_fa100_hang_info[2] = threadIdx.x;
-          g_fa100_hang_info[3] = parity;
+#ifdef FA100_TRACE
+  const long long tb_ = clock64();
+#endif
+  if (!mbar_try_wait(bar, parity)) {
+    const long long t0 = clock64();
+    uint32_t polls = 0;
+    while (!mbar_try_wait(bar, parity)) {
+      if ((++polls & 63u) == 0) {
+        if (g_fa100_abort) break;
+        if (clock64() - t0 > FA100_WATCHDOG_CYCLES) {
+          if (atomicCAS(const_cast<unsigned int*>(&g_fa100_abort), 0u, 1u) == 0u) {
+            g_fa100_hang_info[0] = 0xDEAD0000u | (unsigned)tag;
+            g_fa100_hang_info[1] = blockIdx.x;
+            g_fa100_hang_info[2] = threadIdx.x;
+            g_fa100_hang_info[3] = parity;
+          }
+          __threadfence();
+          break;
         }
-        __threadfence();
-        return;
       }
     }
   }
+#ifdef FA100_TRACE
+  if (trace_on()) trace_emit(tag, tb_, clock64());
+#endif
 }
 
 // ------------------------------------------------------------------ TMA

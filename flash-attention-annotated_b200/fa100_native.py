@@ -7,7 +7,7 @@ import os
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libfa100.so")
+LIB_PATH = os.path.join(HERE, os.environ.get("FA100_LIB", "libfa100.so"))  # FA100_LIB=libfa100_trace.so: timeline build
 
 BF16, FP16, E4M3, FP32 = 0, 1, 2, 3
 ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA = -1, -2, -3
@@ -69,7 +69,8 @@ class Plan(C.Structure):
         ("reserved", i32 * 9)]
 
 
-EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_debug_hang_info")
+EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_debug_hang_info",
+           "fa100_debug_trace")
 
 _lib = None
 
@@ -97,7 +98,8 @@ def lib() -> C.CDLL:
         l.fa100_fwd.argtypes = [C.POINTER(FwdParams), vp]
         l.fa100_combine.argtypes = [C.POINTER(CombineParams), vp]
         l.fa100_debug_hang_info.argtypes = [C.POINTER(C.c_uint32 * 4)]
-        for n in ("fa100_plan", "fa100_fwd", "fa100_combine", "fa100_debug_hang_info"):
+        for n in ("fa100_plan", "fa100_fwd", "fa100_combine", "fa100_debug_hang_info",
+           "fa100_debug_trace"):
             getattr(l, n).restype = C.c_int
         if l.fa100_abi_version() != 1:
             raise RuntimeError("libfa100.so ABI version mismatch")
@@ -118,3 +120,10 @@ def hang_info():
     out = (C.c_uint32 * 4)()
     check(lib().fa100_debug_hang_info(C.byref(out)))
     return list(out)
+
+
+def trace(max_events: int = 49152):
+    """Events of the timeline build as a list of (tag, warp, begin, end); empty from the product library."""
+    buf = (C.c_uint32 * (3 * max_events))()
+    n = lib().fa100_debug_trace(buf, max_events)
+    return [(buf[3 * i] & 0xFFFF, buf[3 * i] >> 16, buf[3 * i + 1], buf[3 * i + 2]) for i in range(max(n, 0))]

@@ -169,6 +169,9 @@ int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream);
 int fa100_combine(const Fa100CombineParams* p, fa100_stream_t stream);
 /* self-test hook used by the GPU tests: returns the hang-watchdog record of the last trapped kernel */
 int fa100_debug_hang_info(uint32_t out[4]);
+/* profiling hook: events {tag | warp << 16, begin_clk, end_clk} of the opt-in timeline build (libfa100_trace.so,
+ * -DFA100_TRACE); returns the event count, always 0 from the product library */
+int fa100_debug_trace(uint32_t* out, int max_events);
 
 #ifdef __cplusplus
 }

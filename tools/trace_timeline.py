@@ -1,0 +1,45 @@
+"""Timeline of one CTA of the forward kernel (needs FA100_LIB=libfa100_trace.so).  Prints per-role wait/busy
+statistics and the first events of a steady-state window.  Usage: FA100_LIB=libfa100_trace.so python tools/trace_timeline.py"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [os.path.join(ROOT, "flash-attention-annotated_b200")]
+os.environ.setdefault("FA100_LIB", "libfa100_trace.so")
+import torch
+import fa100_native as N
+from flash_attn_interface import flash_attn_func
+
+b, s, h, hk, d = 1, 8192, 16, 4, 128
+causal = "--noncausal" not in sys.argv
+dt = torch.float8_e4m3fn if "--fp8" in sys.argv else torch.bfloat16
+q = torch.randn(b, s, h, d, device="cuda", dtype=torch.bfloat16).to(dt)
+k = torch.randn(b, s, hk, d, device="cuda", dtype=torch.bfloat16).to(dt)
+v = torch.randn(b, s, hk, d, device="cuda", dtype=torch.bfloat16).to(dt)
+flash_attn_func(q, k, v, causal=causal); torch.cuda.synchronize(); N.trace()
+flash_attn_func(q, k, v, causal=causal); torch.cuda.synchronize()
+ev = N.trace()
+print("events", len(ev), "hang", N.hang_info())
+NAMES = {0x10: "prod wait q_empty0", 0x11: "prod wait q_empty1", 0x20: "prod wait kv_empty(K)", 0x21: "prod wait kv_empty(V)",
+         0x30: "mma wait q_full0", 0x31: "mma wait q_full1", 0x40: "mma wait kv_full(first K)", 0x41: "mma wait kv_full(V)",
+         0x42: "mma wait kv_full(K next)", 0x50: "mma wait o_empty0", 0x51: "mma wait o_empty1", 0x60: "mma wait p_full0",
+         0x61: "mma wait p_full1", 0x70: "smx wait s_full0", 0x71: "smx wait s_full1", 0x80: "smx wait o_full0",
+         0x81: "smx wait o_full1", 0x90: "smx max done 0", 0x91: "smx max done 1", 0xA0: "smx P published 0", 0xA1: "smx P published 1"}
+t0 = min(e[2] for e in ev)
+byw = {}
+for tag, w, tb, te in ev:
+    byw.setdefault(w, []).append((tag, (tb - t0) & 0xFFFFFFFF, (te - t0) & 0xFFFFFFFF))
+for w in sorted(byw):
+    evs = byw[w]
+    span = evs[-1][2] - evs[0][1]
+    agg = {}
+    for tag, tb, te in evs:
+        a = agg.setdefault(tag, [0, 0]); a[0] += 1; a[1] += te - tb
+    print(f"warp {w}: {len(evs)} events over {span} clk")
+    for tag, (n, tot) in sorted(agg.items()):
+        print(f"    {NAMES.get(tag, hex(tag)):28s} n={n:5d} total wait={tot:9d} clk ({100 * tot / max(span, 1):5.1f}%) avg={tot / n:8.1f}")
+# steady-state window: merge warps 0, 4, 8 (first softmax warp of each tile + MMA thread)
+sel = sorted(((tb, te, tag, w) for w in (0, 4, 8, 9) for tag, tb, te in byw.get(w, [])), key=lambda x: x[1])
+start = len(sel) // 2
+print("\n--- steady-state window (sorted by end time): end_clk  role  event  [wait clk]")
+base = sel[start][1]
+for tb, te, tag, w in sel[start:start + 90]:
+    print(f"{te - base:8d}  w{w:<2d} {NAMES.get(tag, hex(tag)):28s} waited {te - tb:6d}")
