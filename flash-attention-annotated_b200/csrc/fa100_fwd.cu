@@ -9,11 +9,11 @@
 
 namespace fa100 {
 
-template <int HD, int ELT, bool FP8>
+template <int HD, int ELT, bool FP8, bool F16>
 static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK,
                            const CUtensorMap& tmV, uint32_t fmt, int grid, cudaStream_t stream) {
   using L = FwdSmem<HD, ELT>;
-  auto kernel = fa100_fwd_kernel<HD, ELT, FP8>;
+  auto kernel = fa100_fwd_kernel<HD, ELT, FP8, F16>;
   static bool attr_set = false;  // benign race: the call is idempotent
   if (!attr_set) {
     FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes));
@@ -128,9 +128,12 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   const int grid = std::max(1, std::min(kp.num_work, num_sm));
   const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : (p->dtype == FA100_FP16 ? kFmtF16 : kFmtE4M3);
   const int hd = (p->d <= 64 && p->dv <= 64 && !fp8) ? 64 : 128;
-  if (fp8) return launch_instance<128, 1, true>(kp, tmQ, tmK, tmV, fmt, grid, stream);
-  if (hd == 64) return launch_instance<64, 2, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
-  return launch_instance<128, 2, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+  const bool f16 = p->dtype == FA100_FP16;
+  if (fp8) return launch_instance<128, 1, true, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+  if (hd == 64) return f16 ? launch_instance<64, 2, false, true>(kp, tmQ, tmK, tmV, fmt, grid, stream)
+                           : launch_instance<64, 2, false, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+  return f16 ? launch_instance<128, 2, false, true>(kp, tmQ, tmK, tmV, fmt, grid, stream)
+             : launch_instance<128, 2, false, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
 }
 
 }  // namespace fa100

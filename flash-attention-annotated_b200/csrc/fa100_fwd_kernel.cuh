@@ -4,17 +4,19 @@
 // (hopper/mainloop_fwd_sm90_tma_gmma_ws.hpp:591-1352, softmax.h:92-168, mask.h:47-162, block.h:14-60,
 // epilogue_fwd.hpp:215-481, tile_scheduler.hpp), re-designed for Blackwell:
 //
-//   warps 0-3   softmax warpgroup for Q tile 0   (1 thread == 1 query row == 1 TMEM lane)
-//   warps 4-7   softmax warpgroup for Q tile 1
-//   warp  8     MMA issuer (one thread): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
-//   warp  9     TMA producer (one thread): Q tiles once per work item, K/V tiles through an mbarrier ring
-//   warps 10-11 idle (pad the third warpgroup so setmaxnreg can hand its registers to the softmax WGs)
+//   warps 0-7   softmax: warp w owns TMEM lanes (= query rows) 32*(w%4).. of BOTH Q tiles and the key columns
+//               [64*(w/4), +64) of every S tile, so two warps per scheduler work on each tile step (a lone warp
+//               cannot keep the MUFU pipe busy: in-order issue stalls on every ex2 result); the two threads of a
+//               row exchange their partial row max through shared memory (one 64-thread named barrier per step)
+//   warp  8     MMA issuer (elected lane): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
+//   warp  9     TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
+//   warps 10-11 idle (pad the third warpgroup so setmaxnreg can hand its registers to the softmax warps)
 //
 // TMEM (512 columns): S0 @0, S1 @128, O0 @256, O1 @384; P_t (16-bit) overwrites columns [0,64) of S_t.
-// Two 128-row Q tiles per CTA ping-pong through the single MMA thread so that softmax(S_t) overlaps the
-// tensor-core work of the other tile.  O is only rescaled when the running row max grew by more than 2^8
-// (exact: the final 1/rowsum and LSE use the same stale max), and the rescale is done in place in TMEM by
-// the softmax warps, which also run the epilogue (normalise, convert, store O and LSE).
+// Two 128-row Q tiles per CTA ping-pong through the tensor pipe: while the softmax warps turn S_t into P_t the
+// MMAs of the other tile run.  O is only rescaled when the running row max grew by more than 2^8 (exact: the
+// final 1/rowsum and LSE use the same stale max); the rescale is done in place in TMEM by the softmax warps,
+// which also run the epilogue (normalise, convert, store O and LSE).
 #pragma once
 #include "fa100_ptx.cuh"
 
@@ -148,11 +150,11 @@ template <int HD, int ELT>
 struct FwdSmem {
   static constexpr int kQBytes = kBlockM * HD * ELT;   // one Q tile
   static constexpr int kKVBytes = kBlockN * HD * ELT;  // one K or V tile
-  static constexpr int kBudget = 227 * 1024 - 2048;    // barriers + 1 KB alignment slack
+  static constexpr int kBudget = 227 * 1024 - 3072;    // barriers + row-max exchange (the base is 1 KB aligned)
   static constexpr int kStagesRaw = (kBudget - kQTiles * kQBytes) / kKVBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kDataBytes = kQTiles * kQBytes + kStages * kKVBytes;
-  static constexpr int kTotalBytes = kDataBytes + 1024 /*align*/ + 512 /*barriers*/;
+  static constexpr int kTotalBytes = kDataBytes + 3072;
 };
 
 struct FwdBarriers {
@@ -161,6 +163,9 @@ struct FwdBarriers {
   uint64_t o_full[kQTiles], o_empty[kQTiles];
   uint64_t kv_full[8], kv_empty[8];
   uint32_t tmem_base;
+  uint32_t pad_[3];
+  float xchg[2][2][128];  // [step parity][column half][row]: partial row max / row sum handed to the partner thread
 };
+static_assert(sizeof(FwdBarriers) <= 3072, "barrier block outgrew its slot");
 
 }  // namespace fa100

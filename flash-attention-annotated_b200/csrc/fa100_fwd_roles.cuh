@@ -190,16 +190,20 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
           mbar_wait(&bar->p_full[t], p_it[t] & 1, 0x60 + t);
           ++p_it[t];
           tc_fence_after();
+          FA_TRACE_POINT(0xB0 + t);
           issue_pv(t, rv.stage, !first);
+          FA_TRACE_POINT(0xB2 + t);
           if (nb == g.tr[t].n_min) { commit(&bar->o_full[t]); ++o_it[t]; }
         }
         if (has_next && tile_uses(g, t, nb - 1)) {
           issue_qk(t, rk.stage);
+          FA_TRACE_POINT(0xB4 + t);
           if (g.tr[t].n_min == nb - 1) { commit(&bar->q_empty[t]); ++q_it[t]; }
         }
       }
       commit(&bar->kv_empty[rv.stage]);
       if (has_next) commit(&bar->kv_empty[rk.stage]);
+      FA_TRACE_POINT(0xB6);
     }
   }
 }

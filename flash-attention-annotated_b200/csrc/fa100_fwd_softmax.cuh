@@ -12,40 +12,56 @@ FA_DEVICE uint32_t pack_f16(float lo, float hi) {
   __half2 v = __floats2half2_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+FA_DEVICE float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 FA_DEVICE float fast_tanh(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 // Online softmax follows hopper/softmax.h:92-168 (exp2 with the scale folded in, fp32 running max / sum,
-// LSE = max*scale + ln(sum)), with Blackwell's row-per-thread TMEM layout (no shuffles) and lazy rescaling.
-template <int HD, int ELT, bool FP8>
-FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t tmem, int t, int row, int warp_in_wg,
-                            int lane) {
-  const uint32_t lane_base = uint32_t(warp_in_wg * 32) << 16;
-  const uint32_t tS = tmem + lane_base + t * 128;
-  const uint32_t tO = tmem + lane_base + 256 + t * 128;
-  uint32_t s_it = 0, o_it = 0;
-  const bool fp16_io = p.out_fp16 != 0;  // P is written in the input dtype (== output dtype for 16-bit)
+// LSE = max*scale + ln(sum)) with Blackwell's row-per-lane TMEM layout and lazy rescaling.  Warp `warp` (0..7) owns
+// rows 32*(warp%4).. of both Q tiles and the key columns [64*(warp/4), +64) of each S tile.
+struct RowInfo { int pos, hq, col_lo, col_hi; bool valid; };
+
+template <int HD, int ELT, bool FP8, bool F16>
+FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t tmem, int warp, int lane) {
+  const int q = warp & 3, h = warp >> 2;
+  const int row = q * 32 + lane;
+  const uint32_t lane_base = uint32_t(q * 32) << 16;
+  constexpr int kOCols = HD / 2;  // O columns this thread rescales / stores
+  uint32_t s_it[kQTiles] = {0, 0}, o_it[kQTiles] = {0, 0}, xstep = 0;
+
+  // hand a float to the partner thread of this row (same rows, other column half) and get theirs
+  auto exchange = [&](float mine) -> float {
+    float* slot = &bar->xchg[xstep & 1][0][0];
+    slot[h * 128 + row] = mine;
+    named_bar_sync(1 + q, 64);
+    const float theirs = slot[(1 - h) * 128 + row];
+    ++xstep;
+    return theirs;
+  };
 
   for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
     const WorkGeom g = make_geom(p, w);
-    const TileRange tr = g.tr[t];
-    if (!tr.has_rows) continue;
-    // ---- this thread's row
-    const int pos0 = (g.it.m_blk * kQTiles + t) * p.pos_per_tile;
-    const int g_in = p.pack > 1 ? row % p.pack : 0;
-    const int pos = pos0 + (p.pack > 1 ? row / p.pack : row);
-    const int hq = p.pack > 1 ? g.it.head * p.qheads_per_kv + g_in : g.it.head;
-    const bool row_valid = (p.pack > 1 ? row / p.pack : row) < p.pos_per_tile && pos < g.seq.sq;
-    const int shift = g.seq.sk - g.seq.sq;
-    int col_hi = g.seq.sk, col_lo = 0;
-    if (p.is_causal) col_hi = min(col_hi, pos + 1 + shift);
-    if (p.is_local) {
-      if (p.window_right >= 0) col_hi = min(col_hi, pos + 1 + shift + p.window_right);
-      if (p.window_left >= 0) col_lo = max(col_lo, pos + shift - p.window_left);
-      if (p.attention_chunk > 0) {
-        const int x = pos + shift, lo_c = x - floor_mod(x, p.attention_chunk);
-        col_lo = max(col_lo, lo_c);
-        col_hi = min(col_hi, lo_c + p.attention_chunk);
+    if (!g.tr[0].has_rows && !g.tr[1].has_rows) continue;
+    RowInfo ri[kQTiles];
+#pragma unroll
+    for (int t = 0; t < kQTiles; ++t) {
+      const int pos0 = (g.it.m_blk * kQTiles + t) * p.pos_per_tile;
+      const int in_tile = p.pack > 1 ? row / p.pack : row;
+      ri[t].pos = pos0 + in_tile;
+      ri[t].hq = p.pack > 1 ? g.it.head * p.qheads_per_kv + row % p.pack : g.it.head;
+      ri[t].valid = in_tile < p.pos_per_tile && ri[t].pos < g.seq.sq;
+      const int shift = g.seq.sk - g.seq.sq;
+      int col_hi = g.seq.sk, col_lo = 0;
+      if (p.is_causal) col_hi = min(col_hi, ri[t].pos + 1 + shift);
+      if (p.is_local) {
+        if (p.window_right >= 0) col_hi = min(col_hi, ri[t].pos + 1 + shift + p.window_right);
+        if (p.window_left >= 0) col_lo = max(col_lo, ri[t].pos + shift - p.window_left);
+        if (p.attention_chunk > 0) {
+          const int x = ri[t].pos + shift, lo_c = x - floor_mod(x, p.attention_chunk);
+          col_lo = max(col_lo, lo_c);
+          col_hi = min(col_hi, lo_c + p.attention_chunk);
+        }
       }
+      ri[t].col_lo = col_lo; ri[t].col_hi = col_hi;
     }
     float scale_log2 = p.scale_log2, out_scale = 1.0f;
     if (FP8) {
@@ -55,176 +71,193 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       scale_log2 *= qd * kd;  // softcap + fp8 is rejected on the host
     }
 
-    float m_run = -INFINITY, l_run = 0.f;
-    for (int nb = tr.n_max - 1; nb >= tr.n_min; --nb) {
-      mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
-      ++s_it;
-      tc_fence_after();
-      uint32_t s[4][32];
+    float m_run[kQTiles] = {-INFINITY, -INFINITY}, l_run[kQTiles] = {0.f, 0.f};
+    for (int nb = g.n_hi - 1; nb >= g.n_lo; --nb) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
-      tmem_ld_wait();
-      if (p.softcap_pre != 0.f) {
+      for (int t = 0; t < kQTiles; ++t) {
+        if (!tile_uses(g, t, nb)) continue;
+        const uint32_t tS = tmem + lane_base + t * 128;
+        const uint32_t tO = tmem + lane_base + 256 + t * 128 + h * kOCols;
+        mbar_wait(&bar->s_full[t], s_it[t] & 1, 0x70 + t);
+        ++s_it[t];
+        tc_fence_after();
+        uint32_t s[2][32];
+        tmem_ld32(tS + h * 64, s[0]);
+        tmem_ld32(tS + h * 64 + 32, s[1]);
+        tmem_ld_wait();
+        if (p.softcap_pre != 0.f) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+          for (int c = 0; c < 2; ++c)
 #pragma unroll
-          for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(fast_tanh(__uint_as_float(s[c][i]) * p.softcap_pre));
-      }
-      const int n0 = nb * kBlockN;
-      if (n0 + kBlockN > col_hi || n0 < col_lo) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int col = n0 + c * 32 + i;
-            if (col >= col_hi || col < col_lo) s[c][i] = 0xff800000u;  // -inf
-          }
-      }
-      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        mx0 = fmaxf(mx0, __uint_as_float(s[0][i]));
-        mx1 = fmaxf(mx1, __uint_as_float(s[1][i]));
-        mx2 = fmaxf(mx2, __uint_as_float(s[2][i]));
-        mx3 = fmaxf(mx3, __uint_as_float(s[3][i]));
-      }
-      const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-      FA_TRACE_POINT(0x90 + t);  // S loaded, row max known
-      const float m_cand = fmaxf(m_run, m_blk);
-      // lazy rescale: keep the stale max unless it grew by more than 2^8 (NaN from -inf - -inf compares false)
-      const bool grow = (m_cand - m_run) * scale_log2 > (FP8 ? 0.0f : kRescaleThreshold);
-      const float acc_scale = grow ? exp2f((m_run - m_cand) * scale_log2) : 1.0f;
-      if (grow) m_run = m_cand;
-      const bool first = nb == tr.n_max - 1;
-      if (!first && __any_sync(0xffffffffu, grow)) {
-#pragma unroll
-        for (int c = 0; c < HD / 32; ++c) {
-          uint32_t o[32];
-          tmem_ld32(tO + c * 32, o);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * acc_scale);
-          tmem_st32(tO + c * 32, o);
+            for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(fast_tanh(__uint_as_float(s[c][i]) * p.softcap_pre));
         }
-      }
-      const float m_sub = (m_run == -INFINITY) ? 0.f : m_run * scale_log2 - (FP8 ? 8.0f : 0.0f);
-      float sum0 = 0.f, sum1 = 0.f;
+        const int n0 = nb * kBlockN + h * 64;
+        if (n0 + 64 > ri[t].col_hi || n0 < ri[t].col_lo) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        if (!FP8) {
-          uint32_t pk[16];
+          for (int c = 0; c < 2; ++c)
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float p0 = exp2f(__uint_as_float(s[c][2 * i]) * scale_log2 - m_sub);
-            const float p1 = exp2f(__uint_as_float(s[c][2 * i + 1]) * scale_log2 - m_sub);
-            sum0 += p0; sum1 += p1;
-            pk[i] = fp16_io ? pack_f16(p0, p1) : pack_bf16(p0, p1);
-          }
-          tmem_st16(tS + c * 16, pk);
-        } else {
-          uint32_t pk[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            float pv[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              pv[j] = exp2f(__uint_as_float(s[c][4 * i + j]) * scale_log2 - m_sub);
+            for (int i = 0; i < 32; ++i) {
+              const int col = n0 + c * 32 + i;
+              if (col >= ri[t].col_hi || col < ri[t].col_lo) s[c][i] = 0xff800000u;  // -inf
             }
-            sum0 += pv[0] + pv[2]; sum1 += pv[1] + pv[3];
-            uint16_t lo, hi;
-            asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(pv[1]), "f"(pv[0]));
-            asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(pv[3]), "f"(pv[2]));
-            pk[i] = uint32_t(lo) | (uint32_t(hi) << 16);
-          }
-          tmem_st8(tS + c * 8, pk);
         }
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          mx0 = fmaxf(mx0, __uint_as_float(s[0][i]));
+          mx1 = fmaxf(mx1, __uint_as_float(s[0][i + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(s[1][i]));
+          mx3 = fmaxf(mx3, __uint_as_float(s[1][i + 1]));
+        }
+        const float m_half = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+        const float m_blk = fmaxf(m_half, exchange(m_half));
+        FA_TRACE_POINT(0x90 + t);  // S loaded, row max known
+        const float m_cand = fmaxf(m_run[t], m_blk);
+        // lazy rescale: keep the stale max unless it grew by more than 2^8 (NaN from -inf - -inf compares false)
+        const bool grow = (m_cand - m_run[t]) * scale_log2 > (FP8 ? 0.0f : kRescaleThreshold);
+        const float acc_scale = grow ? exp2f((m_run[t] - m_cand) * scale_log2) : 1.0f;
+        if (grow) m_run[t] = m_cand;
+        const bool first = nb == g.tr[t].n_max - 1;
+        if (!first && __any_sync(0xffffffffu, grow)) {
+#pragma unroll
+          for (int c = 0; c < kOCols / 32; ++c) {
+            uint32_t o[32];
+            tmem_ld32(tO + c * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * acc_scale);
+            tmem_st32(tO + c * 32, o);
+          }
+        }
+        const float m_sub = (m_run[t] == -INFINITY) ? 0.f : m_run[t] * scale_log2 - (FP8 ? 8.0f : 0.0f);
+        // P = exp2(S * scale - max) in place, packed to the operand dtype and written over S; the row sum is taken
+        // after P is published so that it overlaps the PV MMA instead of delaying it.
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            s[c][i] = __float_as_uint(ex2_approx(fmaf(__uint_as_float(s[c][i]), scale_log2, -m_sub)));
+          if (!FP8) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float p0 = __uint_as_float(s[c][2 * i]), p1 = __uint_as_float(s[c][2 * i + 1]);
+              pk[i] = F16 ? pack_f16(p0, p1) : pack_bf16(p0, p1);
+            }
+            tmem_st16(tS + h * 32 + c * 16, pk);
+          } else {
+            uint32_t pk[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              uint16_t lo, hi;
+              asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(__uint_as_float(s[c][4 * i + 1])), "f"(__uint_as_float(s[c][4 * i])));
+              asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(__uint_as_float(s[c][4 * i + 3])), "f"(__uint_as_float(s[c][4 * i + 2])));
+              pk[i] = uint32_t(lo) | (uint32_t(hi) << 16);
+            }
+            tmem_st8(tS + h * 16 + c * 8, pk);
+          }
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar->p_full[t]);
+        FA_TRACE_POINT(0xA0 + t);  // P published
+        float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          sum0 += __uint_as_float(s[0][i]); sum1 += __uint_as_float(s[0][i + 1]);
+          sum2 += __uint_as_float(s[1][i]); sum3 += __uint_as_float(s[1][i + 1]);
+        }
+        l_run[t] = l_run[t] * acc_scale + ((sum0 + sum1) + (sum2 + sum3));
       }
-      l_run = l_run * acc_scale + (sum0 + sum1);
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->p_full[t]);
-      FA_TRACE_POINT(0xA0 + t);  // P published
     }
 
     // ---- epilogue: O / rowsum, LSE (hopper/softmax.h:137-155, epilogue_fwd.hpp:215-481)
     const bool split = p.num_splits > 1;
-    const bool live = tr.n_max > tr.n_min;
-    const bool dead_row = (l_run == 0.f) || (l_run != l_run);
-    const float inv = dead_row ? 0.f : out_scale / l_run;  // O carries the same 2^8 offset as l_run (fp8)
-    if (FP8) l_run *= 0.00390625f;                         // undo the offset for the LSE
-    const float lse_val = dead_row ? -INFINITY : (m_run * scale_log2 + log2f(l_run)) * kLn2;
-    if (row_valid) {
-      if (!split) p.lse[g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + g.seq.q_off + pos] = lse_val;
-      else p.lse_accum[g.it.split * p.lseacc_split_stride + g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + g.seq.q_off + pos] = lse_val;
-    }
-    if (live) { mbar_wait(&bar->o_full[t], o_it & 1, 0x80 + t); ++o_it; tc_fence_after(); }
-    const int64_t row_idx = g.seq.q_off + pos;
-    uint4* o16 = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.o) + g.seq.bq * p.o_batch_stride +
-                                          row_idx * p.o_row_stride + hq * p.o_head_stride);
-    float4* o32 = reinterpret_cast<float4*>(p.o_accum + g.it.split * p.oacc_split_stride + g.it.bi * p.oacc_batch_stride +
-                                            hq * p.oacc_head_stride + row_idx * p.dv);
 #pragma unroll
-    for (int c = 0; c < HD / 32; ++c) {
-      uint32_t o[32];
-      if (live) { tmem_ld32(tO + c * 32, o); tmem_ld_wait(); }
-      else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] = 0u;
+    for (int t = 0; t < kQTiles; ++t) {
+      if (!g.tr[t].has_rows) continue;
+      const uint32_t tO = tmem + lane_base + 256 + t * 128 + h * kOCols;
+      const bool live = tile_live(g, t);
+      const float l_other = exchange(l_run[t]);
+      float l_tot = h == 0 ? l_run[t] + l_other : l_other + l_run[t];  // same order in both threads
+      const bool dead_row = (l_tot == 0.f) || (l_tot != l_tot);
+      const float inv = dead_row ? 0.f : out_scale / l_tot;  // O carries the same 2^8 offset as the row sum (fp8)
+      if (FP8) l_tot *= 0.00390625f;                          // undo the offset for the LSE
+      const float lse_val = dead_row ? -INFINITY : (m_run[t] * scale_log2 + log2f(l_tot)) * kLn2;
+      const int64_t row_idx = g.seq.q_off + ri[t].pos;
+      if (ri[t].valid && h == 0) {
+        if (!split) p.lse[g.it.bi * p.lse_batch_stride + ri[t].hq * p.lse_head_stride + row_idx] = lse_val;
+        else p.lse_accum[g.it.split * p.lseacc_split_stride + g.it.bi * p.lse_batch_stride + ri[t].hq * p.lse_head_stride + row_idx] = lse_val;
       }
-      if (row_valid) {
-        if (!split) {
+      if (live) { mbar_wait(&bar->o_full[t], o_it[t] & 1, 0x80 + t); ++o_it[t]; tc_fence_after(); }
+      uint4* o16 = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.o) + g.seq.bq * p.o_batch_stride +
+                                            row_idx * p.o_row_stride + ri[t].hq * p.o_head_stride + h * kOCols);
+      float4* o32 = reinterpret_cast<float4*>(p.o_accum + g.it.split * p.oacc_split_stride + g.it.bi * p.oacc_batch_stride +
+                                              ri[t].hq * p.oacc_head_stride + row_idx * p.dv + h * kOCols);
 #pragma unroll
-          for (int v8 = 0; v8 < 4; ++v8) {
-            if (c * 32 + v8 * 8 < p.dv) {
-              uint4 u;
-              uint32_t* up = reinterpret_cast<uint32_t*>(&u);
+      for (int c = 0; c < kOCols / 32; ++c) {
+        uint32_t o[32];
+        if (live) { tmem_ld32(tO + c * 32, o); tmem_ld_wait(); }
+        else {
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const float a = __uint_as_float(o[v8 * 8 + 2 * i]) * inv, b2 = __uint_as_float(o[v8 * 8 + 2 * i + 1]) * inv;
-                up[i] = fp16_io ? pack_f16(a, b2) : pack_bf16(a, b2);
+          for (int i = 0; i < 32; ++i) o[i] = 0u;
+        }
+        if (ri[t].valid) {
+          if (!split) {
+#pragma unroll
+            for (int v8 = 0; v8 < 4; ++v8) {
+              if (h * kOCols + c * 32 + v8 * 8 < p.dv) {
+                uint4 u;
+                uint32_t* up = reinterpret_cast<uint32_t*>(&u);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float a = __uint_as_float(o[v8 * 8 + 2 * i]) * inv, b2 = __uint_as_float(o[v8 * 8 + 2 * i + 1]) * inv;
+                  up[i] = F16 ? pack_f16(a, b2) : pack_bf16(a, b2);
+                }
+                o16[c * 4 + v8] = u;
               }
-              o16[c * 4 + v8] = u;
             }
-          }
-        } else {
+          } else {
 #pragma unroll
-          for (int v4 = 0; v4 < 8; ++v4) {
-            if (c * 32 + v4 * 4 < p.dv)
-              o32[c * 8 + v4] = make_float4(__uint_as_float(o[v4 * 4]) * inv, __uint_as_float(o[v4 * 4 + 1]) * inv,
-                                            __uint_as_float(o[v4 * 4 + 2]) * inv, __uint_as_float(o[v4 * 4 + 3]) * inv);
+            for (int v4 = 0; v4 < 8; ++v4) {
+              if (h * kOCols + c * 32 + v4 * 4 < p.dv)
+                o32[c * 8 + v4] = make_float4(__uint_as_float(o[v4 * 4]) * inv, __uint_as_float(o[v4 * 4 + 1]) * inv,
+                                              __uint_as_float(o[v4 * 4 + 2]) * inv, __uint_as_float(o[v4 * 4 + 3]) * inv);
+            }
           }
         }
       }
-    }
-    if (live) {
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->o_empty[t]);
+      if (live) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar->o_empty[t]);
+      }
     }
   }
 }
 
 // ----------------------------------------------------------------------------- kernel entry
-template <int HD, int ELT, bool FP8>
+template <int HD, int ELT, bool FP8, bool F16>
 __global__ void __launch_bounds__(kThreads, 1)
 fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constant__ CUtensorMap tmQ,
                  const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
   using L = FwdSmem<HD, ELT>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];  // 128-byte swizzle atoms need 1 KB alignment
   uint8_t* sQ = smem;
   uint8_t* sKV = smem + kQTiles * L::kQBytes;
   FwdBarriers* bar = reinterpret_cast<FwdBarriers*>(smem + L::kDataBytes);
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  FA_TRACE_BEGIN();
+  if (smem_u32(smem) & 1023u) __trap();
 
   if (warp == kLoadWarp && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); }
   if (warp == kMmaWarp && lane == 0) {
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
       mbar_init(&bar->q_full[t], 1); mbar_init(&bar->q_empty[t], 1);
-      mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 4);
-      mbar_init(&bar->o_full[t], 1); mbar_init(&bar->o_empty[t], 4);
+      mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 8);
+      mbar_init(&bar->o_full[t], 1); mbar_init(&bar->o_empty[t], 8);
     }
     for (int s = 0; s < 8; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
     fence_mbar_init();
@@ -237,12 +270,13 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
 
   if (warp < 8) {
     setmaxnreg_inc<224>();
-    softmax_role<HD, ELT, FP8>(p, bar, tmem, warp / 4, threadIdx.x % 128, warp % 4, lane);
+    softmax_role<HD, ELT, FP8, F16>(p, bar, tmem, warp, lane);
   } else {
     setmaxnreg_dec<56>();  // pool = 384 x 168 regs at launch: 4 warps release 112 each, 8 warps take 56 each
     if (warp == kMmaWarp) mma_role<HD, ELT, FP8>(p, fmt, sQ, sKV, bar, tmem);
     if (warp == kLoadWarp) producer_role<HD, ELT>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar);
   }
+  FA_TRACE_END();
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem, 512);

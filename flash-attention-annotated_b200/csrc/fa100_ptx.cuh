@@ -74,18 +74,29 @@ constexpr int kTraceWarps = 12, kTracePerWarp = 4096;
 static __device__ unsigned int g_fa100_trace[kTraceWarps * kTracePerWarp * 3];
 static __device__ unsigned int g_fa100_trace_cnt[kTraceWarps];
 FA_DEVICE bool trace_on() { return blockIdx.x == FA100_TRACE_BLOCK && (threadIdx.x & 31) == 0; }
+FA_DEVICE unsigned int* trace_counter() {  // per-warp event counter in shared memory (a global counter costs an L2 round trip per event)
+  static __shared__ unsigned int s_cnt[kTraceWarps];
+  return &s_cnt[threadIdx.x >> 5];
+}
+FA_DEVICE void trace_begin() { if ((threadIdx.x & 31) == 0) *trace_counter() = 0; }
+FA_DEVICE void trace_end() { if (trace_on()) g_fa100_trace_cnt[threadIdx.x >> 5] = *trace_counter(); }
 FA_DEVICE void trace_emit(int tag, long long tb, long long te) {
   const int w = threadIdx.x >> 5;
-  const unsigned int n = g_fa100_trace_cnt[w];
+  unsigned int* cnt = trace_counter();
+  const unsigned int n = *cnt;
   if (n < kTracePerWarp) {
     unsigned int* dst = g_fa100_trace + (w * kTracePerWarp + n) * 3;
     dst[0] = unsigned(tag) | (unsigned(w) << 16); dst[1] = unsigned(tb); dst[2] = unsigned(te);
-    g_fa100_trace_cnt[w] = n + 1;
+    *cnt = n + 1;
   }
 }
 #define FA_TRACE_POINT(tag) do { if (trace_on()) { long long t_ = clock64(); trace_emit(tag, t_, t_); } } while (0)
+#define FA_TRACE_BEGIN() trace_begin()
+#define FA_TRACE_END() trace_end()
 #else
 #define FA_TRACE_POINT(tag) do { } while (0)
+#define FA_TRACE_BEGIN() do { } while (0)
+#define FA_TRACE_END() do { } while (0)
 #endif
 
 FA_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {

@@ -22,7 +22,9 @@ NAMES = {0x10: "prod wait q_empty0", 0x11: "prod wait q_empty1", 0x20: "prod wai
          0x30: "mma wait q_full0", 0x31: "mma wait q_full1", 0x40: "mma wait kv_full(first K)", 0x41: "mma wait kv_full(V)",
          0x42: "mma wait kv_full(K next)", 0x50: "mma wait o_empty0", 0x51: "mma wait o_empty1", 0x60: "mma wait p_full0",
          0x61: "mma wait p_full1", 0x70: "smx wait s_full0", 0x71: "smx wait s_full1", 0x80: "smx wait o_full0",
-         0x81: "smx wait o_full1", 0x90: "smx max done 0", 0x91: "smx max done 1", 0xA0: "smx P published 0", 0xA1: "smx P published 1"}
+         0x81: "smx wait o_full1", 0x90: "smx max done 0", 0x91: "smx max done 1", 0xA0: "smx P published 0", 0xA1: "smx P published 1",
+         0xB0: "mma begin PV0", 0xB1: "mma begin PV1", 0xB2: "mma issued PV0", 0xB3: "mma issued PV1", 0xB4: "mma issued QK0",
+         0xB5: "mma issued QK1", 0xB6: "mma committed kv_empty"}
 t0 = min(e[2] for e in ev)
 byw = {}
 for tag, w, tb, te in ev:

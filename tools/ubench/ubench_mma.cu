@@ -1,0 +1,125 @@
+// Micro-benchmark: tcgen05.mma issue/execute rate for the attention kernel's instruction shapes, alone and
+// with concurrent TMEM loads / MUFU work from other warps.  Build: nvcc -gencode arch=compute_100a,code=sm_100a
+#include <cstdio>
+#include <cstdlib>
+#include "../../flash-attention-annotated_b200/csrc/fa100_ptx.cuh"
+using namespace fa100;
+
+struct Cfg { int mode; int reps; int bg; int nblocks; };
+
+// mode 0: QK only (SS, 8 x K16, N=128)      mode 1: PV only (TS, B MN-major, 8 x K16)   mode 2: QK+PV interleaved per tile
+// mode 3: QK with N=256 (two tiles' worth)   bg bit0: 8 warps run tcgen05.ld of 128 columns in a loop; bit1: MUFU loop; bit2: tcgen05.st 64 cols
+__global__ void __launch_bounds__(384, 1) k_mma(Cfg c, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar[2];
+  __shared__ uint32_t tmem_base;
+  __shared__ volatile int stop;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  // pseudo-random bf16 payload (values ~ +-1): 192 KB
+  for (int i = threadIdx.x; i < 192 * 1024 / 4; i += blockDim.x) {
+    uint32_t h = (i * 2654435761u) ^ (blockIdx.x * 97u);
+    uint32_t lo = 0x3f00u | (h & 0x80ffu), hi = 0x3f00u | ((h >> 16) & 0x80ffu);
+    reinterpret_cast<uint32_t*>(smem)[i] = lo | (hi << 16);
+  }
+  if (threadIdx.x == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); fence_mbar_init(); stop = 0; }
+  if (warp == 0) { tmem_alloc(&tmem_base, 512); tmem_relinquish(); }
+  fence_proxy_async_smem();
+  tc_fence_before(); __syncthreads(); tc_fence_after();
+  const uint32_t tmem = tmem_base;
+  const uint32_t sbase = smem_u32(smem);
+  constexpr uint64_t kDescK = make_sdesc_base(16, 1024);
+  constexpr uint64_t kDescV = make_sdesc_base(128 * 128, 1024);
+  const uint32_t idesc_qk = make_idesc(kFmtBF16, kFmtBF16, 128, 128, 0, 0);
+  const uint32_t idesc_qk256 = make_idesc(kFmtBF16, kFmtBF16, 128, 256, 0, 0);
+  const uint32_t idesc_pv = make_idesc(kFmtBF16, kFmtBF16, 128, 128, 0, 1);
+  if (warp == 8) {
+    long long t0 = clock64();
+    for (int r = 0; r < c.reps; ++r) {
+      const int t = r & 1;
+      const uint32_t q0 = sbase + t * 32768, kv0 = sbase + 65536 + (r % 3) * 32768;
+      if (elect_one()) {
+        if (c.mode == 0 || c.mode == 2) {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks / 4) * 16384 + (ks % 4) * 32;
+            mma_f16_ss(tmem + t * 128, sdesc_at(kDescK, q0 + off), sdesc_at(kDescK, kv0 + off), idesc_qk, ks > 0);
+          }
+        }
+        if (c.mode == 1 || c.mode == 2) {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            mma_f16_ts(tmem + 256 + t * 128, tmem + t * 128 + ks * 8, sdesc_at(kDescV, kv0 + ks * 16 * 128), idesc_pv, 1);
+        }
+        if (c.mode == 3) {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks / 4) * 16384 + (ks % 4) * 32;
+            mma_f16_ss(tmem, sdesc_at(kDescK, q0 + off), sdesc_at(make_sdesc_base(16, 1024), kv0 + off), idesc_qk256, ks > 0);
+          }
+        }
+      }
+      __syncwarp();
+    }
+    long long t1 = clock64();
+    if (elect_one()) tc_commit(&bar[0]);
+    __syncwarp();
+    mbar_wait(&bar[0], 0);
+    long long t2 = clock64();
+    stop = 1;
+    if (lane == 0 && blockIdx.x == 0) { out[0] = t1 - t0; out[1] = t2 - t0; }
+  } else if (warp < 8 && c.bg) {
+    const uint32_t lane_base = uint32_t((warp % 4) * 32) << 16;
+    float acc = 0.f;
+    long long iters = 0;
+    while (!stop) {
+      if (c.bg & 1) {
+        uint32_t s[32];
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          tmem_ld32(tmem + lane_base + (warp / 4) * 128 + cc * 32, s); tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc += __uint_as_float(s[i]);
+        }
+      }
+      if (c.bg & 2) {
+        float x = acc * 1e-30f + lane;
+#pragma unroll
+        for (int i = 0; i < 128; ++i) { x = exp2f(x * 0.001f - 1.0f); acc += x; }
+      }
+      if (c.bg & 4) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) pk[i] = __float_as_uint(acc) + i;
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) tmem_st16(tmem + lane_base + 384 + cc * 16, pk);
+        tmem_st_wait();
+      }
+      ++iters;
+    }
+    if (acc == 123.456f) out[7] = iters;
+    if (lane == 0 && blockIdx.x == 0 && warp == 0) out[2] = iters;
+  }
+  tc_fence_before(); __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+int main() {
+  long long* d; cudaMalloc(&d, 64); 
+  const int smem = 200 * 1024;
+  cudaFuncSetAttribute(k_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const char* mname[] = {"QK ss 128x128", "PV ts 128x128 (B mn-major)", "QK+PV interleaved", "QK ss 128x256"};
+  for (int nblocks : {1, 148})
+    for (int mode = 0; mode < 4; ++mode)
+      for (int bg : {0, 1, 2, 3, 7}) {
+        Cfg c{mode, 2000, bg, nblocks};
+        cudaMemset(d, 0, 64);
+        k_mma<<<nblocks, 384, smem>>>(c, d);
+        cudaError_t e = cudaDeviceSynchronize();
+        long long h[8]; cudaMemcpy(h, d, 64, cudaMemcpyDeviceToHost);
+        const int mmas = c.reps * (mode == 2 ? 16 : 8);
+        printf("blocks=%3d %-28s bg=%d: issue %.1f clk/mma, complete %.1f clk/mma (ideal %d)  bg iters=%lld  %s\n", nblocks, mname[mode], bg,
+               double(h[0]) / mmas, double(h[1]) / mmas, mode == 3 ? 128 : 64, h[2], e == cudaSuccess ? "" : cudaGetErrorString(e));
+      }
+  return 0;
+}
