@@ -4,13 +4,14 @@
 // (hopper/mainloop_fwd_sm90_tma_gmma_ws.hpp:591-1352, softmax.h:92-168, mask.h:47-162, block.h:14-60,
 // epilogue_fwd.hpp:215-481, tile_scheduler.hpp), re-designed for Blackwell:
 //
-//   warps 0-7   softmax: warp w owns TMEM lanes (= query rows) 32*(w%4).. of BOTH Q tiles and the key columns
-//               [64*(w/4), +64) of every S tile, so two warps per scheduler work on each tile step (a lone warp
-//               cannot keep the MUFU pipe busy: in-order issue stalls on every ex2 result); the two threads of a
-//               row exchange their partial row max through shared memory (one 64-thread named barrier per step)
-//   warp  8     MMA issuer (elected lane): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
-//   warp  9     TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
-//   warps 10-11 idle (pad the third warpgroup so setmaxnreg can hand its registers to the softmax warps)
+//   warps 0-15  softmax: warp w works on Q tile w/8, owns TMEM lanes (= query rows) 32*(w%4).. and the key columns
+//               [64*((w/4)%2), +64) of each S tile: two threads per row, four softmax warps per scheduler, so that
+//               barrier / TMEM latencies of one warp hide behind the MUFU work of the others (a lone warp per
+//               scheduler cannot keep the MUFU pipe busy).  The two threads of a row exchange their partial row
+//               max through shared memory (one 64-thread named barrier per step).
+//   warps 16,17 MMA issuers, one per Q tile (elected lane): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
+//   warp  18    TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
+//   warp  19    idle (completes the fifth warpgroup for setmaxnreg: softmax warps run with 104 registers, the rest 64)
 //
 // TMEM (512 columns): S0 @0, S1 @128, O0 @256, O1 @384; P_t (16-bit) overwrites columns [0,64) of S_t.
 // Two 128-row Q tiles per CTA ping-pong through the tensor pipe: while the softmax warps turn S_t into P_t the
@@ -25,9 +26,10 @@ namespace fa100 {
 constexpr int kBlockM = 128;   // query rows per Q tile
 constexpr int kBlockN = 128;   // keys per main-loop step
 constexpr int kQTiles = 2;     // Q tiles per CTA
-constexpr int kThreads = 384;
-constexpr int kMmaWarp = 8;
-constexpr int kLoadWarp = 9;
+constexpr int kSoftmaxWarps = 16;
+constexpr int kMmaWarp = 16;
+constexpr int kLoadWarp = 18;
+constexpr int kThreads = 20 * 32;  // warps 18, 19 idle: register allocation rounds the CTA to whole warpgroups anyway
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
@@ -150,11 +152,12 @@ template <int HD, int ELT>
 struct FwdSmem {
   static constexpr int kQBytes = kBlockM * HD * ELT;   // one Q tile
   static constexpr int kKVBytes = kBlockN * HD * ELT;  // one K or V tile
-  static constexpr int kBudget = 227 * 1024 - 3072;    // barriers + row-max exchange (the base is 1 KB aligned)
+  static constexpr int kBarrierBytes = 5120;           // barriers + row-max exchange (the base is 1 KB aligned)
+  static constexpr int kBudget = 227 * 1024 - kBarrierBytes;
   static constexpr int kStagesRaw = (kBudget - kQTiles * kQBytes) / kKVBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kDataBytes = kQTiles * kQBytes + kStages * kKVBytes;
-  static constexpr int kTotalBytes = kDataBytes + 3072;
+  static constexpr int kTotalBytes = kDataBytes + kBarrierBytes;
 };
 
 struct FwdBarriers {
@@ -164,8 +167,8 @@ struct FwdBarriers {
   uint64_t kv_full[8], kv_empty[8];
   uint32_t tmem_base;
   uint32_t pad_[3];
-  float xchg[2][2][128];  // [step parity][column half][row]: partial row max / row sum handed to the partner thread
+  float xchg[kQTiles][2][2][128];  // [tile][step parity][column half][row]: partial row max / sum for the partner thread
 };
-static_assert(sizeof(FwdBarriers) <= 3072, "barrier block outgrew its slot");
+static_assert(sizeof(FwdBarriers) <= 5120 - 128, "barrier block outgrew its slot");
 
 }  // namespace fa100

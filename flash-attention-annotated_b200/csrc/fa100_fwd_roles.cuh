@@ -100,12 +100,15 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   }
 }
 
-// ----------------------------------------------------------------------------- MMA issuer
-// All 32 lanes run the loop and the barrier waits (warp-uniform), one elected lane issues tcgen05.mma / commit.
+// ----------------------------------------------------------------------------- MMA issuer (one warp per Q tile)
+// Warp kMmaWarp + t serves Q tile t: S_t = Q_t K^T (SS form) and O_t += P_t V (TS form, P in TMEM).  All 32 lanes run the
+// loop and the barrier waits (warp-uniform control flow keeps descriptors in uniform registers); one elected lane
+// issues.  Two issuing warps keep the two tiles' P -> PV -> QK -> S chains independent: the barrier latencies and the
+// instruction overhead of one tile hide behind the other tile's MMAs on the (shared, in-order) tensor pipe.  Both warps
+// walk every ring stage, including key blocks their tile does not use, and each K/V stage is released by two commits.
 // TMEM columns: S_t = t*128, P_t = S_t (16-bit, 64 columns), O_t = 256 + t*128.
 template <int HD, int ELT, bool FP8>
-FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar,
-                        uint32_t tmem) {
+FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, int t, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar, uint32_t tmem) {
   using L = FwdSmem<HD, ELT>;
   constexpr int kHalfBytes = kBlockN * 128;
   constexpr int kColsPerBox = 128 / ELT;
@@ -115,63 +118,43 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   constexpr int kPVSlices = kBlockN / kKPerMma;
   const uint32_t idesc_qk = make_idesc(fmt, fmt, kBlockM, kBlockN, 0, 0);
   const uint32_t idesc_pv = make_idesc(fmt, fmt, kBlockM, HD, 0, 1);
-  // K-major operand tiles [128 rows][128 B] SW128: 8-row groups 1024 B apart (SBO); LBO unused.
-  constexpr uint64_t kDescK = make_sdesc_base(16, 1024);
-  // V as MN-major B operand: 128-byte rows along dv, 8 key rows per swizzle atom (SBO = 1024 B),
-  // next 64(16-bit)/128(8-bit) dv columns in the next box (LBO = one [128][128 B] region).
-  constexpr uint64_t kDescV = make_sdesc_base(kHalfBytes, 1024);
-  const uint32_t sQ_addr = smem_u32(sQ), sKV_addr = smem_u32(sKV);
+  // K-major operand tiles [128 rows][128 B] SW128: 8-row groups 1024 B apart (SBO); LBO unused (1).
+  // V as MN-major B operand: 128-byte rows along dv, 8 key rows per swizzle atom (SBO = 1024 B), the next
+  // 64 (16-bit) / 128 (8-bit) dv columns in the next box (LBO = one [128][128 B] region).
+  constexpr uint32_t kHi = sdesc_hi(1024);
+  constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboV = sdesc_lo_lbo(kHalfBytes);
+  const uint32_t q_lo = ((smem_u32(sQ) + t * L::kQBytes) >> 4) | kLboK;
+  const uint32_t kv_lo = smem_u32(sKV) >> 4;
+  const uint32_t tS = tmem + t * 128, tO = tmem + 256 + t * 128;
 
   RingState ring;
-  uint32_t q_it[kQTiles] = {0, 0}, p_it[kQTiles] = {0, 0}, o_it[kQTiles] = {0, 0};
-
-  auto issue_qk = [&](int t, int stage) {
-    const uint32_t a0 = sQ_addr + t * L::kQBytes, b0 = sKV_addr + stage * L::kKVBytes;
-    if (elect_one()) {
-#pragma unroll
-      for (int ks = 0; ks < kQKSlices; ++ks) {
-        const uint32_t off = (ks / kSlicesPerBox) * kHalfBytes + (ks % kSlicesPerBox) * 32;
-        const uint64_t ad = sdesc_at(kDescK, a0 + off), bd = sdesc_at(kDescK, b0 + off);
-        if (FP8) mma_f8_ss(tmem + t * 128, ad, bd, idesc_qk, ks > 0);
-        else     mma_f16_ss(tmem + t * 128, ad, bd, idesc_qk, ks > 0);
-      }
-      tc_commit(&bar->s_full[t]);
-    }
-    __syncwarp();
-  };
-  auto commit = [&](uint64_t* b) { if (elect_one()) tc_commit(b); __syncwarp(); };
-  auto issue_pv = [&](int t, int stage, bool accumulate) {
-    const uint32_t b0 = sKV_addr + stage * L::kKVBytes;
-    if (elect_one()) {
-#pragma unroll
-      for (int ks = 0; ks < kPVSlices; ++ks) {
-        const uint64_t bd = sdesc_at(kDescV, b0 + ks * kKPerMma * 128);
-        const uint32_t a_tmem = tmem + t * 128 + ks * 8;  // 8 columns (32 B of P) per K slice
-        if (FP8) mma_f8_ts(tmem + 256 + t * 128, a_tmem, bd, idesc_pv, (accumulate || ks > 0));
-        else     mma_f16_ts(tmem + 256 + t * 128, a_tmem, bd, idesc_pv, (accumulate || ks > 0));
-      }
-    }
-    __syncwarp();
-  };
+  uint32_t q_it = 0, p_it = 0, o_it = 0;
 
   for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
     const WorkGeom g = make_geom(p, w);
     if (g.n_hi <= g.n_lo) continue;
-#pragma unroll
-    for (int t = 0; t < kQTiles; ++t)
-      if (tile_live(g, t)) { mbar_wait(&bar->q_full[t], q_it[t] & 1, 0x30 + t); }
-    tc_fence_after();
-    // prologue: S_t = Q_t K^T for the first (right-most) key block
+    const int n_min = g.tr[t].n_min, n_max = g.tr[t].n_max;  // this tile uses key blocks [n_min, n_max)
+    if (n_max > n_min) { mbar_wait(&bar->q_full[t], q_it & 1, 0x30 + t); }
+    // prologue: S_t = Q_t K^T for the first (right-most) key block of the work item
     {
       mbar_wait(&bar->kv_full[ring.stage], ring.phase, 0x40);
       tc_fence_after();
+      const bool use = g.n_hi - 1 >= n_min && g.n_hi - 1 < n_max;
+      if (elect_one()) {
+        if (use) {
+          const uint32_t b_lo = (kv_lo + ring.stage * (L::kKVBytes >> 4)) | kLboK;
 #pragma unroll
-      for (int t = 0; t < kQTiles; ++t)
-        if (tile_uses(g, t, g.n_hi - 1)) {
-          issue_qk(t, ring.stage);
-          if (g.tr[t].n_min == g.n_hi - 1) { commit(&bar->q_empty[t]); ++q_it[t]; }
+          for (int ks = 0; ks < kQKSlices; ++ks) {
+            const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
+            mma_ss<FP8>(tS, q_lo + off, b_lo + off, kHi, idesc_qk, ks > 0);
+          }
+          tc_commit(&bar->s_full[t]);
+          if (n_min == g.n_hi - 1) tc_commit(&bar->q_empty[t]);
         }
-      commit(&bar->kv_empty[ring.stage]);
+        tc_commit(&bar->kv_empty[ring.stage]);
+      }
+      __syncwarp();
+      if (use && n_min == g.n_hi - 1) ++q_it;
       ring_advance<L::kStages>(ring);
     }
     for (int nb = g.n_hi - 1; nb >= g.n_lo; --nb) {
@@ -181,29 +164,41 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
       const bool has_next = nb - 1 >= g.n_lo;
       mbar_wait(&bar->kv_full[rv.stage], rv.phase, 0x41);
       if (has_next) { mbar_wait(&bar->kv_full[rk.stage], rk.phase, 0x42); ring_advance<L::kStages>(ring); }
-      tc_fence_after();
-#pragma unroll
-      for (int t = 0; t < kQTiles; ++t) {
-        if (tile_uses(g, t, nb)) {
-          const bool first = nb == g.tr[t].n_max - 1;
-          if (first) mbar_wait(&bar->o_empty[t], (o_it[t] & 1) ^ 1, 0x50 + t);  // epilogue of the previous item
-          mbar_wait(&bar->p_full[t], p_it[t] & 1, 0x60 + t);
-          ++p_it[t];
-          tc_fence_after();
-          FA_TRACE_POINT(0xB0 + t);
-          issue_pv(t, rv.stage, !first);
-          FA_TRACE_POINT(0xB2 + t);
-          if (nb == g.tr[t].n_min) { commit(&bar->o_full[t]); ++o_it[t]; }
-        }
-        if (has_next && tile_uses(g, t, nb - 1)) {
-          issue_qk(t, rk.stage);
-          FA_TRACE_POINT(0xB4 + t);
-          if (g.tr[t].n_min == nb - 1) { commit(&bar->q_empty[t]); ++q_it[t]; }
-        }
+      const bool use_pv = nb >= n_min && nb < n_max;
+      const bool use_qk = has_next && nb - 1 >= n_min && nb - 1 < n_max;
+      const bool first = nb == n_max - 1;
+      if (use_pv) {
+        if (first) mbar_wait(&bar->o_empty[t], (o_it & 1) ^ 1, 0x50 + t);  // epilogue of the previous work item
+        mbar_wait(&bar->p_full[t], p_it & 1, 0x60 + t);
+        ++p_it;
       }
-      commit(&bar->kv_empty[rv.stage]);
-      if (has_next) commit(&bar->kv_empty[rk.stage]);
-      FA_TRACE_POINT(0xB6);
+      tc_fence_after();
+      FA_TRACE_POINT(0xB0 + t);
+      if (elect_one()) {
+        if (use_pv) {
+          const uint32_t b_lo = (kv_lo + rv.stage * (L::kKVBytes >> 4)) | kLboV;
+#pragma unroll
+          for (int ks = 0; ks < kPVSlices; ++ks)
+            mma_ts<FP8>(tO, tS + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc_pv, (!first || ks > 0));
+          if (nb == n_min) tc_commit(&bar->o_full[t]);
+        }
+        if (use_qk) {
+          const uint32_t b_lo = (kv_lo + rk.stage * (L::kKVBytes >> 4)) | kLboK;
+#pragma unroll
+          for (int ks = 0; ks < kQKSlices; ++ks) {
+            const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
+            mma_ss<FP8>(tS, q_lo + off, b_lo + off, kHi, idesc_qk, ks > 0);
+          }
+          tc_commit(&bar->s_full[t]);
+          if (n_min == nb - 1) tc_commit(&bar->q_empty[t]);
+        }
+        tc_commit(&bar->kv_empty[rv.stage]);
+        if (has_next) tc_commit(&bar->kv_empty[rk.stage]);
+      }
+      __syncwarp();
+      FA_TRACE_POINT(0xB4 + t);
+      if (use_pv && nb == n_min) ++o_it;
+      if (use_qk && n_min == nb - 1) ++q_it;
     }
   }
 }

@@ -70,13 +70,17 @@ static __device__ volatile unsigned int g_fa100_abort;
 #ifndef FA100_TRACE_BLOCK
 #define FA100_TRACE_BLOCK 0
 #endif
-constexpr int kTraceWarps = 12, kTracePerWarp = 4096;
+constexpr int kTraceWarps = 20, kTracePerWarp = 4096;
 static __device__ unsigned int g_fa100_trace[kTraceWarps * kTracePerWarp * 3];
 static __device__ unsigned int g_fa100_trace_cnt[kTraceWarps];
 FA_DEVICE bool trace_on() { return blockIdx.x == FA100_TRACE_BLOCK && (threadIdx.x & 31) == 0; }
 FA_DEVICE unsigned int* trace_counter() {  // per-warp event counter in shared memory (a global counter costs an L2 round trip per event)
-  static __shared__ unsigned int s_cnt[kTraceWarps];
-  return &s_cnt[threadIdx.x >> 5];
+  // last 128 bytes of the dynamic allocation (free tail of the barrier block): a static array would push the
+  // kernel over the 227 KB limit
+  extern __shared__ __align__(1024) uint8_t fa100_trace_smem[];
+  uint32_t dyn;
+  asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn));
+  return reinterpret_cast<unsigned int*>(fa100_trace_smem + dyn - 128) + (threadIdx.x >> 5);
 }
 FA_DEVICE void trace_begin() { if ((threadIdx.x & 31) == 0) *trace_counter() = 0; }
 FA_DEVICE void trace_end() { if (trace_on()) g_fa100_trace_cnt[threadIdx.x >> 5] = *trace_counter(); }
@@ -99,29 +103,31 @@ FA_DEVICE void trace_emit(int tag, long long tb, long long te) {
 #define FA_TRACE_END() do { } while (0)
 #endif
 
+// Slow path, kept as small as possible because it is inlined at a dozen wait sites and the kernel's three roles
+// already overflow the instruction cache: poll; every 64 polls look at the abort flag and the clock.
+FA_DEVICE void mbar_wait_slow(uint64_t* bar, uint32_t parity, int tag) {
+  const long long t0 = clock64();
+  uint32_t polls = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if ((++polls & 63u) == 0) {
+      if (g_fa100_abort) return;
+      if (clock64() - t0 > FA100_WATCHDOG_CYCLES) {
+        g_fa100_hang_info[0] = 0xDEAD0000u | (unsigned)tag;  // last writer wins: any stuck wait identifies the bug
+        g_fa100_hang_info[1] = blockIdx.x;
+        g_fa100_hang_info[2] = threadIdx.x;
+        g_fa100_hang_info[3] = parity;
+        g_fa100_abort = 1;
+        return;
+      }
+    }
+  }
+}
+
 FA_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
 #ifdef FA100_TRACE
   const long long tb_ = clock64();
 #endif
-  if (!mbar_try_wait(bar, parity)) {
-    const long long t0 = clock64();
-    uint32_t polls = 0;
-    while (!mbar_try_wait(bar, parity)) {
-      if ((++polls & 63u) == 0) {
-        if (g_fa100_abort) break;
-        if (clock64() - t0 > FA100_WATCHDOG_CYCLES) {
-          if (atomicCAS(const_cast<unsigned int*>(&g_fa100_abort), 0u, 1u) == 0u) {
-            g_fa100_hang_info[0] = 0xDEAD0000u | (unsigned)tag;
-            g_fa100_hang_info[1] = blockIdx.x;
-            g_fa100_hang_info[2] = threadIdx.x;
-            g_fa100_hang_info[3] = parity;
-          }
-          __threadfence();
-          break;
-        }
-      }
-    }
-  }
+  if (!mbar_try_wait(bar, parity) && !mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity, tag);
 #ifdef FA100_TRACE
   if (trace_on()) trace_emit(tag, tb_, clock64());
 #endif
@@ -200,6 +206,38 @@ FA_DEVICE void mma_f8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint
       ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+
+// Same instructions with the 64-bit shared-memory descriptors given as {lo, hi} words: hi is a compile-time
+// constant and lo = (address >> 4) + offset | LBO field, so the issue loop spends one integer add per MMA.
+template <bool FP8>
+FA_DEVICE void mma_ss(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc, uint32_t accumulate) {
+  if (FP8)
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], da, db, %4, p;\n\t}\n"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+  else
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}\n"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+template <bool FP8>
+FA_DEVICE void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc, uint32_t accumulate) {
+  if (FP8)
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], [%1], db, %4, p;\n\t}\n"
+        ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+  else
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}\n"
+        ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+// descriptor words for a 128-byte-swizzled operand: hi = SBO >> 4 | version 1 << 14 | SWIZZLE_128B << 29
+__host__ __device__ constexpr uint32_t sdesc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFF) | (1u << 14) | (2u << 29); }
+__host__ __device__ constexpr uint32_t sdesc_lo_lbo(uint32_t lbo_bytes) { return ((lbo_bytes >> 4) & 0x3FFF) << 16; }
 
 // Instruction descriptor (cute::UMMA::InstrDescriptor): c_format[4,6) a_format[7,10) b_format[10,13)
 // a_major[15] b_major[16] (0 = K-major, 1 = MN-major) n_dim[17,23) = N>>3, m_dim[24,29) = M>>4.

@@ -24,7 +24,9 @@ NAMES = {0x10: "prod wait q_empty0", 0x11: "prod wait q_empty1", 0x20: "prod wai
          0x61: "mma wait p_full1", 0x70: "smx wait s_full0", 0x71: "smx wait s_full1", 0x80: "smx wait o_full0",
          0x81: "smx wait o_full1", 0x90: "smx max done 0", 0x91: "smx max done 1", 0xA0: "smx P published 0", 0xA1: "smx P published 1",
          0xB0: "mma begin PV0", 0xB1: "mma begin PV1", 0xB2: "mma issued PV0", 0xB3: "mma issued PV1", 0xB4: "mma issued QK0",
-         0xB5: "mma issued QK1", 0xB6: "mma committed kv_empty"}
+         0xB5: "mma issued QK1", 0xB6: "mma committed kv_empty", 0xC0: "smx exp begin", 0xC1: "smx chunk0 stored", 0xC2: "smx chunk1 stored",
+         0xC3: "smx st_wait done", 0xC4: "smx S in regs", 0xC5: "smx local max done"}
+WARPS = tuple(int(x) for x in os.environ.get("TRACE_WARPS", "0,4,8").split(","))
 t0 = min(e[2] for e in ev)
 byw = {}
 for tag, w, tb, te in ev:
@@ -39,7 +41,7 @@ for w in sorted(byw):
     for tag, (n, tot) in sorted(agg.items()):
         print(f"    {NAMES.get(tag, hex(tag)):28s} n={n:5d} total wait={tot:9d} clk ({100 * tot / max(span, 1):5.1f}%) avg={tot / n:8.1f}")
 # steady-state window: merge warps 0, 4, 8 (first softmax warp of each tile + MMA thread)
-sel = sorted(((tb, te, tag, w) for w in (0, 4, 8, 9) for tag, tb, te in byw.get(w, [])), key=lambda x: x[1])
+sel = sorted(((tb, te, tag, w) for w in WARPS for tag, tb, te in byw.get(w, [])), key=lambda x: x[1])
 start = len(sel) // 2
 print("\n--- steady-state window (sorted by end time): end_clk  role  event  [wait clk]")
 base = sel[start][1]
