@@ -167,3 +167,15 @@ extern "C" int fa100_debug_trace(uint32_t* out, int max_events) {
   return 0;
 #endif
 }
+
+extern "C" int fa100_debug_prof(uint32_t* out, int max_words) {
+  // per-warp cycle buckets of the timeline build (20 warps x 8 buckets); returns the number of words (0 in the product build)
+#ifdef FA100_TRACE
+  const int n = fa100::kTraceWarps * 8 < max_words ? fa100::kTraceWarps * 8 : max_words;
+  if (cudaMemcpyFromSymbol(out, fa100::g_fa100_prof, n * sizeof(uint32_t)) != cudaSuccess) return -3;
+  return n;
+#else
+  (void)out; (void)max_words;
+  return 0;
+#endif
+}

@@ -4,14 +4,11 @@
 // (hopper/mainloop_fwd_sm90_tma_gmma_ws.hpp:591-1352, softmax.h:92-168, mask.h:47-162, block.h:14-60,
 // epilogue_fwd.hpp:215-481, tile_scheduler.hpp), re-designed for Blackwell:
 //
-//   warps 0-15  softmax: warp w works on Q tile w/8, owns TMEM lanes (= query rows) 32*(w%4).. and the key columns
-//               [64*((w/4)%2), +64) of each S tile: two threads per row, four softmax warps per scheduler, so that
-//               barrier / TMEM latencies of one warp hide behind the MUFU work of the others (a lone warp per
-//               scheduler cannot keep the MUFU pipe busy).  The two threads of a row exchange their partial row
-//               max through shared memory (one 64-thread named barrier per step).
-//   warps 16,17 MMA issuers, one per Q tile (elected lane): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
-//   warp  18    TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
-//   warp  19    idle (completes the fifth warpgroup for setmaxnreg: softmax warps run with 104 registers, the rest 64)
+//   warps 0-3   softmax for Q tile 0: one thread == one query row == one TMEM lane (row max / sum without shuffles)
+//   warps 4-7   softmax for Q tile 1
+//   warps 8,9   MMA issuers, one per Q tile (elected lane): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
+//   warp  10    TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
+//   warp  11    idle (completes the third warpgroup for setmaxnreg: softmax warps run with 224 registers, the rest 56)
 //
 // TMEM (512 columns): S0 @0, S1 @128, O0 @256, O1 @384; P_t (16-bit) overwrites columns [0,64) of S_t.
 // Two 128-row Q tiles per CTA ping-pong through the tensor pipe: while the softmax warps turn S_t into P_t the
@@ -26,10 +23,10 @@ namespace fa100 {
 constexpr int kBlockM = 128;   // query rows per Q tile
 constexpr int kBlockN = 128;   // keys per main-loop step
 constexpr int kQTiles = 2;     // Q tiles per CTA
-constexpr int kSoftmaxWarps = 16;
-constexpr int kMmaWarp = 16;
-constexpr int kLoadWarp = 18;
-constexpr int kThreads = 20 * 32;  // warps 18, 19 idle: register allocation rounds the CTA to whole warpgroups anyway
+constexpr int kSoftmaxWarps = 8;
+constexpr int kMmaWarp = 8;
+constexpr int kLoadWarp = 10;
+constexpr int kThreads = 12 * 32;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 units

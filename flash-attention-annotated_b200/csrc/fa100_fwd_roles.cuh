@@ -129,6 +129,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, int t, uint8_t* 
 
   RingState ring;
   uint32_t q_it = 0, p_it = 0, o_it = 0;
+  FA_PROF_DECL();  // 0 kv_full waits, 1 p_full / o_empty waits, 2 issue, 3 everything else
 
   for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
     const WorkGeom g = make_geom(p, w);
@@ -162,8 +163,10 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, int t, uint8_t* 
       ring_advance<L::kStages>(ring);
       const RingState rk = ring;  // K(nb-1)
       const bool has_next = nb - 1 >= g.n_lo;
+      FA_PROF(3);
       mbar_wait(&bar->kv_full[rv.stage], rv.phase, 0x41);
       if (has_next) { mbar_wait(&bar->kv_full[rk.stage], rk.phase, 0x42); ring_advance<L::kStages>(ring); }
+      FA_PROF(0);
       const bool use_pv = nb >= n_min && nb < n_max;
       const bool use_qk = has_next && nb - 1 >= n_min && nb - 1 < n_max;
       const bool first = nb == n_max - 1;
@@ -173,7 +176,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, int t, uint8_t* 
         ++p_it;
       }
       tc_fence_after();
-      FA_TRACE_POINT(0xB0 + t);
+      FA_PROF(1);
       if (elect_one()) {
         if (use_pv) {
           const uint32_t b_lo = (kv_lo + rv.stage * (L::kKVBytes >> 4)) | kLboV;
@@ -196,11 +199,13 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, int t, uint8_t* 
         if (has_next) tc_commit(&bar->kv_empty[rk.stage]);
       }
       __syncwarp();
-      FA_TRACE_POINT(0xB4 + t);
+      FA_PROF(2);
       if (use_pv && nb == n_min) ++o_it;
       if (use_qk && n_min == nb - 1) ++q_it;
     }
   }
+  FA_PROF(3);
+  FA_PROF_FLUSH();
 }
 
 }  // namespace fa100

@@ -70,7 +70,7 @@ static __device__ volatile unsigned int g_fa100_abort;
 #ifndef FA100_TRACE_BLOCK
 #define FA100_TRACE_BLOCK 0
 #endif
-constexpr int kTraceWarps = 20, kTracePerWarp = 4096;
+constexpr int kTraceWarps = 12, kTracePerWarp = 4096;
 static __device__ unsigned int g_fa100_trace[kTraceWarps * kTracePerWarp * 3];
 static __device__ unsigned int g_fa100_trace_cnt[kTraceWarps];
 FA_DEVICE bool trace_on() { return blockIdx.x == FA100_TRACE_BLOCK && (threadIdx.x & 31) == 0; }
@@ -97,7 +97,16 @@ FA_DEVICE void trace_emit(int tag, long long tb, long long te) {
 #define FA_TRACE_POINT(tag) do { if (trace_on()) { long long t_ = clock64(); trace_emit(tag, t_, t_); } } while (0)
 #define FA_TRACE_BEGIN() trace_begin()
 #define FA_TRACE_END() trace_end()
+// Cycle accounting without memory traffic in the loop: FA_PROF(i) charges the cycles since the previous mark to
+// bucket i (registers only); one CTA writes its buckets out at the end.  fa100_debug_prof() reads them.
+static __device__ unsigned int g_fa100_prof[kTraceWarps * 8];
+#define FA_PROF_DECL() uint32_t prof_[8] = {0, 0, 0, 0, 0, 0, 0, 0}; uint32_t prof_t_ = clock()
+#define FA_PROF(i) do { const uint32_t n_ = clock(); prof_[i] += n_ - prof_t_; prof_t_ = n_; } while (0)
+#define FA_PROF_FLUSH() do { if (trace_on()) { for (int i_ = 0; i_ < 8; ++i_) g_fa100_prof[(threadIdx.x >> 5) * 8 + i_] = prof_[i_]; } } while (0)
 #else
+#define FA_PROF_DECL() do { } while (0)
+#define FA_PROF(i) do { } while (0)
+#define FA_PROF_FLUSH() do { } while (0)
 #define FA_TRACE_POINT(tag) do { } while (0)
 #define FA_TRACE_BEGIN() do { } while (0)
 #define FA_TRACE_END() do { } while (0)

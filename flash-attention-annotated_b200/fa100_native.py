@@ -70,7 +70,7 @@ class Plan(C.Structure):
 
 
 EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_debug_hang_info",
-           "fa100_debug_trace")
+           "fa100_debug_trace", "fa100_debug_prof")
 
 _lib = None
 
@@ -98,8 +98,10 @@ def lib() -> C.CDLL:
         l.fa100_fwd.argtypes = [C.POINTER(FwdParams), vp]
         l.fa100_combine.argtypes = [C.POINTER(CombineParams), vp]
         l.fa100_debug_hang_info.argtypes = [C.POINTER(C.c_uint32 * 4)]
+        l.fa100_debug_trace.argtypes = [C.POINTER(C.c_uint32), C.c_int]
+        l.fa100_debug_prof.argtypes = [C.POINTER(C.c_uint32), C.c_int]
         for n in ("fa100_plan", "fa100_fwd", "fa100_combine", "fa100_debug_hang_info",
-           "fa100_debug_trace"):
+           "fa100_debug_trace", "fa100_debug_prof"):
             getattr(l, n).restype = C.c_int
         if l.fa100_abi_version() != 1:
             raise RuntimeError("libfa100.so ABI version mismatch")
@@ -127,3 +129,10 @@ def trace(max_events: int = 49152):
     buf = (C.c_uint32 * (3 * max_events))()
     n = lib().fa100_debug_trace(buf, max_events)
     return [(buf[3 * i] & 0xFFFF, buf[3 * i] >> 16, buf[3 * i + 1], buf[3 * i + 2]) for i in range(max(n, 0))]
+
+
+def prof(words: int = 160):
+    """Per-warp cycle buckets of the timeline build: list of 8-tuples, one per warp; empty from the product library."""
+    buf = (C.c_uint32 * words)()
+    n = lib().fa100_debug_prof(buf, words)
+    return [tuple(buf[w * 8 + i] for i in range(8)) for w in range(max(n, 0) // 8)]

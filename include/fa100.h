@@ -172,6 +172,8 @@ int fa100_debug_hang_info(uint32_t out[4]);
 /* profiling hook: events {tag | warp << 16, begin_clk, end_clk} of the opt-in timeline build (libfa100_trace.so,
  * -DFA100_TRACE); returns the event count, always 0 from the product library */
 int fa100_debug_trace(uint32_t* out, int max_events);
+/* profiling hook: per-warp cycle buckets (8 per warp) of the timeline build; returns words written, 0 from the product library */
+int fa100_debug_prof(uint32_t* out, int max_words);
 
 #ifdef __cplusplus
 }

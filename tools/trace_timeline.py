@@ -18,6 +18,13 @@ flash_attn_func(q, k, v, causal=causal); torch.cuda.synchronize(); N.trace()
 flash_attn_func(q, k, v, causal=causal); torch.cuda.synchronize()
 ev = N.trace()
 print("events", len(ev), "hang", N.hang_info())
+pr = N.prof()
+if pr:
+    print("cycle buckets per warp (softmax: 0 s_full wait, 1 load+max, 2 exchange, 3 rescale, 4 exp/pack/store, 5 publish, 6 rest;"
+          " mma: 0 kv_full, 1 p_full, 2 issue, 3 rest)")
+    for w_, b_ in enumerate(pr):
+        tot = sum(b_) or 1
+        print(f"  warp {w_:2d}: " + " ".join(f"{x:9d}({100 * x / tot:4.1f}%)" for x in b_))
 NAMES = {0x10: "prod wait q_empty0", 0x11: "prod wait q_empty1", 0x20: "prod wait kv_empty(K)", 0x21: "prod wait kv_empty(V)",
          0x30: "mma wait q_full0", 0x31: "mma wait q_full1", 0x40: "mma wait kv_full(first K)", 0x41: "mma wait kv_full(V)",
          0x42: "mma wait kv_full(K next)", 0x50: "mma wait o_empty0", 0x51: "mma wait o_empty1", 0x60: "mma wait p_full0",

@@ -5,7 +5,7 @@
 #include "../../flash-attention-annotated_b200/csrc/fa100_ptx.cuh"
 using namespace fa100;
 
-struct Cfg { int mode; int reps; int bg; int nblocks; };
+struct Cfg { int mode; int reps; int bg; int nblocks; int nbg; int rnd; };
 
 // mode 0: QK only (SS, 8 x K16, N=128)      mode 1: PV only (TS, B MN-major, 8 x K16)   mode 2: QK+PV interleaved per tile
 // mode 3: QK with N=256 (two tiles' worth)   bg bit0: 8 warps run tcgen05.ld of 128 columns in a loop; bit1: MUFU loop; bit2: tcgen05.st 64 cols
@@ -19,7 +19,11 @@ __global__ void __launch_bounds__(384, 1) k_mma(Cfg c, long long* out) {
   // pseudo-random bf16 payload (values ~ +-1): 192 KB
   for (int i = threadIdx.x; i < 192 * 1024 / 4; i += blockDim.x) {
     uint32_t h = (i * 2654435761u) ^ (blockIdx.x * 97u);
-    uint32_t lo = 0x3f00u | (h & 0x80ffu), hi = 0x3f00u | ((h >> 16) & 0x80ffu);
+    h ^= h >> 15; h *= 2246822519u; h ^= h >> 13; h *= 3266489917u; h ^= h >> 16;
+    uint32_t lo, hi;
+    if (c.rnd) {  // random sign / mantissa, exponent 2^-3 .. 2^1: looks like real activations to the power model
+      lo = (h & 0x807fu) | ((124u + ((h >> 8) & 3u)) << 7); hi = ((h >> 16) & 0x807fu) | ((124u + ((h >> 24) & 3u)) << 7);
+    } else { lo = 0x3f00u | (h & 0x80ffu); hi = 0x3f00u | ((h >> 16) & 0x80ffu); }
     reinterpret_cast<uint32_t*>(smem)[i] = lo | (hi << 16);
   }
   if (threadIdx.x == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); fence_mbar_init(); stop = 0; }
@@ -51,6 +55,19 @@ __global__ void __launch_bounds__(384, 1) k_mma(Cfg c, long long* out) {
           for (int ks = 0; ks < 8; ++ks)
             mma_f16_ts(tmem + 256 + t * 128, tmem + t * 128 + ks * 8, sdesc_at(kDescV, kv0 + ks * 16 * 128), idesc_pv, 1);
         }
+        if (c.mode == 4 || c.mode == 5) {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            mma_f16_ts(tmem + 256 + t * 128, tmem + t * 128 + ks * 8, sdesc_at(kDescV, kv0 + ks * 16 * 128), idesc_pv, 1);
+          if (c.mode == 4) {
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) {
+              const uint32_t off = (ks / 4) * 16384 + (ks % 4) * 32;
+              mma_f16_ss(tmem + t * 128, sdesc_at(kDescK, q0 + off), sdesc_at(kDescK, kv0 + off), idesc_qk, ks > 0);
+            }
+          }
+          tc_commit(&bar[1]);
+        }
         if (c.mode == 3) {
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
@@ -60,6 +77,7 @@ __global__ void __launch_bounds__(384, 1) k_mma(Cfg c, long long* out) {
         }
       }
       __syncwarp();
+      if (c.mode == 4 || c.mode == 5) mbar_wait(&bar[1], r & 1);
     }
     long long t1 = clock64();
     if (elect_one()) tc_commit(&bar[0]);
@@ -68,7 +86,7 @@ __global__ void __launch_bounds__(384, 1) k_mma(Cfg c, long long* out) {
     long long t2 = clock64();
     stop = 1;
     if (lane == 0 && blockIdx.x == 0) { out[0] = t1 - t0; out[1] = t2 - t0; }
-  } else if (warp < 8 && c.bg) {
+  } else if (warp < c.nbg && c.bg) {
     const uint32_t lane_base = uint32_t((warp % 4) * 32) << 16;
     float acc = 0.f;
     long long iters = 0;
@@ -86,6 +104,17 @@ __global__ void __launch_bounds__(384, 1) k_mma(Cfg c, long long* out) {
         float x = acc * 1e-30f + lane;
 #pragma unroll
         for (int i = 0; i < 128; ++i) { x = exp2f(x * 0.001f - 1.0f); acc += x; }
+      }
+      if (c.bg & 8) {  // saturating MUFU: 32 independent ex2 per iteration
+        float x[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = acc * 1e-30f - i;
+#pragma unroll
+        for (int r2 = 0; r2 < 4; ++r2)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) x[i] = exp2f(x[i]) - 1.5f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc += x[i];
       }
       if (c.bg & 4) {
         uint32_t pk[16];
@@ -108,18 +137,21 @@ int main() {
   long long* d; cudaMalloc(&d, 64); 
   const int smem = 200 * 1024;
   cudaFuncSetAttribute(k_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  const char* mname[] = {"QK ss 128x128", "PV ts 128x128 (B mn-major)", "QK+PV interleaved", "QK ss 128x256"};
-  for (int nblocks : {1, 148})
-    for (int mode = 0; mode < 4; ++mode)
-      for (int bg : {0, 1, 2, 3, 7}) {
-        Cfg c{mode, 2000, bg, nblocks};
+  const char* mname[] = {"QK ss 128x128", "PV ts 128x128 (B mn-major)", "QK+PV interleaved", "QK ss 128x256", "batch PV8+QK8, commit+wait", "batch PV8, commit+wait"};
+  for (int nblocks : {148})
+    for (int mode : {2, 4})
+      for (int bg : {0, 9}) {
+       for (int nbg : {0, 1}) {
+        Cfg c{mode, 20000, bg, nblocks, 8, nbg};
         cudaMemset(d, 0, 64);
         k_mma<<<nblocks, 384, smem>>>(c, d);
         cudaError_t e = cudaDeviceSynchronize();
         long long h[8]; cudaMemcpy(h, d, 64, cudaMemcpyDeviceToHost);
-        const int mmas = c.reps * (mode == 2 ? 16 : 8);
+        const int mmas = c.reps * ((mode == 2 || mode == 4) ? 16 : 8);
+        printf("rnd=%d ", nbg);
         printf("blocks=%3d %-28s bg=%d: issue %.1f clk/mma, complete %.1f clk/mma (ideal %d)  bg iters=%lld  %s\n", nblocks, mname[mode], bg,
                double(h[0]) / mmas, double(h[1]) / mmas, mode == 3 ? 128 : 64, h[2], e == cudaSuccess ? "" : cudaGetErrorString(e));
+       }
       }
   return 0;
 }
