@@ -6,9 +6,9 @@
 //
 //   warps 0-3   softmax for Q tile 0: one thread == one query row == one TMEM lane (row max / sum without shuffles)
 //   warps 4-7   softmax for Q tile 1
-//   warps 8,9   MMA issuers, one per Q tile (elected lane): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
-//   warp  10    TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
-//   warp  11    idle (completes the third warpgroup for setmaxnreg: softmax warps run with 224 registers, the rest 56)
+//   warp  8     MMA issuer (elected lane): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
+//   warp  9     TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
+//   warps 10,11 idle (complete the third warpgroup for setmaxnreg: softmax warps run with 224 registers, the rest 56)
 //
 // TMEM (512 columns): S0 @0, S1 @128, O0 @256, O1 @384; P_t (16-bit) overwrites columns [0,64) of S_t.
 // Two 128-row Q tiles per CTA ping-pong through the tensor pipe: while the softmax warps turn S_t into P_t the
@@ -25,7 +25,7 @@ constexpr int kBlockN = 128;   // keys per main-loop step
 constexpr int kQTiles = 2;     // Q tiles per CTA
 constexpr int kSoftmaxWarps = 8;
 constexpr int kMmaWarp = 8;
-constexpr int kLoadWarp = 10;
+constexpr int kLoadWarp = 9;
 constexpr int kThreads = 12 * 32;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;

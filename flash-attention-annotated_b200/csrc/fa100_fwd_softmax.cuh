@@ -263,7 +263,7 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
       mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 4);
       mbar_init(&bar->o_full[t], 1); mbar_init(&bar->o_empty[t], 4);
     }
-    for (int s = 0; s < 8; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], kQTiles); }
+    for (int s = 0; s < 8; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc(&bar->tmem_base, 512); tmem_relinquish(); }
@@ -278,7 +278,7 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
     softmax_role<HD, ELT, FP8, F16>(p, bar, tmem, warp, lane);
   } else {
     setmaxnreg_dec<56>();
-    if (warp == kMmaWarp || warp == kMmaWarp + 1) mma_role<HD, ELT, FP8>(p, fmt, warp - kMmaWarp, sQ, sKV, bar, tmem);
+    if (warp == kMmaWarp) mma_role<HD, ELT, FP8>(p, fmt, sQ, sKV, bar, tmem);
     if (warp == kLoadWarp) producer_role<HD, ELT>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar);
   }
   FA_TRACE_END();

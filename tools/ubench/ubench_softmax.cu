@@ -7,10 +7,34 @@ using namespace fa100;
 __device__ __forceinline__ float ex2a(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ uint32_t packbf(float lo, float hi) { __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi); return *reinterpret_cast<uint32_t*>(&v); }
 
+// exp2 of two values on the FMA/ALU pipes (Cody-Waite split by the 1.5*2^23 magic add, degree-3 polynomial, exponent
+// splice), packed f32x2 arithmetic.  Inputs must be <= ~120; values below -126 are clamped.
+__device__ __forceinline__ void ex2_poly2(float& a, float& b) {
+  asm("{\n\t.reg .b64 x, r, f, pl;\n\t.reg .f32 a0, b0, r0, r1, p0, p1;\n\t.reg .b32 i0, i1, q0, q1;\n\t"
+      "max.ftz.f32 a0, %0, 0fC2FC0000;\n\tmax.ftz.f32 b0, %1, 0fC2FC0000;\n\t"
+      "mov.b64 x, {a0, b0};\n\t"
+      "mov.b64 pl, {0f4B400000, 0f4B400000};\n\t"
+      "add.rm.ftz.f32x2 r, x, pl;\n\t"          // floor(x) in the low mantissa bits
+      "sub.rn.ftz.f32x2 f, r, pl;\n\t"           // floor(x) as a float
+      "sub.rn.ftz.f32x2 f, x, f;\n\t"            // frac in [0, 1)
+      "mov.b64 pl, {0f3D9DF09D, 0f3D9DF09D};\n\t" // c3 = 0.077119
+      "mov.b64 x, {0f3E6906A4, 0f3E6906A4};\n\t"  // c2 = 0.227564
+      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
+      "mov.b64 x, {0f3F31F519, 0f3F31F519};\n\t"  // c1 = 0.695146
+      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
+      "mov.b64 x, {0f3F800000, 0f3F800000};\n\t"
+      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
+      "mov.b64 {p0, p1}, pl;\n\tmov.b64 {r0, r1}, r;\n\t"
+      "mov.b32 i0, r0;\n\tmov.b32 i1, r1;\n\tshl.b32 i0, i0, 23;\n\tshl.b32 i1, i1, 23;\n\t"
+      "mov.b32 q0, p0;\n\tmov.b32 q1, p1;\n\tadd.s32 q0, q0, i0;\n\tadd.s32 q1, q1, i1;\n\t"
+      "mov.b32 %0, q0;\n\tmov.b32 %1, q1;\n\t}"
+      : "+f"(a), "+f"(b));
+}
+
 // VARIANT 0: 128 columns per thread, chunked (load all, max, then per chunk ffma/ex2/pack/store), sum at end
 // VARIANT 1: 64 columns per thread (two chunks)
 // VARIANT 2: 128 columns, per-chunk reload (two-pass)
-template <int VARIANT>
+template <int VARIANT, int NP>
 __global__ void __launch_bounds__(VARIANT == 1 ? 512 : 256, 1) k_softmax(int iters, int nwarps, float scale, long long* out, float* sink) {
   __shared__ uint32_t tmem_base;
   const int warp = threadIdx.x / 32;
@@ -47,7 +71,11 @@ __global__ void __launch_bounds__(VARIANT == 1 ? 512 : 256, 1) k_softmax(int ite
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(ex2a(fmaf(__uint_as_float(s[c][i]), scale, -m_sub)));
+        for (int i = 0; i < 32; i += 2) {  // of every 8 elements the last NP go through the polynomial
+          float x0 = fmaf(__uint_as_float(s[c][i]), scale, -m_sub), x1 = fmaf(__uint_as_float(s[c][i + 1]), scale, -m_sub);
+          if ((i & 7) >= 8 - NP) ex2_poly2(x0, x1); else { x0 = ex2a(x0); x1 = ex2a(x1); }
+          s[c][i] = __float_as_uint(x0); s[c][i + 1] = __float_as_uint(x1);
+        }
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) pk[i] = packbf(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1]));
@@ -80,7 +108,10 @@ int main() {
     printf("%-46s warps=%2d: %7.0f clk per step per warp; per SMSP per element: %.2f clk  %s\n", name, nwarps, per,
            per / (elems_per_thread * (nwarps / 4.0)), cudaGetErrorString(cudaGetLastError()));
   };
-  for (int nw : {4, 8}) { k_softmax<0><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread (1 row per thread)", nw, 128); }
-  for (int nw : {8, 16}) { k_softmax<1><<<148, 512>>>(iters, nw, 0.1275f, d, sink); report("64 cols/thread (2 threads per row)", nw, 64); }
+  for (int nw : {4, 8}) { k_softmax<0, 0><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, all MUFU", nw, 128); }
+  for (int nw : {4, 8}) { k_softmax<0, 2><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, 2/8 polynomial", nw, 128); }
+  for (int nw : {4, 8}) { k_softmax<0, 4><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, 4/8 polynomial", nw, 128); }
+  for (int nw : {4, 8}) { k_softmax<0, 6><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, 6/8 polynomial", nw, 128); }
+  for (int nw : {4, 8}) { k_softmax<0, 8><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, all polynomial", nw, 128); }
   return 0;
 }
