@@ -49,6 +49,15 @@ def decode_bytes(w):
     return kv + qo + w["b"] * (w["sk"] // w.get("page", 256)) * 4
 
 
+def ncu_traffic(workload):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(workload)
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -59,35 +68,52 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons sampled through NVML every 5 ms while the timed region runs
+    (B200_PROFILING.md clocks line; nvidia-smi -lms cannot sample an 80 ms region more than once)."""
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.h, self.stop_flag, self.thread, self.nv = index, [], None, False, None, None
 
     def start(self):
-        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._pump, daemon=True).start()
-        except Exception:  # noqa: BLE001
-            self.proc = None
+            import pynvml as nv
+
+            nv.nvmlInit()
+            # NVML enumerates physical devices: map through CUDA_VISIBLE_DEVICES when it holds indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            ids = [x for x in vis.split(",") if x.strip().isdigit()]
+            phys = int(ids[self.index]) if self.index < len(ids) else self.index
+            self.h, self.nv = nv.nvmlDeviceGetHandleByIndex(phys), nv
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception as e:  # noqa: BLE001
+            self.h, self.err = None, repr(e)
 
     def _pump(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                self.rows.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM),
+                                  nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)))
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.005)
 
     def stop(self):
-        if self.proc is None:
-            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
-        self.proc.terminate()
-        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit())
-        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
-        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=max(mx) if mx else None, reasons=reasons,
-                    samples=len(sm))
+        if self.h is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvml unavailable: " + getattr(self, "err", "?")], samples=0)
+        self.stop_flag = True
+        self.thread.join(timeout=1.0)
+        nv = self.nv
+        sm = sorted(r[0] for r in self.rows)
+        bits = 0
+        for r in self.rows:
+            bits |= r[1]
+        names = [("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown), ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                 ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown), ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap)]
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=self.max_mhz,
+                    reasons=[n for n, m in names if bits & m], samples=len(sm))
 
 
 def make_inputs(w, device, seed):
@@ -115,22 +141,24 @@ def make_inputs(w, device, seed):
     return t
 
 
-def cpu_sample(w, threads, slices):
-    """CPU oracle on `slices` (batch, kv-group) slices of the workload; returns (seconds, flops done)."""
+def cpu_sample(w, threads, slices, min_seconds=0.0):
+    """CPU oracle on (batch, kv-group) slices of the workload -- `slices` of them, then more until `min_seconds` have
+    passed; returns (seconds, flops done, slices done)."""
     import attention_oracle as A
 
     torch.set_num_threads(threads)
     g = torch.Generator().manual_seed(0)
     G = w["h"] // w["hk"]
     sq, sk = min(w["sq"], 8192), min(w["sk"], 8192)
-    t0 = time.perf_counter()
-    for _ in range(slices):
-        q = torch.randn(1, sq, G, w["d"], generator=g).to(torch.bfloat16)
-        k = torch.randn(1, sk, 1, w["d"], generator=g).to(torch.bfloat16)
-        v = torch.randn(1, sk, 1, w["d"], generator=g).to(torch.bfloat16)
+    q = torch.randn(1, sq, G, w["d"], generator=g).to(torch.bfloat16)
+    k = torch.randn(1, sk, 1, w["d"], generator=g).to(torch.bfloat16)
+    v = torch.randn(1, sk, 1, w["d"], generator=g).to(torch.bfloat16)
+    done, t0 = 0, time.perf_counter()
+    while done < slices or time.perf_counter() - t0 < min_seconds:
         A.attention_oracle_sliced(q, k, v, rows_per_call=1024, causal=w["causal"])
+        done += 1
     dt = time.perf_counter() - t0
-    return dt, slices * A.flops(1, G, sq, sk, w["d"], w["d"], w["causal"])
+    return dt, done * A.flops(1, G, sq, sk, w["d"], w["d"], w["causal"]), done
 
 
 def run_reference(args, w, rank):
@@ -143,11 +171,11 @@ def run_reference(args, w, rank):
         cpu_sample(w, threads, 1)
     tot_t, tot_f = 0.0, 0.0
     for _ in range(args.steps):
-        dt, fl = cpu_sample(w, threads, slices)
+        dt, fl, _ = cpu_sample(w, threads, slices, min_seconds=8.0)
         tot_t += dt
         tot_f += fl
     val = tot_f / tot_t / 1e12
-    sample = f"{slices} (batch, kv-group) slices of {w['h'] // w['hk']} q-heads per step, seq capped at 8192, q-row-blocked"
+    sample = f">= 8 s of (batch, kv-group) slices of {w['h'] // w['hk']} q-heads per step, seq capped at 8192, q-row-blocked"
     line = dict(impl="reference", metric=metric_name(w), value=val, unit="TFLOP/s", n_gpus=args.gpus, steps=args.steps,
                 warmup=args.warmup, ms_per_step=tot_t / args.steps * 1e3, higher_is_better=True, scaling="weak",
                 vs_baseline=None, dtype="f32", data="synthetic", config=dict(workload=w["desc"]),
@@ -216,17 +244,18 @@ def main():
         out = step(devt)
     barrier()
     sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    if rank == 0:
+        sampler.start()  # samples only while the timed steps run
     e0.record()
     for _ in range(args.steps):
         out = step(devt)
     e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
     barrier()
     ms = e0.elapsed_time(e1) / args.steps
-    clocks = sampler.stop() if rank == 0 else None
     hang = N.hang_info()
     assert hang[0] == 0, f"kernel watchdog fired: {hang}"
 
@@ -278,15 +307,14 @@ def main():
                                 l2="inputs (>= 0.67 GB) exceed the 126 MB L2; no flush between steps"),
                     clocks=clocks, gpu_launches=args.steps * (2 if decode else 1),
                     e2e=dict(value=e2e_val, unit=unit, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h),
-                    roofline=dict(bound=bound, achieved=per_gpu, peak=peak, unit=unit, frac=per_gpu / peak, traffic=None,
+                    roofline=dict(bound=bound, achieved=per_gpu, peak=peak, unit=unit, frac=per_gpu / peak, traffic=ncu_traffic(args.workload),
                                   peak_source=peaks["source"] + (" (bf16 burst x2 for fp8)" if w["dtype"] == "e4m3" and not decode else ""),
                                   frac_of_sustained=(per_gpu / (peaks["tensor_sustained"] * (2.0 if w["dtype"] == "e4m3" else 1.0))
                                                      if bound == "tensor" and peaks["tensor_sustained"] else None),
                                   kernel="fa100_fwd_kernel"))
         if not args.no_cpu_baseline and world == 1:
             threads = os.cpu_count() or 1
-            slices = 4
-            dt, fl = cpu_sample(w, threads, slices)
+            dt, fl, slices = cpu_sample(w, threads, 4, min_seconds=12.0)
             line["cpu_baseline"] = dict(value=fl / dt / 1e12, unit="TFLOP/s", cores=threads, kind="port",
                                         sample=f"{slices} (batch, kv-group) slices ({slices * (w['h'] // w['hk'])} of "
                                                f"{w['b'] * w['h']} q-head rows), seq capped at 8192, {dt:.1f} s")

@@ -94,7 +94,11 @@ FA_DEVICE void trace_emit(int tag, long long tb, long long te) {
     *cnt = n + 1;
   }
 }
+#ifdef FA100_TRACE_NOEVENTS  // libfa100_prof.so: cycle buckets only, no per-event stores to perturb the timing
+#define FA_TRACE_POINT(tag) do { } while (0)
+#else
 #define FA_TRACE_POINT(tag) do { if (trace_on()) { long long t_ = clock64(); trace_emit(tag, t_, t_); } } while (0)
+#endif
 #define FA_TRACE_BEGIN() trace_begin()
 #define FA_TRACE_END() trace_end()
 // Cycle accounting without memory traffic in the loop: FA_PROF(i) charges the cycles since the previous mark to
@@ -133,11 +137,11 @@ FA_DEVICE void mbar_wait_slow(uint64_t* bar, uint32_t parity, int tag) {
 }
 
 FA_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
-#ifdef FA100_TRACE
+#if defined(FA100_TRACE) && !defined(FA100_TRACE_NOEVENTS)
   const long long tb_ = clock64();
 #endif
   if (!mbar_try_wait(bar, parity) && !mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity, tag);
-#ifdef FA100_TRACE
+#if defined(FA100_TRACE) && !defined(FA100_TRACE_NOEVENTS)
   if (trace_on()) trace_emit(tag, tb_, clock64());
 #endif
 }
