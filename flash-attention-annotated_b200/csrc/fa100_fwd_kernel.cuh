@@ -84,14 +84,18 @@ struct SeqInfo {
 struct TileRange { int n_min, n_max; bool has_rows; };
 
 FA_DEVICE WorkItem decode_work(const FwdKernelParams& p, int w) {
-  // w = ((m_rev * b + bi) * heads + head) * splits + split : heads of one KV group and the splits of one
-  // row block are neighbours (run at the same time on different SMs -> share K/V in L2); long (late) causal
-  // row blocks come first (LPT).
+  // w = ((((bi * h_k + hk) * m_blocks + m_rev) * heads_per_group + g) * splits + split.  Everything that reads one
+  // (batch, KV head) -- its splits, the query heads of the group and all their row blocks -- is adjacent, so the ~148
+  // work items in flight share one or two K/V heads (4 MB at C2) in L2 instead of streaming all of K/V at once
+  // (the reference swizzles heads by L2 size for the same reason, hopper/tile_scheduler.hpp:305-360).  Inside a group
+  // the long (late) causal row blocks come first.
   WorkItem it;
-  it.split = w % p.num_splits; w /= p.num_splits;
-  it.head = w % p.heads_work;  w /= p.heads_work;
-  it.bi = w % p.b;             w /= p.b;
-  it.m_blk = p.num_m_blocks - 1 - w;
+  const int gsz = p.heads_work / p.h_k;  // query heads per KV head that are separate work items (1 when packed)
+  it.split = w % p.num_splits;  w /= p.num_splits;
+  const int g = w % gsz;        w /= gsz;
+  it.m_blk = p.num_m_blocks - 1 - w % p.num_m_blocks;  w /= p.num_m_blocks;
+  it.head = (w % p.h_k) * gsz + g;
+  it.bi = w / p.h_k;
   return it;
 }
 
@@ -149,7 +153,7 @@ template <int HD, int ELT>
 struct FwdSmem {
   static constexpr int kQBytes = kBlockM * HD * ELT;   // one Q tile
   static constexpr int kKVBytes = kBlockN * HD * ELT;  // one K or V tile
-  static constexpr int kBarrierBytes = 5120;           // barriers + row-max exchange (the base is 1 KB aligned)
+  static constexpr int kBarrierBytes = 1024;           // mbarriers + TMEM base (+ the trace build's counters in the last 128 B)
   static constexpr int kBudget = 227 * 1024 - kBarrierBytes;
   static constexpr int kStagesRaw = (kBudget - kQTiles * kQBytes) / kKVBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
@@ -159,13 +163,13 @@ struct FwdSmem {
 
 struct FwdBarriers {
   uint64_t q_full[kQTiles], q_empty[kQTiles];
-  uint64_t s_full[kQTiles], p_full[kQTiles];
+  uint64_t s_full[kQTiles], p_full[kQTiles], pv_done[kQTiles];
+  uint64_t s_free;
   uint64_t o_full[kQTiles], o_empty[kQTiles];
   uint64_t kv_full[8], kv_empty[8];
   uint32_t tmem_base;
   uint32_t pad_[3];
-  float xchg[kQTiles][2][2][128];  // [tile][step parity][column half][row]: partial row max / sum for the partner thread
 };
-static_assert(sizeof(FwdBarriers) <= 5120 - 128, "barrier block outgrew its slot");
+static_assert(sizeof(FwdBarriers) <= 1024 - 128, "barrier block outgrew its slot");
 
 }  // namespace fa100

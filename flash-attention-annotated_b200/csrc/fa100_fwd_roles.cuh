@@ -101,12 +101,16 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
 }
 
 // ----------------------------------------------------------------------------- MMA issuer
-// One warp issues for both Q tiles, always tile 0 then tile 1 of a key block: S_t = Q_t K^T (SS form) and
-// O_t += P_t V (TS form, P in TMEM).  The fixed order keeps the two tiles one MMA batch apart, so their softmax phases
-// (which share the MUFU pipe) overlap as little as possible; with one issuing warp per tile both tiles stall on the
-// same K/V stage, start together and contend (measured: 4530 vs 4270 clk per key-block pair).  All 32 lanes run the
-// loop and the barrier waits (warp-uniform control flow keeps descriptors in uniform registers); one elected lane issues.
-// TMEM columns: S_t = t*128, P_t = S_t (16-bit, 64 columns), O_t = 256 + t*128.
+// TMEM columns: S @0 (one score buffer shared by both Q tiles), P_0 @128, P_1 @192 (operand dtype), O_0 @256, O_1 @384.
+//
+// The two Q tiles take turns in the single S buffer.  A softmax warpgroup copies its scores into registers right after
+// s_full[t] and arrives on s_free; from then on S belongs to the other tile, so S_t(next) = Q_t K^T no longer waits for
+// P_t V to drain (with P overlaid on a per-tile S the chain S -> softmax -> PV -> QK -> S bounded the key-block period
+// at ~3400 clk; here QK of one tile runs under the exponentials of both).  P_t has its own columns; pv_done[t] tells
+// the softmax warps that P_t (and O_t, for the rare rescale) may be touched again.
+//
+// One warp issues everything in a fixed order per key block nb: QK_0(nb-1), PV_0(nb), QK_1(nb-1), PV_1(nb).  All 32
+// lanes run the control flow and the barrier waits (descriptors stay in uniform registers); one elected lane issues.
 template <int HD, int ELT, bool FP8>
 FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar, uint32_t tmem) {
   using L = FwdSmem<HD, ELT>;
@@ -128,17 +132,73 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
 
   RingState ring;
   uint32_t q_it[kQTiles] = {0, 0}, p_it[kQTiles] = {0, 0}, o_it[kQTiles] = {0, 0};
-  FA_PROF_DECL();  // 0 kv_full waits, 1 p_full / o_empty waits, 2 issue, 3 everything else
+  uint32_t qk_n = 0;  // QK batches issued so far == phases of s_free consumed + 1
+  // An mbarrier poll costs ~110 clk even when the phase is long complete, and this warp is the only feeder of the
+  // tensor pipe.  Every batch therefore polls the barrier of the NEXT batch after issuing all but its last two MMAs
+  // (the pipe still has queued work to cover the poll) and the next batch blocks only if that poll failed.
+  bool rdy_sfree = false, rdy_p[kQTiles] = {false, false}, rdy_kv_v = false, rdy_kv_k = false;
+  FA_PROF_DECL();     // 0 kv_full waits, 1 s_free waits, 2 p_full / o_empty waits, 3 issue, 4 everything else
 
-  auto issue_qk = [&](int t, int stage) {  // elected lane only
+  auto poll_sfree = [&]() { rdy_sfree = qk_n == 0 || mbar_try_wait(&bar->s_free, (qk_n - 1) & 1); };
+
+  // S = Q_t K(stage)^T once the previous owner of S has taken its scores
+  auto qk_op = [&](int t, int stage, bool last_use_of_q, auto&& poll_next) {
+    if (!rdy_sfree && qk_n > 0) mbar_wait(&bar->s_free, (qk_n - 1) & 1, 0x48 + t);
+    rdy_sfree = false;
+    ++qk_n;
+    tc_fence_after();
+    FA_PROF(1);
     const uint32_t a_lo = q_lo + t * (L::kQBytes >> 4);
     const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboK;
-#pragma unroll
-    for (int ks = 0; ks < kQKSlices; ++ks) {
+    auto mma = [&](int ks) {
       const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
-      mma_ss<FP8>(tmem + t * 128, a_lo + off, b_lo + off, kHi, idesc_qk, ks > 0);
+      mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc_qk, ks > 0);
+    };
+    constexpr int kHead = kQKSlices > 2 ? kQKSlices - 2 : 0;
+    if (elect_one()) {
+#pragma unroll
+      for (int ks = 0; ks < kHead; ++ks) mma(ks);
     }
-    tc_commit(&bar->s_full[t]);
+    __syncwarp();
+    poll_next();
+    if (elect_one()) {
+#pragma unroll
+      for (int ks = kHead; ks < kQKSlices; ++ks) mma(ks);
+      tc_commit(&bar->s_full[t]);
+      if (last_use_of_q) tc_commit(&bar->q_empty[t]);
+    }
+    __syncwarp();
+    FA_PROF(3);
+  };
+
+  // O_t (+)= P_t V(stage)
+  auto pv_op = [&](int t, int stage, bool first, bool last, auto&& poll_next) {
+    if (first) mbar_wait(&bar->o_empty[t], (o_it[t] & 1) ^ 1, 0x50 + t);  // epilogue of the previous work item
+    if (!rdy_p[t]) mbar_wait(&bar->p_full[t], p_it[t] & 1, 0x60 + t);
+    rdy_p[t] = false;
+    ++p_it[t];
+    tc_fence_after();
+    FA_PROF(2);
+    const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboV;
+    auto mma = [&](int ks) {
+      mma_ts<FP8>(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc_pv, (!first || ks > 0));
+    };
+    constexpr int kHead = kPVSlices > 2 ? kPVSlices - 2 : 0;
+    if (elect_one()) {
+#pragma unroll
+      for (int ks = 0; ks < kHead; ++ks) mma(ks);
+    }
+    __syncwarp();
+    poll_next();
+    if (elect_one()) {
+#pragma unroll
+      for (int ks = kHead; ks < kPVSlices; ++ks) mma(ks);
+      tc_commit(&bar->pv_done[t]);
+      if (last) tc_commit(&bar->o_full[t]);
+    }
+    __syncwarp();
+    FA_PROF(3);
+    if (last) ++o_it[t];
   };
 
   for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
@@ -153,72 +213,69 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t)
       if (n_max[t] > n_min[t]) mbar_wait(&bar->q_full[t], q_it[t] & 1, 0x30 + t);
-    // prologue: S_t = Q_t K^T for the first (right-most) key block of the work item
+    // prologue: scores of the first (right-most) key block of the work item
     {
       mbar_wait(&bar->kv_full[ring.stage], ring.phase, 0x40);
-      tc_fence_after();
       const int nb = n_hi - 1;
-      if (elect_one()) {
-#pragma unroll
-        for (int t = 0; t < kQTiles; ++t)
-          if (nb >= n_min[t] && nb < n_max[t]) {
-            issue_qk(t, ring.stage);
-            if (n_min[t] == nb) tc_commit(&bar->q_empty[t]);
-          }
-        tc_commit(&bar->kv_empty[ring.stage]);
-      }
-      __syncwarp();
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t)
-        if (nb >= n_min[t] && nb < n_max[t] && n_min[t] == nb) ++q_it[t];
+        if (nb >= n_min[t] && nb < n_max[t]) {
+          qk_op(t, ring.stage, n_min[t] == nb, [&]() {});
+          if (n_min[t] == nb) ++q_it[t];
+        }
+      if (elect_one()) tc_commit(&bar->kv_empty[ring.stage]);
+      __syncwarp();
       ring_advance<L::kStages>(ring);
     }
+    rdy_kv_v = rdy_kv_k = false;
     for (int nb = n_hi - 1; nb >= n_lo; --nb) {
       const RingState rv = ring;  // V(nb)
       ring_advance<L::kStages>(ring);
       const RingState rk = ring;  // K(nb-1)
       const bool has_next = nb - 1 >= n_lo;
-      FA_PROF(3);
-      mbar_wait(&bar->kv_full[rv.stage], rv.phase, 0x41);
-      if (has_next) { mbar_wait(&bar->kv_full[rk.stage], rk.phase, 0x42); ring_advance<L::kStages>(ring); }
+      FA_PROF(4);
+      if (!rdy_kv_v) mbar_wait(&bar->kv_full[rv.stage], rv.phase, 0x41);
+      if (has_next) {
+        if (!rdy_kv_k) mbar_wait(&bar->kv_full[rk.stage], rk.phase, 0x42);
+        ring_advance<L::kStages>(ring);
+      }
+      rdy_kv_v = rdy_kv_k = false;
       FA_PROF(0);
+      bool use_pv[kQTiles], use_qk[kQTiles];
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) {
-        const bool use_pv = nb >= n_min[t] && nb < n_max[t];
-        const bool use_qk = has_next && nb - 1 >= n_min[t] && nb - 1 < n_max[t];
-        const bool first = nb == n_max[t] - 1;
-        if (use_pv) {
-          if (first) mbar_wait(&bar->o_empty[t], (o_it[t] & 1) ^ 1, 0x50 + t);  // epilogue of the previous work item
-          mbar_wait(&bar->p_full[t], p_it[t] & 1, 0x60 + t);
-          ++p_it[t];
-          tc_fence_after();
-        }
-        FA_PROF(1);
-        if (elect_one()) {
-          if (use_pv) {
-            const uint32_t b_lo = (kv_lo + rv.stage * (L::kKVBytes >> 4)) | kLboV;
-#pragma unroll
-            for (int ks = 0; ks < kPVSlices; ++ks)
-              mma_ts<FP8>(tmem + 256 + t * 128, tmem + t * 128 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc_pv, (!first || ks > 0));
-            if (nb == n_min[t]) tc_commit(&bar->o_full[t]);
-          }
-          if (use_qk) {
-            issue_qk(t, rk.stage);
-            if (n_min[t] == nb - 1) tc_commit(&bar->q_empty[t]);
-          }
-          if (t == kQTiles - 1) {
-            tc_commit(&bar->kv_empty[rv.stage]);
-            if (has_next) tc_commit(&bar->kv_empty[rk.stage]);
-          }
-        }
-        __syncwarp();
-        FA_PROF(2);
-        if (use_pv && nb == n_min[t]) ++o_it[t];
-        if (use_qk && n_min[t] == nb - 1) ++q_it[t];
+        use_pv[t] = nb >= n_min[t] && nb < n_max[t];
+        use_qk[t] = has_next && nb - 1 >= n_min[t] && nb - 1 < n_max[t];
       }
+#pragma unroll
+      for (int t = 0; t < kQTiles; ++t) {
+        if (use_qk[t]) {
+          // next in line: P_t V(nb)
+          qk_op(t, rk.stage, n_min[t] == nb - 1, [&]() { if (use_pv[t]) rdy_p[t] = mbar_try_wait(&bar->p_full[t], p_it[t] & 1); });
+          if (n_min[t] == nb - 1) ++q_it[t];
+        }
+        if (use_pv[t]) {
+          pv_op(t, rv.stage, nb == n_max[t] - 1, nb == n_min[t], [&]() {
+            poll_sfree();  // next in line: the other tile's QK, or the next key block's
+            if (t == kQTiles - 1 && has_next) {
+              rdy_kv_v = mbar_try_wait(&bar->kv_full[ring.stage], ring.phase);
+              if (nb - 2 >= n_lo) {
+                RingState r2 = ring;
+                ring_advance<L::kStages>(r2);
+                rdy_kv_k = mbar_try_wait(&bar->kv_full[r2.stage], r2.phase);
+              }
+            }
+          });
+        }
+      }
+      if (elect_one()) {
+        tc_commit(&bar->kv_empty[rv.stage]);
+        if (has_next) tc_commit(&bar->kv_empty[rk.stage]);
+      }
+      __syncwarp();
     }
   }
-  FA_PROF(3);
+  FA_PROF(4);
   FA_PROF_FLUSH();
 }
 

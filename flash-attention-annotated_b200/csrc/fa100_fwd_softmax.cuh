@@ -63,10 +63,11 @@ template <int HD, int ELT, bool FP8, bool F16>
 FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t tmem, int warp, int lane) {
   const int t = warp >> 2, q = warp & 3;
   const int row = q * 32 + lane;
-  const uint32_t tS = tmem + (uint32_t(q * 32) << 16) + t * 128;
-  const uint32_t tO = tS + 256;
-  uint32_t s_it = 0, o_it = 0;
-  FA_PROF_DECL();  // 0 s_full wait, 1 S load + row max, 3 rescale decision (+ O rescale), 4 exp/pack/store, 5 publish, 6 rest
+  const uint32_t tS = tmem + (uint32_t(q * 32) << 16);  // the score buffer both tiles take turns in
+  const uint32_t tP = tS + 128 + t * 64;                // this tile's probabilities (operand dtype)
+  const uint32_t tO = tS + 256 + t * 128;
+  uint32_t s_it = 0, o_it = 0, pv_n = 0;                // pv_n: P blocks published so far == PV batches requested
+  FA_PROF_DECL();  // 0 s_full wait, 1 S load, 2 s_free + mask + row max, 3 rescale, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait + publish, 7 rest
 
   for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
     const RowGeom rg = row_geom<FP8>(p, w, t, row);
@@ -75,7 +76,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
     const bool softcap = p.softcap_pre != 0.f;
     float m_run = -INFINITY, l_run = 0.f;
     for (int nb = rg.n_max - 1; nb >= rg.n_min; --nb) {
-      FA_PROF(6);
+      FA_PROF(7);
       mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
       FA_PROF(0);
       ++s_it;
@@ -84,6 +85,15 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
 #pragma unroll
       for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
       tmem_ld_wait();
+      FA_PROF(1);
+      // the scores are in registers: hand S to the other tile's QK
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar->s_free);
+      FA_TRACE_POINT(0xC4);
+      // P_t and O_t may be touched again once the previous P_t V has drained; poll now, block only right before the
+      // first write (normally long complete by then)
+      bool pv_drained = pv_n == 0 || mbar_try_wait(&bar->pv_done[t], (pv_n - 1) & 1);
       const int n0 = nb * kBlockN;
       // boundary block for any row of this warp (warp-uniform): softcap first, then the mask (hopper/mainloop...:1073-1077)
       if (__any_sync(0xffffffffu, softcap || n0 + kBlockN > rg.col_hi || n0 < rg.col_lo)) {
@@ -110,13 +120,15 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
           mx2 = fmaxf(mx2, __uint_as_float(s[c][i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[c][i + 3]));
         }
       const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-      FA_PROF(1);
+      FA_PROF(2);
       const float m_cand = fmaxf(m_run, m_blk);
       // lazy rescale: keep the stale max unless it grew by more than 2^8 (NaN from -inf - -inf compares false)
       const bool grow = (m_cand - m_run) * scale_log2 > (FP8 ? 0.0f : kRescaleThreshold);
       const float acc_scale = grow ? exp2f((m_run - m_cand) * scale_log2) : 1.0f;
       if (grow) m_run = m_cand;
       if (nb != rg.n_max - 1 && __any_sync(0xffffffffu, grow)) {
+        if (!pv_drained) { mbar_wait(&bar->pv_done[t], (pv_n - 1) & 1, 0x78 + t); pv_drained = true; }
+        tc_fence_after();
 #pragma unroll
         for (int c = 0; c < HD / 32; ++c) {
           uint32_t o[32];
@@ -137,6 +149,10 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
 #pragma unroll
         for (int i = 0; i < 32; ++i)
           s[c][i] = __float_as_uint(ex2_approx(fmaf(__uint_as_float(s[c][i]), scale_log2, -m_sub)));
+        if (c == 0) {
+          if (!pv_drained) mbar_wait(&bar->pv_done[t], (pv_n - 1) & 1, 0x78 + t);
+          tc_fence_after();
+        }
         if (!FP8) {
           uint32_t pk[16];
 #pragma unroll
@@ -144,7 +160,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
             const float p0 = __uint_as_float(s[c][2 * i]), p1 = __uint_as_float(s[c][2 * i + 1]);
             pk[i] = F16 ? pack_f16(p0, p1) : pack_bf16(p0, p1);
           }
-          tmem_st16(tS + c * 16, pk);
+          tmem_st16(tP + c * 16, pk);
         } else {
           uint32_t pk[8];
 #pragma unroll
@@ -154,20 +170,23 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
             asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(__uint_as_float(s[c][4 * i + 3])), "f"(__uint_as_float(s[c][4 * i + 2])));
             pk[i] = uint32_t(lo) | (uint32_t(hi) << 16);
           }
-          tmem_st8(tS + c * 8, pk);
+          tmem_st8(tP + c * 8, pk);
         }
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
           sum0 += __uint_as_float(s[c][i]); sum1 += __uint_as_float(s[c][i + 1]);
           sum2 += __uint_as_float(s[c][i + 2]); sum3 += __uint_as_float(s[c][i + 3]);
         }
+        if (c == 1) FA_PROF(4);
       }
-      FA_PROF(4);
+      FA_PROF(5);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar->p_full[t]);
-      FA_PROF(5);
+      FA_TRACE_POINT(0xA0 + t);
+      ++pv_n;
+      FA_PROF(6);
       l_run = l_run * acc_scale + ((sum0 + sum1) + (sum2 + sum3));
     }
 
@@ -237,7 +256,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       }
     }
   }
-  FA_PROF(6);
+  FA_PROF(7);
   FA_PROF_FLUSH();
 }
 
@@ -260,9 +279,10 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
       mbar_init(&bar->q_full[t], 1); mbar_init(&bar->q_empty[t], 1);
-      mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 4);
+      mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 4); mbar_init(&bar->pv_done[t], 1);
       mbar_init(&bar->o_full[t], 1); mbar_init(&bar->o_empty[t], 4);
     }
+    mbar_init(&bar->s_free, 4);
     for (int s = 0; s < 8; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
     fence_mbar_init();
   }

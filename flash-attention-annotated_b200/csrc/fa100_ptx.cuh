@@ -73,7 +73,11 @@ static __device__ volatile unsigned int g_fa100_abort;
 constexpr int kTraceWarps = 12, kTracePerWarp = 4096;
 static __device__ unsigned int g_fa100_trace[kTraceWarps * kTracePerWarp * 3];
 static __device__ unsigned int g_fa100_trace_cnt[kTraceWarps];
+#ifndef FA100_TRACE_MAXWARP
+#define FA100_TRACE_MAXWARP 8  // events from the softmax warps only: event stores in the issuing warp distort what they measure
+#endif
 FA_DEVICE bool trace_on() { return blockIdx.x == FA100_TRACE_BLOCK && (threadIdx.x & 31) == 0; }
+FA_DEVICE bool trace_events_on() { return trace_on() && (threadIdx.x >> 5) < FA100_TRACE_MAXWARP; }
 FA_DEVICE unsigned int* trace_counter() {  // per-warp event counter in shared memory (a global counter costs an L2 round trip per event)
   // last 128 bytes of the dynamic allocation (free tail of the barrier block): a static array would push the
   // kernel over the 227 KB limit
@@ -97,7 +101,7 @@ FA_DEVICE void trace_emit(int tag, long long tb, long long te) {
 #ifdef FA100_TRACE_NOEVENTS  // libfa100_prof.so: cycle buckets only, no per-event stores to perturb the timing
 #define FA_TRACE_POINT(tag) do { } while (0)
 #else
-#define FA_TRACE_POINT(tag) do { if (trace_on()) { long long t_ = clock64(); trace_emit(tag, t_, t_); } } while (0)
+#define FA_TRACE_POINT(tag) do { if (trace_events_on()) { long long t_ = clock64(); trace_emit(tag, t_, t_); } } while (0)
 #endif
 #define FA_TRACE_BEGIN() trace_begin()
 #define FA_TRACE_END() trace_end()
@@ -142,7 +146,7 @@ FA_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
 #endif
   if (!mbar_try_wait(bar, parity) && !mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity, tag);
 #if defined(FA100_TRACE) && !defined(FA100_TRACE_NOEVENTS)
-  if (trace_on()) trace_emit(tag, tb_, clock64());
+  if (trace_events_on()) trace_emit(tag, tb_, clock64());
 #endif
 }
 

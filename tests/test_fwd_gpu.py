@@ -259,6 +259,89 @@ def test_split_combine_identity_full_size():
     assert torch.allclose(l1, l8, atol=1e-4, rtol=1e-4)
 
 
+def _gpu_randn(shape, seed, dtype=torch.bfloat16):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    return torch.randn(*shape, generator=g, device=DEV, dtype=torch.bfloat16).to(dtype)
+
+
+def _slice_check(out, lse, q, k, v, bi, g, G, rows, causal, rtol=2.0, **kw):
+    """Oracle on one (batch, kv head) and one block of query rows of a problem too large to check whole; for causal
+    inputs rows r0..r1 of an (s, s) problem equal all rows of an (r1 - r0, r1) one (bottom-right aligned mask)."""
+    r0, r1 = rows
+    kend = r1 if causal else k.shape[1]
+    hs = slice(g * G, (g + 1) * G)
+    qs, ks, vs = q[bi:bi + 1, r0:r1, hs].cpu(), k[bi:bi + 1, :kend, g:g + 1].cpu(), v[bi:bi + 1, :kend, g:g + 1].cpu()
+    kwb = {n: t[bi:bi + 1, g:g + 1].cpu() for n, t in kw.items()}
+    if qs.dtype == torch.float8_e4m3fn:
+        qs, ks, vs = (x.to(torch.bfloat16) for x in (qs, ks, vs))
+        low_kw = dict(intermediate_dtype=torch.float8_e4m3fn)
+    else:
+        low_kw = {}
+    ref, lse_ref = A.attention_oracle(qs, ks, vs, causal=causal, **kwb)
+    low, _ = A.attention_oracle(qs, ks, vs, causal=causal, upcast=False, reorder_ops=True, **low_kw, **kwb)
+    _check(out[bi:bi + 1, r0:r1, hs], lse[bi:bi + 1, hs, r0:r1], ref, low, lse_ref, rtol=rtol)
+
+
+def test_c2_full_size():
+    """BASELINE config C2 (bf16 b8 32q/8kv s8192 d128 causal) at full size: oracle on slices, and the size-independent
+    properties the domain offers -- batch permutation equivariance and exact linearity in V (both bitwise)."""
+    F = _iface()
+    b, s, h, hk, d = 8, 8192, 32, 8, 128
+    q, k, v = _gpu_randn((b, s, h, d), 21), _gpu_randn((b, s, hk, d), 22), _gpu_randn((b, s, hk, d), 23)
+    out, lse = F.flash_attn_func(q, k, v, causal=True, return_attn_probs=True)
+    for bi, g, rows in ((0, 0, (0, 256)), (3, 5, (4000, 4256)), (7, 7, (7936, 8192)), (5, 2, (127, 130))):
+        _slice_check(out, lse, q, k, v, bi, g, h // hk, rows, True)
+    perm = torch.tensor([3, 0, 7, 1, 6, 2, 5, 4], device=DEV)
+    out_p, lse_p = F.flash_attn_func(q[perm], k[perm], v[perm], causal=True, return_attn_probs=True)
+    assert torch.equal(out_p, out[perm]) and torch.equal(lse_p, lse[perm])
+    out_2, lse_2 = F.flash_attn_func(q, k, v * 2, causal=True, return_attn_probs=True)
+    assert torch.equal(out_2, out * 2) and torch.equal(lse_2, lse)
+
+
+@pytest.mark.parametrize("causal", [True, False])
+def test_c3_full_size(causal):
+    """BASELINE config C3 (e4m3 b4 h16 s16384 d128, per-tensor descales) at full size: oracle on slices, V linearity."""
+    F = _iface()
+    b, s, h, d = 4, 16384, 16, 128
+    q, k, v = (_gpu_randn((b, s, h, d), 31 + i, torch.float8_e4m3fn) for i in range(3))
+    ds = {n: torch.full((b, h), x, dtype=torch.float32, device=DEV) for n, x in (("q_descale", 0.5), ("k_descale", 0.75), ("v_descale", 1.25))}
+    out, lse = F.flash_attn_func(q, k, v, causal=causal, return_attn_probs=True, **ds)
+    for bi, g, rows in ((0, 0, (0, 128)), (2, 9, (8100, 8228)), (3, 15, (16256, 16384))):
+        _slice_check(out, lse, q, k, v, bi, g, 1, rows, causal, rtol=4.0, **ds)
+    ds2 = dict(ds, v_descale=ds["v_descale"] * 2)
+    out_2, lse_2 = F.flash_attn_func(q, k, v, causal=causal, return_attn_probs=True, **ds2)
+    assert torch.equal(out_2, out * 2) and torch.equal(lse_2, lse)
+
+
+@pytest.mark.parametrize("ragged", [False, True])
+def test_c4_full_size(ragged):
+    """BASELINE config C4 (decode b64 32q/8kv sq1 sk32768 d128, page 256, split-KV + combine) at full size: oracle on
+    whole sequences of a few batch elements; auto split equals forced 1 / 4 splits within the combine tolerance."""
+    F = _iface()
+    b, sk, h, hk, d, ps = 64, 32768, 32, 8, 128, 256
+    npages = b * sk // ps
+    q = _gpu_randn((b, 1, h, d), 41)
+    kp, vp = _gpu_randn((npages, ps, hk, d), 42), _gpu_randn((npages, ps, hk, d), 43)
+    g = torch.Generator().manual_seed(44)
+    table = torch.randperm(npages, generator=g).to(torch.int32).view(b, sk // ps).to(DEV)
+    lens = (torch.randint(16384, sk + 1, (b,), generator=g, dtype=torch.int32) if ragged else torch.full((b,), sk, dtype=torch.int32)).to(DEV)
+    outs = {}
+    for ns in (0, 1, 4):
+        outs[ns] = F.flash_attn_with_kvcache(q, kp, vp, cache_seqlens=lens, page_table=table, num_splits=ns, return_softmax_lse=True)[:2]
+    for bi in (0, 17, 63):
+        n = int(lens[bi])
+        rows = table[bi].long()
+        kd = kp[rows].reshape(1, sk, hk, d)[:, :n].cpu()
+        vd = vp[rows].reshape(1, sk, hk, d)[:, :n].cpu()
+        ref, lse_ref = A.attention_oracle(q[bi:bi + 1].cpu(), kd, vd)
+        low, _ = A.attention_oracle(q[bi:bi + 1].cpu(), kd, vd, upcast=False, reorder_ops=True)
+        for ns in outs:
+            _check(outs[ns][0][bi:bi + 1], outs[ns][1][bi:bi + 1], ref, low, lse_ref)
+    for ns in (1, 4):
+        assert (outs[0][0].float() - outs[ns][0].float()).abs().max().item() <= 4e-3
+        assert torch.allclose(outs[0][1], outs[ns][1], atol=1e-4, rtol=1e-4)
+
+
 def test_unsupported_raises():
     F = _iface()
     q, k, v = (x.to(DEV) for x in _qkv(1, 64, 64, 2, 2, 256, torch.bfloat16))

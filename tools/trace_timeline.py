@@ -20,14 +20,14 @@ ev = N.trace()
 print("events", len(ev), "hang", N.hang_info())
 pr = N.prof()
 if pr:
-    print("cycle buckets per warp (softmax: 0 s_full wait, 1 load+max, 2 exchange, 3 rescale, 4 exp/pack/store, 5 publish, 6 rest;"
-          " mma: 0 kv_full, 1 p_full, 2 issue, 3 rest)")
+    print("cycle buckets per warp (softmax: 0 s_full wait, 1 S load, 2 s_free+mask+max, 3 rescale, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait+publish, 7 rest;"
+          " mma: 0 kv_full, 1 s_free, 2 p_full/o_empty, 3 issue, 4 rest)")
     for w_, b_ in enumerate(pr):
         tot = sum(b_) or 1
         print(f"  warp {w_:2d}: " + " ".join(f"{x:9d}({100 * x / tot:4.1f}%)" for x in b_))
 NAMES = {0x10: "prod wait q_empty0", 0x11: "prod wait q_empty1", 0x20: "prod wait kv_empty(K)", 0x21: "prod wait kv_empty(V)",
          0x30: "mma wait q_full0", 0x31: "mma wait q_full1", 0x40: "mma wait kv_full(first K)", 0x41: "mma wait kv_full(V)",
-         0x42: "mma wait kv_full(K next)", 0x50: "mma wait o_empty0", 0x51: "mma wait o_empty1", 0x60: "mma wait p_full0",
+         0x42: "mma wait kv_full(K next)", 0x48: "mma wait s_free (QK0)", 0x49: "mma wait s_free (QK1)", 0x78: "smx wait pv_done0", 0x79: "smx wait pv_done1", 0x50: "mma wait o_empty0", 0x51: "mma wait o_empty1", 0x60: "mma wait p_full0",
          0x61: "mma wait p_full1", 0x70: "smx wait s_full0", 0x71: "smx wait s_full1", 0x80: "smx wait o_full0",
          0x81: "smx wait o_full1", 0x90: "smx max done 0", 0x91: "smx max done 1", 0xA0: "smx P published 0", 0xA1: "smx P published 1",
          0xB0: "mma begin PV0", 0xB1: "mma begin PV1", 0xB2: "mma issued PV0", 0xB3: "mma issued PV1", 0xB4: "mma issued QK0",

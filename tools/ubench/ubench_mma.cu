@@ -68,6 +68,14 @@ __global__ void __launch_bounds__(384, 1) k_mma(Cfg c, long long* out) {
           }
           tc_commit(&bar[1]);
         }
+        if (c.mode == 6) {  // QK with N = 64: same A tile (4 KB / MMA), half the B bytes
+          const uint32_t idesc_qk64 = make_idesc(kFmtBF16, kFmtBF16, 128, 64, 0, 0);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks / 4) * 16384 + (ks % 4) * 32;
+            mma_f16_ss(tmem + t * 128, sdesc_at(kDescK, q0 + off), sdesc_at(kDescK, kv0 + off), idesc_qk64, ks > 0);
+          }
+        }
         if (c.mode == 3) {
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
@@ -137,11 +145,11 @@ int main() {
   long long* d; cudaMalloc(&d, 64); 
   const int smem = 200 * 1024;
   cudaFuncSetAttribute(k_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  const char* mname[] = {"QK ss 128x128", "PV ts 128x128 (B mn-major)", "QK+PV interleaved", "QK ss 128x256", "batch PV8+QK8, commit+wait", "batch PV8, commit+wait"};
+  const char* mname[] = {"QK ss 128x128", "PV ts 128x128 (B mn-major)", "QK+PV interleaved", "QK ss 128x256", "batch PV8+QK8, commit+wait", "batch PV8, commit+wait", "QK ss 128x64"};
   for (int nblocks : {148})
-    for (int mode : {2, 4})
-      for (int bg : {0, 9}) {
-       for (int nbg : {0, 1}) {
+    for (int mode : {0, 1, 3, 6, 2})
+      for (int bg : {0}) {
+       for (int nbg : {0}) {
         Cfg c{mode, 20000, bg, nblocks, 8, nbg};
         cudaMemset(d, 0, 64);
         k_mma<<<nblocks, 384, smem>>>(c, d);
@@ -150,7 +158,7 @@ int main() {
         const int mmas = c.reps * ((mode == 2 || mode == 4) ? 16 : 8);
         printf("rnd=%d ", nbg);
         printf("blocks=%3d %-28s bg=%d: issue %.1f clk/mma, complete %.1f clk/mma (ideal %d)  bg iters=%lld  %s\n", nblocks, mname[mode], bg,
-               double(h[0]) / mmas, double(h[1]) / mmas, mode == 3 ? 128 : 64, h[2], e == cudaSuccess ? "" : cudaGetErrorString(e));
+               double(h[0]) / mmas, double(h[1]) / mmas, mode == 3 ? 128 : (mode == 6 ? 32 : 64), h[2], e == cudaSuccess ? "" : cudaGetErrorString(e));
        }
       }
   return 0;
