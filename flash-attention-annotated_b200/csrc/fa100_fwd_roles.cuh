@@ -46,7 +46,7 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   RingState ring;
   uint32_t q_it[kQTiles] = {0, 0};
   const uint32_t q_tx = uint32_t(HD * ELT) * p.pack * p.pos_per_tile;
-  for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
+  for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
     const WorkGeom g = make_geom(p, w);
     if (g.n_hi <= g.n_lo) continue;
 #pragma unroll
@@ -201,7 +201,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
     if (last) ++o_it[t];
   };
 
-  for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
+  for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
     int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi;
     {
       const WorkGeom g = make_geom(p, w);
