@@ -69,7 +69,7 @@ class Plan(C.Structure):
         ("reserved", i32 * 9)]
 
 
-EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_debug_hang_info",
+EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_debug_hang_info",
            "fa100_debug_trace", "fa100_debug_prof")
 
 _lib = None
@@ -97,10 +97,11 @@ def lib() -> C.CDLL:
         l.fa100_plan.argtypes = [C.POINTER(Shape), C.POINTER(Plan)]
         l.fa100_fwd.argtypes = [C.POINTER(FwdParams), vp]
         l.fa100_combine.argtypes = [C.POINTER(CombineParams), vp]
+        l.fa100_append_kv.argtypes = [C.POINTER(FwdParams), vp, i64, i64, i64, vp, vp]
         l.fa100_debug_hang_info.argtypes = [C.POINTER(C.c_uint32 * 4)]
         l.fa100_debug_trace.argtypes = [C.POINTER(C.c_uint32), C.c_int]
         l.fa100_debug_prof.argtypes = [C.POINTER(C.c_uint32), C.c_int]
-        for n in ("fa100_plan", "fa100_fwd", "fa100_combine", "fa100_debug_hang_info",
+        for n in ("fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_debug_hang_info",
            "fa100_debug_trace", "fa100_debug_prof"):
             getattr(l, n).restype = C.c_int
         if l.fa100_abi_version() != 1:

@@ -104,8 +104,13 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
         _chk(not paged, "leftpad_k is not supported with paged KV")
     align = 16 if qt == torch.float8_e4m3fn else 8
     _chk(d % align == 0 and dv % align == 0, f"head dims must be multiples of {align} for {qt}")
-    if k_new is not None or v_new is not None or rotary_cos is not None:
-        raise NotImplementedError("fa100: append-KV / rotary (k, v, rotary_cos of flash_attn_with_kvcache) is not built yet")
+    if rotary_cos is not None:
+        _chk(k_new is not None, "If rotary cos/sin are provided, new key / value to be appended to KV cache must also be provided")
+    if k_new is not None:  # append-KV (+ rotary) pass, hopper/flash_api.cpp:929-975, 1052-1082
+        q, seqused_k = _append_kv(q, k, v, k_new, v_new, cu_seqlens_q, cu_seqlens_k_new, seqused_q, seqused_k, page_table,
+                                  kv_batch_idx, rotary_cos, rotary_sin, seqlens_rotary, is_rotary_interleaved, is_causal,
+                                  window_size_left, window_size_right, attention_chunk, b, seqlen_q, seqlen_k, h, h_k, d, dv,
+                                  varlen_q, varlen_k, paged, page_size)
     if softmax_scale is None:
         softmax_scale = d ** -0.5
     if is_causal:
@@ -183,6 +188,69 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
             else:
                 _combine_into(out_accum.permute(0, 1, 3, 2, 4), lse_accum.permute(0, 1, 3, 2), out, lse.permute(0, 2, 1))
     return out, lse, (out_accum if out_accum is not None else empty), (lse_accum if lse_accum is not None else empty)
+
+
+def _append_kv(q, k, v, k_new, v_new, cu_seqlens_q, cu_seqlens_k_new, seqused_q, seqused_k, page_table, kv_batch_idx,
+               rotary_cos, rotary_sin, seqlens_rotary, interleaved, is_causal, wl, wr, chunk, b, seqlen_q, seqlen_k, h, h_k, d, dv,
+               varlen_q, varlen_k, paged, page_size):
+    """Write k_new (rotated) / v_new into the cache in place, rotate a copy of q, return (q', cache_seqlens + n_new)."""
+    qt = q.dtype
+    _chk(v_new is not None, "If k_new is supplied, v_new must also be passed in")
+    _chk(seqused_k is not None, "If k_new is supplied, seqlens_k must also be passed in")
+    _chk(seqlen_q <= seqlen_k, "If k_new is supplied, it must have seqlen <= the seqlen of the KV cache")
+    _chk(not varlen_k, "appending to a packed (cu_seqlens_k) cache is not supported")
+    _chk(k_new.dtype == qt and v_new.dtype == qt, "k_new must have the same dtype as query")
+    _chk(k_new.is_cuda and v_new.is_cuda, "k_new, v_new must be CUDA tensors")
+    _chk(k_new.stride(-1) == 1 and v_new.stride(-1) == 1, "k_new tensor must have contiguous last dimension")
+    varlen_new = cu_seqlens_k_new is not None
+    pa = N.FwdParams()
+    if varlen_new:
+        _i32(cu_seqlens_k_new, "cu_seqlens_k_new", b + 1)
+        total_new = k_new.shape[0]
+        _chk(tuple(k_new.shape) == (total_new, h_k, d) and tuple(v_new.shape) == (total_new, h_k, dv), "k_new / v_new have the wrong shape")
+        pa.knew_batch_stride, pa.knew_row_stride, pa.knew_head_stride = 0, k_new.stride(0), k_new.stride(1)
+        pa.vnew_batch_stride, pa.vnew_row_stride, pa.vnew_head_stride = 0, v_new.stride(0), v_new.stride(1)
+        pa.seqlen_knew, pa.total_knew, pa.cu_seqlens_knew = 0, total_new, _ptr(cu_seqlens_k_new)
+    else:
+        s_new = k_new.shape[1]
+        _chk(tuple(k_new.shape) == (b, s_new, h_k, d) and tuple(v_new.shape) == (b, s_new, h_k, dv), "k_new / v_new have the wrong shape")
+        pa.knew_batch_stride, pa.knew_row_stride, pa.knew_head_stride = k_new.stride(0), k_new.stride(1), k_new.stride(2)
+        pa.vnew_batch_stride, pa.vnew_row_stride, pa.vnew_head_stride = v_new.stride(0), v_new.stride(1), v_new.stride(2)
+        pa.seqlen_knew, pa.total_knew = s_new, b * s_new
+    pa.k_new, pa.v_new = _ptr(k_new), _ptr(v_new)
+    pa.q, pa.k, pa.v = _ptr(q), _ptr(k), _ptr(v)
+    if varlen_q:
+        pa.q_batch_stride, pa.q_row_stride, pa.q_head_stride = 0, q.stride(0), q.stride(1)
+    else:
+        pa.q_batch_stride, pa.q_row_stride, pa.q_head_stride = q.stride(0), q.stride(1), q.stride(2)
+    pa.k_batch_stride, pa.k_row_stride, pa.k_head_stride = k.stride(0), k.stride(1), k.stride(2)
+    pa.v_batch_stride, pa.v_row_stride, pa.v_head_stride = v.stride(0), v.stride(1), v.stride(2)
+    pa.b, pa.seqlen_q, pa.seqlen_k, pa.h, pa.h_k, pa.d, pa.dv, pa.dtype = b, seqlen_q, seqlen_k, h, h_k, d, dv, _DT[qt]
+    pa.cu_seqlens_q, pa.seqused_q, pa.seqused_k, pa.kv_batch_idx = _ptr(cu_seqlens_q), _ptr(seqused_q), _ptr(seqused_k), _ptr(kv_batch_idx)
+    if paged:
+        pa.page_table, pa.page_table_batch_stride, pa.page_size = _ptr(page_table), page_table.stride(0), page_size
+    pa.is_causal, pa.window_left, pa.window_right, pa.attention_chunk = int(is_causal), wl, wr, chunk
+    q_rot = None
+    if rotary_cos is not None:
+        _chk(rotary_sin is not None, "If rotary cos is provided, rotary sin must also be provided")
+        _chk(rotary_cos.is_cuda and rotary_cos.is_contiguous() and rotary_sin.is_cuda and rotary_sin.is_contiguous(),
+             "rotary_cos / rotary_sin must be contiguous CUDA tensors")
+        rotary_dim = rotary_cos.shape[1] * 2
+        _chk(rotary_dim <= d, "rotary_dim must be <= headdim")
+        _chk(rotary_dim % 16 == 0, "Only rotary dimensions divisible by 16 are currently supported")
+        _chk(tuple(rotary_sin.shape) == tuple(rotary_cos.shape), "rotary_sin must have the shape of rotary_cos")
+        _chk(rotary_cos.dtype == qt and rotary_sin.dtype == qt, "rotary_cos must have the same dtype as query")
+        if seqlens_rotary is not None:
+            _i32(seqlens_rotary, "seqlens_rotary", b)
+        pa.rotary_cos, pa.rotary_sin, pa.seqlens_rotary = _ptr(rotary_cos), _ptr(rotary_sin), _ptr(seqlens_rotary)
+        pa.rotary_dim, pa.is_rotary_interleaved = rotary_dim, int(bool(interleaved))
+        q_rot = torch.empty(q.shape, dtype=qt, device=q.device)
+    new_lens = torch.empty(b, dtype=torch.int32, device=q.device)
+    qs = (0, q_rot.stride(0), q_rot.stride(1)) if (q_rot is not None and varlen_q) else (
+        (q_rot.stride(0), q_rot.stride(1), q_rot.stride(2)) if q_rot is not None else (0, 0, 0))
+    with torch.cuda.device(q.device):
+        N.check(N.lib().fa100_append_kv(C.byref(pa), _ptr(q_rot), qs[0], qs[1], qs[2], _ptr(new_lens), _stream()))
+    return (q_rot if q_rot is not None else q), new_lens
 
 
 def _combine_into(op, lp, out, lse):

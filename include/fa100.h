@@ -167,6 +167,17 @@ const char* fa100_last_error(void);
 int fa100_plan(const Fa100Shape* shape, Fa100Plan* out);
 int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream);
 int fa100_combine(const Fa100CombineParams* p, fa100_stream_t stream);
+/* Append-KV + rotary pass that precedes fa100_fwd when flash_attn_with_kvcache is given k / v (and rotary_cos / sin).
+ * Replaces the AppendKV phases of the reference kernel: store_kv_new and the Q rotation
+ * (hopper/mainloop_fwd_sm90_tma_gmma_ws.hpp:1447-1713, :1098-1123; hopper/rotary.h:17-485; positions
+ * hopper/seqlen.h:60-93).  Reads p->k_new / v_new (+ strides, seqlen_knew / cu_seqlens_knew), p->seqused_k (lengths
+ * BEFORE the append), p->kv_batch_idx / page_table, p->rotary_* and p->seqlens_rotary, p->q (+ strides, cu_seqlens_q,
+ * seqused_q), p->is_causal / window_* / attention_chunk (causal or local: query row i is rotated at position base + i,
+ * else every query row at base).  Writes the new rows into p->k / p->v in place, the rotated copy of q into `q_rotated`
+ * (element strides given; ignored without rotary; the caller's q is never modified) and seqused_k + n_new into
+ * `seqused_k_out` (b int32).  The caller then runs fa100_fwd with q = q_rotated and seqused_k = seqused_k_out. */
+int fa100_append_kv(const Fa100FwdParams* p, void* q_rotated, int64_t qr_batch_stride, int64_t qr_row_stride,
+                    int64_t qr_head_stride, int32_t* seqused_k_out, fa100_stream_t stream);
 /* self-test hook used by the GPU tests: returns the hang-watchdog record of the last trapped kernel */
 int fa100_debug_hang_info(uint32_t out[4]);
 /* profiling hook: events {tag | warp << 16, begin_clk, end_clk} of the opt-in timeline build (libfa100_trace.so,

@@ -7,6 +7,8 @@ Tolerances (written here as north_star requires):
   fp8:       same rule with the e4m3-intermediate low-precision arm and multiplier 4
   LSE:       |lse - lse_ref| <= 1e-3 * max(1, |lse_ref|), and -inf exactly where the oracle has -inf
 """
+import math
+
 import pytest
 import torch
 
@@ -196,6 +198,104 @@ def test_kvcache_batch_idx_and_leftpad():
     ref, lse_ref = A.attention_oracle(q, kd, vd, k_lens=lens - pad, key_leftpad=pad, causal=True)
     low, _ = A.attention_oracle(q, kd, vd, k_lens=lens - pad, key_leftpad=pad, causal=True, upcast=False, reorder_ops=True)
     _check(out, lse, ref, low, lse_ref)
+
+
+@pytest.mark.parametrize("rotary", [None, "interleaved", "halves", "halves_seqlens", "partial"])
+@pytest.mark.parametrize("layout", ["dense", "batch_idx", "paged64", "paged256", "varlen_new"])
+@pytest.mark.parametrize("mask", ["none", "causal", "local"])
+@pytest.mark.parametrize("sq,s_new", [(1, 1), (5, 5), (64, 37), (3, 130)])
+def test_kvcache_append_rotary(sq, s_new, mask, layout, rotary):
+    """k / v appended in place at cache_seqlens, rotary on k_new and on a copy of q (hopper/test_flash_attn.py:601-989):
+    the cache must hold exactly the new rows (bit-exact without rotary, 1e-3 with) and nothing else may change."""
+    if sq > s_new:
+        pytest.skip("seqlen_q <= seqlen_new in the reference test")
+    F = _iface()
+    g = torch.Generator().manual_seed(11)
+    b, h, hk, d, cap = 3, 4, 2, 128, 512
+    dt = torch.bfloat16
+    q = torch.randn(b, sq, h, d, generator=g).to(dt)
+    kn = torch.randn(b, s_new, hk, d, generator=g).to(dt)
+    vn = torch.randn(b, s_new, hk, d, generator=g).to(dt)
+    lens = torch.randint(0, cap - s_new + 1, (b,), generator=g, dtype=torch.int32)
+    new_lens = torch.full((b,), s_new, dtype=torch.int32)
+    if layout == "varlen_new":
+        new_lens = torch.randint(1, s_new + 1, (b,), generator=g, dtype=torch.int32)
+        new_lens[0] = s_new
+    causal, window = mask == "causal", ((40, 10) if mask == "local" else (-1, -1))
+    if causal or mask == "local":  # keep sq <= the shortest final key length so no query row is fully masked
+        lens = lens.clamp_min(sq)
+    nb = 5 if layout == "batch_idx" else b
+    idx = torch.tensor([4, 1, 2], dtype=torch.int32) if layout == "batch_idx" else None
+    table = None
+    if layout.startswith("paged"):
+        ps = int(layout[5:])
+        kd, vd, table, kc, vc = A.paged_kvcache(cap, ps, b, hk, d, d, dt, generator=g)
+        kd, vd = kd.clone(), vd.clone()
+    else:
+        kc = torch.randn(nb, cap, hk, d, generator=g).to(dt)
+        vc = torch.randn(nb, cap, hk, d, generator=g).to(dt)
+        sel = idx.long() if idx is not None else torch.arange(b)
+        kd, vd = kc[sel].clone(), vc[sel].clone()
+    cos = sin = rot_lens = None
+    q_ref, kn_ref = q, kn
+    if rotary is not None:
+        rd = 64 if rotary == "partial" else d
+        ang = torch.rand(cap + 64, rd // 2, generator=g) * 2 * math.pi
+        cos, sin = torch.cos(ang).to(dt), torch.sin(ang).to(dt)
+        inter = rotary == "interleaved"
+        rot_lens = (lens // 2) if rotary == "halves_seqlens" else None
+        base = rot_lens if rot_lens is not None else lens
+        kn_ref = A.rotary_oracle(kn, cos, sin, base, interleaved=inter)
+        if causal or mask == "local":
+            q_ref = A.rotary_oracle(q, cos, sin, base, interleaved=inter)
+        else:  # every query row sits at position cache_seqlens
+            q_ref = A.rotary_oracle(q.reshape(b, 1, sq * h, d), cos, sin, base, interleaved=inter).reshape(b, sq, h, d)
+    for i in range(b):  # the dense view after the append
+        n = int(new_lens[i])
+        kd[i, int(lens[i]):int(lens[i]) + n] = kn_ref[i, :n]
+        vd[i, int(lens[i]):int(lens[i]) + n] = vn[i, :n]
+    tot = lens + new_lens
+    kw = dict(causal=causal, window_size=window)
+    ref, lse_ref = A.attention_oracle(q_ref, kd, vd, k_lens=tot, **kw)
+    low, _ = A.attention_oracle(q_ref, kd, vd, k_lens=tot, upcast=False, reorder_ops=True, **kw)
+    kc_dev, vc_dev = kc.to(DEV), vc.to(DEV)
+    k_before, v_before = kc_dev.clone(), vc_dev.clone()
+    if layout == "varlen_new":
+        cu_new = torch.nn.functional.pad(new_lens.cumsum(0), (1, 0)).to(torch.int32)
+        kn_in = torch.cat([kn[i, :int(new_lens[i])] for i in range(b)]).to(DEV)
+        vn_in = torch.cat([vn[i, :int(new_lens[i])] for i in range(b)]).to(DEV)
+        extra = dict(cu_seqlens_k_new=cu_new.to(DEV))
+    else:
+        kn_in, vn_in, extra = kn.to(DEV), vn.to(DEV), {}
+    q_dev = q.to(DEV)
+    q_copy = q_dev.clone()
+    out, lse, *_ = F.flash_attn_with_kvcache(
+        q_dev, kc_dev, vc_dev, k=kn_in, v=vn_in, rotary_cos=None if cos is None else cos.to(DEV),
+        rotary_sin=None if sin is None else sin.to(DEV), cache_seqlens=lens.to(DEV),
+        cache_batch_idx=None if idx is None else idx.to(DEV), page_table=None if table is None else table.to(DEV),
+        rotary_seqlens=None if rot_lens is None else rot_lens.to(DEV), rotary_interleaved=(rotary == "interleaved"),
+        return_softmax_lse=True, **kw, **extra)
+    _check(out, lse, ref, low, lse_ref)
+    assert torch.equal(q_dev, q_copy), "q must not be modified"
+    # cache contents: dense view of what the device now holds
+    if table is not None:
+        kd_dev = kc_dev.cpu()[table.flatten().long()].view(b, -1, hk, d)[:, :cap]
+        vd_dev = vc_dev.cpu()[table.flatten().long()].view(b, -1, hk, d)[:, :cap]
+    else:
+        sel = idx.long() if idx is not None else torch.arange(b)
+        kd_dev, vd_dev = kc_dev.cpu()[sel], vc_dev.cpu()[sel]
+    assert torch.equal(vd_dev, vd)
+    if rotary is None:
+        assert torch.equal(kd_dev, kd)
+    else:
+        assert torch.allclose(kd_dev.float(), kd.float(), rtol=1e-3, atol=1e-3)
+    # rows outside the appended ranges are untouched (also the cache entries no batch element points at)
+    changed_k = (kc_dev != k_before).flatten(1).any(1).sum().item() if table is None else None
+    if table is None:
+        assert changed_k <= b
+        untouched = [i for i in range(nb) if idx is None or i not in idx.tolist()] if idx is not None else []
+        for i in untouched:
+            assert torch.equal(kc_dev[i], k_before[i]) and torch.equal(vc_dev[i], v_before[i])
 
 
 @pytest.mark.parametrize("causal", [False, True])
