@@ -34,6 +34,9 @@ WORKLOADS = {
                  desc="FA fwd FP8 e4m3 per-tensor descale: b4 h16 s16384 d128 non-causal"),
     "c4": dict(dtype="bf16", b=64, sq=1, sk=32768, h=32, hk=8, d=128, causal=False, page=256,
                desc="split-KV decode, paged KV (page 256): b64 32q/8kv sq1 sk32768 d128"),
+    # one 131072-token sequence sharded over the ranks (zig-zag ring / context parallel): total work is fixed -> strong scaling
+    "c5": dict(dtype="bf16", b=1, sq=131072, sk=131072, h=32, hk=32, d=128, causal=True, ring=True,
+               desc="ring/context-parallel FA fwd bf16: 131072 tokens, 32 heads (MHA), d128, causal, zig-zag over the ranks"),
 }
 
 
@@ -116,11 +119,16 @@ class ClockSampler:
                     reasons=[n for n, m in names if bits & m], samples=len(sm))
 
 
-def make_inputs(w, device, seed):
+def make_inputs(w, device, seed, world=1):
     g = torch.Generator(device="cpu").manual_seed(seed)
     dt = torch.bfloat16
     b, sq, sk, h, hk, d = w["b"], w["sq"], w["sk"], w["h"], w["hk"], w["d"]
     t = dict()
+    if w.get("ring"):  # this rank's zig-zag shard (2 chunks of s / 2N rows); synthetic, so it is drawn directly
+        rows = sq // world
+        mk = lambda *s: torch.randn(*s, dtype=dt, device=device).cpu()  # noqa: E731
+        t["q"], t["k"], t["v"] = mk(b, rows, h, d), mk(b, rows, hk, d), mk(b, rows, hk, d)
+        return t
     if "page" in w:
         ps = w["page"]
         npages = b * sk // ps
@@ -187,6 +195,8 @@ def run_reference(args, w, rank):
 def metric_name(w):
     if "page" in w:
         return "decode HBM GB/s (split-KV paged decode)"
+    if w.get("ring"):
+        return "ring/context-parallel fwd TFLOPS (aggregate) bf16 hdim128 causal 131072 tokens"
     return f"fwd TFLOPS/GPU {w['dtype']} hdim128 {'causal' if w['causal'] else 'non-causal'}"
 
 
@@ -221,13 +231,19 @@ def main():
 
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    host = make_inputs(w, dev, seed=1234 + rank)
+    host = make_inputs(w, dev, seed=1234 + rank, world=world)
     pin = {k_: (v_.pin_memory() if v_.device.type == "cpu" else v_) for k_, v_ in host.items()}
     devt = {k_: v_.to(dev, non_blocking=True) for k_, v_ in pin.items()}
     torch.cuda.synchronize()
     decode = "page" in w
 
+    ring = bool(w.get("ring"))
+    if ring:
+        import ring_attention as R
+
     def step(t):
+        if ring:
+            return R.ring_flash_attn_func(t["q"], t["k"], t["v"], causal=True)
         if decode:
             return flash_attn_with_kvcache(t["q"], t["k"], t["v"], cache_seqlens=t["cache_seqlens"], page_table=t["page_table"],
                                            causal=False)
@@ -290,6 +306,10 @@ def main():
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
     ms, e2e_ms = vals[0].item(), (vals[1].item() if e2e_ms is not None else None)
 
+    launches_per_step = 2 if decode else 1
+    if ring:  # partial-attention launches of this rank's hop plan + one merge per partial after the first of a row group
+        n_part = sum(len(work) for _, work in R.hop_plan(0, world))
+        launches_per_step = n_part + max(0, n_part - 2)
     if rank == 0:
         peaks = measured_peaks()
         if decode:
@@ -297,15 +317,17 @@ def main():
             unit, bound, peak = "GB/s", "hbm", peaks["hbm"]
             e2e_val = decode_bytes(w) * world / (e2e_ms * 1e-3) / 1e9 if e2e_ms else None
         else:
-            per_gpu = flops(w) / (ms * 1e-3) / 1e12
+            share = 1.0 / world if ring else 1.0  # ring: the ranks split ONE problem
+            per_gpu = flops(w) * share / (ms * 1e-3) / 1e12
             unit, bound, peak = "TFLOP/s", "tensor", peaks["tensor"] * (2.0 if w["dtype"] == "e4m3" else 1.0)
-            e2e_val = flops(w) * world / (e2e_ms * 1e-3) / 1e12 if e2e_ms else None
+            e2e_val = flops(w) * share * world / (e2e_ms * 1e-3) / 1e12 if e2e_ms else None
         line = dict(metric=metric_name(w), value=per_gpu * world, unit=unit, n_gpus=world, steps=args.steps, warmup=args.warmup,
-                    ms_per_step=ms, higher_is_better=True, scaling="weak", vs_baseline=None,
+                    ms_per_step=ms, higher_is_better=True, scaling="strong" if ring else "weak", vs_baseline=None,
                     dtype={"bf16": "bf16", "e4m3": "fp8_e4m3"}[w["dtype"]], data="synthetic",
-                    config=dict(workload=w["desc"], per_gpu="full workload on every GPU (batch x heads sharding, no communication)",
+                    config=dict(workload=w["desc"], per_gpu=("1/N of the sequence per GPU, K/V ring over NCCL send/recv" if ring else
+                                                            "full workload on every GPU (batch x heads sharding, no communication)"),
                                 l2="inputs (>= 0.67 GB) exceed the 126 MB L2; no flush between steps"),
-                    clocks=clocks, gpu_launches=args.steps * (2 if decode else 1),
+                    clocks=clocks, gpu_launches=args.steps * launches_per_step,
                     e2e=dict(value=e2e_val, unit=unit, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h),
                     roofline=dict(bound=bound, achieved=per_gpu, peak=peak, unit=unit, frac=per_gpu / peak, traffic=ncu_traffic(args.workload),
                                   peak_source=peaks["source"] + (" (bf16 burst x2 for fp8)" if w["dtype"] == "e4m3" and not decode else ""),

@@ -33,7 +33,6 @@ __global__ void __launch_bounds__(kCombineWarps * 32) fa100_combine_kernel(const
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     const float lse = (sum == 0.f || sum != sum) ? -INFINITY : logf(sum) + mx_use;
-    if (lane == 0) p.lse[bb * p.lse_batch_stride + ss * p.lse_row_stride + hh * p.lse_head_stride] = lse;
     const float lse_use = lse == -INFINITY ? 0.f : lse;
     // 2. weighted sum, 4 columns per lane per pass, splits in order
     const float* op = p.o_partial + bb * p.op_batch_stride + ss * p.op_row_stride + hh * p.op_head_stride;
@@ -59,6 +58,10 @@ __global__ void __launch_bounds__(kCombineWarps * 32) fa100_combine_kernel(const
         *reinterpret_cast<uint2*>(static_cast<__half*>(p.o) + off) = u;
       }
     }
+    // the merged LSE goes out last: o / lse may alias split 0 of the partials (in-place running merge of ring attention),
+    // and the weights above re-read the split LSEs
+    __syncwarp();
+    if (lane == 0) p.lse[bb * p.lse_batch_stride + ss * p.lse_row_stride + hh * p.lse_head_stride] = lse;
   }
 }
 

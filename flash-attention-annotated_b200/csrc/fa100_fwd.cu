@@ -26,7 +26,7 @@ static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, co
 
 int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stream) {
   // ---- validation (hopper/flash_api.cpp:710-856)
-  FA_CHECK_ARG(p->q && p->k && p->v && p->o && p->lse, "q, k, v, o and lse must be non-null");
+  FA_CHECK_ARG(p->q && p->k && p->v, "q, k and v must be non-null");
   FA_CHECK_ARG(p->dtype == FA100_BF16 || p->dtype == FA100_FP16 || p->dtype == FA100_E4M3, "unsupported dtype %d", p->dtype);
   FA_CHECK_ARG(p->b > 0 && p->h > 0 && p->h_k > 0 && p->h % p->h_k == 0, "bad batch/head counts b=%d h=%d h_k=%d", p->b, p->h, p->h_k);
   FA_CHECK_ARG(p->d > 0 && p->dv > 0 && p->d % 8 == 0 && p->dv % 8 == 0, "head dims must be multiples of 8 (d=%d dv=%d)", p->d, p->dv);
@@ -48,6 +48,8 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   }
   const int splits = plan->num_splits;
   if (splits > 1) FA_CHECK_ARG(p->o_accum && p->lse_accum, "num_splits > 1 needs o_accum and lse_accum");
+  FA_CHECK_ARG((p->o_accum == nullptr) == (p->lse_accum == nullptr), "o_accum and lse_accum must be given together");
+  FA_CHECK_ARG(p->o_accum != nullptr || (p->o != nullptr && p->lse != nullptr), "o and lse are required without o_accum");
 
   // ---- kernel parameters
   FwdKernelParams kp;
@@ -120,9 +122,11 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
     rc = encode_tensor_map(&tmV, p->dtype, 4, p->v, dimsV, strV, box);
     if (rc) return rc;
   }
-  FA_CHECK_ARG((p->o_row_stride % 8 == 0) && (p->o_head_stride % 8 == 0) && (p->o_batch_stride % 8 == 0) &&
-                   (reinterpret_cast<uintptr_t>(p->o) % 16 == 0),
-               "o must be 16-byte aligned with strides that are multiples of 8 elements");
+  if (p->o_accum == nullptr) {
+    FA_CHECK_ARG((p->o_row_stride % 8 == 0) && (p->o_head_stride % 8 == 0) && (p->o_batch_stride % 8 == 0) &&
+                     (reinterpret_cast<uintptr_t>(p->o) % 16 == 0),
+                 "o must be 16-byte aligned with strides that are multiples of 8 elements");
+  }
 
   int num_sm = plan->num_sm;
   const int grid = std::max(1, std::min(kp.num_work, num_sm));

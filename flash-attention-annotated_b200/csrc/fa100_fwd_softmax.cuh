@@ -193,7 +193,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
     // ---- epilogue: O / rowsum, LSE (hopper/softmax.h:137-155, epilogue_fwd.hpp:215-481); geometry is recomputed here
     {
       const WorkGeom g = make_geom(p, w);
-      const bool split = p.num_splits > 1;
+      const bool split = p.o_accum != nullptr;  // fp32 partials (split-KV, or one hop of ring attention)
       const bool live = rg.n_max > rg.n_min;
       const int in_tile = p.pack > 1 ? row / p.pack : row;
       const int pos = (g.it.m_blk * kQTiles + t) * p.pos_per_tile + in_tile;

@@ -54,7 +54,9 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
             page_table=None, kv_batch_idx=None, leftpad_k=None, rotary_cos=None, rotary_sin=None,
             seqlens_rotary=None, q_descale=None, k_descale=None, v_descale=None, softmax_scale=None,
             is_causal=False, window_size_left=-1, window_size_right=-1, attention_chunk=0, softcap=0.0,
-            is_rotary_interleaved=False, scheduler_metadata=None, num_splits=0, pack_gqa=None, sm_margin=0):
+            is_rotary_interleaved=False, scheduler_metadata=None, num_splits=0, pack_gqa=None, sm_margin=0, _partial=None):
+    """torch.ops.flash_attn_3.fwd.  `_partial=(o_accum, lse_accum)` (not part of the schema; used by ring_attention) makes
+    the kernel write one fp32 partial -- o_accum (1, b, h, sq, dv), lse_accum (1, b, h, sq) -- instead of out / lse."""
     _chk(q.is_cuda and k.is_cuda and v.is_cuda, "q, k, v must be CUDA tensors (there is no CPU path)")
     qt = q.dtype
     _chk(qt in (torch.bfloat16, torch.float16, torch.float8_e4m3fn), "FlashAttention only supports fp16, bf16, and fp8_e4m3 data type")
@@ -120,14 +122,16 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
 
     out_dtype = torch.bfloat16 if qt == torch.float8_e4m3fn else qt
     out_shape = (total_q, h, dv) if varlen_q else (b, seqlen_q, h, dv)
-    if out is None:
+    if _partial is not None:  # the kernel writes only the fp32 partial
+        out = torch.empty((0,) * len(out_shape), dtype=out_dtype, device=q.device)
+    elif out is None:
         out = torch.empty(out_shape, dtype=out_dtype, device=q.device)
     else:
         _chk(out.dtype == out_dtype and tuple(out.shape) == out_shape and out.stride(-1) == 1 and out.device == q.device,
              "out has the wrong dtype / shape / layout")
-    lse = torch.empty((h, total_q) if varlen_q else (b, h, seqlen_q), dtype=torch.float32, device=q.device)
+    lse = torch.empty(((h, total_q) if varlen_q else (b, h, seqlen_q)) if _partial is None else (0,), dtype=torch.float32, device=q.device)
     empty = torch.empty(0, dtype=torch.float32, device=q.device)
-    if seqlen_k == 0 or out.numel() == 0:  # hopper/flash_api.cpp:1190-1194
+    if _partial is None and (seqlen_k == 0 or out.numel() == 0):  # hopper/flash_api.cpp:1190-1194
         out.zero_()
         lse.fill_(float("inf"))
         return out, lse, empty, empty
@@ -135,10 +139,17 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
         _chk(scheduler_metadata.dtype == torch.int32 and scheduler_metadata.is_cuda and scheduler_metadata.is_contiguous(),
              "scheduler_metadata must be a contiguous int32 CUDA tensor")
 
+    if _partial is not None:
+        num_splits = 1
     pl = plan(b, seqlen_q, seqlen_k, h, h_k, d, dv, qt, is_causal, is_local, num_splits, pack_gqa, sm_margin, q.device)
     splits = pl.num_splits
     out_accum = lse_accum = None
-    if splits > 1:
+    if _partial is not None:
+        out_accum, lse_accum = _partial
+        _chk(not varlen_q and out_accum.dtype == torch.float32 and out_accum.is_contiguous() and lse_accum.is_contiguous()
+             and tuple(out_accum.shape) == (1, b, h, seqlen_q, dv) and tuple(lse_accum.shape) == (1, b, h, seqlen_q),
+             "_partial buffers must be contiguous fp32 (1, b, h, sq, dv) / (1, b, h, sq)")
+    elif splits > 1:
         if varlen_q:
             out_accum = torch.empty((splits, h, total_q, dv), dtype=torch.float32, device=q.device)
             lse_accum = torch.empty((splits, h, total_q), dtype=torch.float32, device=q.device)
@@ -180,7 +191,7 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     p.num_splits, p.pack_gqa, p.num_sm = splits, pl.pack_gqa, pl.num_sm
     with torch.cuda.device(q.device):
         N.check(N.lib().fa100_fwd(C.byref(p), _stream()))
-        if splits > 1:
+        if _partial is None and splits > 1:
             if varlen_q:  # (splits, h, total_q, dv) viewed as (splits, b=1, s=total_q, h, dv)
                 op = out_accum.permute(0, 2, 1, 3).unsqueeze(1)
                 lp = lse_accum.permute(0, 2, 1).unsqueeze(1)

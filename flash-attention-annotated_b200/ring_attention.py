@@ -1,0 +1,204 @@
+"""Context-parallel (ring) causal attention over the fa100 forward -- BASELINE config C5, SURVEY.md 8(e).
+
+The reference has no multi-GPU attention; its contract for merging partial results is the combine kernel
+(hopper/flash_fwd_combine_kernel.h:345-458, oracle ``attention_combine_ref`` hopper/test_flash_attn.py:1105-1114):
+``LSE = logaddexp_s LSE_s``, ``O = sum_s exp(LSE_s - LSE) O_s``.  This module shards ONE long sequence over the ranks of
+a process group and computes exactly ``flash_attn_func(q, k, v, causal=True)`` of the unsharded problem.
+
+Layout (zig-zag): the sequence is cut into 2N chunks of c rows; rank r owns chunks r ("lo") and 2N-1-r ("hi") of Q, K
+and V, so every rank has the same causal work in every hop.  Hop t uses the K/V that originated at rank s = (r-t) mod N:
+
+  t = 0 (s = r)   lo rows x lo keys causal;  hi rows x (lo, hi) keys causal (bottom-right aligned)
+  s < r           lo rows and hi rows x lo keys of s, unmasked   (hi keys of s lie in the future of both)
+  s > r           hi rows x (lo, hi) keys of s, unmasked         (lo rows see nothing of s)
+
+Each launch writes an fp32 partial (O_t, LSE_t); partials are merged into running fp32 (O, LSE) per row group with
+``fa100_combine`` (two-way, in place), the last merge writing the 16-bit output.  K/V travel around the ring as one
+packed buffer with NCCL send/recv on a side stream, double-buffered so hop t+1's transfer overlaps hop t's attention;
+the final O stays sequence-sharded (no gather).  Message per hop: 2 * 2c * h_k * d * 2 B (268 MB at C5 on 8 GPUs).
+
+The arithmetic lives behind a small backend object so that the ring logic (schedule, masks, merge order, exchange)
+is testable on CPU with gloo; the product backend is CUDA only and there is no fallback.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+# --------------------------------------------------------------------------- zig-zag sharding helpers
+def zigzag_shard(x: torch.Tensor, rank: int, world: int, dim: int = 1) -> torch.Tensor:
+    """Rows of rank `rank`: chunks rank and 2*world-1-rank of `x` along `dim`, concatenated (lo then hi)."""
+    n = x.shape[dim]
+    assert n % (2 * world) == 0, "sequence length must be a multiple of 2 * world_size"
+    chunks = x.chunk(2 * world, dim=dim)
+    return torch.cat((chunks[rank], chunks[2 * world - 1 - rank]), dim=dim).contiguous()
+
+
+def zigzag_unshard(shards: List[torch.Tensor], dim: int = 1) -> torch.Tensor:
+    """Inverse of zigzag_shard given the shards of ranks 0..world-1."""
+    world = len(shards)
+    chunks: List[Optional[torch.Tensor]] = [None] * (2 * world)
+    for r, s in enumerate(shards):
+        lo, hi = s.chunk(2, dim=dim)
+        chunks[r], chunks[2 * world - 1 - r] = lo, hi
+    return torch.cat(chunks, dim=dim)
+
+
+def hop_plan(rank: int, world: int) -> List[Tuple[int, List[Tuple[str, str, bool]]]]:
+    """[(source rank, [(row group, key range, causal), ...]), ...] for hops t = 0..world-1.
+    row group: "lo" | "hi"; key range: "lo" (first c keys of the source's buffer) | "all" (its 2c keys)."""
+    plan = []
+    for t in range(world):
+        s = (rank - t) % world
+        if t == 0:
+            plan.append((s, [("lo", "lo", True), ("hi", "all", True)]))
+        elif s < rank:
+            plan.append((s, [("lo", "lo", False), ("hi", "lo", False)]))
+        else:
+            plan.append((s, [("hi", "all", False)]))
+    return plan
+
+
+# --------------------------------------------------------------------------- CUDA backend (product path)
+class Fa100Backend:
+    """Partial attention = fa100_fwd in partial mode; merge = fa100_combine.  CUDA only."""
+
+    def __init__(self, softmax_scale: Optional[float] = None):
+        import fa100_ops as ops  # raises if the library is missing; no fallback
+
+        self.ops = ops
+        self.scale = softmax_scale
+
+    def alloc(self, b, h, rows, dv, device):
+        o = torch.empty((2, b, h, rows, dv), dtype=torch.float32, device=device)  # slot 0 running, slot 1 this hop
+        lse = torch.empty((2, b, h, rows), dtype=torch.float32, device=device)
+        return o, lse
+
+    def partial(self, q, k, v, causal, o_slot, lse_slot):
+        self.ops.mha_fwd(q, k, v, softmax_scale=self.scale, is_causal=causal, _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)))
+
+    def merge(self, o, lse, out=None, out_lse=None):
+        """slot 0 <- merge(slot 0, slot 1) in fp32, or into the 16-bit `out` (b, rows, h, dv) / `out_lse` (b, h, rows)."""
+        op = o.permute(0, 1, 3, 2, 4)   # (2, b, rows, h, dv)
+        lp = lse.permute(0, 1, 3, 2)    # (2, b, rows, h)
+        if out is None:
+            self.ops._combine_into(op, lp, op[0], lp[0])
+        else:
+            self.ops._combine_into(op, lp, out, out_lse.permute(0, 2, 1))
+
+    def finish_single(self, o, lse, out, out_lse):
+        out.copy_(o[0].permute(0, 2, 1, 3))
+        out_lse.copy_(lse[0])
+
+
+# --------------------------------------------------------------------------- K/V exchange
+class _RingExchange:
+    """K and V travel as one buffer; two buffers alternate so the next hop's transfer overlaps this hop's attention."""
+
+    def __init__(self, k, v, rank, world, group):
+        assert k.shape == v.shape, "ring exchange packs K and V in one message: d must equal dv"
+        self.kv = [torch.stack((k, v)), torch.empty((2,) + tuple(k.shape), dtype=k.dtype, device=k.device) if world > 1 else None]
+        self.world, self.group, self.dev = world, group, k.device
+        self.comm_stream = torch.cuda.Stream(device=k.device) if (k.is_cuda and world > 1) else None
+        self.nxt, self.prv = (rank + 1) % world, (rank - 1) % world
+        if group is not None and world > 1:
+            self.nxt, self.prv = dist.get_global_rank(group, self.nxt), dist.get_global_rank(group, self.prv)
+        self.reqs = []
+
+    def begin(self, t):
+        """Start moving the buffer of hop t on to the next rank (and receiving hop t+1's); return hop t's (K, V)."""
+        cur = self.kv[t % 2]
+        if t + 1 < self.world:
+            recv = self.kv[(t + 1) % 2]
+            ops = [dist.P2POp(dist.isend, cur, self.nxt, self.group), dist.P2POp(dist.irecv, recv, self.prv, self.group)]
+            if self.comm_stream is not None:
+                self.comm_stream.wait_stream(torch.cuda.current_stream(self.dev))  # recv's last readers (hop t-1) are done
+                with torch.cuda.stream(self.comm_stream):
+                    self.reqs = dist.batch_isend_irecv(ops)
+            else:
+                self.reqs = dist.batch_isend_irecv(ops)
+        return cur[0], cur[1]
+
+    def end(self, t):
+        for r in self.reqs:
+            r.wait()
+        if self.comm_stream is not None and self.reqs:
+            torch.cuda.current_stream(self.dev).wait_stream(self.comm_stream)
+        self.reqs = []
+
+
+class _LocalExchange:
+    """All shards live in this process (single-device simulation of the ring, used by tests and for debugging)."""
+
+    def __init__(self, k_shards, v_shards, rank):
+        self.k, self.v, self.rank = k_shards, v_shards, rank
+
+    def begin(self, t):
+        s = (self.rank - t) % len(self.k)
+        return self.k[s], self.v[s]
+
+    def end(self, t):
+        pass
+
+
+# --------------------------------------------------------------------------- the ring
+def ring_flash_attn_func(q, k, v, softmax_scale=None, causal=True, group=None, backend=None, return_lse=False, _exchange=None,
+                         _rank_world=None):
+    """q, k, v: this rank's zig-zag shard, (b, 2c, h, d) / (b, 2c, h_k, d) / (b, 2c, h_k, dv), contiguous.
+    Returns this rank's shard of the output (b, 2c, h, dv) [and LSE (b, h, 2c)]."""
+    assert causal, "ring attention is built for the causal C5 case (non-causal needs no zig-zag; use flash_attn_func per hop)"
+    if _rank_world is not None:
+        rank, world = _rank_world
+    else:
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        rank = dist.get_rank(group) if dist.is_initialized() else 0
+    be = backend if backend is not None else Fa100Backend(softmax_scale)
+    b, rows2, h, d = q.shape
+    c = rows2 // 2
+    dv = v.shape[-1]
+    assert rows2 % 2 == 0 and k.shape[1] == rows2 and v.shape[1] == rows2
+    out = torch.empty((b, rows2, h, dv), dtype=q.dtype if q.dtype != torch.float8_e4m3fn else torch.bfloat16, device=q.device)
+    out_lse = torch.empty((b, h, rows2), dtype=torch.float32, device=q.device)
+    groups = {"lo": slice(0, c), "hi": slice(c, rows2)}
+    acc = {g: be.alloc(b, h, c, dv, q.device) for g in groups}
+    filled = {g: False for g in groups}
+    plan = hop_plan(rank, world)
+    last_use = {g: max(t for t, (_, work) in enumerate(plan) if any(w[0] == g for w in work)) for g in groups}
+    ex = _exchange if _exchange is not None else _RingExchange(k, v, rank, world, group)
+
+    for t, (src, work) in enumerate(plan):
+        k_t, v_t = ex.begin(t)
+        for g, keys, is_causal in work:
+            o, lse = acc[g]
+            kk = k_t[:, :c] if keys == "lo" else k_t
+            vv = v_t[:, :c] if keys == "lo" else v_t
+            slot = 1 if filled[g] else 0
+            be.partial(q[:, groups[g]], kk, vv, is_causal, o[slot], lse[slot])
+            final = t == last_use[g]
+            if filled[g]:
+                if final:
+                    be.merge(o, lse, out[:, groups[g]], out_lse[:, :, groups[g]])
+                else:
+                    be.merge(o, lse)
+            elif final:
+                be.finish_single(o, lse, out[:, groups[g]], out_lse[:, :, groups[g]])
+            filled[g] = True
+        ex.end(t)
+    return (out, out_lse) if return_lse else out
+
+
+def simulate_ring(q, k, v, world, softmax_scale=None, backend=None):
+    """Run every rank of a `world`-way ring in this process on the full (b, s, h, d) tensors and reassemble the result:
+    same schedule, partial launches and merges as the distributed path, no communication."""
+    qs = [zigzag_shard(q, r, world) for r in range(world)]
+    ks = [zigzag_shard(k, r, world) for r in range(world)]
+    vs = [zigzag_shard(v, r, world) for r in range(world)]
+    outs, lses = [], []
+    for r in range(world):
+        o, l = ring_flash_attn_func(qs[r], ks[r], vs[r], softmax_scale, True, None, backend, True, _LocalExchange(ks, vs, r), (r, world))
+        outs.append(o)
+        lses.append(l)
+    return zigzag_unshard(outs, 1), zigzag_unshard(lses, 2)

@@ -55,7 +55,10 @@ typedef struct Fa100FwdParams {
   int64_t o_batch_stride, o_row_stride, o_head_stride;
 
   /* split-KV partials, required when num_splits > 1 (hopper/flash_api.cpp:1094-1113):
-   * o_accum fp32 (splits, b, h, sq, dv) / (splits, h, total_q, dv); lse_accum fp32 (splits, b, h, sq) / (splits, h, total_q) */
+   * o_accum fp32 (splits, b, h, sq, dv) / (splits, h, total_q, dv); lse_accum fp32 (splits, b, h, sq) / (splits, h, total_q).
+   * When non-null the kernel writes ONLY these fp32 partials (each normalised by its own row sum, with its LSE) and
+   * leaves o / lse untouched -- also with num_splits == 1, which is how one hop of ring attention gets a partial
+   * that fa100_combine can merge.  Pass null for a plain single-pass forward. */
   float* o_accum;
   float* lse_accum;
 
@@ -124,6 +127,8 @@ typedef struct Fa100FwdParams {
 
 /* LSE-weighted merge of split partials (hopper/flash_fwd_combine_kernel.h:200-483,
  * mha_combine hopper/flash_api.cpp:1569-1670).  Element strides; d stride is 1. */
+/* `o` / `lse` may alias split 0 of `o_partial` / `lse_partial` (same strides): every row is read completely before it is
+ * written, which is how ring attention keeps a running fp32 merge in place. */
 typedef struct Fa100CombineParams {
   const float* o_partial;   /* (splits, b, s, h, d) logical */
   const float* lse_partial; /* (splits, b, s, h)   logical */

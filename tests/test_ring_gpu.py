@@ -1,0 +1,81 @@
+"""Ring (context-parallel) attention on the GPU: the CUDA backend (fa100_fwd partial mode + fa100_combine) driven by
+the ring schedule.  Single device: every rank of a simulated 2/4/8-way ring runs in this process.  Two devices (skipped
+when only one is visible): a real NCCL ring, launched as two processes."""
+import os
+import sys
+
+import pytest
+import torch
+
+import attention_oracle as A
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _inputs(b, s, h, hk, d, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    mk = lambda *shape: torch.randn(*shape, generator=g, device="cuda", dtype=torch.bfloat16)  # noqa: E731
+    return mk(b, s, h, d), mk(b, s, hk, d), mk(b, s, hk, d)
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("s,h,hk", [(2048, 4, 4), (4096, 8, 2)])
+def test_simulated_ring_matches_single_pass(world, s, h, hk):
+    import ring_attention as R
+    from flash_attn_interface import flash_attn_func
+
+    q, k, v = _inputs(2, s, h, hk, 128, 5)
+    out, lse = R.simulate_ring(q, k, v, world)
+    ref_o, ref_lse = flash_attn_func(q, k, v, causal=True, return_attn_probs=True)
+    # oracle on a slice (fp32), reference tolerance rule; and agreement with the single-pass kernel
+    oref, lref = A.attention_oracle(q[:1, :, :h // hk].cpu(), k[:1, :, :1].cpu(), v[:1, :, :1].cpu(), causal=True)
+    low, _ = A.attention_oracle(q[:1, :, :h // hk].cpu(), k[:1, :, :1].cpu(), v[:1, :, :1].cpu(), causal=True, upcast=False, reorder_ops=True)
+    err = (out[:1, :, :h // hk].float().cpu() - oref.float()).abs().max().item()
+    assert err <= A.fwd_tolerance(oref, low, 2.0), err
+    assert (out.float() - ref_o.float()).abs().max().item() <= 2e-2
+    assert torch.allclose(lse, ref_lse, atol=1e-4, rtol=1e-4)
+    assert torch.allclose(lse[:1, :h // hk].cpu(), lref, atol=1e-3, rtol=1e-3)
+
+
+def _nccl_worker(rank, world, port, q_out):
+    sys.path[:0] = [os.path.join(ROOT, "flash-attention-annotated_b200"), os.path.join(ROOT, "oracle")]
+    import torch.distributed as dist
+    import ring_attention as R
+    from flash_attn_interface import flash_attn_func
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        g = torch.Generator(device="cuda").manual_seed(77)  # same full problem on every rank
+        mk = lambda *shape: torch.randn(*shape, generator=g, device="cuda", dtype=torch.bfloat16)  # noqa: E731
+        q, k, v = mk(1, 8192, 8, 128), mk(1, 8192, 8, 128), mk(1, 8192, 8, 128)
+        out, lse = R.ring_flash_attn_func(R.zigzag_shard(q, rank, world), R.zigzag_shard(k, rank, world),
+                                          R.zigzag_shard(v, rank, world), causal=True, return_lse=True)
+        ref_o, ref_lse = flash_attn_func(q, k, v, causal=True, return_attn_probs=True)
+        err = (out.float() - R.zigzag_shard(ref_o, rank, world).float()).abs().max().item()
+        lerr = (lse - R.zigzag_shard(ref_lse, rank, world, dim=2)).abs().max().item()
+        torch.cuda.synchronize()
+        q_out.put((rank, err, lerr))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (run with gpurun --gpus 2)")
+def test_nccl_ring_two_gpus():
+    import torch.multiprocessing as mp
+
+    world = min(torch.cuda.device_count(), 4)
+    world = 2 if world < 4 else 4
+    ctx = mp.get_context("spawn")
+    q_out = ctx.Queue()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, 29871, q_out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q_out.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err, lerr in res:
+        assert err <= 2e-2 and lerr <= 1e-4, (rank, err, lerr)
