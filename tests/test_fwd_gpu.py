@@ -442,6 +442,33 @@ def test_c4_full_size(ragged):
         assert torch.allclose(outs[0][1], outs[ns][1], atol=1e-4, rtol=1e-4)
 
 
+def test_cuda_graph_decode_with_scheduler_metadata():
+    """hopper/test_flash_attn.py:879-929: get_scheduler_metadata + a CUDA-graph-captured decode call; the captured call
+    must follow cache_seqlens updated in place between replays (no host sync, no allocation inside the C ABI)."""
+    F = _iface()
+    g = torch.Generator().manual_seed(12)
+    b, h, hk, d, cap, ps = 4, 8, 2, 128, 2048, 256
+    kd, vd, table, kp, vp = A.paged_kvcache(cap, ps, b, hk, d, d, torch.bfloat16, generator=g)
+    q = torch.randn(b, 1, h, d, generator=g).to(torch.bfloat16)
+    lens = torch.tensor([100, 2048, 777, 1], dtype=torch.int32)
+    qd, kpd, vpd, td, ld = q.to(DEV), kp.to(DEV), vp.to(DEV), table.to(DEV), lens.to(DEV)
+    meta = F.get_scheduler_metadata(b, 1, cap, h, hk, d, ld, qkv_dtype=torch.bfloat16, page_size=ps, num_splits=4)
+    kw = dict(cache_seqlens=ld, page_table=td, scheduler_metadata=meta, num_splits=4, return_softmax_lse=True)
+    F.flash_attn_with_kvcache(qd, kpd, vpd, **kw)  # warm-up outside the capture (function attributes, tensor maps)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out, lse, *_ = F.flash_attn_with_kvcache(qd, kpd, vpd, **kw)
+    for new_lens in ([100, 2048, 777, 1], [2048, 5, 1300, 640]):
+        ld.copy_(torch.tensor(new_lens, dtype=torch.int32))
+        graph.replay()
+        torch.cuda.synchronize()
+        kl = torch.tensor(new_lens, dtype=torch.int32)
+        ref, lse_ref = A.attention_oracle(q, kd, vd, k_lens=kl)
+        low, _ = A.attention_oracle(q, kd, vd, k_lens=kl, upcast=False, reorder_ops=True)
+        _check(out, lse, ref, low, lse_ref)
+
+
 def test_unsupported_raises():
     F = _iface()
     q, k, v = (x.to(DEV) for x in _qkv(1, 64, 64, 2, 2, 256, torch.bfloat16))
