@@ -97,32 +97,41 @@ int make_plan(const Fa100Shape* s, Fa100Plan* out) {
   const int tiles = s->b * heads_work * m_blocks;
   int n_blocks = std::max(1, ceil_div(s->seqlen_k, 128));
   if ((s->is_causal || s->is_local) && s->seqlen_q > 1) n_blocks = std::max(1, std::min(n_blocks, ceil_div(s->seqlen_k, 128)));
+  // Dual-stream decode: when every item's query rows fit one 128-row tile, the CTA's two tile pipelines take alternate key
+  // blocks of the same rows and emit two partials per CTA-level split (fa100_fwd_roles.cuh make_geom<DUAL>), so the total
+  // number of partials is even.  A caller-forced odd num_splits keeps the single-stream kernel.
+  const bool dual_ok = s->seqlen_q <= pos_per_tile && n_blocks >= 2;
   int splits = s->num_splits;
+  bool dual = dual_ok && (splits <= 0 || splits % 2 == 0);
   if (splits <= 0) {
     // fill the machine: smallest split count whose wave efficiency is within 85% of the best one
     splits = 1;
-    if (tiles < 0.8f * num_sm && n_blocks > 1) {
-      const int max_splits = std::min({128, n_blocks, num_sm});
+    const int nb_cta = dual ? ceil_div(n_blocks, 2) : n_blocks;  // key blocks one pipeline walks per unit of split
+    if (tiles < 0.8f * num_sm && nb_cta > 1) {
+      const int max_splits = std::min({dual ? 64 : 128, nb_cta, num_sm});
       float best = 0.f;
       auto eff = [&](int sp) {
         const float waves = float(tiles) * sp / num_sm;
         // a split only helps if it really shortens the per-CTA chain of key blocks
-        const int per = ceil_div(n_blocks, sp);
-        if (sp > 1 && ceil_div(n_blocks, sp - 1) == per) return 0.f;
+        const int per = ceil_div(nb_cta, sp);
+        if (sp > 1 && ceil_div(nb_cta, sp - 1) == per) return 0.f;
         return waves / std::ceil(waves);
       };
       for (int sp = 1; sp <= max_splits; ++sp) best = std::max(best, eff(sp));
       for (int sp = 1; sp <= max_splits; ++sp)
         if (eff(sp) >= 0.85f * best) { splits = sp; break; }
     }
+    if (dual) splits *= 2;
   }
   splits = std::max(1, std::min(splits, 128));
+  const int cta_splits = dual ? splits / 2 : splits;
   out->block_m = rows_cta;
   out->block_n = 128;
   out->num_splits = splits;
   out->pack_gqa = pack;
   out->num_sm = num_sm;
-  out->num_work = tiles * splits;
+  out->num_work = tiles * cta_splits;
+  out->dual_stream = dual ? 1 : 0;  // dual-stream decode kernel (num_splits counts partials: two per CTA-level split)
   out->smem_bytes = 0;
   return FA100_OK;
 }

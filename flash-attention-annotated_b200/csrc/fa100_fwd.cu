@@ -9,11 +9,11 @@
 
 namespace fa100 {
 
-template <int HD, int ELT, bool FP8, bool F16>
+template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
 static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK,
                            const CUtensorMap& tmV, uint32_t fmt, int grid, cudaStream_t stream) {
   using L = FwdSmem<HD, ELT>;
-  auto kernel = fa100_fwd_kernel<HD, ELT, FP8, F16>;
+  auto kernel = fa100_fwd_kernel<HD, ELT, FP8, F16, DUAL>;
   static bool attr_set = false;  // benign race: the call is idempotent
   if (!attr_set) {
     FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes));
@@ -78,10 +78,12 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   kp.qheads_per_kv = G;
   kp.pack = plan->pack_gqa ? G : 1;
   kp.pos_per_tile = 128 / kp.pack;
-  kp.num_m_blocks = std::max(1, (p->seqlen_q + 2 * kp.pos_per_tile - 1) / (2 * kp.pos_per_tile));
+  const bool dual = plan->dual_stream != 0;  // two partials per CTA-level split (make_geom<DUAL>)
+  const int cta_splits = dual ? splits / 2 : splits;
+  kp.num_m_blocks = dual ? 1 : std::max(1, (p->seqlen_q + 2 * kp.pos_per_tile - 1) / (2 * kp.pos_per_tile));
   kp.heads_work = plan->pack_gqa ? p->h_k : p->h;
-  kp.num_splits = splits;
-  kp.num_work = kp.num_m_blocks * p->b * kp.heads_work * splits;
+  kp.num_splits = cta_splits;
+  kp.num_work = kp.num_m_blocks * p->b * kp.heads_work * cta_splits;
   // causal / local normalisation (hopper/flash_api.cpp:148-160, 796-805)
   int wl = p->window_left, wr = p->window_right;
   bool causal = p->is_causal != 0;
@@ -133,11 +135,13 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : (p->dtype == FA100_FP16 ? kFmtF16 : kFmtE4M3);
   const int hd = (p->d <= 64 && p->dv <= 64 && !fp8) ? 64 : 128;
   const bool f16 = p->dtype == FA100_FP16;
-  if (fp8) return launch_instance<128, 1, true, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
-  if (hd == 64) return f16 ? launch_instance<64, 2, false, true>(kp, tmQ, tmK, tmV, fmt, grid, stream)
-                           : launch_instance<64, 2, false, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
-  return f16 ? launch_instance<128, 2, false, true>(kp, tmQ, tmK, tmV, fmt, grid, stream)
-             : launch_instance<128, 2, false, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+#define FA_LAUNCH(HD_, ELT_, FP8_, F16_)                                                                      \
+  (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, fmt, grid, stream)                 \
+        : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, fmt, grid, stream))
+  if (fp8) return FA_LAUNCH(128, 1, true, false);
+  if (hd == 64) return f16 ? FA_LAUNCH(64, 2, false, true) : FA_LAUNCH(64, 2, false, false);
+  return f16 ? FA_LAUNCH(128, 2, false, true) : FA_LAUNCH(128, 2, false, false);
+#undef FA_LAUNCH
 }
 
 }  // namespace fa100

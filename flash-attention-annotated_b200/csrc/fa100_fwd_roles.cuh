@@ -13,18 +13,35 @@ struct WorkGeom {
   int hk;          // kv head
 };
 
+// DUAL (decode, all query rows of an item fit one 128-row tile): both TMEM tile pipelines work on the SAME rows and
+// split the item's key blocks between them -- tile 0 takes blocks n_hi-1, n_hi-3, ..., tile 1 takes n_hi-2, n_hi-4, ... --
+// and each writes its own fp32 partial (split index 2 * split + t) for the combine kernel.  Without it the second
+// pipeline idles and the per-block chain QK -> softmax -> PV (~3300 clk) is longer than the 64 KB block takes to
+// arrive from HBM (~2450 clk at 6.5 TB/s over 148 SMs).
+template <bool DUAL>
 FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w) {
   WorkGeom g;
   g.it = decode_work(p, w);
   g.seq = load_seq(p, g.it.bi);
   g.hk = p.pack > 1 ? g.it.head : g.it.head / p.qheads_per_kv;
   g.n_lo = 0x7fffffff; g.n_hi = 0;
+  if (DUAL) {
+    const TileRange r = tile_range(p, g.seq, g.it.m_blk * p.pos_per_tile, g.it.split);
+    g.tr[0] = r;
+    g.tr[1] = r;
+    g.tr[1].n_max = max(r.n_min, r.n_max - 1);
+    if (r.n_max > r.n_min) { g.n_lo = r.n_min; g.n_hi = r.n_max; }
+    return g;
+  }
 #pragma unroll
   for (int t = 0; t < kQTiles; ++t) {
     g.tr[t] = tile_range(p, g.seq, (g.it.m_blk * kQTiles + t) * p.pos_per_tile, g.it.split);
     if (g.tr[t].n_max > g.tr[t].n_min) { g.n_lo = min(g.n_lo, g.tr[t].n_min); g.n_hi = max(g.n_hi, g.tr[t].n_max); }
   }
   return g;
+}
+template <bool DUAL> FA_DEVICE int tile_pos0(const FwdKernelParams& p, const WorkItem& it, int t) {
+  return (DUAL ? it.m_blk : it.m_blk * kQTiles + t) * p.pos_per_tile;
 }
 FA_DEVICE bool tile_live(const WorkGeom& g, int t) { return g.tr[t].n_max > g.tr[t].n_min; }
 FA_DEVICE bool tile_uses(const WorkGeom& g, int t, int nb) { return nb >= g.tr[t].n_min && nb < g.tr[t].n_max; }
@@ -35,7 +52,7 @@ template <int STAGES> FA_DEVICE void ring_advance(RingState& r) { if (++r.stage 
 // ----------------------------------------------------------------------------- TMA producer
 // The whole warp walks the schedule (warp-uniform control flow keeps descriptors and coordinates in uniform
 // registers); one elected lane issues the bulk copies.
-template <int HD, int ELT>
+template <int HD, int ELT, bool DUAL>
 FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, const CUtensorMap* tmK,
                              const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar) {
   using L = FwdSmem<HD, ELT>;
@@ -47,13 +64,13 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   uint32_t q_it[kQTiles] = {0, 0};
   const uint32_t q_tx = uint32_t(HD * ELT) * p.pack * p.pos_per_tile;
   for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
-    const WorkGeom g = make_geom(p, w);
+    const WorkGeom g = make_geom<DUAL>(p, w);
     if (g.n_hi <= g.n_lo) continue;
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
       if (!tile_live(g, t)) continue;
       mbar_wait(&bar->q_empty[t], (q_it[t] & 1) ^ 1, 0x10 + t);
-      const int pos0 = (g.it.m_blk * kQTiles + t) * p.pos_per_tile;
+      const int pos0 = tile_pos0<DUAL>(p, g.it, t);
       if (elect_one()) {
         mbar_arrive_expect_tx(&bar->q_full[t], q_tx);
 #pragma unroll
@@ -64,37 +81,49 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
       __syncwarp();
       ++q_it[t];
     }
-    for (int nb = g.n_hi - 1; nb >= g.n_lo; --nb) {
+    // one K or V tile of key block nb into the next ring stage
+    auto load_tile = [&](int kv, int nb) {
+      const CUtensorMap* tm = kv == 0 ? tmK : tmV;
+      mbar_wait(&bar->kv_empty[ring.stage], ring.phase ^ 1, 0x20 + kv);
+      uint8_t* dst = sKV + ring.stage * L::kKVBytes;
+      if (p.page_size == 0) {
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
 #pragma unroll
-      for (int kv = 0; kv < 2; ++kv) {  // K tile then V tile of this key block
-        const CUtensorMap* tm = kv == 0 ? tmK : tmV;
-        mbar_wait(&bar->kv_empty[ring.stage], ring.phase ^ 1, 0x20 + kv);
-        uint8_t* dst = sKV + ring.stage * L::kKVBytes;
-        if (p.page_size == 0) {
+          for (int hb = 0; hb < kBoxesD; ++hb)
+            tma_load_4d(dst + hb * kHalfBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
+                        g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
+        }
+      } else {
+        // paged: kv_box_rows = min(128, page_size) rows per box; page ids come from the table
+        const int32_t* tbl = p.page_table + int64_t(g.it.bi) * p.page_table_batch_stride;
+        if (elect_one()) mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
+        for (int r0 = 0; r0 < kBlockN; r0 += p.kv_box_rows) {
+          const int row = nb * kBlockN + r0;
+          const int page = tbl[row / p.page_size];
           if (elect_one()) {
-            mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
 #pragma unroll
             for (int hb = 0; hb < kBoxesD; ++hb)
-              tma_load_4d(dst + hb * kHalfBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
-                          g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
-          }
-        } else {
-          // paged: kv_box_rows = min(128, page_size) rows per box; page ids come from the table
-          const int32_t* tbl = p.page_table + int64_t(g.it.bi) * p.page_table_batch_stride;
-          if (elect_one()) mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
-          for (int r0 = 0; r0 < kBlockN; r0 += p.kv_box_rows) {
-            const int row = nb * kBlockN + r0;
-            const int page = tbl[row / p.page_size];
-            if (elect_one()) {
-#pragma unroll
-              for (int hb = 0; hb < kBoxesD; ++hb)
-                tma_load_4d(dst + hb * kHalfBytes + r0 * kRowBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
-                            row % p.page_size, g.hk, page);
-            }
+              tma_load_4d(dst + hb * kHalfBytes + r0 * kRowBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
+                          row % p.page_size, g.hk, page);
           }
         }
-        __syncwarp();
-        ring_advance<L::kStages>(ring);
+      }
+      __syncwarp();
+      ring_advance<L::kStages>(ring);
+    };
+    if (!DUAL) {
+      // ring order == the order the MMA warp consumes: K(first), then V(nb), K(nb-1) per key block
+      for (int nb = g.n_hi - 1; nb >= g.n_lo; --nb) { load_tile(0, nb); load_tile(1, nb); }
+    } else {
+      // two interleaved streams: K of both tiles' first blocks, then per step V_0, K_0(next), V_1, K_1(next)
+      load_tile(0, g.n_hi - 1);
+      if (g.n_hi - 2 >= g.n_lo) load_tile(0, g.n_hi - 2);
+      for (int nb = g.n_hi - 1; nb >= g.n_lo; nb -= 2) {
+        load_tile(1, nb);
+        if (nb - 2 >= g.n_lo) load_tile(0, nb - 2);
+        if (nb - 1 >= g.n_lo) load_tile(1, nb - 1);
+        if (nb - 3 >= g.n_lo) load_tile(0, nb - 3);
       }
     }
   }
@@ -111,7 +140,7 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
 //
 // One warp issues everything in a fixed order per key block nb: QK_0(nb-1), PV_0(nb), QK_1(nb-1), PV_1(nb).  All 32
 // lanes run the control flow and the barrier waits (descriptors stay in uniform registers); one elected lane issues.
-template <int HD, int ELT, bool FP8>
+template <int HD, int ELT, bool FP8, bool DUAL>
 FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar, uint32_t tmem) {
   using L = FwdSmem<HD, ELT>;
   constexpr int kHalfBytes = kBlockN * 128;
@@ -204,7 +233,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
     int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi;
     {
-      const WorkGeom g = make_geom(p, w);
+      const WorkGeom g = make_geom<DUAL>(p, w);
       n_lo = g.n_lo; n_hi = g.n_hi;
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) { n_min[t] = g.tr[t].n_min; n_max[t] = g.tr[t].n_max; }
@@ -213,6 +242,50 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t)
       if (n_max[t] > n_min[t]) mbar_wait(&bar->q_full[t], q_it[t] & 1, 0x30 + t);
+    if constexpr (DUAL) {
+      // tile t walks blocks n_max[t]-1, n_max[t]-3, ... ; ring order K_0, K_1, then per step V_0, K_0(next), V_1, K_1(next)
+      int left[kQTiles];  // key blocks tile t still has to score
+#pragma unroll
+      for (int t = 0; t < kQTiles; ++t) left[t] = (n_max[t] - n_min[t] + 1) / 2;
+#pragma unroll
+      for (int t = 0; t < kQTiles; ++t)
+        if (left[t] > 0) {
+          mbar_wait(&bar->kv_full[ring.stage], ring.phase, 0x40);
+          qk_op(t, ring.stage, left[t] == 1, [&]() {});
+          if (left[t] == 1) ++q_it[t];
+          if (elect_one()) tc_commit(&bar->kv_empty[ring.stage]);
+          __syncwarp();
+          ring_advance<L::kStages>(ring);
+          --left[t];
+        }
+      const int steps = (n_hi - n_lo + 1) / 2;  // tile 0 never has fewer blocks than tile 1
+      for (int j = 0; j < steps; ++j) {
+#pragma unroll
+        for (int t = 0; t < kQTiles; ++t) {
+          const int nb = n_max[t] - 1 - 2 * j;
+          if (nb < n_min[t]) continue;
+          const RingState rv = ring;
+          ring_advance<L::kStages>(ring);
+          FA_PROF(4);
+          mbar_wait(&bar->kv_full[rv.stage], rv.phase, 0x41);
+          if (left[t] > 0) {
+            const RingState rk = ring;
+            ring_advance<L::kStages>(ring);
+            mbar_wait(&bar->kv_full[rk.stage], rk.phase, 0x42);
+            FA_PROF(0);
+            qk_op(t, rk.stage, left[t] == 1, [&]() { rdy_p[t] = mbar_try_wait(&bar->p_full[t], p_it[t] & 1); });
+            if (left[t] == 1) ++q_it[t];
+            if (elect_one()) tc_commit(&bar->kv_empty[rk.stage]);
+            __syncwarp();
+            --left[t];
+          }
+          pv_op(t, rv.stage, j == 0, nb - 2 < n_min[t], [&]() { poll_sfree(); });
+          if (elect_one()) tc_commit(&bar->kv_empty[rv.stage]);
+          __syncwarp();
+        }
+      }
+      continue;
+    }
     // prologue: scores of the first (right-most) key block of the work item
     {
       mbar_wait(&bar->kv_full[ring.stage], ring.phase, 0x40);

@@ -25,13 +25,13 @@ struct RowGeom {
   bool has_rows;
 };
 
-template <bool FP8>
+template <bool FP8, bool DUAL>
 FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row) {
-  const WorkGeom g = make_geom(p, w);
+  const WorkGeom g = make_geom<DUAL>(p, w);
   RowGeom r;
   r.has_rows = g.tr[t].has_rows;
   r.n_min = g.tr[t].n_min; r.n_max = g.tr[t].n_max;
-  const int pos = (g.it.m_blk * kQTiles + t) * p.pos_per_tile + (p.pack > 1 ? row / p.pack : row);
+  const int pos = tile_pos0<DUAL>(p, g.it, t) + (p.pack > 1 ? row / p.pack : row);
   const int shift = g.seq.sk - g.seq.sq;
   int col_hi = g.seq.sk, col_lo = 0;
   if (p.is_causal) col_hi = min(col_hi, pos + 1 + shift);
@@ -59,7 +59,7 @@ FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row) {
 // on Q tile t = w / 4 and owns TMEM lanes (= query rows) 32*(w%4)..; one thread owns one row, so the row max and the
 // row sum need no shuffles.  The step loop has two bodies: a lean one for interior key blocks (no mask, no softcap; it
 // is the instruction stream tools/ubench/ubench_softmax.cu measures in isolation) and a general one for boundary blocks.
-template <int HD, int ELT, bool FP8, bool F16>
+template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
 FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t tmem, int warp, int lane) {
   const int t = warp >> 2, q = warp & 3;
   const int row = q * 32 + lane;
@@ -70,12 +70,12 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
   FA_PROF_DECL();  // 0 s_full wait, 1 S load, 2 s_free + mask + row max, 3 rescale, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait + publish, 7 rest
 
   for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
-    const RowGeom rg = row_geom<FP8>(p, w, t, row);
+    const RowGeom rg = row_geom<FP8, DUAL>(p, w, t, row);
     if (!rg.has_rows) continue;
     const float scale_log2 = rg.scale_log2;
     const bool softcap = p.softcap_pre != 0.f;
     float m_run = -INFINITY, l_run = 0.f;
-    for (int nb = rg.n_max - 1; nb >= rg.n_min; --nb) {
+    for (int nb = rg.n_max - 1; nb >= rg.n_min; nb -= (DUAL ? 2 : 1)) {
       FA_PROF(7);
       mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
       FA_PROF(0);
@@ -192,11 +192,12 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
 
     // ---- epilogue: O / rowsum, LSE (hopper/softmax.h:137-155, epilogue_fwd.hpp:215-481); geometry is recomputed here
     {
-      const WorkGeom g = make_geom(p, w);
+      const WorkGeom g = make_geom<DUAL>(p, w);
       const bool split = p.o_accum != nullptr;  // fp32 partials (split-KV, or one hop of ring attention)
+      const int part = DUAL ? g.it.split * 2 + t : g.it.split;  // index of this partial
       const bool live = rg.n_max > rg.n_min;
       const int in_tile = p.pack > 1 ? row / p.pack : row;
-      const int pos = (g.it.m_blk * kQTiles + t) * p.pos_per_tile + in_tile;
+      const int pos = tile_pos0<DUAL>(p, g.it, t) + in_tile;
       const int hq = p.pack > 1 ? g.it.head * p.qheads_per_kv + row % p.pack : g.it.head;
       const bool row_valid = in_tile < p.pos_per_tile && pos < g.seq.sq;
       float out_scale = 1.0f;
@@ -209,12 +210,12 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       const int64_t row_idx = g.seq.q_off + pos;
       if (row_valid) {
         if (!split) p.lse[g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + row_idx] = lse_val;
-        else p.lse_accum[g.it.split * p.lseacc_split_stride + g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + row_idx] = lse_val;
+        else p.lse_accum[part * p.lseacc_split_stride + g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + row_idx] = lse_val;
       }
       if (live) { mbar_wait(&bar->o_full[t], o_it & 1, 0x80 + t); ++o_it; tc_fence_after(); }
       uint4* o16 = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.o) + g.seq.bq * p.o_batch_stride +
                                             row_idx * p.o_row_stride + hq * p.o_head_stride);
-      float4* o32 = reinterpret_cast<float4*>(p.o_accum + g.it.split * p.oacc_split_stride + g.it.bi * p.oacc_batch_stride +
+      float4* o32 = reinterpret_cast<float4*>(p.o_accum + part * p.oacc_split_stride + g.it.bi * p.oacc_batch_stride +
                                               hq * p.oacc_head_stride + row_idx * p.dv);
 #pragma unroll
       for (int c = 0; c < HD / 32; ++c) {
@@ -261,7 +262,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
 }
 
 // ----------------------------------------------------------------------------- kernel entry
-template <int HD, int ELT, bool FP8, bool F16>
+template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
 __global__ void __launch_bounds__(kThreads, 1)
 fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constant__ CUtensorMap tmQ,
                  const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
@@ -295,11 +296,11 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
   // register pool at launch: 384 threads x 168; warps 8-11 give 112 each to the 8 softmax warps (+56 each)
   if (warp < kSoftmaxWarps) {
     setmaxnreg_inc<224>();
-    softmax_role<HD, ELT, FP8, F16>(p, bar, tmem, warp, lane);
+    softmax_role<HD, ELT, FP8, F16, DUAL>(p, bar, tmem, warp, lane);
   } else {
     setmaxnreg_dec<56>();
-    if (warp == kMmaWarp) mma_role<HD, ELT, FP8>(p, fmt, sQ, sKV, bar, tmem);
-    if (warp == kLoadWarp) producer_role<HD, ELT>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar);
+    if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL>(p, fmt, sQ, sKV, bar, tmem);
+    if (warp == kLoadWarp) producer_role<HD, ELT, DUAL>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar);
   }
   FA_TRACE_END();
   tc_fence_before();

@@ -65,8 +65,8 @@ class Shape(C.Structure):
 
 
 class Plan(C.Structure):
-    _fields_ = [(n, i32) for n in ("block_m", "block_n", "num_splits", "pack_gqa", "num_sm", "num_work", "smem_bytes")] + [
-        ("reserved", i32 * 9)]
+    _fields_ = [(n, i32) for n in ("block_m", "block_n", "num_splits", "pack_gqa", "num_sm", "num_work", "smem_bytes",
+                                   "dual_stream")] + [("reserved", i32 * 8)]
 
 
 EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_debug_hang_info",

@@ -164,7 +164,8 @@ typedef struct Fa100Plan {
   int32_t num_sm;
   int32_t num_work;     /* CTA work items the forward kernel will iterate */
   int32_t smem_bytes;
-  int32_t reserved[9];
+  int32_t dual_stream;  /* 1: decode kernel whose two tile pipelines split the key blocks; num_splits (even) counts partials */
+  int32_t reserved[8];
 } Fa100Plan;
 
 int fa100_abi_version(void);
