@@ -6,9 +6,10 @@
 //
 //   warps 0-3   softmax for Q tile 0: one thread == one query row == one TMEM lane (row max / sum without shuffles)
 //   warps 4-7   softmax for Q tile 1
-//   warp  8     MMA issuer (elected lane): S_t = Q_t K^T (SS form), O_t += P_t V (TS form, P in TMEM)
+//   warp  8     QK issuer (elected lane): S = Q_t K^T (SS form) into the score buffer the two tiles share
 //   warp  9     TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
-//   warps 10,11 idle (complete the third warpgroup for setmaxnreg: softmax warps run with 224 registers, the rest 56)
+//   warp  10    PV issuer (elected lane): O_t += P_t V (TS form, P in TMEM)
+//   warp  11    idle (completes the third warpgroup for setmaxnreg: softmax warps run with 224 registers, the rest 56)
 //
 // TMEM (512 columns): S0 @0, S1 @128, O0 @256, O1 @384; P_t (16-bit) overwrites columns [0,64) of S_t.
 // Two 128-row Q tiles per CTA ping-pong through the tensor pipe: while the softmax warps turn S_t into P_t the
@@ -26,6 +27,7 @@ constexpr int kQTiles = 2;     // Q tiles per CTA
 constexpr int kSoftmaxWarps = 8;
 constexpr int kMmaWarp = 8;
 constexpr int kLoadWarp = 9;
+constexpr int kPvWarp = 10;
 constexpr int kThreads = 12 * 32;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -175,6 +177,7 @@ struct FwdBarriers {
   uint64_t o_full[kQTiles], o_empty[kQTiles];
   uint64_t kv_full[8], kv_empty[8];
   uint32_t tmem_base;
+  uint32_t ts[8];  // latency-probe timestamps of the profiling build (0,1: QK_t issued; 2: s_free arrive; 4,5: p_full[t] arrive)
   uint32_t pad_[3];
 };
 static_assert(sizeof(FwdBarriers) <= 1024 - 128, "barrier block outgrew its slot");

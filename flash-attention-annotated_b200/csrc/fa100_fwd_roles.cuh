@@ -129,18 +129,22 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   }
 }
 
-// ----------------------------------------------------------------------------- MMA issuer
+// ----------------------------------------------------------------------------- MMA issuers
 // TMEM columns: S @0 (one score buffer shared by both Q tiles), P_0 @128, P_1 @192 (operand dtype), O_0 @256, O_1 @384.
 //
 // The two Q tiles take turns in the single S buffer.  A softmax warpgroup copies its scores into registers right after
-// s_full[t] and arrives on s_free; from then on S belongs to the other tile, so S_t(next) = Q_t K^T no longer waits for
-// P_t V to drain (with P overlaid on a per-tile S the chain S -> softmax -> PV -> QK -> S bounded the key-block period
-// at ~3400 clk; here QK of one tile runs under the exponentials of both).  P_t has its own columns; pv_done[t] tells
-// the softmax warps that P_t (and O_t, for the rare rescale) may be touched again.
+// s_full[t] and arrives on s_free; from then on S belongs to the other tile, so S_t(next) = Q_t K^T never waits for
+// P_t V.  P_t has its own columns; pv_done[t] tells the softmax warps that P_t (and O_t, for the rare rescale) may be
+// touched again.
 //
-// One warp issues everything in a fixed order per key block nb: QK_0(nb-1), PV_0(nb), QK_1(nb-1), PV_1(nb).  All 32
-// lanes run the control flow and the barrier waits (descriptors stay in uniform registers); one elected lane issues.
-template <int HD, int ELT, bool FP8, bool DUAL>
+// Two warps feed the tensor pipe: the QK warp issues S = Q_t K^T (SS form) and owns the K stages of the ring, the PV
+// warp issues O_t += P_t V (TS form, P in TMEM) and owns the V stages.  With a single issuing warp every barrier it
+// polls (~110 clk even when complete) and every hand-off it waits for leaves the pipe idle -- measured 500 clk of
+// 1520 per half key-block period; with two, one warp's waiting overlaps the other's issuing.  Both warps walk the
+// same ring sequence (kIsQK selects which stages a warp acts on): K(first), then V(nb), K(nb-1) per key block, or in
+// DUAL mode K_0, K_1, then V_0, K_0(next), V_1, K_1(next) per step.  All 32 lanes run the control flow and the waits
+// (descriptors stay in uniform registers); one elected lane issues.
+template <int HD, int ELT, bool FP8, bool DUAL, bool kIsQK>
 FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar, uint32_t tmem) {
   using L = FwdSmem<HD, ELT>;
   constexpr int kHalfBytes = kBlockN * 128;
@@ -149,8 +153,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   constexpr int kSlicesPerBox = kColsPerBox / kKPerMma;       // 4
   constexpr int kQKSlices = HD / kKPerMma;
   constexpr int kPVSlices = kBlockN / kKPerMma;
-  const uint32_t idesc_qk = make_idesc(fmt, fmt, kBlockM, kBlockN, 0, 0);
-  const uint32_t idesc_pv = make_idesc(fmt, fmt, kBlockM, HD, 0, 1);
+  const uint32_t idesc = kIsQK ? make_idesc(fmt, fmt, kBlockM, kBlockN, 0, 0) : make_idesc(fmt, fmt, kBlockM, HD, 0, 1);
   // K-major operand tiles [128 rows][128 B] SW128: 8-row groups 1024 B apart (SBO); LBO unused (1).
   // V as MN-major B operand: 128-byte rows along dv, 8 key rows per swizzle atom (SBO = 1024 B), the next
   // 64 (16-bit) / 128 (8-bit) dv columns in the next box (LBO = one [128][128 B] region).
@@ -162,72 +165,62 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   RingState ring;
   uint32_t q_it[kQTiles] = {0, 0}, p_it[kQTiles] = {0, 0}, o_it[kQTiles] = {0, 0};
   uint32_t qk_n = 0;  // QK batches issued so far == phases of s_free consumed + 1
-  // An mbarrier poll costs ~110 clk even when the phase is long complete, and this warp is the only feeder of the
-  // tensor pipe.  Every batch therefore polls the barrier of the NEXT batch after issuing all but its last two MMAs
-  // (the pipe still has queued work to cover the poll) and the next batch blocks only if that poll failed.
-  bool rdy_sfree = false, rdy_p[kQTiles] = {false, false}, rdy_kv_v = false, rdy_kv_k = false;
   FA_PROF_DECL();     // 0 kv_full waits, 1 s_free waits, 2 p_full / o_empty waits, 3 issue, 4 everything else
 
-  auto poll_sfree = [&]() { rdy_sfree = qk_n == 0 || mbar_try_wait(&bar->s_free, (qk_n - 1) & 1); };
-
   // S = Q_t K(stage)^T once the previous owner of S has taken its scores
-  auto qk_op = [&](int t, int stage, bool last_use_of_q, auto&& poll_next) {
-    if (!rdy_sfree && qk_n > 0) mbar_wait(&bar->s_free, (qk_n - 1) & 1, 0x48 + t);
-    rdy_sfree = false;
+  auto qk_op = [&](int t, int stage, bool last_use_of_q) {
+    if (qk_n > 0) mbar_wait(&bar->s_free, (qk_n - 1) & 1, 0x48 + t);
     ++qk_n;
     tc_fence_after();
     FA_PROF(1);
-    const uint32_t a_lo = q_lo + t * (L::kQBytes >> 4);
-    const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboK;
-    auto mma = [&](int ks) {
-      const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
-      mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc_qk, ks > 0);
-    };
-    constexpr int kHead = kQKSlices > 2 ? kQKSlices - 2 : 0;
     if (elect_one()) {
+      const uint32_t a_lo = q_lo + t * (L::kQBytes >> 4);
+      const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboK;
 #pragma unroll
-      for (int ks = 0; ks < kHead; ++ks) mma(ks);
-    }
-    __syncwarp();
-    poll_next();
-    if (elect_one()) {
-#pragma unroll
-      for (int ks = kHead; ks < kQKSlices; ++ks) mma(ks);
+      for (int ks = 0; ks < kQKSlices; ++ks) {
+        const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
+        mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
+      }
       tc_commit(&bar->s_full[t]);
       if (last_use_of_q) tc_commit(&bar->q_empty[t]);
+      FA_LAT_STAMP(&bar->ts[t]);
     }
     __syncwarp();
     FA_PROF(3);
   };
-
   // O_t (+)= P_t V(stage)
-  auto pv_op = [&](int t, int stage, bool first, bool last, auto&& poll_next) {
+  auto pv_op = [&](int t, int stage, bool first, bool last) {
     if (first) mbar_wait(&bar->o_empty[t], (o_it[t] & 1) ^ 1, 0x50 + t);  // epilogue of the previous work item
-    if (!rdy_p[t]) mbar_wait(&bar->p_full[t], p_it[t] & 1, 0x60 + t);
-    rdy_p[t] = false;
+    mbar_wait(&bar->p_full[t], p_it[t] & 1, 0x60 + t);
     ++p_it[t];
     tc_fence_after();
     FA_PROF(2);
-    const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboV;
-    auto mma = [&](int ks) {
-      mma_ts<FP8>(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc_pv, (!first || ks > 0));
-    };
-    constexpr int kHead = kPVSlices > 2 ? kPVSlices - 2 : 0;
+    FA_LAT_ACC(6, &bar->ts[4 + t]);
     if (elect_one()) {
+      const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboV;
 #pragma unroll
-      for (int ks = 0; ks < kHead; ++ks) mma(ks);
-    }
-    __syncwarp();
-    poll_next();
-    if (elect_one()) {
-#pragma unroll
-      for (int ks = kHead; ks < kPVSlices; ++ks) mma(ks);
+      for (int ks = 0; ks < kPVSlices; ++ks)
+        mma_ts<FP8>(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc, (!first || ks > 0));
       tc_commit(&bar->pv_done[t]);
       if (last) tc_commit(&bar->o_full[t]);
     }
     __syncwarp();
     FA_PROF(3);
     if (last) ++o_it[t];
+  };
+  // take the next ring stage if it is this warp's kind (K for the QK warp, V for the PV warp); returns its index or -1
+  auto next_stage = [&](bool is_k) {
+    const RingState r = ring;
+    ring_advance<L::kStages>(ring);
+    if (is_k != kIsQK) return -1;
+    FA_PROF(4);
+    mbar_wait(&bar->kv_full[r.stage], r.phase, is_k ? 0x42 : 0x41);
+    FA_PROF(0);
+    return r.stage;
+  };
+  auto release = [&](int stage) {
+    if (elect_one()) tc_commit(&bar->kv_empty[stage]);
+    __syncwarp();
   };
 
   for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
@@ -239,23 +232,21 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
       for (int t = 0; t < kQTiles; ++t) { n_min[t] = g.tr[t].n_min; n_max[t] = g.tr[t].n_max; }
     }
     if (n_hi <= n_lo) continue;
+    if (kIsQK) {
 #pragma unroll
-    for (int t = 0; t < kQTiles; ++t)
-      if (n_max[t] > n_min[t]) mbar_wait(&bar->q_full[t], q_it[t] & 1, 0x30 + t);
+      for (int t = 0; t < kQTiles; ++t)
+        if (n_max[t] > n_min[t]) { mbar_wait(&bar->q_full[t], q_it[t] & 1, 0x30 + t); ++q_it[t]; }
+    }
     if constexpr (DUAL) {
-      // tile t walks blocks n_max[t]-1, n_max[t]-3, ... ; ring order K_0, K_1, then per step V_0, K_0(next), V_1, K_1(next)
+      // tile t walks blocks n_max[t]-1, n_max[t]-3, ...
       int left[kQTiles];  // key blocks tile t still has to score
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) left[t] = (n_max[t] - n_min[t] + 1) / 2;
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t)
         if (left[t] > 0) {
-          mbar_wait(&bar->kv_full[ring.stage], ring.phase, 0x40);
-          qk_op(t, ring.stage, left[t] == 1, [&]() {});
-          if (left[t] == 1) ++q_it[t];
-          if (elect_one()) tc_commit(&bar->kv_empty[ring.stage]);
-          __syncwarp();
-          ring_advance<L::kStages>(ring);
+          const int sk = next_stage(true);
+          if (kIsQK) { qk_op(t, sk, left[t] == 1); release(sk); }
           --left[t];
         }
       const int steps = (n_hi - n_lo + 1) / 2;  // tile 0 never has fewer blocks than tile 1
@@ -264,88 +255,44 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
         for (int t = 0; t < kQTiles; ++t) {
           const int nb = n_max[t] - 1 - 2 * j;
           if (nb < n_min[t]) continue;
-          const RingState rv = ring;
-          ring_advance<L::kStages>(ring);
-          FA_PROF(4);
-          mbar_wait(&bar->kv_full[rv.stage], rv.phase, 0x41);
+          const int sv = next_stage(false);
           if (left[t] > 0) {
-            const RingState rk = ring;
-            ring_advance<L::kStages>(ring);
-            mbar_wait(&bar->kv_full[rk.stage], rk.phase, 0x42);
-            FA_PROF(0);
-            qk_op(t, rk.stage, left[t] == 1, [&]() { rdy_p[t] = mbar_try_wait(&bar->p_full[t], p_it[t] & 1); });
-            if (left[t] == 1) ++q_it[t];
-            if (elect_one()) tc_commit(&bar->kv_empty[rk.stage]);
-            __syncwarp();
+            const int sk = next_stage(true);
+            if (kIsQK) { qk_op(t, sk, left[t] == 1); release(sk); }
             --left[t];
           }
-          pv_op(t, rv.stage, j == 0, nb - 2 < n_min[t], [&]() { poll_sfree(); });
-          if (elect_one()) tc_commit(&bar->kv_empty[rv.stage]);
-          __syncwarp();
+          if (!kIsQK) { pv_op(t, sv, j == 0, nb - 2 < n_min[t]); release(sv); }
         }
       }
-      continue;
-    }
-    // prologue: scores of the first (right-most) key block of the work item
-    {
-      mbar_wait(&bar->kv_full[ring.stage], ring.phase, 0x40);
-      const int nb = n_hi - 1;
+    } else {
+      {  // scores of the first (right-most) key block of the work item
+        const int sk = next_stage(true);
+        const int nb = n_hi - 1;
+        if (kIsQK) {
 #pragma unroll
-      for (int t = 0; t < kQTiles; ++t)
-        if (nb >= n_min[t] && nb < n_max[t]) {
-          qk_op(t, ring.stage, n_min[t] == nb, [&]() {});
-          if (n_min[t] == nb) ++q_it[t];
+          for (int t = 0; t < kQTiles; ++t)
+            if (nb >= n_min[t] && nb < n_max[t]) qk_op(t, sk, n_min[t] == nb);
+          release(sk);
         }
-      if (elect_one()) tc_commit(&bar->kv_empty[ring.stage]);
-      __syncwarp();
-      ring_advance<L::kStages>(ring);
-    }
-    rdy_kv_v = rdy_kv_k = false;
-    for (int nb = n_hi - 1; nb >= n_lo; --nb) {
-      const RingState rv = ring;  // V(nb)
-      ring_advance<L::kStages>(ring);
-      const RingState rk = ring;  // K(nb-1)
-      const bool has_next = nb - 1 >= n_lo;
-      FA_PROF(4);
-      if (!rdy_kv_v) mbar_wait(&bar->kv_full[rv.stage], rv.phase, 0x41);
-      if (has_next) {
-        if (!rdy_kv_k) mbar_wait(&bar->kv_full[rk.stage], rk.phase, 0x42);
-        ring_advance<L::kStages>(ring);
       }
-      rdy_kv_v = rdy_kv_k = false;
-      FA_PROF(0);
-      bool use_pv[kQTiles], use_qk[kQTiles];
+      for (int nb = n_hi - 1; nb >= n_lo; --nb) {
+        const bool has_next = nb - 1 >= n_lo;
+        const int sv = next_stage(false);
+        const int sk = has_next ? next_stage(true) : -1;
+        if (kIsQK) {
+          if (has_next) {
 #pragma unroll
-      for (int t = 0; t < kQTiles; ++t) {
-        use_pv[t] = nb >= n_min[t] && nb < n_max[t];
-        use_qk[t] = has_next && nb - 1 >= n_min[t] && nb - 1 < n_max[t];
-      }
+            for (int t = 0; t < kQTiles; ++t)
+              if (nb - 1 >= n_min[t] && nb - 1 < n_max[t]) qk_op(t, sk, n_min[t] == nb - 1);
+            release(sk);
+          }
+        } else {
 #pragma unroll
-      for (int t = 0; t < kQTiles; ++t) {
-        if (use_qk[t]) {
-          // next in line: P_t V(nb)
-          qk_op(t, rk.stage, n_min[t] == nb - 1, [&]() { if (use_pv[t]) rdy_p[t] = mbar_try_wait(&bar->p_full[t], p_it[t] & 1); });
-          if (n_min[t] == nb - 1) ++q_it[t];
-        }
-        if (use_pv[t]) {
-          pv_op(t, rv.stage, nb == n_max[t] - 1, nb == n_min[t], [&]() {
-            poll_sfree();  // next in line: the other tile's QK, or the next key block's
-            if (t == kQTiles - 1 && has_next) {
-              rdy_kv_v = mbar_try_wait(&bar->kv_full[ring.stage], ring.phase);
-              if (nb - 2 >= n_lo) {
-                RingState r2 = ring;
-                ring_advance<L::kStages>(r2);
-                rdy_kv_k = mbar_try_wait(&bar->kv_full[r2.stage], r2.phase);
-              }
-            }
-          });
+          for (int t = 0; t < kQTiles; ++t)
+            if (nb >= n_min[t] && nb < n_max[t]) pv_op(t, sv, nb == n_max[t] - 1, nb == n_min[t]);
+          release(sv);
         }
       }
-      if (elect_one()) {
-        tc_commit(&bar->kv_empty[rv.stage]);
-        if (has_next) tc_commit(&bar->kv_empty[rk.stage]);
-      }
-      __syncwarp();
     }
   }
   FA_PROF(4);

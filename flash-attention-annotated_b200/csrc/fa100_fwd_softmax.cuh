@@ -79,6 +79,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       FA_PROF(7);
       mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
       FA_PROF(0);
+      FA_LAT_ACC(3, &bar->ts[t]);
       ++s_it;
       tc_fence_after();
       uint32_t s[4][32];
@@ -90,6 +91,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar->s_free);
+      if (q == 3) FA_LAT_STAMP(&bar->ts[2]);
       FA_TRACE_POINT(0xC4);
       // P_t and O_t may be touched again once the previous P_t V has drained; poll now, block only right before the
       // first write (normally long complete by then)
@@ -140,7 +142,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
         }
       }
       const float m_sub = (m_run == -INFINITY) ? 0.f : m_run * scale_log2 - (FP8 ? 8.0f : 0.0f);
-      FA_PROF(3);
+      FA_PROF(2);
       // P = exp2(S * scale - max), packed to the operand dtype and written over S: keys [32c, 32c + 32) of the tile go to
       // columns [16c, +16) (16-bit operands) or [8c, +8) (e4m3)
       float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
@@ -184,6 +186,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar->p_full[t]);
+      if (q == 3) FA_LAT_STAMP(&bar->ts[4 + t]);
       FA_TRACE_POINT(0xA0 + t);
       ++pv_n;
       FA_PROF(6);
@@ -299,7 +302,8 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
     softmax_role<HD, ELT, FP8, F16, DUAL>(p, bar, tmem, warp, lane);
   } else {
     setmaxnreg_dec<56>();
-    if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL>(p, fmt, sQ, sKV, bar, tmem);
+    if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL, true>(p, fmt, sQ, sKV, bar, tmem);
+    if (warp == kPvWarp) mma_role<HD, ELT, FP8, DUAL, false>(p, fmt, sQ, sKV, bar, tmem);
     if (warp == kLoadWarp) producer_role<HD, ELT, DUAL>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar);
   }
   FA_TRACE_END();

@@ -110,11 +110,16 @@ FA_DEVICE void trace_emit(int tag, long long tb, long long te) {
 static __device__ unsigned int g_fa100_prof[kTraceWarps * 8];
 #define FA_PROF_DECL() uint32_t prof_[8] = {0, 0, 0, 0, 0, 0, 0, 0}; uint32_t prof_t_ = clock()
 #define FA_PROF(i) do { const uint32_t n_ = clock(); prof_[i] += n_ - prof_t_; prof_t_ = n_; } while (0)
+// latency probes: one role stamps the SM clock into shared memory, another charges "now - stamp" to a bucket
+#define FA_LAT_STAMP(word) do { *reinterpret_cast<volatile uint32_t*>(word) = clock(); } while (0)
+#define FA_LAT_ACC(i, word) do { prof_[i] += clock() - *reinterpret_cast<volatile uint32_t*>(word); } while (0)
 #define FA_PROF_FLUSH() do { if (trace_on()) { for (int i_ = 0; i_ < 8; ++i_) g_fa100_prof[(threadIdx.x >> 5) * 8 + i_] = prof_[i_]; } } while (0)
 #else
 #define FA_PROF_DECL() do { } while (0)
 #define FA_PROF(i) do { } while (0)
 #define FA_PROF_FLUSH() do { } while (0)
+#define FA_LAT_STAMP(word) do { } while (0)
+#define FA_LAT_ACC(i, word) do { } while (0)
 #define FA_TRACE_POINT(tag) do { } while (0)
 #define FA_TRACE_BEGIN() do { } while (0)
 #define FA_TRACE_END() do { } while (0)

@@ -8,7 +8,11 @@ import torch
 import fa100_native as N
 from flash_attn_interface import flash_attn_func
 
-b, s, h, hk, d = 1, 8192, 16, 4, 128
+def _arg(name, default):
+    return int(sys.argv[sys.argv.index(name) + 1]) if name in sys.argv else default
+
+
+b, s, h, hk, d = _arg("--b", 1), _arg("--s", 8192), _arg("--h", 16), _arg("--hk", 4), 128
 causal = "--noncausal" not in sys.argv
 dt = torch.float8_e4m3fn if "--fp8" in sys.argv else torch.bfloat16
 q = torch.randn(b, s, h, d, device="cuda", dtype=torch.bfloat16).to(dt)
@@ -20,8 +24,8 @@ ev = N.trace()
 print("events", len(ev), "hang", N.hang_info())
 pr = N.prof()
 if pr:
-    print("cycle buckets per warp (softmax: 0 s_full wait, 1 S load, 2 s_free+mask+max, 3 rescale, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait+publish, 7 rest;"
-          " mma: 0 kv_full, 1 s_free, 2 p_full/o_empty, 3 issue, 4 rest)")
+    print("cycle buckets per warp (softmax: 0 s_full wait, 1 S load, 2 s_free+mask+max+rescale, 3 LAT QK issued->S seen, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait+publish, 7 rest;"
+          " mma: 0 kv_full, 1 s_free, 2 p_full/o_empty, 3 issue, 4 rest, 5 LAT s_free arrive->QK start, 6 LAT p_full arrive->PV start)")
     for w_, b_ in enumerate(pr):
         tot = sum(b_) or 1
         print(f"  warp {w_:2d}: " + " ".join(f"{x:9d}({100 * x / tot:4.1f}%)" for x in b_))
