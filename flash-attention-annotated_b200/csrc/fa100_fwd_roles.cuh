@@ -60,7 +60,11 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   constexpr int kColsPerBox = kRowBytes / ELT;         // 64 (16-bit) or 128 (8-bit)
   constexpr int kBoxesD = HD / kColsPerBox > 0 ? HD / kColsPerBox : 1;  // boxes along the head dim
   constexpr int kHalfBytes = kBlockN * kRowBytes;      // one [128 rows][128 B] region
-  RingState ring;
+  // K tiles cycle through the first half of the stages, V tiles through the second half: every stage (and its pair of
+  // mbarriers) then has exactly one consumer warp.  With one mixed ring the kind of tile a stage holds changes from fill
+  // to fill in DUAL mode, a warp that only watches "its" fills skips phases of the barrier, and the parity test aliases.
+  constexpr int kRing = L::kStages / 2;
+  RingState rings[2];
   uint32_t q_it[kQTiles] = {0, 0};
   const uint32_t q_tx = uint32_t(HD * ELT) * p.pack * p.pos_per_tile;
   for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
@@ -84,33 +88,35 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
     // one K or V tile of key block nb into the next ring stage
     auto load_tile = [&](int kv, int nb) {
       const CUtensorMap* tm = kv == 0 ? tmK : tmV;
-      mbar_wait(&bar->kv_empty[ring.stage], ring.phase ^ 1, 0x20 + kv);
-      uint8_t* dst = sKV + ring.stage * L::kKVBytes;
+      RingState& ring = rings[kv];
+      const int stage = kv * kRing + ring.stage;
+      mbar_wait(&bar->kv_empty[stage], ring.phase ^ 1, 0x20 + kv);
+      uint8_t* dst = sKV + stage * L::kKVBytes;
       if (p.page_size == 0) {
         if (elect_one()) {
-          mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
+          mbar_arrive_expect_tx(&bar->kv_full[stage], L::kKVBytes);
 #pragma unroll
           for (int hb = 0; hb < kBoxesD; ++hb)
-            tma_load_4d(dst + hb * kHalfBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
+            tma_load_4d(dst + hb * kHalfBytes, tm, &bar->kv_full[stage], hb * kColsPerBox,
                         g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
         }
       } else {
         // paged: kv_box_rows = min(128, page_size) rows per box; page ids come from the table
         const int32_t* tbl = p.page_table + int64_t(g.it.bi) * p.page_table_batch_stride;
-        if (elect_one()) mbar_arrive_expect_tx(&bar->kv_full[ring.stage], L::kKVBytes);
+        if (elect_one()) mbar_arrive_expect_tx(&bar->kv_full[stage], L::kKVBytes);
         for (int r0 = 0; r0 < kBlockN; r0 += p.kv_box_rows) {
           const int row = nb * kBlockN + r0;
           const int page = tbl[row / p.page_size];
           if (elect_one()) {
 #pragma unroll
             for (int hb = 0; hb < kBoxesD; ++hb)
-              tma_load_4d(dst + hb * kHalfBytes + r0 * kRowBytes, tm, &bar->kv_full[ring.stage], hb * kColsPerBox,
+              tma_load_4d(dst + hb * kHalfBytes + r0 * kRowBytes, tm, &bar->kv_full[stage], hb * kColsPerBox,
                           row % p.page_size, g.hk, page);
           }
         }
       }
       __syncwarp();
-      ring_advance<L::kStages>(ring);
+      ring_advance<kRing>(ring);
     };
     if (!DUAL) {
       // ring order == the order the MMA warp consumes: K(first), then V(nb), K(nb-1) per key block
@@ -208,15 +214,16 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
     FA_PROF(3);
     if (last) ++o_it[t];
   };
-  // take the next ring stage if it is this warp's kind (K for the QK warp, V for the PV warp); returns its index or -1
+  // the next tile of this warp's kind (K tiles live in stages [0, kRing), V tiles in [kRing, 2 kRing)); -1 for the other kind
+  constexpr int kRing = L::kStages / 2;
   auto next_stage = [&](bool is_k) {
-    const RingState r = ring;
-    ring_advance<L::kStages>(ring);
     if (is_k != kIsQK) return -1;
+    const int stage = (kIsQK ? 0 : kRing) + ring.stage;
     FA_PROF(4);
-    mbar_wait(&bar->kv_full[r.stage], r.phase, is_k ? 0x42 : 0x41);
+    mbar_wait(&bar->kv_full[stage], ring.phase, is_k ? 0x42 : 0x41);
     FA_PROF(0);
-    return r.stage;
+    ring_advance<kRing>(ring);
+    return stage;
   };
   auto release = [&](int stage) {
     if (elect_one()) tc_commit(&bar->kv_empty[stage]);

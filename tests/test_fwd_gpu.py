@@ -442,6 +442,33 @@ def test_c4_full_size(ragged):
         assert torch.allclose(outs[0][1], outs[ns][1], atol=1e-4, rtol=1e-4)
 
 
+@pytest.mark.parametrize("num_splits", [0, 1, 4])
+def test_decode_many_items_per_cta(num_splits):
+    """Decode with more work items than SMs and 16 key blocks each, repeated: every CTA walks several items, the two
+    issuing warps drift across item boundaries (regression test for a barrier-phase aliasing fault in the dual-stream
+    decode kernel that only showed up with several long items per CTA)."""
+    F = _iface()
+    b, hk, sk, d = 40, 8, 2048, 128
+    h = hk * 4
+    g = torch.Generator(device=DEV).manual_seed(13)
+    q = torch.randn(b, 1, h, d, generator=g, device=DEV, dtype=torch.bfloat16)
+    k = torch.randn(b, sk, hk, d, generator=g, device=DEV, dtype=torch.bfloat16)
+    v = torch.randn(b, sk, hk, d, generator=g, device=DEV, dtype=torch.bfloat16)
+    lens = torch.randint(sk // 2, sk + 1, (b,), device=DEV, dtype=torch.int32, generator=g)
+    first = None
+    for _ in range(10):
+        out, lse, *_ = F.flash_attn_with_kvcache(q, k, v, cache_seqlens=lens, num_splits=num_splits, return_softmax_lse=True)
+        torch.cuda.synchronize()
+        if first is None:
+            first = (out.clone(), lse.clone())
+        assert torch.equal(out, first[0]) and torch.equal(lse, first[1])
+    for bi in (0, 17, 39):
+        n = int(lens[bi])
+        ref, lse_ref = A.attention_oracle(q[bi:bi + 1].cpu(), k[bi:bi + 1, :n].cpu(), v[bi:bi + 1, :n].cpu())
+        low, _ = A.attention_oracle(q[bi:bi + 1].cpu(), k[bi:bi + 1, :n].cpu(), v[bi:bi + 1, :n].cpu(), upcast=False, reorder_ops=True)
+        _check(out[bi:bi + 1], lse[bi:bi + 1], ref, low, lse_ref)
+
+
 def test_cuda_graph_decode_with_scheduler_metadata():
     """hopper/test_flash_attn.py:879-929: get_scheduler_metadata + a CUDA-graph-captured decode call; the captured call
     must follow cache_seqlens updated in place between replays (no host sync, no allocation inside the C ABI)."""
