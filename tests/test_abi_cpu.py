@@ -53,10 +53,14 @@ def _plan(native, **kw):
 def test_plan_policy(native):
     rc, p = _plan(native, b=8, seqlen_q=8192, seqlen_k=8192, h=32, h_k=8, is_causal=1)
     assert rc == 0 and p.num_splits == 1 and p.pack_gqa == 0 and p.num_work == 8 * 32 * 32
-    rc, p = _plan(native, b=64, seqlen_q=1, seqlen_k=32768, h=32, h_k=8)          # C4: decode packs the 4 group heads
-    assert rc == 0 and p.pack_gqa == 1 and p.num_work == 64 * 8 * p.num_splits
+    assert p.dual_stream == 0                                                      # two live Q tiles per item: single stream
+    rc, p = _plan(native, b=64, seqlen_q=1, seqlen_k=32768, h=32, h_k=8)          # C4: decode packs the 4 group heads and
+    assert rc == 0 and p.pack_gqa == 1 and p.dual_stream == 1                      # runs dual-stream: two partials per CTA split
+    assert p.num_splits == 2 and p.num_work == 64 * 8 * (p.num_splits // 2)
+    rc, p = _plan(native, b=64, seqlen_q=1, seqlen_k=32768, h=32, h_k=8, num_splits=3)   # a forced odd split count keeps
+    assert rc == 0 and p.dual_stream == 0 and p.num_splits == 3 and p.num_work == 64 * 8 * 3  # the single-stream kernel
     rc, p = _plan(native, b=1, seqlen_q=1, seqlen_k=32768, h=8, h_k=8)             # tiny batch: split to fill the SMs
-    assert rc == 0 and p.num_splits > 8 and p.num_work <= 148
+    assert rc == 0 and p.num_splits > 8 and p.num_splits % 2 == 0 and p.dual_stream == 1 and p.num_work <= 148
     rc, p = _plan(native, b=2, seqlen_q=64, seqlen_k=100, h=4, h_k=4)              # one key block: never split
     assert rc == 0 and p.num_splits == 1
     rc, p = _plan(native, b=2, seqlen_q=64, seqlen_k=4096, h=4, h_k=4, num_splits=7, pack_gqa=0)  # forced values are kept
