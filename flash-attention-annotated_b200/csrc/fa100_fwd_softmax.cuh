@@ -15,6 +15,48 @@ FA_DEVICE uint32_t pack_f16(float lo, float hi) {
 FA_DEVICE float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 FA_DEVICE float fast_tanh(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
+// Packed f32x2 arithmetic (one issue slot for two lanes of the row): (a, b) = (a, b) * sc + m and (acc0, acc1) += (a, b).
+FA_DEVICE void ffma2(float& a, float& b, float sc, float m) {
+  asm("{\n\t.reg .b64 x, s2, m2;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 s2, {%2, %2};\n\tmov.b64 m2, {%3, %3};\n\t"
+      "fma.rn.ftz.f32x2 x, x, s2, m2;\n\tmov.b64 {%0, %1}, x;\n\t}" : "+f"(a), "+f"(b) : "f"(sc), "f"(m));
+}
+FA_DEVICE void fadd2(float& acc0, float& acc1, float a, float b) {
+  asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tadd.rn.ftz.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
+      : "+f"(acc0), "+f"(acc1) : "f"(a), "f"(b));
+}
+// exp2 of two values on the FMA/ALU pipes instead of the MUFU pipe (which both tiles' softmax warps share at 16
+// results/clk/SM): Cody-Waite split with the 1.5 * 2^23 magic add (round toward -inf), degree-3 minimax polynomial of
+// 2^f on [0, 1) (relative error ~1e-4, below the 16-bit rounding of P), exponent spliced with an integer add.
+// Arguments are <= 0 here; below -126 the result is clamped to 2^-126 instead of 0, so this is used only on interior
+// key blocks (a masked -inf score must give an exact 0 for the dead-row test).
+FA_DEVICE void ex2_poly2(float& a, float& b) {
+  asm("{\n\t.reg .b64 x, r, f, pl;\n\t.reg .f32 a0, b0, r0, r1, p0, p1;\n\t.reg .b32 i0, i1, q0, q1;\n\t"
+      "max.ftz.f32 a0, %0, 0fC2FC0000;\n\tmax.ftz.f32 b0, %1, 0fC2FC0000;\n\t"
+      "mov.b64 x, {a0, b0};\n\t"
+      "mov.b64 pl, {0f4B400000, 0f4B400000};\n\t"
+      "add.rm.ftz.f32x2 r, x, pl;\n\t"
+      "sub.rn.ftz.f32x2 f, r, pl;\n\t"
+      "sub.rn.ftz.f32x2 f, x, f;\n\t"
+      "mov.b64 pl, {0f3D9DF09D, 0f3D9DF09D};\n\t"
+      "mov.b64 x, {0f3E6906A4, 0f3E6906A4};\n\t"
+      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
+      "mov.b64 x, {0f3F31F519, 0f3F31F519};\n\t"
+      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
+      "mov.b64 x, {0f3F800000, 0f3F800000};\n\t"
+      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
+      "mov.b64 {p0, p1}, pl;\n\tmov.b64 {r0, r1}, r;\n\t"
+      "mov.b32 i0, r0;\n\tmov.b32 i1, r1;\n\tshl.b32 i0, i0, 23;\n\tshl.b32 i1, i1, 23;\n\t"
+      "mov.b32 q0, p0;\n\tmov.b32 q1, p1;\n\tadd.s32 q0, q0, i0;\n\tadd.s32 q1, q1, i1;\n\t"
+      "mov.b32 %0, q0;\n\tmov.b32 %1, q1;\n\t}"
+      : "+f"(a), "+f"(b));
+}
+#ifndef FA100_POLY
+#define FA100_POLY 0   // of every 8 scores of an interior key block, how many take the polynomial exp2 (measured slower at full size: 2/8 -> 1217, 4/8 -> 1151 vs 1274 TFLOPS; kept as an experiment switch)
+#endif
+#ifndef FA100_F32X2
+#define FA100_F32X2 1  // packed f32x2 scale-subtract and row sum (measured: C2 1209 -> 1274 TFLOPS, C3 1115 -> 1199)
+#endif
+
 // What one softmax thread needs about its row while it walks the key blocks of a work item.  Kept this small on
 // purpose: with 227 KB of shared memory carved out the L1 is tiny, so a register spill in the step loop costs an L2
 // round trip; everything the epilogue needs is recomputed there instead of being carried across the loop.
@@ -98,7 +140,8 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       bool pv_drained = pv_n == 0 || mbar_try_wait(&bar->pv_done[t], (pv_n - 1) & 1);
       const int n0 = nb * kBlockN;
       // boundary block for any row of this warp (warp-uniform): softcap first, then the mask (hopper/mainloop...:1073-1077)
-      if (__any_sync(0xffffffffu, softcap || n0 + kBlockN > rg.col_hi || n0 < rg.col_lo)) {
+      const bool boundary = __any_sync(0xffffffffu, softcap || n0 + kBlockN > rg.col_hi || n0 < rg.col_lo);
+      if (boundary) {
         if (softcap) {
 #pragma unroll
           for (int c = 0; c < 4; ++c)
@@ -148,9 +191,25 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
+        if (FA100_POLY > 0 && !boundary) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          s[c][i] = __float_as_uint(ex2_approx(fmaf(__uint_as_float(s[c][i]), scale_log2, -m_sub)));
+          for (int i = 0; i < 32; i += 2) {
+            float x0 = __uint_as_float(s[c][i]), x1 = __uint_as_float(s[c][i + 1]);
+            if (FA100_F32X2) ffma2(x0, x1, scale_log2, -m_sub);
+            else { x0 = fmaf(x0, scale_log2, -m_sub); x1 = fmaf(x1, scale_log2, -m_sub); }
+            if ((i & 7) >= 8 - FA100_POLY) ex2_poly2(x0, x1);
+            else { x0 = ex2_approx(x0); x1 = ex2_approx(x1); }
+            s[c][i] = __float_as_uint(x0); s[c][i + 1] = __float_as_uint(x1);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            float x0 = __uint_as_float(s[c][i]), x1 = __uint_as_float(s[c][i + 1]);
+            if (FA100_F32X2) ffma2(x0, x1, scale_log2, -m_sub);
+            else { x0 = fmaf(x0, scale_log2, -m_sub); x1 = fmaf(x1, scale_log2, -m_sub); }
+            s[c][i] = __float_as_uint(ex2_approx(x0)); s[c][i + 1] = __float_as_uint(ex2_approx(x1));
+          }
+        }
         if (c == 0) {
           if (!pv_drained) mbar_wait(&bar->pv_done[t], (pv_n - 1) & 1, 0x78 + t);
           tc_fence_after();
@@ -176,8 +235,13 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
         }
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
-          sum0 += __uint_as_float(s[c][i]); sum1 += __uint_as_float(s[c][i + 1]);
-          sum2 += __uint_as_float(s[c][i + 2]); sum3 += __uint_as_float(s[c][i + 3]);
+          if (FA100_F32X2) {
+            fadd2(sum0, sum1, __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
+            fadd2(sum2, sum3, __uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3]));
+          } else {
+            sum0 += __uint_as_float(s[c][i]); sum1 += __uint_as_float(s[c][i + 1]);
+            sum2 += __uint_as_float(s[c][i + 2]); sum3 += __uint_as_float(s[c][i + 3]);
+          }
         }
         if (c == 1) FA_PROF(4);
       }

@@ -31,6 +31,16 @@ __device__ __forceinline__ void ex2_poly2(float& a, float& b) {
       : "+f"(a), "+f"(b));
 }
 
+// packed f32x2 helpers: (a, b) = (a, b) * s + m ;  (acc0, acc1) += (a, b)
+__device__ __forceinline__ void ffma2(float& a, float& b, float sc, float m) {
+  asm("{\n\t.reg .b64 x, s2, m2;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 s2, {%2, %2};\n\tmov.b64 m2, {%3, %3};\n\t"
+      "fma.rn.ftz.f32x2 x, x, s2, m2;\n\tmov.b64 {%0, %1}, x;\n\t}" : "+f"(a), "+f"(b) : "f"(sc), "f"(m));
+}
+__device__ __forceinline__ void fadd2(float& acc0, float& acc1, float a, float b) {
+  asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tadd.rn.ftz.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
+      : "+f"(acc0), "+f"(acc1) : "f"(a), "f"(b));
+}
+
 // VARIANT 0: 128 columns per thread, chunked (load all, max, then per chunk ffma/ex2/pack/store), sum at end
 // VARIANT 1: 64 columns per thread (two chunks)
 // VARIANT 2: 128 columns, per-chunk reload (two-pass)
@@ -72,7 +82,9 @@ __global__ void __launch_bounds__(VARIANT == 1 ? 512 : 256, 1) k_softmax(int ite
       for (int c = 0; c < NC; ++c) {
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {  // of every 8 elements the last NP go through the polynomial
-          float x0 = fmaf(__uint_as_float(s[c][i]), scale, -m_sub), x1 = fmaf(__uint_as_float(s[c][i + 1]), scale, -m_sub);
+          float x0 = __uint_as_float(s[c][i]), x1 = __uint_as_float(s[c][i + 1]);
+          if (VARIANT == 3) ffma2(x0, x1, scale, -m_sub);
+          else { x0 = fmaf(x0, scale, -m_sub); x1 = fmaf(x1, scale, -m_sub); }
           if ((i & 7) >= 8 - NP) ex2_poly2(x0, x1); else { x0 = ex2a(x0); x1 = ex2a(x1); }
           s[c][i] = __float_as_uint(x0); s[c][i + 1] = __float_as_uint(x1);
         }
@@ -82,8 +94,13 @@ __global__ void __launch_bounds__(VARIANT == 1 ? 512 : 256, 1) k_softmax(int ite
         tmem_st16(tS + c * 16, pk);
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
-          sum0 += __uint_as_float(s[c][i]); sum1 += __uint_as_float(s[c][i + 1]);
-          sum2 += __uint_as_float(s[c][i + 2]); sum3 += __uint_as_float(s[c][i + 3]);
+          if (VARIANT == 3) {
+            fadd2(sum0, sum1, __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
+            fadd2(sum2, sum3, __uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3]));
+          } else {
+            sum0 += __uint_as_float(s[c][i]); sum1 += __uint_as_float(s[c][i + 1]);
+            sum2 += __uint_as_float(s[c][i + 2]); sum3 += __uint_as_float(s[c][i + 3]);
+          }
         }
       }
       tmem_st_wait();
@@ -110,6 +127,8 @@ int main() {
   };
   for (int nw : {4, 8}) { k_softmax<0, 0><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, all MUFU", nw, 128); }
   for (int nw : {4, 8}) { k_softmax<0, 2><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, 2/8 polynomial", nw, 128); }
+  for (int nw : {4, 8}) { k_softmax<3, 0><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, all MUFU, f32x2 fma/add", nw, 128); }
+  for (int nw : {4, 8}) { k_softmax<3, 2><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, 2/8 poly, f32x2 fma/add", nw, 128); }
   for (int nw : {4, 8}) { k_softmax<0, 4><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, 4/8 polynomial", nw, 128); }
   for (int nw : {4, 8}) { k_softmax<0, 6><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, 6/8 polynomial", nw, 128); }
   for (int nw : {4, 8}) { k_softmax<0, 8><<<148, 256>>>(iters, nw, 0.1275f, d, sink); report("128 cols/thread, all polynomial", nw, 128); }
