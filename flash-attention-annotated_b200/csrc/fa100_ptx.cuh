@@ -57,9 +57,6 @@ FA_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // FA100_WATCHDOG_CYCLES records {tag, block, thread, parity}, raises a device-wide abort flag and returns;
 // every other wait then falls through as well, the kernel ends (with garbage) and the host reads the
 // record through fa100_debug_hang_info().
-#ifndef FA100_EXP
-#define FA100_EXP 0  // debugging experiments (never set in the product build)
-#endif
 #ifndef FA100_WATCHDOG_CYCLES
 #define FA100_WATCHDOG_CYCLES (4000000000ll)
 #endif

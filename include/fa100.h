@@ -121,7 +121,7 @@ typedef struct Fa100FwdParams {
   int32_t num_splits;          /* >= 1 (resolved by the caller, e.g. through fa100_plan) */
   int32_t pack_gqa;            /* 0/1 (resolved by the caller) */
   int32_t num_sm;              /* SMs this call may use (multiProcessorCount - sm_margin); 0 = all */
-  int32_t* tile_counter;       /* optional int32[1] zeroed by the caller: dynamic tile scheduler */
+  int32_t* tile_counter;       /* reserved for a device-counter scheduler; ignored (the schedule is static) */
   int32_t reserved[8];
 } Fa100FwdParams;
 
