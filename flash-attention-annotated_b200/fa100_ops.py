@@ -329,6 +329,40 @@ def mha_bwd(*args, **kwargs):
     raise NotImplementedError("fa100 is a forward-only build: flash_attn_3::bwd is out of scope (SURVEY.md 8f rank 2)")
 
 
+# ----------------------------------------------------------------------------- shape-only (Meta) kernels for tracing
+def mha_fwd_meta(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=None, cu_seqlens_k=None,
+                 cu_seqlens_k_new=None, seqused_q=None, seqused_k=None, max_seqlen_q=None, max_seqlen_k=None,
+                 page_table=None, kv_batch_idx=None, leftpad_k=None, rotary_cos=None, rotary_sin=None,
+                 seqlens_rotary=None, q_descale=None, k_descale=None, v_descale=None, softmax_scale=None,
+                 is_causal=False, window_size_left=-1, window_size_right=-1, attention_chunk=0, softcap=0.0,
+                 is_rotary_interleaved=False, scheduler_metadata=None, num_splits=0, pack_gqa=None, sm_margin=0):
+    """Output shapes / dtypes of flash_attn_3::fwd for FakeTensor / torch.compile tracing (SURVEY.md 8f rank 3; the
+    reference registers no Meta kernel, hopper/flash_api.cpp:1763-1768).  Partials are only materialised for an explicit
+    num_splits > 1; with num_splits = 0 the real kernel may return non-empty accumulators."""
+    varlen_q = cu_seqlens_q is not None
+    h, dv = q.shape[-2], v.shape[-1]
+    out_dtype = torch.bfloat16 if q.dtype == torch.float8_e4m3fn else q.dtype
+    if varlen_q:
+        total_q = q.shape[0]
+        out_shape, lse_shape = (total_q, h, dv), (h, total_q)
+        acc_shape, lacc_shape = (num_splits, h, total_q, dv), (num_splits, h, total_q)
+    else:
+        b, sq = q.shape[0], q.shape[1]
+        out_shape, lse_shape = (b, sq, h, dv), (b, h, sq)
+        acc_shape, lacc_shape = (num_splits, b, h, sq, dv), (num_splits, b, h, sq)
+    o = out if out is not None else q.new_empty(out_shape, dtype=out_dtype)
+    lse = q.new_empty(lse_shape, dtype=torch.float32)
+    if num_splits > 1:
+        return o, lse, q.new_empty(acc_shape, dtype=torch.float32), q.new_empty(lacc_shape, dtype=torch.float32)
+    return o, lse, q.new_empty((0,), dtype=torch.float32), q.new_empty((0,), dtype=torch.float32)
+
+
+def mha_combine_meta(out_partial, lse_partial, out=None, out_dtype=None):
+    splits, b, s, h, d = out_partial.shape
+    o = out if out is not None else out_partial.new_empty((b, s, h, d), dtype=out_dtype or out_partial.dtype)
+    return o, out_partial.new_empty((b, h, s), dtype=torch.float32).transpose(1, 2)
+
+
 # ----------------------------------------------------------------------------- torch.library registration
 _FWD_SCHEMA = (
     "(Tensor q, Tensor k, Tensor v, Tensor(k_new!)? k_new = None, Tensor(v_new!)? v_new = None, Tensor? q_v = None, "
@@ -359,7 +393,8 @@ _lib_def = None
 
 
 def register_ops():
-    """Define flash_attn_3::* once per process; CUDA dispatch key only, like the reference (no CPU/Meta kernels)."""
+    """Define flash_attn_3::* once per process: CUDA kernels like the reference (no CPU kernel), plus shape-only Meta
+    kernels so that FakeTensor / torch.compile can trace through the ops."""
     global _lib_def
     if _lib_def is not None:
         return
@@ -374,3 +409,5 @@ def register_ops():
     _lib_def.impl("bwd", mha_bwd, "CUDA")
     _lib_def.impl("fwd_combine", mha_combine, "CUDA")
     _lib_def.impl("get_scheduler_metadata", mha_fwd_get_scheduler_metadata, "CUDA")
+    _lib_def.impl("fwd", mha_fwd_meta, "Meta")
+    _lib_def.impl("fwd_combine", mha_combine_meta, "Meta")

@@ -124,3 +124,28 @@ def test_no_cpu_fallback(native):
     q = torch.randn(1, 8, 2, 64, dtype=torch.bfloat16)
     with pytest.raises((RuntimeError, NotImplementedError)):
         F.flash_attn_func(q, q, q)
+
+
+def test_meta_kernels_trace_shapes():
+    """FakeTensor / Meta dispatch: flash_attn_3::fwd and ::fwd_combine infer output shapes without a GPU
+    (what torch.compile needs to trace through the ops)."""
+    import torch
+
+    import flash_attn_interface  # noqa: F401  (registers the ops)
+
+    q = torch.empty(2, 300, 8, 128, dtype=torch.bfloat16, device="meta")
+    k = torch.empty(2, 500, 2, 128, dtype=torch.bfloat16, device="meta")
+    v = torch.empty(2, 500, 2, 64, dtype=torch.bfloat16, device="meta")
+    out, lse, oacc, lacc = torch.ops.flash_attn_3.fwd(q, k, v, is_causal=True)
+    assert out.shape == (2, 300, 8, 64) and out.dtype == torch.bfloat16 and lse.shape == (2, 8, 300) and lse.dtype == torch.float32
+    assert oacc.numel() == 0 and lacc.numel() == 0
+    out, lse, oacc, lacc = torch.ops.flash_attn_3.fwd(q, k, v, num_splits=3)
+    assert oacc.shape == (3, 2, 8, 300, 64) and lacc.shape == (3, 2, 8, 300)
+    q8 = torch.empty(700, 4, 128, dtype=torch.float8_e4m3fn, device="meta")
+    cu = torch.empty(4, dtype=torch.int32, device="meta")
+    out, lse, *_ = torch.ops.flash_attn_3.fwd(q8, q8, q8, cu_seqlens_q=cu, cu_seqlens_k=cu, max_seqlen_q=300, max_seqlen_k=300)
+    assert out.shape == (700, 4, 128) and out.dtype == torch.bfloat16 and lse.shape == (4, 700)
+    op = torch.empty(5, 2, 100, 4, 64, device="meta")
+    lp = torch.empty(5, 2, 100, 4, device="meta")
+    o, l = torch.ops.flash_attn_3.fwd_combine(op, lp, None, torch.bfloat16)
+    assert o.shape == (2, 100, 4, 64) and o.dtype == torch.bfloat16 and l.shape == (2, 100, 4)
