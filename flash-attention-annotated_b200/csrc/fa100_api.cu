@@ -81,7 +81,8 @@ int make_plan(const Fa100Shape* s, Fa100Plan* out) {
   int num_sm = s->num_sm;
   if (num_sm <= 0) { int rc = device_sm_count(&num_sm); if (rc) return rc; }
   const int G = s->h / s->h_k;
-  const int rows_cta = 256;  // two 128-row Q tiles per CTA
+  const bool solo = std::max(s->d, s->dv) > 128;  // head dim > 128: one 128-row Q tile per work item (O fills TMEM)
+  const int rows_cta = solo ? 128 : 256;          // else two 128-row Q tiles per CTA
   // pack GQA (rows = positions x group heads) when that fills the 256-row CTA tile >10% better, or always for
   // single-token decode where positions alone would leave 255 of 256 rows empty.
   int pack = s->pack_gqa;
@@ -92,7 +93,7 @@ int make_plan(const Fa100Shape* s, Fa100Plan* out) {
   }
   if (pack && G > 128) pack = 0;
   const int pos_per_tile = pack ? 128 / G : 128;
-  const int m_blocks = std::max(1, ceil_div(s->seqlen_q, 2 * pos_per_tile));
+  const int m_blocks = std::max(1, ceil_div(s->seqlen_q, (solo ? 1 : 2) * pos_per_tile));
   const int heads_work = pack ? s->h_k : s->h;
   const int tiles = s->b * heads_work * m_blocks;
   int n_blocks = std::max(1, ceil_div(s->seqlen_k, 128));
@@ -100,7 +101,7 @@ int make_plan(const Fa100Shape* s, Fa100Plan* out) {
   // Dual-stream decode: when every item's query rows fit one 128-row tile, the CTA's two tile pipelines take alternate key
   // blocks of the same rows and emit two partials per CTA-level split (fa100_fwd_roles.cuh make_geom<DUAL>), so the total
   // number of partials is even.  A caller-forced odd num_splits keeps the single-stream kernel.
-  const bool dual_ok = s->seqlen_q <= pos_per_tile && n_blocks >= 2;
+  const bool dual_ok = !solo && s->seqlen_q <= pos_per_tile && n_blocks >= 2;
   int splits = s->num_splits;
   bool dual = dual_ok && (splits <= 0 || splits % 2 == 0);
   if (splits <= 0) {

@@ -33,7 +33,8 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   const bool fp8 = p->dtype == FA100_E4M3;
   const int elt = fp8 ? 1 : 2;
   if (fp8) FA_CHECK_ARG(p->d % 16 == 0 && p->dv % 16 == 0, "fp8 head dims must be multiples of 16");
-  FA_UNSUPPORTED(p->d > 128 || p->dv > 128, "head dim > 128 not built yet (d=%d dv=%d)", p->d, p->dv);
+  FA_UNSUPPORTED(p->d > 256 || p->dv > 256, "head dim > 256 is not supported (d=%d dv=%d)", p->d, p->dv);
+  FA_UNSUPPORTED(fp8 && (p->d > 128 || p->dv > 128), "fp8 with head dim > 128 not built yet (d=%d dv=%d)", p->d, p->dv);
   FA_UNSUPPORTED(p->k_new || p->v_new || p->rotary_cos, "append-KV / rotary handled by the caller-side kernel, not fa100_fwd");
   FA_UNSUPPORTED(fp8 && p->softcap > 0.f, "softcap with fp8 not supported");
   const bool varlen_q = p->cu_seqlens_q != nullptr;
@@ -78,9 +79,14 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   kp.qheads_per_kv = G;
   kp.pack = plan->pack_gqa ? G : 1;
   kp.pos_per_tile = 128 / kp.pack;
+  kp.qk_boxes = (p->d * elt + 127) / 128;
+  kp.v_boxes = (p->dv * elt + 127) / 128;
+  kp.qk_slices = (p->d * elt + 31) / 32;
+  kp.pv_n = (p->dv + 15) / 16 * 16;
   const bool dual = plan->dual_stream != 0;  // two partials per CTA-level split (make_geom<DUAL>)
   const int cta_splits = dual ? splits / 2 : splits;
-  kp.num_m_blocks = dual ? 1 : std::max(1, (p->seqlen_q + 2 * kp.pos_per_tile - 1) / (2 * kp.pos_per_tile));
+  const bool solo = std::max(p->d, p->dv) > 128;  // one Q tile per work item (make_geom<.., SOLO>)
+  kp.num_m_blocks = dual ? 1 : std::max(1, (p->seqlen_q + (solo ? 1 : 2) * kp.pos_per_tile - 1) / ((solo ? 1 : 2) * kp.pos_per_tile));
   kp.heads_work = plan->pack_gqa ? p->h_k : p->h;
   kp.num_splits = cta_splits;
   kp.num_work = kp.num_m_blocks * p->b * kp.heads_work * cta_splits;
@@ -133,12 +139,15 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   int num_sm = plan->num_sm;
   const int grid = std::max(1, std::min(kp.num_work, num_sm));
   const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : (p->dtype == FA100_FP16 ? kFmtF16 : kFmtE4M3);
-  const int hd = (p->d <= 64 && p->dv <= 64 && !fp8) ? 64 : 128;
+  const int hd = solo ? 256 : ((p->d <= 64 && p->dv <= 64 && !fp8) ? 64 : 128);
   const bool f16 = p->dtype == FA100_FP16;
 #define FA_LAUNCH(HD_, ELT_, FP8_, F16_)                                                                      \
   (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, fmt, grid, stream)                 \
         : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, fmt, grid, stream))
   if (fp8) return FA_LAUNCH(128, 1, true, false);
+  if (hd == 256)
+    return f16 ? launch_instance<256, 2, false, true, false>(kp, tmQ, tmK, tmV, fmt, grid, stream)
+               : launch_instance<256, 2, false, false, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
   if (hd == 64) return f16 ? FA_LAUNCH(64, 2, false, true) : FA_LAUNCH(64, 2, false, false);
   return f16 ? FA_LAUNCH(128, 2, false, true) : FA_LAUNCH(128, 2, false, false);
 #undef FA_LAUNCH

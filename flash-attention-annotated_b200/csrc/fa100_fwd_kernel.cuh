@@ -59,6 +59,10 @@ struct FwdKernelParams {
   int32_t b, h, h_k, seqlen_q, seqlen_k, d, dv;
   int32_t page_size;      // 0 = not paged
   int32_t kv_box_rows;    // rows per K/V TMA box: min(128, page_size)
+  int32_t qk_boxes;       // 128-byte column boxes of Q / K actually loaded: ceil(d * elt / 128) <= HD * elt / 128
+  int32_t v_boxes;        // same for V: ceil(dv * elt / 128)
+  int32_t qk_slices;      // MMA k-slices of S = Q K^T actually issued: ceil(d / (32 / elt))
+  int32_t pv_n;           // N of O += P V: dv rounded up to 16
   int32_t qheads_per_kv;  // G
   int32_t pack;           // Gp: G when pack_gqa else 1
   int32_t pos_per_tile;   // 128 / Gp query positions per Q tile
@@ -164,9 +168,13 @@ struct FwdSmem {
   static constexpr int kKVBytes = kBlockN * HD * ELT;  // one K or V tile
   static constexpr int kBarrierBytes = 1024;           // mbarriers + TMEM base (+ the trace build's counters in the last 128 B)
   static constexpr int kBudget = 227 * 1024 - kBarrierBytes;
-  static constexpr int kStagesRaw = (kBudget - kQTiles * kQBytes) / kKVBytes;
+  // head dims above 128 run one Q tile per work item: O alone needs 256 TMEM columns, so the second tile pipeline stays
+  // idle (SOLO geometry in fa100_fwd_roles.cuh) and only one Q slot is carved out
+  static constexpr int kQSlots = HD > 128 ? 1 : kQTiles;
+  static constexpr int kStagesRaw = ((kBudget - kQSlots * kQBytes) / kKVBytes) & ~1;  // even: half K stages, half V stages
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-  static constexpr int kDataBytes = kQTiles * kQBytes + kStages * kKVBytes;
+  static_assert(kStages >= 2, "need at least one K and one V stage");
+  static constexpr int kDataBytes = kQSlots * kQBytes + kStages * kKVBytes;
   static constexpr int kTotalBytes = kDataBytes + kBarrierBytes;
 };
 

@@ -18,18 +18,20 @@ struct WorkGeom {
 // and each writes its own fp32 partial (split index 2 * split + t) for the combine kernel.  Without it the second
 // pipeline idles and the per-block chain QK -> softmax -> PV (~3300 clk) is longer than the 64 KB block takes to
 // arrive from HBM (~2450 clk at 6.5 TB/s over 148 SMs).
-template <bool DUAL>
+// SOLO (head dim > 128): a work item is ONE 128-row tile; tile 1 never has rows.
+template <bool DUAL, bool SOLO = false>
 FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w) {
   WorkGeom g;
   g.it = decode_work(p, w);
   g.seq = load_seq(p, g.it.bi);
   g.hk = p.pack > 1 ? g.it.head : g.it.head / p.qheads_per_kv;
   g.n_lo = 0x7fffffff; g.n_hi = 0;
-  if (DUAL) {
+  if (DUAL || SOLO) {
     const TileRange r = tile_range(p, g.seq, g.it.m_blk * p.pos_per_tile, g.it.split);
     g.tr[0] = r;
     g.tr[1] = r;
-    g.tr[1].n_max = max(r.n_min, r.n_max - 1);
+    if (SOLO) { g.tr[1].has_rows = false; g.tr[1].n_min = g.tr[1].n_max = 0; }
+    else g.tr[1].n_max = max(r.n_min, r.n_max - 1);
     if (r.n_max > r.n_min) { g.n_lo = r.n_min; g.n_hi = r.n_max; }
     return g;
   }
@@ -40,8 +42,8 @@ FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w) {
   }
   return g;
 }
-template <bool DUAL> FA_DEVICE int tile_pos0(const FwdKernelParams& p, const WorkItem& it, int t) {
-  return (DUAL ? it.m_blk : it.m_blk * kQTiles + t) * p.pos_per_tile;
+template <bool ONE_TILE> FA_DEVICE int tile_pos0(const FwdKernelParams& p, const WorkItem& it, int t) {
+  return (ONE_TILE ? it.m_blk : it.m_blk * kQTiles + t) * p.pos_per_tile;  // ONE_TILE = DUAL or SOLO
 }
 FA_DEVICE bool tile_live(const WorkGeom& g, int t) { return g.tr[t].n_max > g.tr[t].n_min; }
 FA_DEVICE bool tile_uses(const WorkGeom& g, int t, int nb) { return nb >= g.tr[t].n_min && nb < g.tr[t].n_max; }
@@ -66,20 +68,21 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   constexpr int kRing = L::kStages / 2;
   RingState rings[2];
   uint32_t q_it[kQTiles] = {0, 0};
-  const uint32_t q_tx = uint32_t(HD * ELT) * p.pack * p.pos_per_tile;
+  // only the boxes that hold real head-dim columns are loaded (d = 192 in the 256 instance: 3 of 4)
+  const uint32_t q_tx = uint32_t(p.qk_boxes * kRowBytes) * p.pack * p.pos_per_tile;
   for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
-    const WorkGeom g = make_geom<DUAL>(p, w);
+    const WorkGeom g = make_geom<DUAL, (HD > 128)>(p, w);
     if (g.n_hi <= g.n_lo) continue;
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
       if (!tile_live(g, t)) continue;
       mbar_wait(&bar->q_empty[t], (q_it[t] & 1) ^ 1, 0x10 + t);
-      const int pos0 = tile_pos0<DUAL>(p, g.it, t);
+      const int pos0 = tile_pos0<DUAL || (HD > 128)>(p, g.it, t);
       if (elect_one()) {
         mbar_arrive_expect_tx(&bar->q_full[t], q_tx);
 #pragma unroll
         for (int hb = 0; hb < kBoxesD; ++hb)
-          tma_load_5d(sQ + t * L::kQBytes + hb * kHalfBytes, tmQ, &bar->q_full[t], hb * kColsPerBox, 0,
+          if (hb < p.qk_boxes) tma_load_5d(sQ + t * L::kQBytes + hb * kHalfBytes, tmQ, &bar->q_full[t], hb * kColsPerBox, 0,
                       g.seq.q_off + pos0, g.it.head, g.seq.bq);
       }
       __syncwarp();
@@ -92,25 +95,26 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
       const int stage = kv * kRing + ring.stage;
       mbar_wait(&bar->kv_empty[stage], ring.phase ^ 1, 0x20 + kv);
       uint8_t* dst = sKV + stage * L::kKVBytes;
+      const int boxes = kv == 0 ? p.qk_boxes : p.v_boxes;
       if (p.page_size == 0) {
         if (elect_one()) {
-          mbar_arrive_expect_tx(&bar->kv_full[stage], L::kKVBytes);
+          mbar_arrive_expect_tx(&bar->kv_full[stage], boxes * kHalfBytes);
 #pragma unroll
           for (int hb = 0; hb < kBoxesD; ++hb)
-            tma_load_4d(dst + hb * kHalfBytes, tm, &bar->kv_full[stage], hb * kColsPerBox,
+            if (hb < boxes) tma_load_4d(dst + hb * kHalfBytes, tm, &bar->kv_full[stage], hb * kColsPerBox,
                         g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
         }
       } else {
         // paged: kv_box_rows = min(128, page_size) rows per box; page ids come from the table
         const int32_t* tbl = p.page_table + int64_t(g.it.bi) * p.page_table_batch_stride;
-        if (elect_one()) mbar_arrive_expect_tx(&bar->kv_full[stage], L::kKVBytes);
+        if (elect_one()) mbar_arrive_expect_tx(&bar->kv_full[stage], boxes * kHalfBytes);
         for (int r0 = 0; r0 < kBlockN; r0 += p.kv_box_rows) {
           const int row = nb * kBlockN + r0;
           const int page = tbl[row / p.page_size];
           if (elect_one()) {
 #pragma unroll
             for (int hb = 0; hb < kBoxesD; ++hb)
-              tma_load_4d(dst + hb * kHalfBytes + r0 * kRowBytes, tm, &bar->kv_full[stage], hb * kColsPerBox,
+              if (hb < boxes) tma_load_4d(dst + hb * kHalfBytes + r0 * kRowBytes, tm, &bar->kv_full[stage], hb * kColsPerBox,
                           row % p.page_size, g.hk, page);
           }
         }
@@ -159,7 +163,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   constexpr int kSlicesPerBox = kColsPerBox / kKPerMma;       // 4
   constexpr int kQKSlices = HD / kKPerMma;
   constexpr int kPVSlices = kBlockN / kKPerMma;
-  const uint32_t idesc = kIsQK ? make_idesc(fmt, fmt, kBlockM, kBlockN, 0, 0) : make_idesc(fmt, fmt, kBlockM, HD, 0, 1);
+  const uint32_t idesc = kIsQK ? make_idesc(fmt, fmt, kBlockM, kBlockN, 0, 0) : make_idesc(fmt, fmt, kBlockM, p.pv_n, 0, 1);
   // K-major operand tiles [128 rows][128 B] SW128: 8-row groups 1024 B apart (SBO); LBO unused (1).
   // V as MN-major B operand: 128-byte rows along dv, 8 key rows per swizzle atom (SBO = 1024 B), the next
   // 64 (16-bit) / 128 (8-bit) dv columns in the next box (LBO = one [128][128 B] region).
@@ -185,7 +189,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
 #pragma unroll
       for (int ks = 0; ks < kQKSlices; ++ks) {
         const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
-        mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
+        if (ks < p.qk_slices) mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
       }
       tc_commit(&bar->s_full[t]);
       if (last_use_of_q) tc_commit(&bar->q_empty[t]);
@@ -233,7 +237,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
     int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi;
     {
-      const WorkGeom g = make_geom<DUAL>(p, w);
+      const WorkGeom g = make_geom<DUAL, (HD > 128)>(p, w);
       n_lo = g.n_lo; n_hi = g.n_hi;
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) { n_min[t] = g.tr[t].n_min; n_max[t] = g.tr[t].n_max; }

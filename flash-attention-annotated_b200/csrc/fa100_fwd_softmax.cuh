@@ -67,13 +67,13 @@ struct RowGeom {
   bool has_rows;
 };
 
-template <bool FP8, bool DUAL>
+template <bool FP8, bool DUAL, bool SOLO>
 FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row) {
-  const WorkGeom g = make_geom<DUAL>(p, w);
+  const WorkGeom g = make_geom<DUAL, SOLO>(p, w);
   RowGeom r;
   r.has_rows = g.tr[t].has_rows;
   r.n_min = g.tr[t].n_min; r.n_max = g.tr[t].n_max;
-  const int pos = tile_pos0<DUAL>(p, g.it, t) + (p.pack > 1 ? row / p.pack : row);
+  const int pos = tile_pos0<DUAL || SOLO>(p, g.it, t) + (p.pack > 1 ? row / p.pack : row);
   const int shift = g.seq.sk - g.seq.sq;
   int col_hi = g.seq.sk, col_lo = 0;
   if (p.is_causal) col_hi = min(col_hi, pos + 1 + shift);
@@ -112,7 +112,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
   FA_PROF_DECL();  // 0 s_full wait, 1 S load, 2 s_free + mask + row max, 3 rescale, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait + publish, 7 rest
 
   for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
-    const RowGeom rg = row_geom<FP8, DUAL>(p, w, t, row);
+    const RowGeom rg = row_geom<FP8, DUAL, (HD > 128)>(p, w, t, row);
     if (!rg.has_rows) continue;
     const float scale_log2 = rg.scale_log2;
     const bool softcap = p.softcap_pre != 0.f;
@@ -176,6 +176,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
         tc_fence_after();
 #pragma unroll
         for (int c = 0; c < HD / 32; ++c) {
+          if (c * 32 >= p.dv) break;
           uint32_t o[32];
           tmem_ld32(tO + c * 32, o);
           tmem_ld_wait();
@@ -259,12 +260,12 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
 
     // ---- epilogue: O / rowsum, LSE (hopper/softmax.h:137-155, epilogue_fwd.hpp:215-481); geometry is recomputed here
     {
-      const WorkGeom g = make_geom<DUAL>(p, w);
+      const WorkGeom g = make_geom<DUAL, (HD > 128)>(p, w);
       const bool split = p.o_accum != nullptr;  // fp32 partials (split-KV, or one hop of ring attention)
       const int part = DUAL ? g.it.split * 2 + t : g.it.split;  // index of this partial
       const bool live = rg.n_max > rg.n_min;
       const int in_tile = p.pack > 1 ? row / p.pack : row;
-      const int pos = tile_pos0<DUAL>(p, g.it, t) + in_tile;
+      const int pos = tile_pos0<DUAL || (HD > 128)>(p, g.it, t) + in_tile;
       const int hq = p.pack > 1 ? g.it.head * p.qheads_per_kv + row % p.pack : g.it.head;
       const bool row_valid = in_tile < p.pos_per_tile && pos < g.seq.sq;
       float out_scale = 1.0f;
@@ -286,6 +287,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
                                               hq * p.oacc_head_stride + row_idx * p.dv);
 #pragma unroll
       for (int c = 0; c < HD / 32; ++c) {
+        if (c * 32 >= p.dv) break;
         uint32_t o[32];
         if (live) { tmem_ld32(tO + c * 32, o); tmem_ld_wait(); }
         else {
@@ -336,7 +338,7 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
   using L = FwdSmem<HD, ELT>;
   extern __shared__ __align__(1024) uint8_t smem[];  // 128-byte swizzle atoms need 1 KB alignment
   uint8_t* sQ = smem;
-  uint8_t* sKV = smem + kQTiles * L::kQBytes;
+  uint8_t* sKV = smem + L::kQSlots * L::kQBytes;
   FwdBarriers* bar = reinterpret_cast<FwdBarriers*>(smem + L::kDataBytes);
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   FA_TRACE_BEGIN();

@@ -65,6 +65,10 @@ def test_plan_policy(native):
     assert rc == 0 and p.num_splits == 1
     rc, p = _plan(native, b=2, seqlen_q=64, seqlen_k=4096, h=4, h_k=4, num_splits=7, pack_gqa=0)  # forced values are kept
     assert rc == 0 and p.num_splits == 7 and p.pack_gqa == 0
+    rc, p = _plan(native, b=4, seqlen_q=8192, seqlen_k=8192, h=16, h_k=4, d=256, dv=256, is_causal=1)   # head dim > 128:
+    assert rc == 0 and p.block_m == 128 and p.num_work == 4 * 16 * 64 and p.dual_stream == 0            # one Q tile per item
+    rc, p = _plan(native, b=64, seqlen_q=1, seqlen_k=32768, h=32, h_k=8, d=192, dv=128)                  # and never dual-stream
+    assert rc == 0 and p.dual_stream == 0 and p.block_m == 128
     rc, _ = _plan(native, h=6, h_k=4)
     assert rc == native.ERR_INVALID and b"multiple" in native.lib().fa100_last_error()
 

@@ -96,6 +96,61 @@ def test_odd_head_dims(d, dv):
     _check(out, lse, ref, low, lse_ref)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d,dv", [(256, 256), (192, 192), (192, 128), (160, 160), (136, 136), (64, 256), (256, 64)])
+@pytest.mark.parametrize("sq,sk", [(1, 1), (128, 128), (113, 203), (300, 411), (1, 1024), (640, 128), (1023, 1024)])
+def test_large_head_dims(sq, sk, d, dv, causal, dtype):
+    """head dims in (128, 256] (hopper/flash_api.cpp:710, tile_size_fwd_sm90 hdim 192 / 256 rows): the one-Q-tile-per-CTA
+    instance, every scheduling mode."""
+    F = _iface()
+    q, k, v = _qkv(2, sq, sk, 4, 2, d, dtype, seed=3, dv=dv)
+    ref, lse_ref = A.attention_oracle(q, k, v, causal=causal)
+    low, _ = A.attention_oracle(q, k, v, causal=causal, upcast=False, reorder_ops=True)
+    for pack_gqa, num_splits in ((False, 1), (True, 1), (False, 3), (True, 2)):
+        out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), causal=causal, pack_gqa=pack_gqa, num_splits=num_splits,
+                                     return_attn_probs=True)
+        _check(out, lse, ref, low, lse_ref)
+
+
+def test_large_head_dim_kvcache_varlen():
+    """hdim 256 through the paged KV cache (split chosen by the plan) and the varlen entry point."""
+    F = _iface()
+    b, h, hk, d, ps, cap = 3, 4, 2, 256, 64, 1024
+    g = torch.Generator().manual_seed(11)
+    q = torch.randn(b, 2, h, d, generator=g).to(torch.bfloat16)
+    kc = torch.randn(b, cap, hk, d, generator=g).to(torch.bfloat16)
+    vc = torch.randn(b, cap, hk, d, generator=g).to(torch.bfloat16)
+    lens = torch.tensor([1024, 517, 1], dtype=torch.int32)
+    ref, lse_ref = A.attention_oracle(q, kc, vc, causal=True, k_lens=lens)
+    low, _ = A.attention_oracle(q, kc, vc, causal=True, k_lens=lens, upcast=False, reorder_ops=True)
+    npg = cap // ps
+    perm = torch.randperm(b * npg, generator=g).to(torch.int32)
+    table = perm.view(b, npg)
+    kp = torch.empty(b * npg, ps, hk, d, dtype=torch.bfloat16)
+    vp = torch.empty_like(kp)
+    kp[table.flatten().long()] = kc.view(b * npg, ps, hk, d)
+    vp[table.flatten().long()] = vc.view(b * npg, ps, hk, d)
+    for kk, vv, tb in ((kc, vc, None), (kp, vp, table)):
+        out, lse = F.flash_attn_with_kvcache(q.to(DEV), kk.to(DEV), vv.to(DEV), cache_seqlens=lens.to(DEV), causal=True,
+                                             page_table=None if tb is None else tb.to(DEV), return_softmax_lse=True)[:2]
+        _check(out, lse, ref, low, lse_ref)
+    lens_q, lens_k = [5, 200, 131], [64, 333, 131]
+    qs = [torch.randn(n, h, d, generator=g).to(torch.bfloat16) for n in lens_q]
+    ks = [torch.randn(n, hk, d, generator=g).to(torch.bfloat16) for n in lens_k]
+    vs = [torch.randn(n, hk, d, generator=g).to(torch.bfloat16) for n in lens_k]
+    cu = lambda ls: torch.tensor([0] + list(torch.tensor(ls).cumsum(0)), dtype=torch.int32).to(DEV)
+    out, lse = F.flash_attn_varlen_func(torch.cat(qs).to(DEV), torch.cat(ks).to(DEV), torch.cat(vs).to(DEV), cu(lens_q), cu(lens_k),
+                                        max(lens_q), max(lens_k), causal=True, return_attn_probs=True)
+    off = 0
+    for qi, ki, vi in zip(qs, ks, vs):
+        ref, lse_ref = A.attention_oracle(qi[None], ki[None], vi[None], causal=True)
+        low, _ = A.attention_oracle(qi[None], ki[None], vi[None], causal=True, upcast=False, reorder_ops=True)
+        n = qi.shape[0]
+        _check(out[off:off + n][None], lse[:, off:off + n][None], ref, low, lse_ref)
+        off += n
+
+
 def test_noncontiguous_inputs():
     """only last-dim contiguity is required (hopper/flash_api.cpp:726-728)."""
     F = _iface()
@@ -498,9 +553,12 @@ def test_cuda_graph_decode_with_scheduler_metadata():
 
 def test_unsupported_raises():
     F = _iface()
-    q, k, v = (x.to(DEV) for x in _qkv(1, 64, 64, 2, 2, 256, torch.bfloat16))
+    q, k, v = (x.to(DEV) for x in _qkv(1, 64, 64, 2, 2, 512, torch.bfloat16))
     with pytest.raises(NotImplementedError):
-        F.flash_attn_func(q, k, v)
+        F.flash_attn_func(q, k, v)  # head dim > 256 (hopper/flash_api.cpp:710 has the same limit)
+    q, k, v = (x.to(DEV).to(torch.float8_e4m3fn) for x in _qkv(1, 64, 64, 2, 2, 256, torch.bfloat16))
+    with pytest.raises(NotImplementedError):
+        F.flash_attn_func(q, k, v)  # fp8 with head dim > 128: no instance yet
     q, k, v = _qkv(1, 64, 64, 2, 2, 64, torch.bfloat16)
     with pytest.raises((RuntimeError, NotImplementedError)):
         F.flash_attn_func(q, k, v)  # CPU tensors: no fallback
