@@ -34,7 +34,6 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   const int elt = fp8 ? 1 : 2;
   if (fp8) FA_CHECK_ARG(p->d % 16 == 0 && p->dv % 16 == 0, "fp8 head dims must be multiples of 16");
   FA_UNSUPPORTED(p->d > 256 || p->dv > 256, "head dim > 256 is not supported (d=%d dv=%d)", p->d, p->dv);
-  FA_UNSUPPORTED(fp8 && (p->d > 128 || p->dv > 128), "fp8 with head dim > 128 not built yet (d=%d dv=%d)", p->d, p->dv);
   FA_UNSUPPORTED(p->k_new || p->v_new || p->rotary_cos, "append-KV / rotary handled by the caller-side kernel, not fa100_fwd");
   FA_UNSUPPORTED(fp8 && p->softcap > 0.f, "softcap with fp8 not supported");
   const bool varlen_q = p->cu_seqlens_q != nullptr;
@@ -144,6 +143,7 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
 #define FA_LAUNCH(HD_, ELT_, FP8_, F16_)                                                                      \
   (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, fmt, grid, stream)                 \
         : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, fmt, grid, stream))
+  if (fp8 && hd == 256) return launch_instance<256, 1, true, false, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
   if (fp8) return FA_LAUNCH(128, 1, true, false);
   if (hd == 256)
     return f16 ? launch_instance<256, 2, false, true, false>(kp, tmQ, tmK, tmV, fmt, grid, stream)

@@ -32,6 +32,15 @@ constexpr int kThreads = 12 * 32;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
+// e4m3 P = 2^(x - m + kFp8Offset): the offset keeps small probabilities out of the subnormal range (hopper/softmax.h:18-40
+// uses 8 with an exact running max).  Here the max may lag by kFp8RescaleThreshold, so the largest P is
+// 2^(offset + threshold) = 2^8.75 = 430 < 448 with offset 6, threshold 2.75 (e4m3 max; the cvt saturates anyway).  A threshold of 0 made every early key
+// block rescale O in tensor memory (any row of the warp with a new max): 325 clk per block on random data.
+#ifndef FA100_FP8_OFFSET
+#define FA100_FP8_OFFSET 6.0f
+#define FA100_FP8_THRESHOLD 2.75f
+#endif
+constexpr float kFp8Offset = FA100_FP8_OFFSET, kFp8RescaleThreshold = FA100_FP8_THRESHOLD;
 
 struct FwdKernelParams {
   void* o;

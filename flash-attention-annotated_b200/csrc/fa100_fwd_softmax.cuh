@@ -50,6 +50,30 @@ FA_DEVICE void ex2_poly2(float& a, float& b) {
       "mov.b32 %0, q0;\n\tmov.b32 %1, q1;\n\t}"
       : "+f"(a), "+f"(b));
 }
+// Degree-2 variant for e4m3 P (3 mantissa bits): 2^f on [0, 1) to 1.7e-3 relative, exponent spliced by one IMAD.
+// 9 issue slots per pair of scores and none of them on the MUFU pipe.
+FA_DEVICE void ex2_poly2_deg2(float& a, float& b) {
+  asm("{\n\t.reg .b64 x, r, f, pl;\n\t.reg .f32 a0, b0, r0, r1, p0, p1;\n\t.reg .b32 i0, i1, q0, q1;\n\t"
+      "max.ftz.f32 a0, %0, 0fC2800000;\n\tmax.ftz.f32 b0, %1, 0fC2800000;\n\t"
+      "mov.b64 x, {a0, b0};\n\t"
+      "mov.b64 pl, {0f4B400000, 0f4B400000};\n\t"
+      "add.rm.ftz.f32x2 r, x, pl;\n\t"
+      "sub.rn.ftz.f32x2 f, r, pl;\n\t"
+      "sub.rn.ftz.f32x2 f, x, f;\n\t"
+      "mov.b64 pl, {0f3EACA418, 0f3EACA418};\n\t"
+      "mov.b64 x, {0f3F285ADA, 0f3F285ADA};\n\t"
+      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
+      "mov.b64 x, {0f3F803884, 0f3F803884};\n\t"
+      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
+      "mov.b64 {p0, p1}, pl;\n\tmov.b64 {r0, r1}, r;\n\t"
+      "mov.b32 i0, r0;\n\tmov.b32 i1, r1;\n\tmov.b32 q0, p0;\n\tmov.b32 q1, p1;\n\t"
+      "mad.lo.s32 q0, i0, 8388608, q0;\n\tmad.lo.s32 q1, i1, 8388608, q1;\n\t"
+      "mov.b32 %0, q0;\n\tmov.b32 %1, q1;\n\t}"
+      : "+f"(a), "+f"(b));
+}
+#ifndef FA100_POLY_FP8
+#define FA100_POLY_FP8 0  // of every 8 scores of an interior e4m3 key block, how many take ex2_poly2_deg2
+#endif
 #ifndef FA100_POLY
 #define FA100_POLY 0   // of every 8 scores of an interior key block, how many take the polynomial exp2 (measured slower at full size: 2/8 -> 1217, 4/8 -> 1151 vs 1274 TFLOPS; kept as an experiment switch)
 #endif
@@ -168,7 +192,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       FA_PROF(2);
       const float m_cand = fmaxf(m_run, m_blk);
       // lazy rescale: keep the stale max unless it grew by more than 2^8 (NaN from -inf - -inf compares false)
-      const bool grow = (m_cand - m_run) * scale_log2 > (FP8 ? 0.0f : kRescaleThreshold);
+      const bool grow = (m_cand - m_run) * scale_log2 > (FP8 ? kFp8RescaleThreshold : kRescaleThreshold);
       const float acc_scale = grow ? exp2f((m_run - m_cand) * scale_log2) : 1.0f;
       if (grow) m_run = m_cand;
       if (nb != rg.n_max - 1 && __any_sync(0xffffffffu, grow)) {
@@ -185,20 +209,21 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
           tmem_st32(tO + c * 32, o);
         }
       }
-      const float m_sub = (m_run == -INFINITY) ? 0.f : m_run * scale_log2 - (FP8 ? 8.0f : 0.0f);
+      const float m_sub = (m_run == -INFINITY) ? 0.f : m_run * scale_log2 - (FP8 ? kFp8Offset : 0.0f);
       FA_PROF(2);
       // P = exp2(S * scale - max), packed to the operand dtype and written over S: keys [32c, 32c + 32) of the tile go to
       // columns [16c, +16) (16-bit operands) or [8c, +8) (e4m3)
       float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        if (FA100_POLY > 0 && !boundary) {
+        if ((FP8 ? FA100_POLY_FP8 : FA100_POLY) > 0 && !boundary) {
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
             float x0 = __uint_as_float(s[c][i]), x1 = __uint_as_float(s[c][i + 1]);
             if (FA100_F32X2) ffma2(x0, x1, scale_log2, -m_sub);
             else { x0 = fmaf(x0, scale_log2, -m_sub); x1 = fmaf(x1, scale_log2, -m_sub); }
-            if ((i & 7) >= 8 - FA100_POLY) ex2_poly2(x0, x1);
+            if (FP8 && (i & 7) >= 8 - FA100_POLY_FP8) ex2_poly2_deg2(x0, x1);
+            else if (!FP8 && (i & 7) >= 8 - FA100_POLY) ex2_poly2(x0, x1);
             else { x0 = ex2_approx(x0); x1 = ex2_approx(x1); }
             s[c][i] = __float_as_uint(x0); s[c][i + 1] = __float_as_uint(x1);
           }
@@ -272,8 +297,8 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       if (FP8) out_scale = p.v_descale ? p.v_descale[g.it.bi * p.v_descale_batch_stride + g.hk * p.v_descale_head_stride] : 1.f;
       float l_tot = l_run;
       const bool dead_row = (l_tot == 0.f) || (l_tot != l_tot);
-      const float inv = dead_row ? 0.f : out_scale / l_tot;  // O carries the same 2^8 offset as the row sum (fp8)
-      if (FP8) l_tot *= 0.00390625f;                          // undo the offset for the LSE
+      const float inv = dead_row ? 0.f : out_scale / l_tot;  // O carries the same 2^kFp8Offset as the row sum (fp8)
+      if (FP8) l_tot *= exp2f(-kFp8Offset);                        // undo the offset for the LSE
       const float lse_val = dead_row ? -INFINITY : (m_run * scale_log2 + log2f(l_tot)) * kLn2;
       const int64_t row_idx = g.seq.q_off + pos;
       if (row_valid) {

@@ -354,15 +354,16 @@ def test_kvcache_append_rotary(sq, s_new, mask, layout, rotary):
 
 
 @pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d,dv", [(128, 128), (64, 64), (96, 96), (256, 256), (192, 128)])
 @pytest.mark.parametrize("sq,sk", [(128, 128), (700, 700), (113, 203), (1, 900)])
-def test_fp8(sq, sk, causal):
+def test_fp8(sq, sk, d, dv, causal):
     """e4m3 inputs, fp32 (b, h_k) descales, bf16 output (hopper/test_flash_attn.py:118-149, multipliers :986-989)."""
     F = _iface()
     g = torch.Generator().manual_seed(8)
-    b, h, hk, d = 2, 4, 2, 128
+    b, h, hk = 2, 4, 2
     q = torch.randn(b, sq, h, d, generator=g).to(torch.float8_e4m3fn)
     k = torch.randn(b, sk, hk, d, generator=g).to(torch.float8_e4m3fn)
-    v = torch.randn(b, sk, hk, d, generator=g).to(torch.float8_e4m3fn)
+    v = torch.randn(b, sk, hk, dv, generator=g).to(torch.float8_e4m3fn)
     ds = [torch.rand(b, hk, generator=g) * 2 for _ in range(3)]
     qr, kr, vr = (x.to(torch.bfloat16) for x in (q, k, v))
     kw = dict(causal=causal, q_descale=ds[0], k_descale=ds[1], v_descale=ds[2])
@@ -372,6 +373,32 @@ def test_fp8(sq, sk, causal):
                                  v_descale=ds[2].to(DEV), return_attn_probs=True)
     assert out.dtype == torch.bfloat16
     _check(out, lse, ref, low, lse_ref, rtol=4.0)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float8_e4m3fn])
+@pytest.mark.parametrize("step", [0.5, 2.0, 6.0])
+def test_growing_row_max(step, dtype):
+    """Scores that keep growing in the order the kernel walks the key blocks (last block first): every block raises the row
+    max by `step` nats, so the lazy rescale (stale max within 2^8, or 2^2.75 for e4m3 P) and the accumulator rescale in
+    tensor memory are exercised at every step; random data almost never triggers them."""
+    F = _iface()
+    g = torch.Generator().manual_seed(21)
+    b, h, sq, sk, d = 1, 2, 160, 1280, 128
+    q = torch.randn(b, sq, h, d, generator=g)
+    k = torch.randn(b, sk, h, d, generator=g) * 0.1
+    v = torch.randn(b, sk, h, d, generator=g)
+    q[..., 0] = 4.0                                            # s = q . k / sqrt(d): the first component carries the ramp
+    ramp = (sk // 128 - 1 - torch.arange(sk) // 128).float() * step * (d ** 0.5) / 4.0
+    k[..., 0] = ramp[None, :, None]
+    lo = torch.float8_e4m3fn if dtype == torch.float8_e4m3fn else dtype
+    q, k, v = (x.to(lo) for x in (q, k, v))
+    qr, kr, vr = (x.to(torch.bfloat16) for x in (q, k, v)) if dtype == torch.float8_e4m3fn else (q, k, v)
+    ref, lse_ref = A.attention_oracle(qr, kr, vr)
+    kw = dict(intermediate_dtype=torch.float8_e4m3fn) if dtype == torch.float8_e4m3fn else {}
+    low, _ = A.attention_oracle(qr, kr, vr, upcast=False, reorder_ops=True, **kw)
+    for num_splits in (1, 3):
+        out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), num_splits=num_splits, return_attn_probs=True)
+        _check(out, lse, ref, low, lse_ref, rtol=4.0 if dtype == torch.float8_e4m3fn else 2.0)
 
 
 @pytest.mark.parametrize("num_splits", [1, 2, 3, 5, 17, 32, 55, 97, 133])
@@ -556,9 +583,6 @@ def test_unsupported_raises():
     q, k, v = (x.to(DEV) for x in _qkv(1, 64, 64, 2, 2, 512, torch.bfloat16))
     with pytest.raises(NotImplementedError):
         F.flash_attn_func(q, k, v)  # head dim > 256 (hopper/flash_api.cpp:710 has the same limit)
-    q, k, v = (x.to(DEV).to(torch.float8_e4m3fn) for x in _qkv(1, 64, 64, 2, 2, 256, torch.bfloat16))
-    with pytest.raises(NotImplementedError):
-        F.flash_attn_func(q, k, v)  # fp8 with head dim > 128: no instance yet
     q, k, v = _qkv(1, 64, 64, 2, 2, 64, torch.bfloat16)
     with pytest.raises((RuntimeError, NotImplementedError)):
         F.flash_attn_func(q, k, v)  # CPU tensors: no fallback

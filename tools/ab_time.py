@@ -8,7 +8,7 @@ sys.path[:0] = [os.path.join(%r, "flash-attention-annotated_b200")]
 from flash_attn_interface import flash_attn_func
 dev = "cuda"
 res = []
-for (b, s, h, hk, causal, dt) in ((8, 8192, 32, 8, True, torch.bfloat16), (4, 8192, 32, 8, False, torch.bfloat16), (4, 16384, 16, 16, True, torch.float8_e4m3fn)):
+for (b, s, h, hk, causal, dt) in ((8, 8192, 32, 8, True, torch.bfloat16), (4, 8192, 32, 8, False, torch.bfloat16), (4, 16384, 16, 16, True, torch.float8_e4m3fn), (4, 16384, 16, 16, False, torch.float8_e4m3fn)):
     q = torch.randn(b, s, h, 128, device=dev, dtype=torch.bfloat16).to(dt)
     k = torch.randn(b, s, hk, 128, device=dev, dtype=torch.bfloat16).to(dt)
     v = torch.randn(b, s, hk, 128, device=dev, dtype=torch.bfloat16).to(dt)
@@ -28,12 +28,12 @@ rounds = int(os.environ.get("AB_ROUNDS", "3"))
 out = {l: [] for l in libs}
 for r in range(rounds):
     for l in libs:
-        p = subprocess.run([sys.executable, "-c", CHILD], env=dict(os.environ, FA100_LIB=l), capture_output=True, text=True, timeout=150)
+        p = subprocess.run([sys.executable, "-c", CHILD], env=dict(os.environ, FA100_LIB=l), capture_output=True, text=True, timeout=200)
         line = [x for x in p.stdout.splitlines() if x.startswith("RES")]
         if not line:
             print(l, "FAILED", p.stderr[-500:]); continue
         out[l].append([float(x) for x in line[0].split()[1:]])
-print(f"{'library':28s} {'bf16 causal':>22s} {'bf16 non-causal':>22s} {'fp8 causal':>22s}   (TFLOPS: best / median of {rounds})")
+print(f"{'library':28s} {'bf16 causal':>22s} {'bf16 non-causal':>22s} {'fp8 causal':>22s} {'fp8 non-causal':>22s}   (TFLOPS: best / median of {rounds})")
 for l in libs:
     if out[l]:
         cols = list(zip(*out[l]))
