@@ -2,6 +2,10 @@
 #pragma once
 #include "fa100_fwd_kernel.cuh"
 
+#ifndef FA100_GARBAGE
+#define FA100_GARBAGE 0
+#endif
+
 namespace fa100 {
 
 // Work-item geometry every role derives identically (no communication needed).
@@ -96,7 +100,8 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
       mbar_wait(&bar->kv_empty[stage], ring.phase ^ 1, 0x20 + kv);
       uint8_t* dst = sKV + stage * L::kKVBytes;
       const int boxes = kv == 0 ? p.qk_boxes : p.v_boxes;
-      if (p.page_size == 0) {
+      if (FA100_GARBAGE & 16) { if (elect_one()) mbar_arrive(&bar->kv_full[stage]); }  // timing only: no K/V traffic into shared memory
+      else if (p.page_size == 0) {
         if (elect_one()) {
           mbar_arrive_expect_tx(&bar->kv_full[stage], boxes * kHalfBytes);
 #pragma unroll
@@ -189,7 +194,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
 #pragma unroll
       for (int ks = 0; ks < kQKSlices; ++ks) {
         const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
-        if (ks < p.qk_slices) mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
+        if (ks < p.qk_slices && !(FA100_GARBAGE & 64)) mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
       }
       tc_commit(&bar->s_full[t]);
       if (last_use_of_q) tc_commit(&bar->q_empty[t]);
@@ -210,7 +215,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
       const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboV;
 #pragma unroll
       for (int ks = 0; ks < kPVSlices; ++ks)
-        mma_ts<FP8>(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc, (!first || ks > 0));
+        if (!(FA100_GARBAGE & 32)) mma_ts<FP8>(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc, (!first || ks > 0));
       tc_commit(&bar->pv_done[t]);
       if (last) tc_commit(&bar->o_full[t]);
     }
