@@ -5,13 +5,15 @@
 #include "fa100_fwd_softmax.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
+#include <numeric>
 
 namespace fa100 {
 
 template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
 static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK,
-                           const CUtensorMap& tmV, uint32_t fmt, int grid, cudaStream_t stream) {
+                           const CUtensorMap& tmV, const CUtensorMap& tmO, uint32_t fmt, int grid, cudaStream_t stream) {
   using L = FwdSmem<HD, ELT>;
   auto kernel = fa100_fwd_kernel<HD, ELT, FP8, F16, DUAL>;
   static bool attr_set = false;  // benign race: the call is idempotent
@@ -19,7 +21,7 @@ static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, co
     FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes));
     attr_set = true;
   }
-  kernel<<<grid, kThreads, L::kTotalBytes, stream>>>(kp, tmQ, tmK, tmV, fmt);
+  kernel<<<grid, kThreads, L::kTotalBytes, stream>>>(kp, tmQ, tmK, tmV, tmO, fmt);
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
@@ -42,8 +44,6 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   FA_CHECK_ARG(!(paged && varlen_k), "page_table and cu_seqlens_k are exclusive");
   if (paged) {
     FA_CHECK_ARG(p->page_size > 0 && p->num_pages > 0, "paged KV needs page_size and num_pages");
-    FA_UNSUPPORTED(!(p->page_size % 128 == 0 || (p->page_size >= 8 && 128 % p->page_size == 0)),
-                   "page_size %d: TMA path needs a multiple of 128 or a divisor of 128 that is >= 8", p->page_size);
     FA_UNSUPPORTED(p->leftpad_k != nullptr, "leftpad_k with paged KV not supported");
   }
   const int splits = plan->num_splits;
@@ -73,7 +73,10 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   kp.v_descale_batch_stride = p->v_descale_batch_stride; kp.v_descale_head_stride = p->v_descale_head_stride;
   kp.b = p->b; kp.h = p->h; kp.h_k = p->h_k; kp.seqlen_q = p->seqlen_q; kp.seqlen_k = p->seqlen_k; kp.d = p->d; kp.dv = p->dv;
   kp.page_size = paged ? p->page_size : 0;
-  kp.kv_box_rows = paged ? std::min(128, p->page_size) : 128;
+  // paged K/V: one TMA box never crosses a page.  gcd(page_size, 128) rows per box serves every page size (the reference
+  // falls back to cp.async gathers when the page does not hold whole key blocks, hopper/paged_kv.h:233-283); pages of
+  // 128 rows or a multiple are one box per key block, a page of 1 row is 128 boxes.
+  kp.kv_box_rows = paged ? std::gcd(128, p->page_size) : 128;
   const int G = p->h / p->h_k;
   kp.qheads_per_kv = G;
   kp.pack = plan->pack_gqa ? G : 1;
@@ -129,6 +132,23 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
     rc = encode_tensor_map(&tmV, p->dtype, 4, p->v, dimsV, strV, box);
     if (rc) return rc;
   }
+  // O through TMA stores when a tile's rows are one dense run of one (batch, head): no packed-varlen q (a box would run
+  // into the next sequence), no seqused_q, no pack-GQA (rows interleave heads), no fp32 partials; hdim <= 128.
+  CUtensorMap tmO = tmQ;
+  {
+    static const bool no_tma_store = getenv("FA100_NO_TMA_STORE") != nullptr;  // A/B switch: register stores everywhere
+    const bool o_tma = !no_tma_store && p->o_accum == nullptr && !varlen_q && !p->seqused_q && kp.pack == 1 &&
+                       std::max(p->d, p->dv) <= 128 && (p->o_row_stride * 2) % 16 == 0 && (p->o_head_stride * 2) % 16 == 0 &&
+                       (p->o_batch_stride * 2) % 16 == 0 && reinterpret_cast<uintptr_t>(p->o) % 16 == 0;
+    if (o_tma) {
+      uint64_t dims[4] = {uint64_t(p->dv), uint64_t(p->seqlen_q), uint64_t(p->h), uint64_t(p->b)};
+      uint64_t str[4] = {0, uint64_t(p->o_row_stride) * 2, uint64_t(p->o_head_stride) * 2, uint64_t(p->o_batch_stride) * 2};
+      uint32_t box[4] = {64, 128, 1, 1};
+      int rc = encode_tensor_map(&tmO, p->dtype == FA100_FP16 ? FA100_FP16 : FA100_BF16, 4, p->o, dims, str, box);
+      if (rc) return rc;
+      kp.o_tma = 1;
+    }
+  }
   if (p->o_accum == nullptr) {
     FA_CHECK_ARG((p->o_row_stride % 8 == 0) && (p->o_head_stride % 8 == 0) && (p->o_batch_stride % 8 == 0) &&
                      (reinterpret_cast<uintptr_t>(p->o) % 16 == 0),
@@ -141,13 +161,13 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   const int hd = solo ? 256 : ((p->d <= 64 && p->dv <= 64 && !fp8) ? 64 : 128);
   const bool f16 = p->dtype == FA100_FP16;
 #define FA_LAUNCH(HD_, ELT_, FP8_, F16_)                                                                      \
-  (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, fmt, grid, stream)                 \
-        : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, fmt, grid, stream))
-  if (fp8 && hd == 256) return launch_instance<256, 1, true, false, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+  (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)                 \
+        : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream))
+  if (fp8 && hd == 256) return launch_instance<256, 1, true, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
   if (fp8) return FA_LAUNCH(128, 1, true, false);
   if (hd == 256)
-    return f16 ? launch_instance<256, 2, false, true, false>(kp, tmQ, tmK, tmV, fmt, grid, stream)
-               : launch_instance<256, 2, false, false, false>(kp, tmQ, tmK, tmV, fmt, grid, stream);
+    return f16 ? launch_instance<256, 2, false, true, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
+               : launch_instance<256, 2, false, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
   if (hd == 64) return f16 ? FA_LAUNCH(64, 2, false, true) : FA_LAUNCH(64, 2, false, false);
   return f16 ? FA_LAUNCH(128, 2, false, true) : FA_LAUNCH(128, 2, false, false);
 #undef FA_LAUNCH

@@ -67,7 +67,7 @@ struct FwdKernelParams {
   int64_t v_descale_batch_stride, v_descale_head_stride;
   int32_t b, h, h_k, seqlen_q, seqlen_k, d, dv;
   int32_t page_size;      // 0 = not paged
-  int32_t kv_box_rows;    // rows per K/V TMA box: min(128, page_size)
+  int32_t kv_box_rows;    // rows per K/V TMA box: 128, or gcd(128, page_size) when paged
   int32_t qk_boxes;       // 128-byte column boxes of Q / K actually loaded: ceil(d * elt / 128) <= HD * elt / 128
   int32_t v_boxes;        // same for V: ceil(dv * elt / 128)
   int32_t qk_slices;      // MMA k-slices of S = Q K^T actually issued: ceil(d / (32 / elt))
@@ -81,6 +81,7 @@ struct FwdKernelParams {
   int32_t num_work;
   int32_t is_causal, is_local, window_left, window_right, attention_chunk;
   int32_t out_fp16;       // 1: fp16 output, 0: bf16 output
+  int32_t o_tma;          // 1: O leaves through shared memory and TMA stores (dense batch, no pack-GQA, no partials)
   float scale_log2;       // softmax_scale * log2(e)   (softcap: softcap * log2(e))
   float softcap_pre;      // softmax_scale / softcap, 0 when softcap is off
   float softmax_scale;
@@ -180,10 +181,14 @@ struct FwdSmem {
   // head dims above 128 run one Q tile per work item: O alone needs 256 TMEM columns, so the second tile pipeline stays
   // idle (SOLO geometry in fa100_fwd_roles.cuh) and only one Q slot is carved out
   static constexpr int kQSlots = HD > 128 ? 1 : kQTiles;
-  static constexpr int kStagesRaw = ((kBudget - kQSlots * kQBytes) / kKVBytes) & ~1;  // even: half K stages, half V stages
+  // O staging for the TMA-store epilogue: per Q tile one [128 rows][128 B] box (64 output columns of 16 bits), reused for
+  // every 64-column slice of the tile.  The hdim-256 instance has no room for it and keeps the register stores.
+  static constexpr int kOStageBytes = kBlockM * 128;
+  static constexpr int kOBytes = HD > 128 ? 0 : kQTiles * kOStageBytes;
+  static constexpr int kStagesRaw = ((kBudget - kQSlots * kQBytes - kOBytes) / kKVBytes) & ~1;  // even: half K stages, half V stages
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static_assert(kStages >= 2, "need at least one K and one V stage");
-  static constexpr int kDataBytes = kQSlots * kQBytes + kStages * kKVBytes;
+  static constexpr int kDataBytes = kQSlots * kQBytes + kStages * kKVBytes + kOBytes;
   static constexpr int kTotalBytes = kDataBytes + kBarrierBytes;
 };
 

@@ -42,6 +42,7 @@ FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w) {
 #pragma unroll
   for (int t = 0; t < kQTiles; ++t) {
     g.tr[t] = tile_range(p, g.seq, (g.it.m_blk * kQTiles + t) * p.pos_per_tile, g.it.split);
+    if ((FA100_GARBAGE & 128) && t == 1) { g.tr[t].has_rows = false; g.tr[t].n_min = g.tr[t].n_max = 0; }  // timing only: tile 1 idle
     if (g.tr[t].n_max > g.tr[t].n_min) { g.n_lo = min(g.n_lo, g.tr[t].n_min); g.n_hi = max(g.n_hi, g.tr[t].n_max); }
   }
   return g;
@@ -110,12 +111,12 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
                         g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
         }
       } else {
-        // paged: kv_box_rows = min(128, page_size) rows per box; page ids come from the table
+        // paged: kv_box_rows = gcd(128, page_size) rows per box (a box never crosses a page); page ids come from the table
         const int32_t* tbl = p.page_table + int64_t(g.it.bi) * p.page_table_batch_stride;
         if (elect_one()) mbar_arrive_expect_tx(&bar->kv_full[stage], boxes * kHalfBytes);
         for (int r0 = 0; r0 < kBlockN; r0 += p.kv_box_rows) {
           const int row = nb * kBlockN + r0;
-          const int page = tbl[row / p.page_size];
+          const int page = tbl[min(row, max(g.seq.sk - 1, 0)) / p.page_size];  // rows past the end are masked; keep the table read in range
           if (elect_one()) {
 #pragma unroll
             for (int hb = 0; hb < kBoxesD; ++hb)

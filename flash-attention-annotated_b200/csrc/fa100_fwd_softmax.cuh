@@ -156,7 +156,7 @@ FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row) {
 // row sum need no shuffles.  The step loop has two bodies: a lean one for interior key blocks (no mask, no softcap; it
 // is the instruction stream tools/ubench/ubench_softmax.cu measures in isolation) and a general one for boundary blocks.
 template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
-FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t tmem, int warp, int lane) {
+FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, uint8_t* sO, FwdBarriers* bar, uint32_t tmem, int warp, int lane) {
   const int t = warp >> 2, q = warp & 3;
   const int row = q * 32 + lane;
   const uint32_t tS = tmem + (uint32_t(q * 32) << 16);  // the score buffer both tiles take turns in
@@ -376,6 +376,47 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
                                             row_idx * p.o_row_stride + hq * p.o_head_stride);
       float4* o32 = reinterpret_cast<float4*>(p.o_accum + part * p.oacc_split_stride + g.it.bi * p.oacc_batch_stride +
                                               hq * p.oacc_head_stride + row_idx * p.dv);
+      if (HD <= 128 && p.o_tma) {
+        // TMA-store epilogue (role of the reference's smem_o + TMA store, hopper/epilogue_fwd.hpp:262-318): per 64-column
+        // slice every thread converts its row, writes it into this tile's [128][128 B] staging box in the 128-byte
+        // swizzle, and one thread sends the box with a bulk tensor store; rows past seqlen_q are clipped by the tensor map.
+        // The staging box is free again once the previous store has read it (wait_group.read by the issuing thread,
+        // at the top of the next slice or the next work item).
+        uint8_t* stage = sO + t * FwdSmem<HD, ELT>::kOStageBytes;
+        const bool issuer = (q == 0 && lane == 0);
+#pragma unroll
+        for (int sl = 0; sl < HD / 64; ++sl) {
+          if (sl * 64 >= p.dv) break;
+          uint32_t pk[32];
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            uint32_t o[32];
+            if (live) { tmem_ld32(tO + sl * 64 + hf * 32, o); tmem_ld_wait(); }
+            else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = 0u;
+            }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float a = __uint_as_float(o[2 * i]) * inv, b2 = __uint_as_float(o[2 * i + 1]) * inv;
+              pk[hf * 16 + i] = F16 ? pack_f16(a, b2) : pack_bf16(a, b2);
+            }
+          }
+          if (issuer) tma_store_wait_read0();
+          named_bar_sync(1 + t, 128);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            uint4 u = make_uint4(pk[ch * 4], pk[ch * 4 + 1], pk[ch * 4 + 2], pk[ch * 4 + 3]);
+            *reinterpret_cast<uint4*>(stage + row * 128 + ((ch ^ (row & 7)) << 4)) = u;
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(1 + t, 128);
+          if (issuer) {
+            tma_store_4d(tmO, stage, sl * 64, pos - in_tile, hq, g.seq.bq);
+            tma_store_commit();
+          }
+        }
+      } else
 #pragma unroll
       for (int c = 0; c < HD / 32; ++c) {
         if (c * 32 >= p.dv) break;
@@ -417,6 +458,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
       }
     }
   }
+  if (HD <= 128 && p.o_tma && q == 0 && lane == 0) tma_store_wait0();  // the staging box must outlive the last store
   FA_PROF(7);
   FA_PROF_FLUSH();
 }
@@ -425,17 +467,19 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, FwdBarriers* bar, uint32_t
 template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
 __global__ void __launch_bounds__(kThreads, 1)
 fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constant__ CUtensorMap tmQ,
-                 const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
+                 const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                 const __grid_constant__ CUtensorMap tmO, uint32_t fmt) {
   using L = FwdSmem<HD, ELT>;
   extern __shared__ __align__(1024) uint8_t smem[];  // 128-byte swizzle atoms need 1 KB alignment
   uint8_t* sQ = smem;
   uint8_t* sKV = smem + L::kQSlots * L::kQBytes;
+  uint8_t* sO = sKV + L::kStages * L::kKVBytes;
   FwdBarriers* bar = reinterpret_cast<FwdBarriers*>(smem + L::kDataBytes);
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   FA_TRACE_BEGIN();
   if (smem_u32(smem) & 1023u) __trap();
 
-  if (warp == kLoadWarp && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); }
+  if (warp == kLoadWarp && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); if (p.o_tma) tma_prefetch_desc(&tmO); }
   if (warp == kMmaWarp && lane == 0) {
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
@@ -456,7 +500,7 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
   // register pool at launch: 384 threads x 168; warps 8-11 give 112 each to the 8 softmax warps (+56 each)
   if (warp < kSoftmaxWarps) {
     setmaxnreg_inc<224>();
-    softmax_role<HD, ELT, FP8, F16, DUAL>(p, bar, tmem, warp, lane);
+    softmax_role<HD, ELT, FP8, F16, DUAL>(p, &tmO, sO, bar, tmem, warp, lane);
   } else {
     setmaxnreg_dec<56>();
     if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL, true>(p, fmt, sQ, sKV, bar, tmem);

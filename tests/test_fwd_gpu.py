@@ -237,6 +237,26 @@ def test_kvcache(sq, sk, page_size, causal):
         _check(out, lse, ref, low, lse_ref)
 
 
+@pytest.mark.parametrize("page_size", [1, 3, 8, 24, 48, 96, 384])
+@pytest.mark.parametrize("sq,sk", [(1, 339), (16, 1000)])
+def test_kvcache_any_page_size(sq, sk, page_size):
+    """Page sizes that neither divide nor are a multiple of the 128-key block (the reference serves them with its
+    cp.async gather path, hopper/paged_kv.h:233-283; here gcd(page, 128) rows per TMA box)."""
+    F = _iface()
+    g = torch.Generator().manual_seed(60 + page_size)
+    b, h, hk, d = 3, 8, 2, 128
+    q = torch.randn(b, sq, h, d, generator=g).to(torch.bfloat16)
+    lens = torch.randint(max(sq, sk // 2), sk + 1, (b,), generator=g, dtype=torch.int32)
+    kd, vd, table, kin, vin = A.paged_kvcache(sk, page_size, b, hk, d, d, torch.bfloat16, generator=g)
+    ref, lse_ref = A.attention_oracle(q, kd, vd, k_lens=lens, causal=True)
+    low, _ = A.attention_oracle(q, kd, vd, k_lens=lens, causal=True, upcast=False, reorder_ops=True)
+    for num_splits in (0, 3):
+        out, lse, *_ = F.flash_attn_with_kvcache(q.to(DEV), kin.to(DEV), vin.to(DEV), cache_seqlens=lens.to(DEV),
+                                                 page_table=table.to(DEV), causal=True, num_splits=num_splits,
+                                                 return_softmax_lse=True)
+        _check(out, lse, ref, low, lse_ref)
+
+
 def test_kvcache_batch_idx_and_leftpad():
     F = _iface()
     g = torch.Generator().manual_seed(7)

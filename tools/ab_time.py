@@ -28,7 +28,8 @@ rounds = int(os.environ.get("AB_ROUNDS", "3"))
 out = {l: [] for l in libs}
 for r in range(rounds):
     for l in libs:
-        p = subprocess.run([sys.executable, "-c", CHILD], env=dict(os.environ, FA100_LIB=l), capture_output=True, text=True, timeout=200)
+        lib, *envs = l.split(":")  # "libfa100.so:FA100_NO_TMA_STORE=1" = that library with an environment switch set
+        p = subprocess.run([sys.executable, "-c", CHILD], env=dict(os.environ, FA100_LIB=lib, **dict(e.split("=") for e in envs)), capture_output=True, text=True, timeout=200)
         line = [x for x in p.stdout.splitlines() if x.startswith("RES")]
         if not line:
             print(l, "FAILED", p.stderr[-500:]); continue
