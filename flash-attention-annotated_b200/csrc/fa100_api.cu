@@ -146,8 +146,7 @@ const char* fa100_last_error(void) { return fa100::last_error(); }
 
 int fa100_plan(const Fa100Shape* shape, Fa100Plan* out) { return fa100::make_plan(shape, out); }
 
-int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream) {
-  if (!p) return fa100::set_error(FA100_ERR_INVALID, "null params");
+static int plan_of(const Fa100FwdParams* p, Fa100Plan* plan) {
   Fa100Shape s;
   std::memset(&s, 0, sizeof(s));
   s.b = p->b; s.seqlen_q = p->seqlen_q; s.seqlen_k = p->seqlen_k; s.h = p->h; s.h_k = p->h_k; s.d = p->d; s.dv = p->dv;
@@ -156,10 +155,25 @@ int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream) {
   s.num_splits = p->num_splits < 1 ? 1 : p->num_splits;
   s.pack_gqa = p->pack_gqa ? 1 : 0;
   s.num_sm = p->num_sm;
+  return fa100::make_plan(&s, plan);
+}
+
+int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream) {
+  if (!p) return fa100::set_error(FA100_ERR_INVALID, "null params");
   Fa100Plan plan;
-  int rc = fa100::make_plan(&s, &plan);
+  int rc = plan_of(p, &plan);
   if (rc) return rc;
   return fa100::launch_fwd(p, &plan, static_cast<cudaStream_t>(stream));
+}
+
+int64_t fa100_scheduler_metadata_words(int32_t b) { return fa100::scheduler_metadata_words(b); }
+
+int fa100_prepare_scheduler(const Fa100FwdParams* p, int32_t* metadata, int64_t metadata_words, fa100_stream_t stream) {
+  if (!p) return fa100::set_error(FA100_ERR_INVALID, "null params");
+  Fa100Plan plan;
+  int rc = plan_of(p, &plan);
+  if (rc) return rc;
+  return fa100::launch_prepare_scheduler(p, &plan, metadata, metadata_words, static_cast<cudaStream_t>(stream));
 }
 
 int fa100_combine(const Fa100CombineParams* p, fa100_stream_t stream) {

@@ -26,33 +26,14 @@ static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, co
   return FA100_OK;
 }
 
-int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stream) {
-  // ---- validation (hopper/flash_api.cpp:710-856)
-  FA_CHECK_ARG(p->q && p->k && p->v, "q, k and v must be non-null");
-  FA_CHECK_ARG(p->dtype == FA100_BF16 || p->dtype == FA100_FP16 || p->dtype == FA100_E4M3, "unsupported dtype %d", p->dtype);
-  FA_CHECK_ARG(p->b > 0 && p->h > 0 && p->h_k > 0 && p->h % p->h_k == 0, "bad batch/head counts b=%d h=%d h_k=%d", p->b, p->h, p->h_k);
-  FA_CHECK_ARG(p->d > 0 && p->dv > 0 && p->d % 8 == 0 && p->dv % 8 == 0, "head dims must be multiples of 8 (d=%d dv=%d)", p->d, p->dv);
+// Everything the kernels need that is not a tensor map; shared by the forward launch and the schedule kernel.
+static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, FwdKernelParams& kp) {
   const bool fp8 = p->dtype == FA100_E4M3;
   const int elt = fp8 ? 1 : 2;
-  if (fp8) FA_CHECK_ARG(p->d % 16 == 0 && p->dv % 16 == 0, "fp8 head dims must be multiples of 16");
-  FA_UNSUPPORTED(p->d > 256 || p->dv > 256, "head dim > 256 is not supported (d=%d dv=%d)", p->d, p->dv);
-  FA_UNSUPPORTED(p->k_new || p->v_new || p->rotary_cos, "append-KV / rotary handled by the caller-side kernel, not fa100_fwd");
-  FA_UNSUPPORTED(fp8 && p->softcap > 0.f, "softcap with fp8 not supported");
   const bool varlen_q = p->cu_seqlens_q != nullptr;
   const bool varlen_k = p->cu_seqlens_k != nullptr;
   const bool paged = p->page_table != nullptr;
-  FA_CHECK_ARG(!(paged && varlen_k), "page_table and cu_seqlens_k are exclusive");
-  if (paged) {
-    FA_CHECK_ARG(p->page_size > 0 && p->num_pages > 0, "paged KV needs page_size and num_pages");
-    FA_UNSUPPORTED(p->leftpad_k != nullptr, "leftpad_k with paged KV not supported");
-  }
   const int splits = plan->num_splits;
-  if (splits > 1) FA_CHECK_ARG(p->o_accum && p->lse_accum, "num_splits > 1 needs o_accum and lse_accum");
-  FA_CHECK_ARG((p->o_accum == nullptr) == (p->lse_accum == nullptr), "o_accum and lse_accum must be given together");
-  FA_CHECK_ARG(p->o_accum != nullptr || (p->o != nullptr && p->lse != nullptr), "o and lse are required without o_accum");
-
-  // ---- kernel parameters
-  FwdKernelParams kp;
   std::memset(&kp, 0, sizeof(kp));
   kp.o = p->o; kp.lse = p->lse; kp.o_accum = p->o_accum; kp.lse_accum = p->lse_accum;
   kp.o_batch_stride = p->o_batch_stride; kp.o_row_stride = p->o_row_stride; kp.o_head_stride = p->o_head_stride;
@@ -92,6 +73,8 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   kp.heads_work = plan->pack_gqa ? p->h_k : p->h;
   kp.num_splits = cta_splits;
   kp.num_work = kp.num_m_blocks * p->b * kp.heads_work * cta_splits;
+  kp.tiles_per_item = (dual || solo) ? 1 : 2;
+  kp.sched = p->scheduler_metadata ? p->scheduler_metadata + kSchedHeaderWords : nullptr;
   // causal / local normalisation (hopper/flash_api.cpp:148-160, 796-805)
   int wl = p->window_left, wr = p->window_right;
   bool causal = p->is_causal != 0;
@@ -106,6 +89,110 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   kp.softmax_scale = p->softmax_scale;
   if (p->softcap > 0.f) { kp.softcap_pre = p->softmax_scale / p->softcap; kp.scale_log2 = p->softcap * kLog2e; }
   else { kp.softcap_pre = 0.f; kp.scale_log2 = p->softmax_scale * kLog2e; }
+
+  (void)varlen_k;
+}
+
+// ----------------------------------------------------------------------------- schedule for ragged batches
+// Role of prepare_varlen_num_blocks_kernel (hopper/flash_prepare_scheduler.cu:43-215): one CTA looks at every batch
+// element's real lengths, counts its row blocks and key blocks with the same arithmetic the forward kernel uses
+// (load_seq, tile_range), orders the batch elements by key-block count (longest first, the reference's LPT sort
+// `:150-190`) and writes the prefix of work items over that order.  The forward kernel then walks a list without
+// entries for rows past a sequence's end, with the expensive sequences at the front of every CTA's walk.
+__global__ void __launch_bounds__(1024, 1)
+fa100_schedule_kernel(const FwdKernelParams p, int32_t* __restrict__ meta, int32_t* __restrict__ scratch) {
+  int32_t* order = meta + 2;
+  int32_t* prefix = order + p.b;
+  int32_t* cost = scratch;             // key blocks of the batch element (sort key)
+  int32_t* items = scratch + p.b;      // work items of the batch element
+  const int rows_item = p.tiles_per_item * p.pos_per_tile;
+  FwdKernelParams whole = p;  // key blocks of a tile before they are cut into splits
+  whole.num_splits = 1;
+  for (int bi = threadIdx.x; bi < p.b; bi += blockDim.x) {
+    const SeqInfo sq = load_seq(p, bi);
+    const int m_blocks = sq.sq > 0 ? (sq.sq + rows_item - 1) / rows_item : 0;
+    int c = 0;
+    for (int t = 0; t < m_blocks * p.tiles_per_item; ++t) {
+      const TileRange r = tile_range(whole, sq, t * p.pos_per_tile, 0);
+      c += r.n_max - r.n_min;
+    }
+    cost[bi] = c;
+    items[bi] = m_blocks * p.heads_work * p.num_splits;
+  }
+  __syncthreads();
+  // rank sort (stable): position = batches with a larger cost, or the same cost and a smaller index
+  for (int bi = threadIdx.x; bi < p.b; bi += blockDim.x) {
+    const int c = cost[bi];
+    int rank = 0;
+    for (int j = 0; j < p.b; ++j) { const int cj = cost[j]; rank += (cj > c) || (cj == c && j < bi); }
+    order[rank] = bi;
+  }
+  __syncthreads();
+  // exclusive prefix of work items over the order: per-thread runs, then a scan of the 1024 run totals
+  __shared__ int32_t run_total[1024];
+  const int per = (p.b + blockDim.x - 1) / blockDim.x;
+  const int lo = min(int(threadIdx.x) * per, p.b), hi = min(lo + per, p.b);
+  int sum = 0;
+  for (int r = lo; r < hi; ++r) sum += items[order[r]];
+  run_total[threadIdx.x] = sum;
+  __syncthreads();
+  for (int off = 1; off < int(blockDim.x); off <<= 1) {
+    const int v = threadIdx.x >= off ? run_total[threadIdx.x - off] : 0;
+    __syncthreads();
+    run_total[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int acc = run_total[threadIdx.x] - sum;
+  for (int r = lo; r < hi; ++r) { prefix[r] = acc; acc += items[order[r]]; }
+  if (threadIdx.x == blockDim.x - 1) { prefix[p.b] = run_total[threadIdx.x]; meta[0] = run_total[threadIdx.x]; meta[1] = p.b; }
+}
+
+int64_t scheduler_metadata_words(int b) { return kSchedHeaderWords + 2 + int64_t(b) + (b + 1) + 2 * int64_t(b); }
+
+int launch_prepare_scheduler(const Fa100FwdParams* p, const Fa100Plan* plan, int32_t* metadata, int64_t words, cudaStream_t stream) {
+  FA_CHECK_ARG(metadata != nullptr, "metadata must be non-null");
+  FA_CHECK_ARG(p->b > 0 && p->h > 0 && p->h_k > 0 && p->h % p->h_k == 0, "bad batch/head counts b=%d h=%d h_k=%d", p->b, p->h, p->h_k);
+  FA_CHECK_ARG(words >= scheduler_metadata_words(p->b), "metadata holds %lld words, %lld needed for batch %d", (long long)words,
+               (long long)scheduler_metadata_words(p->b), p->b);
+  FwdKernelParams kp;
+  fill_kernel_params(p, plan, kp);
+  int32_t* body = metadata + kSchedHeaderWords;
+  fa100_schedule_kernel<<<1, 1024, 0, stream>>>(kp, body, body + 2 + p->b + (p->b + 1));
+  FA_CUDA(cudaGetLastError());
+  return FA100_OK;
+}
+
+int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stream) {
+  // ---- validation (hopper/flash_api.cpp:710-856)
+  FA_CHECK_ARG(p->q && p->k && p->v, "q, k and v must be non-null");
+  FA_CHECK_ARG(p->dtype == FA100_BF16 || p->dtype == FA100_FP16 || p->dtype == FA100_E4M3, "unsupported dtype %d", p->dtype);
+  FA_CHECK_ARG(p->b > 0 && p->h > 0 && p->h_k > 0 && p->h % p->h_k == 0, "bad batch/head counts b=%d h=%d h_k=%d", p->b, p->h, p->h_k);
+  FA_CHECK_ARG(p->d > 0 && p->dv > 0 && p->d % 8 == 0 && p->dv % 8 == 0, "head dims must be multiples of 8 (d=%d dv=%d)", p->d, p->dv);
+  const bool fp8 = p->dtype == FA100_E4M3;
+  const int elt = fp8 ? 1 : 2;
+  if (fp8) FA_CHECK_ARG(p->d % 16 == 0 && p->dv % 16 == 0, "fp8 head dims must be multiples of 16");
+  FA_UNSUPPORTED(p->d > 256 || p->dv > 256, "head dim > 256 is not supported (d=%d dv=%d)", p->d, p->dv);
+  FA_UNSUPPORTED(p->k_new || p->v_new || p->rotary_cos, "append-KV / rotary handled by the caller-side kernel, not fa100_fwd");
+  FA_UNSUPPORTED(fp8 && p->softcap > 0.f, "softcap with fp8 not supported");
+  const bool varlen_q = p->cu_seqlens_q != nullptr;
+  const bool varlen_k = p->cu_seqlens_k != nullptr;
+  const bool paged = p->page_table != nullptr;
+  FA_CHECK_ARG(!(paged && varlen_k), "page_table and cu_seqlens_k are exclusive");
+  if (paged) {
+    FA_CHECK_ARG(p->page_size > 0 && p->num_pages > 0, "paged KV needs page_size and num_pages");
+    FA_UNSUPPORTED(p->leftpad_k != nullptr, "leftpad_k with paged KV not supported");
+  }
+  const int splits = plan->num_splits;
+  if (splits > 1) FA_CHECK_ARG(p->o_accum && p->lse_accum, "num_splits > 1 needs o_accum and lse_accum");
+  FA_CHECK_ARG((p->o_accum == nullptr) == (p->lse_accum == nullptr), "o_accum and lse_accum must be given together");
+  FA_CHECK_ARG(p->o_accum != nullptr || (p->o != nullptr && p->lse != nullptr), "o and lse are required without o_accum");
+
+  // ---- kernel parameters
+  FwdKernelParams kp;
+  fill_kernel_params(p, plan, kp);
+  const bool dual = plan->dual_stream != 0;
+  const bool solo = std::max(p->d, p->dv) > 128;
+  const int64_t rows_q = varlen_q ? p->total_q : p->seqlen_q;
 
   // ---- tensor maps
   const int cols_per_box = 128 / elt;

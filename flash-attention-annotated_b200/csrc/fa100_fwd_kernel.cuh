@@ -78,7 +78,11 @@ struct FwdKernelParams {
   int32_t num_m_blocks;   // ceil(max_seqlen_q / (2 * pos_per_tile))
   int32_t heads_work;     // h_k when packed else h
   int32_t num_splits;
-  int32_t num_work;
+  int32_t num_work;       // static schedule: every (m block, batch, head, split); an upper bound when sched is set
+  int32_t tiles_per_item; // 128-row Q tiles one work item covers: 2, or 1 in the dual-stream and head-dim-256 kernels
+  // Device-built schedule for ragged batches (fa100_prepare_scheduler): [0] work items, [1] batches, [2 .. 2+b) batch
+  // ids, most key blocks first, [2+b .. 2+2b] exclusive prefix of work items over that order.  Null: static schedule.
+  const int32_t* sched;
   int32_t is_causal, is_local, window_left, window_right, attention_chunk;
   int32_t out_fp16;       // 1: fp16 output, 0: bf16 output
   int32_t o_tma;          // 1: O leaves through shared memory and TMA stores (dense batch, no pack-GQA, no partials)
@@ -106,6 +110,9 @@ FA_DEVICE int work_index(int round) {
   return round * int(gridDim.x) + ((round & 1) ? int(gridDim.x) - 1 - int(blockIdx.x) : int(blockIdx.x));
 }
 
+constexpr int kSchedHeaderWords = 8;  // [magic, num_splits, pack_gqa, num_sm, num_work bound, 0, 0, 0] written by the host (get_scheduler_metadata)
+FA_DEVICE int total_work(const FwdKernelParams& p) { return p.sched ? p.sched[0] : p.num_work; }
+
 FA_DEVICE WorkItem decode_work(const FwdKernelParams& p, int w) {
   // w = ((((bi * h_k + hk) * m_blocks + m_rev) * heads_per_group + g) * splits + split.  Everything that reads one
   // (batch, KV head) -- its splits, the query heads of the group and all their row blocks -- is adjacent, so the ~148
@@ -114,6 +121,23 @@ FA_DEVICE WorkItem decode_work(const FwdKernelParams& p, int w) {
   // the long (late) causal row blocks come first.
   WorkItem it;
   const int gsz = p.heads_work / p.h_k;  // query heads per KV head that are separate work items (1 when packed)
+  if (p.sched) {
+    // ragged batch: batches in the order the schedule kernel chose (most key blocks first), each with its own number
+    // of row blocks and no entries for rows past its end; inside a batch the order below is unchanged
+    const int32_t* order = p.sched + 2;
+    const int32_t* prefix = order + p.b;
+    int lo = 0, hi = p.b - 1;  // largest r with prefix[r] <= w
+    while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (prefix[mid] <= w) lo = mid; else hi = mid - 1; }
+    const int per_batch = prefix[lo + 1] - prefix[lo];
+    const int m_blocks = per_batch / (p.heads_work * p.num_splits);
+    w -= prefix[lo];
+    it.bi = order[lo];
+    it.split = w % p.num_splits;  w /= p.num_splits;
+    const int g = w % gsz;        w /= gsz;
+    it.m_blk = m_blocks - 1 - w % m_blocks;  w /= m_blocks;
+    it.head = w * gsz + g;
+    return it;
+  }
   it.split = w % p.num_splits;  w /= p.num_splits;
   const int g = w % gsz;        w /= gsz;
   it.m_blk = p.num_m_blocks - 1 - w % p.num_m_blocks;  w /= p.num_m_blocks;

@@ -75,7 +75,8 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   uint32_t q_it[kQTiles] = {0, 0};
   // only the boxes that hold real head-dim columns are loaded (d = 192 in the 256 instance: 3 of 4)
   const uint32_t q_tx = uint32_t(p.qk_boxes * kRowBytes) * p.pack * p.pos_per_tile;
-  for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
+  const int n_work = total_work(p);
+  for (int wi = 0, w; (w = work_index(wi)) < n_work; ++wi) {
     const WorkGeom g = make_geom<DUAL, (HD > 128)>(p, w);
     if (g.n_hi <= g.n_lo) continue;
 #pragma unroll
@@ -240,7 +241,8 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
     __syncwarp();
   };
 
-  for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
+  const int n_work = total_work(p);
+  for (int wi = 0, w; (w = work_index(wi)) < n_work; ++wi) {
     int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi;
     {
       const WorkGeom g = make_geom<DUAL, (HD > 128)>(p, w);

@@ -165,7 +165,8 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
   uint32_t s_it = 0, o_it = 0, pv_n = 0;                // pv_n: P blocks published so far == PV batches requested
   FA_PROF_DECL();  // 0 s_full wait, 1 S load, 2 s_free + mask + row max, 3 rescale, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait + publish, 7 rest
 
-  for (int wi = 0, w; (w = work_index(wi)) < p.num_work; ++wi) {
+  const int n_work = total_work(p);
+  for (int wi = 0, w; (w = work_index(wi)) < n_work; ++wi) {
     const RowGeom rg = row_geom<FP8, DUAL, (HD > 128)>(p, w, t, row);
     if (!rg.has_rows) continue;
     const float scale_log2 = rg.scale_log2;

@@ -35,6 +35,8 @@ int device_sm_count(int* out);
 
 int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stream);
 int launch_combine(const Fa100CombineParams* p, cudaStream_t stream);
+int launch_prepare_scheduler(const Fa100FwdParams* p, const Fa100Plan* plan, int32_t* metadata, int64_t words, cudaStream_t stream);
+int64_t scheduler_metadata_words(int b);
 int make_plan(const Fa100Shape* s, Fa100Plan* out);
 
 }  // namespace fa100

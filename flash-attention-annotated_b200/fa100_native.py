@@ -41,7 +41,7 @@ class FwdParams(C.Structure):
         + [("softmax_scale", f32), ("softcap", f32)]
         + [(n, i32) for n in ("is_causal", "window_left", "window_right", "attention_chunk")]
         + [(n, i32) for n in ("num_splits", "pack_gqa", "num_sm")]
-        + [("tile_counter", vp), ("reserved", i32 * 8)]
+        + [("scheduler_metadata", vp), ("reserved", i32 * 8)]
     )
 
 
@@ -69,7 +69,8 @@ class Plan(C.Structure):
                                    "dual_stream")] + [("reserved", i32 * 8)]
 
 
-EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_debug_hang_info",
+EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_prepare_scheduler",
+           "fa100_scheduler_metadata_words", "fa100_debug_hang_info",
            "fa100_debug_trace", "fa100_debug_prof")
 
 _lib = None
@@ -98,10 +99,13 @@ def lib() -> C.CDLL:
         l.fa100_fwd.argtypes = [C.POINTER(FwdParams), vp]
         l.fa100_combine.argtypes = [C.POINTER(CombineParams), vp]
         l.fa100_append_kv.argtypes = [C.POINTER(FwdParams), vp, i64, i64, i64, vp, vp]
+        l.fa100_prepare_scheduler.argtypes = [C.POINTER(FwdParams), vp, i64, vp]
+        l.fa100_scheduler_metadata_words.argtypes = [i32]
+        l.fa100_scheduler_metadata_words.restype = i64
         l.fa100_debug_hang_info.argtypes = [C.POINTER(C.c_uint32 * 4)]
         l.fa100_debug_trace.argtypes = [C.POINTER(C.c_uint32), C.c_int]
         l.fa100_debug_prof.argtypes = [C.POINTER(C.c_uint32), C.c_int]
-        for n in ("fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_debug_hang_info",
+        for n in ("fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_prepare_scheduler", "fa100_debug_hang_info",
            "fa100_debug_trace", "fa100_debug_prof"):
             getattr(l, n).restype = C.c_int
         if l.fa100_abi_version() != 1:

@@ -9,6 +9,7 @@ device memory, the current stream, nothing else -- all arithmetic runs in the CU
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -189,7 +190,17 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     p.softmax_scale, p.softcap = float(softmax_scale), float(softcap)
     p.is_causal, p.window_left, p.window_right, p.attention_chunk = int(is_causal), window_size_left, window_size_right, attention_chunk
     p.num_splits, p.pack_gqa, p.num_sm = splits, pl.pack_gqa, pl.num_sm
+    ragged = b > 1 and any(t is not None for t in (cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k, leftpad_k)) and not _NO_SCHED
     with torch.cuda.device(q.device):
+        if scheduler_metadata is not None and scheduler_metadata.numel() >= META_HEADER + _sched_words(b):
+            # the schedule get_scheduler_metadata built ahead of time (CUDA-graphed decode): used as is
+            _chk(int(scheduler_metadata.numel()) >= META_HEADER, "scheduler_metadata is too short")
+            p.scheduler_metadata = _ptr(scheduler_metadata)
+        elif ragged:
+            # the reference launches prepare_varlen_num_blocks in front of every ragged forward (hopper/flash_api.cpp:1166)
+            meta = torch.empty(META_HEADER + _sched_words(b), dtype=torch.int32, device=q.device)
+            N.check(N.lib().fa100_prepare_scheduler(C.byref(p), _ptr(meta), meta.numel(), _stream()))
+            p.scheduler_metadata = _ptr(meta)
         N.check(N.lib().fa100_fwd(C.byref(p), _stream()))
         if _partial is None and splits > 1:
             if varlen_q:  # (splits, h, total_q, dv) viewed as (splits, b=1, s=total_q, h, dv)
@@ -199,6 +210,14 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
             else:
                 _combine_into(out_accum.permute(0, 1, 3, 2, 4), lse_accum.permute(0, 1, 3, 2), out, lse.permute(0, 2, 1))
     return out, lse, (out_accum if out_accum is not None else empty), (lse_accum if lse_accum is not None else empty)
+
+
+META_HEADER = 8  # host-written words in front of the device-built schedule
+_NO_SCHED = bool(os.environ.get("FA100_NO_SCHED"))  # A/B switch: static schedule for ragged batches too
+
+
+def _sched_words(b: int) -> int:
+    return int(N.lib().fa100_scheduler_metadata_words(b)) - META_HEADER
 
 
 def _append_kv(q, k, v, k_new, v_new, cu_seqlens_q, cu_seqlens_k_new, seqused_q, seqused_k, page_table, kv_batch_idx,
@@ -319,10 +338,27 @@ def mha_fwd_get_scheduler_metadata(batch_size, max_seqlen_q, max_seqlen_k, num_h
         window_size_right = 0
     is_local = (window_size_left >= 0 or window_size_right >= 0 or attention_chunk > 0) and not (
         window_size_left < 0 and window_size_right == 0 and attention_chunk == 0)
+    dev = seqused_k.device
     pl = plan(batch_size, max_seqlen_q, max_seqlen_k + max_seqlen_k_new, num_heads, num_heads_k, headdim, headdim_v, qkv_dtype,
-              is_causal, is_local, num_splits, pack_gqa, sm_margin, seqused_k.device)
-    return torch.tensor([0xFA100, pl.num_splits, pl.pack_gqa, pl.num_sm, pl.num_work, 0, 0, 0], dtype=torch.int32,
-                        device=seqused_k.device)
+              is_causal, is_local, num_splits, pack_gqa, sm_margin, dev)
+    header = torch.tensor([0xFA100, pl.num_splits, pl.pack_gqa, pl.num_sm, pl.num_work, 0, 0, 0], dtype=torch.int32, device=dev)
+    if batch_size <= 1 or cu_seqlens_k_new is not None or max_seqlen_k_new > 0:
+        # one sequence has nothing to order; with appended keys the lengths change before the forward reads them
+        return header
+    # ragged batch: the device-built list of work items (role of prepare_varlen_num_blocks, hopper/flash_api.cpp:640-660)
+    meta = torch.empty(META_HEADER + _sched_words(batch_size), dtype=torch.int32, device=dev)
+    meta[:META_HEADER] = header
+    p = N.FwdParams()
+    p.b, p.b_k, p.seqlen_q, p.seqlen_k = batch_size, batch_size, max_seqlen_q, max_seqlen_k
+    p.h, p.h_k, p.d, p.dv, p.dtype = num_heads, num_heads_k, headdim, headdim_v, _DT[qkv_dtype]
+    p.cu_seqlens_q, p.cu_seqlens_k = _ptr(cu_seqlens_q), _ptr(cu_seqlens_k)
+    p.seqused_q, p.seqused_k, p.leftpad_k = _ptr(seqused_q), _ptr(seqused_k), _ptr(leftpad_k)
+    p.total_q = 1 if cu_seqlens_q is not None else 0  # sizes of the packed tensors play no part in the schedule
+    p.is_causal, p.window_left, p.window_right, p.attention_chunk = int(is_causal), window_size_left, window_size_right, attention_chunk
+    p.num_splits, p.pack_gqa, p.num_sm = pl.num_splits, pl.pack_gqa, pl.num_sm
+    with torch.cuda.device(dev):
+        N.check(N.lib().fa100_prepare_scheduler(C.byref(p), _ptr(meta), meta.numel(), _stream()))
+    return meta
 
 
 def mha_bwd(*args, **kwargs):

@@ -121,7 +121,9 @@ typedef struct Fa100FwdParams {
   int32_t num_splits;          /* >= 1 (resolved by the caller, e.g. through fa100_plan) */
   int32_t pack_gqa;            /* 0/1 (resolved by the caller) */
   int32_t num_sm;              /* SMs this call may use (multiProcessorCount - sm_margin); 0 = all */
-  int32_t* tile_counter;       /* reserved for a device-counter scheduler; ignored (the schedule is static) */
+  /* Optional device-built schedule for ragged batches: a buffer of fa100_scheduler_metadata_words(b) int32 that
+   * fa100_prepare_scheduler has filled for the SAME sizes, lengths, num_splits and pack_gqa.  Null = static schedule. */
+  const int32_t* scheduler_metadata;
   int32_t reserved[8];
 } Fa100FwdParams;
 
@@ -173,6 +175,16 @@ const char* fa100_last_error(void);
 int fa100_plan(const Fa100Shape* shape, Fa100Plan* out);
 int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream);
 int fa100_combine(const Fa100CombineParams* p, fa100_stream_t stream);
+
+/* Device-side schedule for ragged batches: the role of prepare_varlen_num_blocks (hopper/flash.h:220,
+ * hopper/flash_prepare_scheduler.cu:43-215) and of the metadata tensor mha_fwd_get_scheduler_metadata returns
+ * (hopper/flash_api.cpp:521-662, layout :996-1025).  One small kernel on `stream` reads cu_seqlens / seqused / leftpad
+ * of `p` (q, k, v, o may be null), counts every batch element's row blocks and key blocks, orders the batch elements
+ * longest first and writes, after an 8-word header the caller owns, [work items, b, order[b], prefix[b + 1], scratch].
+ * fa100_fwd then walks that list instead of the static (row block, batch, head) grid: no entries for rows past a
+ * sequence's end, expensive sequences first.  `metadata` must hold fa100_scheduler_metadata_words(p->b) int32. */
+int64_t fa100_scheduler_metadata_words(int32_t b);
+int fa100_prepare_scheduler(const Fa100FwdParams* p, int32_t* metadata, int64_t metadata_words, fa100_stream_t stream);
 /* Append-KV + rotary pass that precedes fa100_fwd when flash_attn_with_kvcache is given k / v (and rotary_cos / sin).
  * Replaces the AppendKV phases of the reference kernel: store_kv_new and the Q rotation
  * (hopper/mainloop_fwd_sm90_tma_gmma_ws.hpp:1447-1713, :1098-1123; hopper/rotary.h:17-485; positions

@@ -24,7 +24,7 @@ def native():
 
 def test_exports_match_header(native):
     hdr = open(os.path.join(ROOT, "include", "fa100.h")).read()
-    declared = set(re.findall(r"^(?:int|const char\*)\s+(fa100_\w+)\s*\(", hdr, flags=re.M))
+    declared = set(re.findall(r"^(?:int|int64_t|const char\*)\s+(fa100_\w+)\s*\(", hdr, flags=re.M))
     assert declared == set(native.EXPORTS)
     lib = native.lib()
     for name in declared:

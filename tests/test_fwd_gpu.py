@@ -606,3 +606,45 @@ def test_unsupported_raises():
     q, k, v = _qkv(1, 64, 64, 2, 2, 64, torch.bfloat16)
     with pytest.raises((RuntimeError, NotImplementedError)):
         F.flash_attn_func(q, k, v)  # CPU tensors: no fallback
+
+
+def test_prepare_scheduler_metadata():
+    """fa100_prepare_scheduler (role of prepare_varlen_num_blocks, hopper/flash_prepare_scheduler.cu:43-215): batch
+    elements ordered by key-block count, longest first; the prefix counts only row blocks that exist."""
+    F = _iface()
+    b, h, hk, d = 7, 8, 2, 128
+    lens_q = torch.tensor([300, 0, 1024, 17, 512, 256, 257], dtype=torch.int32)
+    lens_k = torch.tensor([900, 64, 1024, 4000, 0, 256, 257], dtype=torch.int32)
+    cu_q = torch.nn.functional.pad(lens_q.cumsum(0), (1, 0)).to(torch.int32)
+    cu_k = torch.nn.functional.pad(lens_k.cumsum(0), (1, 0)).to(torch.int32)
+    meta = F.get_scheduler_metadata(b, int(lens_q.max()), int(lens_k.max()), h, hk, d, lens_k.to(DEV), qkv_dtype=torch.bfloat16,
+                                    cu_seqlens_q=cu_q.to(DEV), causal=False, num_splits=1).cpu()
+    assert meta[0].item() == 0xFA100
+    body = meta[8:]
+    m_blocks = [(int(x) + 255) // 256 for x in lens_q]                       # 256 query rows per work item (no pack-GQA here)
+    # a tile past the end of the sequence has no key blocks: count the real 128-row tiles
+    cost = [((int(q) + 127) // 128 if mb else 0) * ((int(k) + 127) // 128) for q, mb, k in zip(lens_q, m_blocks, lens_k)]
+    order = sorted(range(b), key=lambda i: (-cost[i], i))
+    items = [m_blocks[i] * h for i in order]
+    assert body[1].item() == b and body[2:2 + b].tolist() == order
+    pref = [0]
+    for x in items:
+        pref.append(pref[-1] + x)
+    assert body[2 + b:2 + 2 * b + 1].tolist() == pref and body[0].item() == pref[-1]
+    # and the forward that walks this list agrees with the oracle
+    g = torch.Generator().manual_seed(77)
+    q = torch.randn(int(cu_q[-1]), h, d, generator=g).to(torch.bfloat16)
+    k = torch.randn(int(cu_k[-1]), hk, d, generator=g).to(torch.bfloat16)
+    v = torch.randn(int(cu_k[-1]), hk, d, generator=g).to(torch.bfloat16)
+    out, lse = F.flash_attn_varlen_func(q.to(DEV), k.to(DEV), v.to(DEV), cu_q.to(DEV), cu_k.to(DEV), int(lens_q.max()), int(lens_k.max()),
+                                        return_attn_probs=True)
+    for i in range(b):
+        if lens_q[i] == 0:
+            continue
+        qs, ks = slice(int(cu_q[i]), int(cu_q[i + 1])), slice(int(cu_k[i]), int(cu_k[i + 1]))
+        if lens_k[i] == 0:
+            assert out[qs].abs().max().item() == 0
+            continue
+        ref, lse_ref = A.attention_oracle(q[qs][None], k[ks][None], v[ks][None])
+        low, _ = A.attention_oracle(q[qs][None], k[ks][None], v[ks][None], upcast=False, reorder_ops=True)
+        _check(out[qs][None], lse[:, qs][None], ref, low, lse_ref)
