@@ -51,6 +51,9 @@ FA_DEVICE uint16_t pack8_v(uint32_t lo, uint32_t hi) {
 #ifndef FA100_GARBAGE
 #define FA100_GARBAGE 0  // timing-only experiments (wrong results): 1 half the exponentials, 2 no row sum, 4 no pack, 8 no row max
 #endif
+#ifndef FA100_PREFETCH
+#define FA100_PREFETCH 0  // experiment switch, measured slower (profiles/r01b_ab_prefetch.log): bit 0 early non-blocking look at pv_done (-1..2 %), bit 1 next block's S loads issued behind the P stores (-0.5..2 %), both -2..3 %
+#endif
 #ifndef FA100_PIPE
 #define FA100_PIPE 1   // software-pipelined exp phase with all P stores at the end (0: the per-chunk loops)
 #endif
@@ -172,16 +175,19 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
     const float scale_log2 = rg.scale_log2;
     const bool softcap = p.softcap_pre != 0.f;
     float m_run = -INFINITY, l_run = 0.f;
+    uint32_t s[4][32];
+    bool s_loaded = false;  // the next block's scores are already on their way into s (loads issued behind the P stores)
     for (int nb = rg.n_max - 1; nb >= rg.n_min; nb -= (DUAL ? 2 : 1)) {
       FA_PROF(7);
-      mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
-      FA_PROF(0);
-      FA_LAT_ACC(3, &bar->ts[t]);
-      ++s_it;
-      tc_fence_after();
-      uint32_t s[4][32];
+      if (!s_loaded) {
+        mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
+        FA_PROF(0);
+        FA_LAT_ACC(3, &bar->ts[t]);
+        ++s_it;
+        tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
+        for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
+      }
       tmem_ld_wait();
       FA_PROF(1);
       // the scores are in registers: hand S to the other tile's QK
@@ -192,7 +198,9 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
       FA_TRACE_POINT(0xC4);
       // P_t and O_t may be touched again once the previous P_t V has drained; poll now, block only right before the
       // first write (normally long complete by then)
-      bool pv_drained = pv_n == 0 || (!FA100_PIPE && mbar_try_wait(&bar->pv_done[t], (pv_n - 1) & 1));
+      // (a non-blocking look: it costs nothing when the phase is still open, and its latency hides behind the row max)
+      bool pv_drained = pv_n == 0 || (FA100_PIPE ? ((FA100_PREFETCH & 1) && __all_sync(0xffffffffu, mbar_test_wait(&bar->pv_done[t], (pv_n - 1) & 1)))
+                                                 : mbar_try_wait(&bar->pv_done[t], (pv_n - 1) & 1));
       const int n0 = nb * kBlockN;
       // boundary block for any row of this warp (warp-uniform): softcap first, then the mask (hopper/mainloop...:1073-1077)
       const bool boundary = __any_sync(0xffffffffu, softcap || n0 + kBlockN > rg.col_hi || n0 < rg.col_lo);
@@ -278,6 +286,19 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
           if (!FP8) tmem_st16(tP + c * 16, pk + c * 16);
           else tmem_st8(tP + c * 8, pk + c * 8);
         }
+#if (FA100_PREFETCH & 2)
+        // The score registers are free: if this tile's next scores are already in S (the usual case), start copying them
+        // now, so that the 16 KB tensor-memory read per warp, and the hand-over of S to the other tile behind it, overlap
+        // the store wait, the publish and the loop tail instead of following them.
+        s_loaded = false;
+        if (nb - (DUAL ? 2 : 1) >= rg.n_min && __all_sync(0xffffffffu, mbar_test_wait(&bar->s_full[t], s_it & 1))) {
+          ++s_it;
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
+          s_loaded = true;
+        }
+#endif
       }
 #else
 #pragma unroll

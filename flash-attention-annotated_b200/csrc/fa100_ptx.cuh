@@ -53,6 +53,19 @@ FA_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 
+// Non-blocking look at a phase (try_wait may park the thread for a while when the phase is still open).
+FA_DEVICE bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
 // Watchdog: a wrong phase/count must never hang the GPU box.  A wait that lasts longer than
 // FA100_WATCHDOG_CYCLES records {tag, block, thread, parity}, raises a device-wide abort flag and returns;
 // every other wait then falls through as well, the kernel ends (with garbage) and the host reads the
