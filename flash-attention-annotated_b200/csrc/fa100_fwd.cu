@@ -74,6 +74,7 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   kp.num_splits = cta_splits;
   kp.num_work = kp.num_m_blocks * p->b * kp.heads_work * cta_splits;
   kp.tiles_per_item = (dual || solo) ? 1 : 2;
+  kp.num_sm = plan->num_sm;
   kp.sched = p->scheduler_metadata ? p->scheduler_metadata + kSchedHeaderWords : nullptr;
   // causal / local normalisation (hopper/flash_api.cpp:148-160, 796-805)
   int wl = p->window_left, wr = p->window_right;
@@ -103,37 +104,49 @@ __global__ void __launch_bounds__(1024, 1)
 fa100_schedule_kernel(const FwdKernelParams p, int32_t* __restrict__ meta, int32_t* __restrict__ scratch) {
   int32_t* order = meta + 2;
   int32_t* prefix = order + p.b;
+  int32_t* nsplit = prefix + p.b + 1;  // per ordered batch element
   int32_t* cost = scratch;             // key blocks of the batch element (sort key)
-  int32_t* items = scratch + p.b;      // work items of the batch element
+  int32_t* mblk = scratch + p.b;       // row blocks of the batch element
+  __shared__ int32_t run_total[1024];
+  __shared__ unsigned long long total_blocks;
+  if (threadIdx.x == 0) total_blocks = 0ull;
+  __syncthreads();
   const int rows_item = p.tiles_per_item * p.pos_per_tile;
-  FwdKernelParams whole = p;  // key blocks of a tile before they are cut into splits
-  whole.num_splits = 1;
   for (int bi = threadIdx.x; bi < p.b; bi += blockDim.x) {
     const SeqInfo sq = load_seq(p, bi);
     const int m_blocks = sq.sq > 0 ? (sq.sq + rows_item - 1) / rows_item : 0;
     int c = 0;
     for (int t = 0; t < m_blocks * p.tiles_per_item; ++t) {
-      const TileRange r = tile_range(whole, sq, t * p.pos_per_tile, 0);
+      const TileRange r = tile_range(p, sq, t * p.pos_per_tile, 0, 1);  // the whole range, before it is cut into splits
       c += r.n_max - r.n_min;
     }
     cost[bi] = c;
-    items[bi] = m_blocks * p.heads_work * p.num_splits;
+    mblk[bi] = m_blocks;
+    atomicAdd(&total_blocks, (unsigned long long)c * p.heads_work);
   }
   __syncthreads();
+  // Split counts per batch element (hopper/flash_prepare_scheduler.cu:96-120): every CTA-level split should hold about
+  // total key blocks * 1.1 / SMs key blocks, never more splits than the caller's buffers hold (num_splits).
+  const long long per_cta = max(1ll, (long long)((double)total_blocks * 1.1 / max(p.num_sm, 1)) + 1);
   // rank sort (stable): position = batches with a larger cost, or the same cost and a smaller index
   for (int bi = threadIdx.x; bi < p.b; bi += blockDim.x) {
     const int c = cost[bi];
     int rank = 0;
     for (int j = 0; j < p.b; ++j) { const int cj = cost[j]; rank += (cj > c) || (cj == c && j < bi); }
     order[rank] = bi;
+    int ns = 1;
+    if (p.num_splits > 1 && mblk[bi] > 0) {
+      const long long blocks_item = c / (mblk[bi] * p.tiles_per_item);  // key blocks one row block walks (average)
+      ns = int(min((long long)p.num_splits, max(1ll, (blocks_item + per_cta - 1) / per_cta)));
+    }
+    nsplit[rank] = ns;
   }
   __syncthreads();
   // exclusive prefix of work items over the order: per-thread runs, then a scan of the 1024 run totals
-  __shared__ int32_t run_total[1024];
   const int per = (p.b + blockDim.x - 1) / blockDim.x;
   const int lo = min(int(threadIdx.x) * per, p.b), hi = min(lo + per, p.b);
   int sum = 0;
-  for (int r = lo; r < hi; ++r) sum += items[order[r]];
+  for (int r = lo; r < hi; ++r) sum += mblk[order[r]] * p.heads_work * nsplit[r];
   run_total[threadIdx.x] = sum;
   __syncthreads();
   for (int off = 1; off < int(blockDim.x); off <<= 1) {
@@ -143,11 +156,16 @@ fa100_schedule_kernel(const FwdKernelParams p, int32_t* __restrict__ meta, int32
     __syncthreads();
   }
   int acc = run_total[threadIdx.x] - sum;
-  for (int r = lo; r < hi; ++r) { prefix[r] = acc; acc += items[order[r]]; }
+  for (int r = lo; r < hi; ++r) { prefix[r] = acc; acc += mblk[order[r]] * p.heads_work * nsplit[r]; }
   if (threadIdx.x == blockDim.x - 1) { prefix[p.b] = run_total[threadIdx.x]; meta[0] = run_total[threadIdx.x]; meta[1] = p.b; }
 }
 
-int64_t scheduler_metadata_words(int b) { return kSchedHeaderWords + 2 + int64_t(b) + (b + 1) + 2 * int64_t(b); }
+// splits a batch element does not use must read as empty in the combine pass
+__global__ void fa100_fill_neg_inf_kernel(float* __restrict__ x, int64_t n) {
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) x[i] = -INFINITY;
+}
+
+int64_t scheduler_metadata_words(int b) { return kSchedHeaderWords + 2 + int64_t(b) + (b + 1) + int64_t(b) + 2 * int64_t(b); }
 
 int launch_prepare_scheduler(const Fa100FwdParams* p, const Fa100Plan* plan, int32_t* metadata, int64_t words, cudaStream_t stream) {
   FA_CHECK_ARG(metadata != nullptr, "metadata must be non-null");
@@ -157,7 +175,7 @@ int launch_prepare_scheduler(const Fa100FwdParams* p, const Fa100Plan* plan, int
   FwdKernelParams kp;
   fill_kernel_params(p, plan, kp);
   int32_t* body = metadata + kSchedHeaderWords;
-  fa100_schedule_kernel<<<1, 1024, 0, stream>>>(kp, body, body + 2 + p->b + (p->b + 1));
+  fa100_schedule_kernel<<<1, 1024, 0, stream>>>(kp, body, body + 2 + p->b + (p->b + 1) + p->b);
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
@@ -242,6 +260,12 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
                  "o must be 16-byte aligned with strides that are multiples of 8 elements");
   }
 
+  if (kp.sched && splits > 1) {
+    // with per-batch split counts some partials are never written: make them read as empty (LSE = -inf) for fa100_combine
+    const int64_t n = kp.lseacc_split_stride * splits;
+    fa100_fill_neg_inf_kernel<<<int(std::min<int64_t>((n + 255) / 256, 1184)), 256, 0, stream>>>(p->lse_accum, n);
+    FA_CUDA(cudaGetLastError());
+  }
   int num_sm = plan->num_sm;
   const int grid = std::max(1, std::min(kp.num_work, num_sm));
   const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : (p->dtype == FA100_FP16 ? kFmtF16 : kFmtE4M3);

@@ -81,8 +81,10 @@ struct FwdKernelParams {
   int32_t num_work;       // static schedule: every (m block, batch, head, split); an upper bound when sched is set
   int32_t tiles_per_item; // 128-row Q tiles one work item covers: 2, or 1 in the dual-stream and head-dim-256 kernels
   // Device-built schedule for ragged batches (fa100_prepare_scheduler): [0] work items, [1] batches, [2 .. 2+b) batch
-  // ids, most key blocks first, [2+b .. 2+2b] exclusive prefix of work items over that order.  Null: static schedule.
+  // ids, most key blocks first, [2+b .. 2+2b] exclusive prefix of work items over that order, [3+2b .. 3+3b) CTA-level
+  // split count of each batch element in that order (<= num_splits).  Null: static schedule.
   const int32_t* sched;
+  int32_t num_sm;         // SMs the launch may use (the schedule kernel sizes the per-batch split counts with it)
   int32_t is_causal, is_local, window_left, window_right, attention_chunk;
   int32_t out_fp16;       // 1: fp16 output, 0: bf16 output
   int32_t o_tma;          // 1: O leaves through shared memory and TMA stores (dense batch, no pack-GQA, no partials)
@@ -92,7 +94,7 @@ struct FwdKernelParams {
 };
 
 // ----------------------------------------------------------------------------- geometry shared by all roles
-struct WorkItem { int m_blk, head, bi, split; };
+struct WorkItem { int m_blk, head, bi, split, nsplits; };  // nsplits: CTA-level splits of this batch element
 
 struct SeqInfo {
   int sq, sk;      // this batch element's lengths
@@ -129,15 +131,17 @@ FA_DEVICE WorkItem decode_work(const FwdKernelParams& p, int w) {
     int lo = 0, hi = p.b - 1;  // largest r with prefix[r] <= w
     while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (prefix[mid] <= w) lo = mid; else hi = mid - 1; }
     const int per_batch = prefix[lo + 1] - prefix[lo];
-    const int m_blocks = per_batch / (p.heads_work * p.num_splits);
+    it.nsplits = prefix[p.b + 1 + lo];
+    const int m_blocks = per_batch / (p.heads_work * it.nsplits);
     w -= prefix[lo];
     it.bi = order[lo];
-    it.split = w % p.num_splits;  w /= p.num_splits;
+    it.split = w % it.nsplits;  w /= it.nsplits;
     const int g = w % gsz;        w /= gsz;
     it.m_blk = m_blocks - 1 - w % m_blocks;  w /= m_blocks;
     it.head = w * gsz + g;
     return it;
   }
+  it.nsplits = p.num_splits;
   it.split = w % p.num_splits;  w /= p.num_splits;
   const int g = w % gsz;        w /= gsz;
   it.m_blk = p.num_m_blocks - 1 - w % p.num_m_blocks;  w /= p.num_m_blocks;
@@ -161,7 +165,7 @@ FA_DEVICE SeqInfo load_seq(const FwdKernelParams& p, int bi) {
 FA_DEVICE int floor_mod(int x, int m) { int r = x % m; return r < 0 ? r + m : r; }
 
 // Key-block range of one Q tile (arithmetic of hopper/block.h:14-60, on 128-row tiles; -1 windows = unbounded).
-FA_DEVICE TileRange tile_range(const FwdKernelParams& p, const SeqInfo& s, int pos0, int split) {
+FA_DEVICE TileRange tile_range(const FwdKernelParams& p, const SeqInfo& s, int pos0, int split, int nsplits) {
   TileRange r;
   r.has_rows = pos0 < s.sq;
   r.n_min = 0; r.n_max = 0;
@@ -186,8 +190,8 @@ FA_DEVICE TileRange tile_range(const FwdKernelParams& p, const SeqInfo& s, int p
       n_min = max(0, left / kBlockN);
     }
   }
-  if (p.num_splits > 1) {
-    const int per = n_max <= n_min ? 0 : (n_max - n_min + p.num_splits - 1) / p.num_splits;
+  if (nsplits > 1) {
+    const int per = n_max <= n_min ? 0 : (n_max - n_min + nsplits - 1) / nsplits;
     n_min = n_min + split * per;
     n_max = min(n_min + per, n_max);
   }

@@ -31,7 +31,7 @@ FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w) {
   g.hk = p.pack > 1 ? g.it.head : g.it.head / p.qheads_per_kv;
   g.n_lo = 0x7fffffff; g.n_hi = 0;
   if (DUAL || SOLO) {
-    const TileRange r = tile_range(p, g.seq, g.it.m_blk * p.pos_per_tile, g.it.split);
+    const TileRange r = tile_range(p, g.seq, g.it.m_blk * p.pos_per_tile, g.it.split, g.it.nsplits);
     g.tr[0] = r;
     g.tr[1] = r;
     if (SOLO) { g.tr[1].has_rows = false; g.tr[1].n_min = g.tr[1].n_max = 0; }
@@ -41,7 +41,7 @@ FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w) {
   }
 #pragma unroll
   for (int t = 0; t < kQTiles; ++t) {
-    g.tr[t] = tile_range(p, g.seq, (g.it.m_blk * kQTiles + t) * p.pos_per_tile, g.it.split);
+    g.tr[t] = tile_range(p, g.seq, (g.it.m_blk * kQTiles + t) * p.pos_per_tile, g.it.split, g.it.nsplits);
     if ((FA100_GARBAGE & 128) && t == 1) { g.tr[t].has_rows = false; g.tr[t].n_min = g.tr[t].n_max = 0; }  // timing only: tile 1 idle
     if (g.tr[t].n_max > g.tr[t].n_min) { g.n_lo = min(g.n_lo, g.tr[t].n_min); g.n_hi = max(g.n_hi, g.tr[t].n_max); }
   }

@@ -143,6 +143,11 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     if _partial is not None:
         num_splits = 1
     pl = plan(b, seqlen_q, seqlen_k, h, h_k, d, dv, qt, is_causal, is_local, num_splits, pack_gqa, sm_margin, q.device)
+    ragged = b > 1 and any(t is not None for t in (cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k, leftpad_k)) and not _NO_SCHED
+    if ragged and num_splits == 0 and pl.dual_stream and pl.num_splits < DYN_SPLIT_BOUND and scheduler_metadata is None and _partial is None:
+        # ragged decode: the schedule kernel picks a split count per batch element (long sequences are cut, short ones are
+        # not; hopper/flash_prepare_scheduler.cu:96-120); the plan only sets the bound the partial buffers are sized for
+        pl = plan(b, seqlen_q, seqlen_k, h, h_k, d, dv, qt, is_causal, is_local, DYN_SPLIT_BOUND, pack_gqa, sm_margin, q.device)
     splits = pl.num_splits
     out_accum = lse_accum = None
     if _partial is not None:
@@ -190,7 +195,6 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     p.softmax_scale, p.softcap = float(softmax_scale), float(softcap)
     p.is_causal, p.window_left, p.window_right, p.attention_chunk = int(is_causal), window_size_left, window_size_right, attention_chunk
     p.num_splits, p.pack_gqa, p.num_sm = splits, pl.pack_gqa, pl.num_sm
-    ragged = b > 1 and any(t is not None for t in (cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k, leftpad_k)) and not _NO_SCHED
     with torch.cuda.device(q.device):
         if scheduler_metadata is not None and scheduler_metadata.numel() >= META_HEADER + _sched_words(b):
             # the schedule get_scheduler_metadata built ahead of time (CUDA-graphed decode): used as is
@@ -213,6 +217,7 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
 
 
 META_HEADER = 8  # host-written words in front of the device-built schedule
+DYN_SPLIT_BOUND = 8  # partials a ragged decode call is sized for when the caller leaves num_splits to the library
 _NO_SCHED = bool(os.environ.get("FA100_NO_SCHED"))  # A/B switch: static schedule for ragged batches too
 
 

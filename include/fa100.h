@@ -180,7 +180,8 @@ int fa100_combine(const Fa100CombineParams* p, fa100_stream_t stream);
  * hopper/flash_prepare_scheduler.cu:43-215) and of the metadata tensor mha_fwd_get_scheduler_metadata returns
  * (hopper/flash_api.cpp:521-662, layout :996-1025).  One small kernel on `stream` reads cu_seqlens / seqused / leftpad
  * of `p` (q, k, v, o may be null), counts every batch element's row blocks and key blocks, orders the batch elements
- * longest first and writes, after an 8-word header the caller owns, [work items, b, order[b], prefix[b + 1], scratch].
+ * longest first, gives each its own split count (<= num_splits, sized so that every split holds about the same number of
+ * key blocks) and writes, after an 8-word header the caller owns, [work items, b, order[b], prefix[b + 1], nsplit[b], scratch].
  * fa100_fwd then walks that list instead of the static (row block, batch, head) grid: no entries for rows past a
  * sequence's end, expensive sequences first.  `metadata` must hold fa100_scheduler_metadata_words(p->b) int32. */
 int64_t fa100_scheduler_metadata_words(int32_t b);

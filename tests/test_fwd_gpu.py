@@ -631,6 +631,7 @@ def test_prepare_scheduler_metadata():
     for x in items:
         pref.append(pref[-1] + x)
     assert body[2 + b:2 + 2 * b + 1].tolist() == pref and body[0].item() == pref[-1]
+    assert body[3 + 2 * b:3 + 3 * b].tolist() == [1] * b   # num_splits = 1: nothing to cut
     # and the forward that walks this list agrees with the oracle
     g = torch.Generator().manual_seed(77)
     q = torch.randn(int(cu_q[-1]), h, d, generator=g).to(torch.bfloat16)
@@ -648,3 +649,33 @@ def test_prepare_scheduler_metadata():
         ref, lse_ref = A.attention_oracle(q[qs][None], k[ks][None], v[ks][None])
         low, _ = A.attention_oracle(q[qs][None], k[ks][None], v[ks][None], upcast=False, reorder_ops=True)
         _check(out[qs][None], lse[:, qs][None], ref, low, lse_ref)
+
+
+@pytest.mark.parametrize("page_size", [None, 256])
+def test_ragged_decode_dynamic_splits(page_size):
+    """Ragged decode with num_splits left to the library: the schedule kernel cuts the long sequences into several
+    splits and leaves the short ones whole (hopper/flash_prepare_scheduler.cu:96-120); unused partials read as empty."""
+    F = _iface()
+    g = torch.Generator().manual_seed(91)
+    b, h, hk, d, cap = 12, 8, 2, 128, 8192
+    lens = torch.tensor([8192, 130, 64, 8000, 1, 512, 300, 4097, 128, 129, 2048, 7], dtype=torch.int32)
+    q = torch.randn(b, 1, h, d, generator=g).to(torch.bfloat16)
+    if page_size is None:
+        kd = torch.randn(b, cap, hk, d, generator=g).to(torch.bfloat16)
+        vd = torch.randn(b, cap, hk, d, generator=g).to(torch.bfloat16)
+        kin, vin, table = kd, vd, None
+    else:
+        kd, vd, table, kin, vin = A.paged_kvcache(cap, page_size, b, hk, d, d, torch.bfloat16, generator=g)
+    ref, lse_ref = A.attention_oracle(q, kd, vd, k_lens=lens)
+    low, _ = A.attention_oracle(q, kd, vd, k_lens=lens, upcast=False, reorder_ops=True)
+    out, lse, *_ = F.flash_attn_with_kvcache(q.to(DEV), kin.to(DEV), vin.to(DEV), cache_seqlens=lens.to(DEV),
+                                             page_table=None if table is None else table.to(DEV), return_softmax_lse=True)
+    _check(out, lse, ref, low, lse_ref)
+    meta = F.get_scheduler_metadata(b, 1, cap, h, hk, d, lens.to(DEV), qkv_dtype=torch.bfloat16, page_size=page_size, num_splits=8).cpu()
+    body = meta[8:]
+    order, ns = body[2:2 + b].tolist(), body[3 + 2 * b:3 + 3 * b].tolist()
+    assert order[0] == 0 and max(ns) > 1 and ns[order.index(4)] == 1 and all(1 <= x <= 4 for x in ns)   # 8 partials = 4 CTA-level splits
+    out2, lse2, *_ = F.flash_attn_with_kvcache(q.to(DEV), kin.to(DEV), vin.to(DEV), cache_seqlens=lens.to(DEV),
+                                               page_table=None if table is None else table.to(DEV), scheduler_metadata=meta.to(DEV),
+                                               num_splits=8, return_softmax_lse=True)
+    _check(out2, lse2, ref, low, lse_ref)
