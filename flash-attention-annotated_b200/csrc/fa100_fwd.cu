@@ -11,19 +11,43 @@
 
 namespace fa100 {
 
-template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
+template <int HD, int ELT, bool FP8, bool F16, bool DUAL, bool PAIR = false>
 static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK,
                            const CUtensorMap& tmV, const CUtensorMap& tmO, uint32_t fmt, int grid, cudaStream_t stream) {
-  using L = FwdSmem<HD, ELT>;
-  auto kernel = fa100_fwd_kernel<HD, ELT, FP8, F16, DUAL>;
+  using L = FwdSmem<HD, ELT, PAIR>;
+  auto kernel = fa100_fwd_kernel<HD, ELT, FP8, F16, DUAL, PAIR>;
   static bool attr_set = false;  // benign race: the call is idempotent
   if (!attr_set) {
     FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes));
     attr_set = true;
   }
-  kernel<<<grid, kThreads, L::kTotalBytes, stream>>>(kp, tmQ, tmK, tmV, tmO, fmt);
+  if (PAIR) {
+    // clusters of two CTAs: the pair shares every K / V tile (cta_group::2 MMAs); grid = 2 x pairs
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = L::kTotalBytes; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    FA_CUDA(cudaLaunchKernelEx(&cfg, kernel, kp, tmQ, tmK, tmV, tmO, fmt));
+  } else {
+    kernel<<<grid, kThreads, L::kTotalBytes, stream>>>(kp, tmQ, tmK, tmV, tmO, fmt);
+  }
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
+}
+
+// The 2-CTA variant (cta_group::2; the second MMA form SURVEY 8(a) a2 names): bf16 / fp16, head dims of exactly 128,
+// dense or packed K/V (not paged), not the dual-stream decode kernel.  Parity-green on the whole GPU suite when forced on
+// and bitwise equal to the 1-CTA kernel.  Interleaved bursts in one process (tools/pair_ab.py, profiles/r01c_pair_ab.log):
+// within +-1 % of the 1-CTA kernel without a mask (1269 vs 1274 and 1290 vs 1283 TFLOP/s), 1 to 4 % behind it under a causal
+// mask (1208 vs 1220 MHA s32768, 1138 vs 1191 on C2: a causal pair walks the union of its two tiles' key ranges, one fully
+// masked block per tile pair, and its 512-row work items balance worse).  The tensor
+// chain is shorter with pairs, but the softmax chain is co-critical, so nothing is gained yet and the
+// default stays one CTA per work item.  Fa100FwdParams.variant: 0 / 2 = one CTA per work item, 1 = pairs where eligible.
+static bool use_pair(const Fa100FwdParams* p, const Fa100Plan* plan) {
+  return p->variant == 1 && p->dtype != FA100_E4M3 && p->d == 128 && p->dv == 128 && p->page_table == nullptr && !plan->dual_stream &&
+         plan->num_sm >= 2;
 }
 
 // Everything the kernels need that is not a tensor map; shared by the forward launch and the schedule kernel.
@@ -69,11 +93,13 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   const bool dual = plan->dual_stream != 0;  // two partials per CTA-level split (make_geom<DUAL>)
   const int cta_splits = dual ? splits / 2 : splits;
   const bool solo = std::max(p->d, p->dv) > 128;  // one Q tile per work item (make_geom<.., SOLO>)
-  kp.num_m_blocks = dual ? 1 : std::max(1, (p->seqlen_q + (solo ? 1 : 2) * kp.pos_per_tile - 1) / ((solo ? 1 : 2) * kp.pos_per_tile));
+  const bool pair = use_pair(p, plan);            // four Q tiles per work item, two per CTA of a pair (make_geom<.., PAIR>)
+  const int tiles_item = (dual || solo) ? 1 : (pair ? 4 : 2);
+  kp.num_m_blocks = dual ? 1 : std::max(1, (p->seqlen_q + tiles_item * kp.pos_per_tile - 1) / (tiles_item * kp.pos_per_tile));
   kp.heads_work = plan->pack_gqa ? p->h_k : p->h;
   kp.num_splits = cta_splits;
   kp.num_work = kp.num_m_blocks * p->b * kp.heads_work * cta_splits;
-  kp.tiles_per_item = (dual || solo) ? 1 : 2;
+  kp.tiles_per_item = tiles_item;
   kp.num_sm = plan->num_sm;
   kp.sched = p->scheduler_metadata ? p->scheduler_metadata + kSchedHeaderWords : nullptr;
   // causal / local normalisation (hopper/flash_api.cpp:148-160, 796-805)
@@ -210,6 +236,7 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   fill_kernel_params(p, plan, kp);
   const bool dual = plan->dual_stream != 0;
   const bool solo = std::max(p->d, p->dv) > 128;
+  const bool pair = use_pair(p, plan);
   const int64_t rows_q = varlen_q ? p->total_q : p->seqlen_q;
 
   // ---- tensor maps
@@ -228,9 +255,10 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
     const uint64_t rows_k = paged ? uint64_t(p->page_size) : uint64_t(varlen_k ? p->total_k : p->seqlen_k);
     const uint64_t nb = paged ? uint64_t(p->num_pages) : uint64_t(varlen_k ? 1 : p->b_k);
     uint32_t box[4] = {uint32_t(cols_per_box), uint32_t(kp.kv_box_rows), 1, 1};
+    uint32_t boxK[4] = {uint32_t(cols_per_box), uint32_t(pair ? 64 : kp.kv_box_rows), 1, 1};  // a CTA of a pair holds 64 of the 128 keys
     uint64_t dimsK[4] = {uint64_t(p->d), rows_k, uint64_t(p->h_k), nb};
     uint64_t strK[4] = {0, uint64_t(p->k_row_stride) * elt, uint64_t(p->k_head_stride) * elt, uint64_t(p->k_batch_stride) * elt};
-    int rc = encode_tensor_map(&tmK, p->dtype, 4, p->k, dimsK, strK, box);
+    int rc = encode_tensor_map(&tmK, p->dtype, 4, p->k, dimsK, strK, boxK);
     if (rc) return rc;
     uint64_t dimsV[4] = {uint64_t(p->dv), rows_k, uint64_t(p->h_k), nb};
     uint64_t strV[4] = {0, uint64_t(p->v_row_stride) * elt, uint64_t(p->v_head_stride) * elt, uint64_t(p->v_batch_stride) * elt};
@@ -267,7 +295,7 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
     FA_CUDA(cudaGetLastError());
   }
   int num_sm = plan->num_sm;
-  const int grid = std::max(1, std::min(kp.num_work, num_sm));
+  const int grid = pair ? 2 * std::max(1, std::min(kp.num_work, num_sm / 2)) : std::max(1, std::min(kp.num_work, num_sm));
   const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : (p->dtype == FA100_FP16 ? kFmtF16 : kFmtE4M3);
   const int hd = solo ? 256 : ((p->d <= 64 && p->dv <= 64 && !fp8) ? 64 : 128);
   const bool f16 = p->dtype == FA100_FP16;
@@ -280,6 +308,9 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
     return f16 ? launch_instance<256, 2, false, true, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
                : launch_instance<256, 2, false, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
   if (hd == 64) return f16 ? FA_LAUNCH(64, 2, false, true) : FA_LAUNCH(64, 2, false, false);
+  if (pair)
+    return f16 ? launch_instance<128, 2, false, true, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
+               : launch_instance<128, 2, false, false, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
   return f16 ? FA_LAUNCH(128, 2, false, true) : FA_LAUNCH(128, 2, false, false);
 #undef FA_LAUNCH
 }

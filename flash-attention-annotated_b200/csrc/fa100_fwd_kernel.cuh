@@ -108,8 +108,11 @@ struct TileRange { int n_min, n_max; bool has_rows; };
 // Static persistent schedule: CTA c runs list positions c, 2 grid - 1 - c, 2 grid + c, ... (boustrophedon).  Item lengths
 // fall linearly inside a K/V group, so pairing a forward pass with a reversed one evens out what plain round-robin
 // leaves (makespan / mean 1.11 -> 1.05 at C3, measured on the host model in DESIGN.md section 4.1).
+// PAIR: the two CTAs of a cluster walk the list together (one entry = four 128-row Q tiles, two per CTA).
+template <bool PAIR = false>
 FA_DEVICE int work_index(int round) {
-  return round * int(gridDim.x) + ((round & 1) ? int(gridDim.x) - 1 - int(blockIdx.x) : int(blockIdx.x));
+  const int grid = PAIR ? int(gridDim.x) >> 1 : int(gridDim.x), cta = PAIR ? int(blockIdx.x) >> 1 : int(blockIdx.x);
+  return round * grid + ((round & 1) ? grid - 1 - cta : cta);
 }
 
 constexpr int kSchedHeaderWords = 8;  // [magic, num_splits, pack_gqa, num_sm, num_work bound, 0, 0, 0] written by the host (get_scheduler_metadata)
@@ -200,10 +203,11 @@ FA_DEVICE TileRange tile_range(const FwdKernelParams& p, const SeqInfo& s, int p
 }
 
 // ----------------------------------------------------------------------------- shared memory
-template <int HD, int ELT>
+template <int HD, int ELT, bool PAIR = false>
 struct FwdSmem {
   static constexpr int kQBytes = kBlockM * HD * ELT;   // one Q tile
-  static constexpr int kKVBytes = kBlockN * HD * ELT;  // one K or V tile
+  // one K or V tile; a CTA of a pair holds half of it (K: 64 of the 128 keys, V: 64 of the 128 value columns)
+  static constexpr int kKVBytes = kBlockN * HD * ELT / (PAIR ? 2 : 1);
   static constexpr int kBarrierBytes = 1024;           // mbarriers + TMEM base (+ the trace build's counters in the last 128 B)
   static constexpr int kBudget = 227 * 1024 - kBarrierBytes;
   // head dims above 128 run one Q tile per work item: O alone needs 256 TMEM columns, so the second tile pipeline stays

@@ -23,13 +23,40 @@ struct WorkGeom {
 // pipeline idles and the per-block chain QK -> softmax -> PV (~3300 clk) is longer than the 64 KB block takes to
 // arrive from HBM (~2450 clk at 6.5 TB/s over 148 SMs).
 // SOLO (head dim > 128): a work item is ONE 128-row tile; tile 1 never has rows.
-template <bool DUAL, bool SOLO = false>
-FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w) {
+// PAIR (cta_group::2): a work item is four 128-row tiles, tile t of CTA r being row block 4 m + 2 t + r.  The t-th tiles
+// of the two CTAs form one M = 256 MMA, so both walk the UNION of their key-block ranges; a block outside a CTA's own
+// range is simply fully masked for its rows (at most one block per tile pair under a causal mask).
+template <bool DUAL, bool SOLO = false, bool PAIR = false>
+FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w, int rank = 0) {
   WorkGeom g;
   g.it = decode_work(p, w);
   g.seq = load_seq(p, g.it.bi);
   g.hk = p.pack > 1 ? g.it.head : g.it.head / p.qheads_per_kv;
   g.n_lo = 0x7fffffff; g.n_hi = 0;
+  if (PAIR) {
+#pragma unroll
+    for (int t = 0; t < kQTiles; ++t) {
+      // the union of the two whole ranges is what gets cut into splits: both CTAs must walk the same blocks, and a block
+      // may belong to one split only (cutting each tile's own range, as the 1-CTA kernel does, would give the two
+      // CTAs different shares of the same split)
+      const TileRange a = tile_range(p, g.seq, (g.it.m_blk * 4 + 2 * t + rank) * p.pos_per_tile, 0, 1);
+      const TileRange b = tile_range(p, g.seq, (g.it.m_blk * 4 + 2 * t + (rank ^ 1)) * p.pos_per_tile, 0, 1);
+      const bool la = a.n_max > a.n_min, lb = b.n_max > b.n_min;
+      TileRange u;
+      u.has_rows = a.has_rows || b.has_rows;
+      u.n_min = la && lb ? min(a.n_min, b.n_min) : (la ? a.n_min : b.n_min);
+      u.n_max = la && lb ? max(a.n_max, b.n_max) : (la ? a.n_max : b.n_max);
+      if (!la && !lb) u.n_min = u.n_max = 0;
+      if (g.it.nsplits > 1) {
+        const int per = u.n_max <= u.n_min ? 0 : (u.n_max - u.n_min + g.it.nsplits - 1) / g.it.nsplits;
+        u.n_min = u.n_min + g.it.split * per;
+        u.n_max = max(min(u.n_min + per, u.n_max), u.n_min);
+      }
+      g.tr[t] = u;
+      if (u.n_max > u.n_min) { g.n_lo = min(g.n_lo, u.n_min); g.n_hi = max(g.n_hi, u.n_max); }
+    }
+    return g;
+  }
   if (DUAL || SOLO) {
     const TileRange r = tile_range(p, g.seq, g.it.m_blk * p.pos_per_tile, g.it.split, g.it.nsplits);
     g.tr[0] = r;
@@ -47,7 +74,8 @@ FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w) {
   }
   return g;
 }
-template <bool ONE_TILE> FA_DEVICE int tile_pos0(const FwdKernelParams& p, const WorkItem& it, int t) {
+template <bool ONE_TILE, bool PAIR = false> FA_DEVICE int tile_pos0(const FwdKernelParams& p, const WorkItem& it, int t, int rank = 0) {
+  if (PAIR) return (it.m_blk * 4 + 2 * t + rank) * p.pos_per_tile;
   return (ONE_TILE ? it.m_blk : it.m_blk * kQTiles + t) * p.pos_per_tile;  // ONE_TILE = DUAL or SOLO
 }
 FA_DEVICE bool tile_live(const WorkGeom& g, int t) { return g.tr[t].n_max > g.tr[t].n_min; }
@@ -59,10 +87,10 @@ template <int STAGES> FA_DEVICE void ring_advance(RingState& r) { if (++r.stage 
 // ----------------------------------------------------------------------------- TMA producer
 // The whole warp walks the schedule (warp-uniform control flow keeps descriptors and coordinates in uniform
 // registers); one elected lane issues the bulk copies.
-template <int HD, int ELT, bool DUAL>
+template <int HD, int ELT, bool DUAL, bool PAIR = false>
 FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, const CUtensorMap* tmK,
-                             const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar) {
-  using L = FwdSmem<HD, ELT>;
+                             const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar, int rank = 0) {
+  using L = FwdSmem<HD, ELT, PAIR>;
   constexpr int kRowBytes = 128;                       // 128B-swizzled rows
   constexpr int kColsPerBox = kRowBytes / ELT;         // 64 (16-bit) or 128 (8-bit)
   constexpr int kBoxesD = HD / kColsPerBox > 0 ? HD / kColsPerBox : 1;  // boxes along the head dim
@@ -76,20 +104,25 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   // only the boxes that hold real head-dim columns are loaded (d = 192 in the 256 instance: 3 of 4)
   const uint32_t q_tx = uint32_t(p.qk_boxes * kRowBytes) * p.pack * p.pos_per_tile;
   const int n_work = total_work(p);
-  for (int wi = 0, w; (w = work_index(wi)) < n_work; ++wi) {
-    const WorkGeom g = make_geom<DUAL, (HD > 128)>(p, w);
+  for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
+    const WorkGeom g = make_geom<DUAL, (HD > 128), PAIR>(p, w, rank);
     if (g.n_hi <= g.n_lo) continue;
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
       if (!tile_live(g, t)) continue;
       mbar_wait(&bar->q_empty[t], (q_it[t] & 1) ^ 1, 0x10 + t);
-      const int pos0 = tile_pos0<DUAL || (HD > 128)>(p, g.it, t);
+      const int pos0 = tile_pos0<DUAL || (HD > 128), PAIR>(p, g.it, t, rank);
       if (elect_one()) {
-        mbar_arrive_expect_tx(&bar->q_full[t], q_tx);
+        // PAIR: both CTAs' Q tiles are counted on the leader's barrier; the leader announces the bytes of both
+        if (!PAIR || rank == 0) mbar_arrive_expect_tx(&bar->q_full[t], PAIR ? 2 * q_tx : q_tx);
 #pragma unroll
         for (int hb = 0; hb < kBoxesD; ++hb)
-          if (hb < p.qk_boxes) tma_load_5d(sQ + t * L::kQBytes + hb * kHalfBytes, tmQ, &bar->q_full[t], hb * kColsPerBox, 0,
-                      g.seq.q_off + pos0, g.it.head, g.seq.bq);
+          if (hb < p.qk_boxes) {
+            if (PAIR) tma_load_5d_2sm(sQ + t * L::kQBytes + hb * kHalfBytes, tmQ, &bar->q_full[t], hb * kColsPerBox, 0,
+                                      g.seq.q_off + pos0, g.it.head, g.seq.bq);
+            else tma_load_5d(sQ + t * L::kQBytes + hb * kHalfBytes, tmQ, &bar->q_full[t], hb * kColsPerBox, 0,
+                             g.seq.q_off + pos0, g.it.head, g.seq.bq);
+          }
       }
       __syncwarp();
       ++q_it[t];
@@ -102,7 +135,21 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
       mbar_wait(&bar->kv_empty[stage], ring.phase ^ 1, 0x20 + kv);
       uint8_t* dst = sKV + stage * L::kKVBytes;
       const int boxes = kv == 0 ? p.qk_boxes : p.v_boxes;
-      if (FA100_GARBAGE & 16) { if (elect_one()) mbar_arrive(&bar->kv_full[stage]); }  // timing only: no K/V traffic into shared memory
+      if (PAIR) {
+        // this CTA's half of the tile: keys [64 rank, +64) of K (boxes of 64 rows), value columns [64 rank, +64) of V
+        // (one box of 128 rows); the bytes of both halves are counted on the leader's barrier
+        if (elect_one()) {
+          if (rank == 0) mbar_arrive_expect_tx(&bar->kv_full[stage], 2 * (kv == 0 ? boxes * (kHalfBytes / 2) : kHalfBytes));
+          if (kv == 0) {
+#pragma unroll
+            for (int hb = 0; hb < kBoxesD; ++hb)
+              if (hb < boxes) tma_load_4d_2sm(dst + hb * (kHalfBytes / 2), tm, &bar->kv_full[stage], hb * kColsPerBox,
+                                              g.seq.k_off + nb * kBlockN + rank * (kBlockN / 2), g.hk, g.seq.bk);
+          } else {
+            tma_load_4d_2sm(dst, tm, &bar->kv_full[stage], rank * kColsPerBox, g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
+          }
+        }
+      } else if (FA100_GARBAGE & 16) { if (elect_one()) mbar_arrive(&bar->kv_full[stage]); }  // timing only: no K/V traffic into shared memory
       else if (p.page_size == 0) {
         if (elect_one()) {
           mbar_arrive_expect_tx(&bar->kv_full[stage], boxes * kHalfBytes);
@@ -161,16 +208,17 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
 // same ring sequence (kIsQK selects which stages a warp acts on): K(first), then V(nb), K(nb-1) per key block, or in
 // DUAL mode K_0, K_1, then V_0, K_0(next), V_1, K_1(next) per step.  All 32 lanes run the control flow and the waits
 // (descriptors stay in uniform registers); one elected lane issues.
-template <int HD, int ELT, bool FP8, bool DUAL, bool kIsQK>
+template <int HD, int ELT, bool FP8, bool DUAL, bool kIsQK, bool PAIR = false>
 FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar, uint32_t tmem) {
-  using L = FwdSmem<HD, ELT>;
+  using L = FwdSmem<HD, ELT, PAIR>;
   constexpr int kHalfBytes = kBlockN * 128;
   constexpr int kColsPerBox = 128 / ELT;
   constexpr int kKPerMma = 32 / ELT;                          // 16 (16-bit) / 32 (8-bit)
   constexpr int kSlicesPerBox = kColsPerBox / kKPerMma;       // 4
   constexpr int kQKSlices = HD / kKPerMma;
   constexpr int kPVSlices = kBlockN / kKPerMma;
-  const uint32_t idesc = kIsQK ? make_idesc(fmt, fmt, kBlockM, kBlockN, 0, 0) : make_idesc(fmt, fmt, kBlockM, p.pv_n, 0, 1);
+  constexpr int kM = PAIR ? 2 * kBlockM : kBlockM;  // PAIR: one instruction covers the t-th tiles of both CTAs
+  const uint32_t idesc = kIsQK ? make_idesc(fmt, fmt, kM, kBlockN, 0, 0) : make_idesc(fmt, fmt, kM, p.pv_n, 0, 1);
   // K-major operand tiles [128 rows][128 B] SW128: 8-row groups 1024 B apart (SBO); LBO unused (1).
   // V as MN-major B operand: 128-byte rows along dv, 8 key rows per swizzle atom (SBO = 1024 B), the next
   // 64 (16-bit) / 128 (8-bit) dv columns in the next box (LBO = one [128][128 B] region).
@@ -179,6 +227,9 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   const uint32_t q_lo = (smem_u32(sQ) >> 4) | kLboK;
   const uint32_t kv_lo = smem_u32(sKV) >> 4;
 
+  // completion signals: PAIR multicasts every arrival to the same barrier in both CTAs (the peer's producer and softmax
+  // warps wait on their own copies)
+  auto commit = [&](uint64_t* b) { if (PAIR) tc_commit_2sm(b); else tc_commit(b); };
   RingState ring;
   uint32_t q_it[kQTiles] = {0, 0}, p_it[kQTiles] = {0, 0}, o_it[kQTiles] = {0, 0};
   uint32_t qk_n = 0;  // QK batches issued so far == phases of s_free consumed + 1
@@ -196,10 +247,15 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
 #pragma unroll
       for (int ks = 0; ks < kQKSlices; ++ks) {
         const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
-        if (ks < p.qk_slices && !(FA100_GARBAGE & 64)) mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
+        // PAIR: this CTA's K boxes hold 64 keys, so the next 64 head-dim columns are half as far away
+        const uint32_t off_b = PAIR ? (ks / kSlicesPerBox) * (kHalfBytes >> 5) + (ks % kSlicesPerBox) * 2 : off;
+        if (ks < p.qk_slices && !(FA100_GARBAGE & 64)) {
+          if (PAIR) mma_ss_2sm(tmem, a_lo + off, b_lo + off_b, kHi, idesc, ks > 0);
+          else mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
+        }
       }
-      tc_commit(&bar->s_full[t]);
-      if (last_use_of_q) tc_commit(&bar->q_empty[t]);
+      commit(&bar->s_full[t]);
+      if (last_use_of_q) commit(&bar->q_empty[t]);
       FA_LAT_STAMP(&bar->ts[t]);
     }
     __syncwarp();
@@ -217,9 +273,12 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
       const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboV;
 #pragma unroll
       for (int ks = 0; ks < kPVSlices; ++ks)
-        if (!(FA100_GARBAGE & 32)) mma_ts<FP8>(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc, (!first || ks > 0));
-      tc_commit(&bar->pv_done[t]);
-      if (last) tc_commit(&bar->o_full[t]);
+        if (!(FA100_GARBAGE & 32)) {
+          if (PAIR) mma_ts_2sm(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc, (!first || ks > 0));
+          else mma_ts<FP8>(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc, (!first || ks > 0));
+        }
+      commit(&bar->pv_done[t]);
+      if (last) commit(&bar->o_full[t]);
     }
     __syncwarp();
     FA_PROF(3);
@@ -237,15 +296,15 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
     return stage;
   };
   auto release = [&](int stage) {
-    if (elect_one()) tc_commit(&bar->kv_empty[stage]);
+    if (elect_one()) commit(&bar->kv_empty[stage]);
     __syncwarp();
   };
 
   const int n_work = total_work(p);
-  for (int wi = 0, w; (w = work_index(wi)) < n_work; ++wi) {
+  for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
     int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi;
     {
-      const WorkGeom g = make_geom<DUAL, (HD > 128)>(p, w);
+      const WorkGeom g = make_geom<DUAL, (HD > 128), PAIR>(p, w, 0);
       n_lo = g.n_lo; n_hi = g.n_hi;
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) { n_min[t] = g.tr[t].n_min; n_max[t] = g.tr[t].n_max; }

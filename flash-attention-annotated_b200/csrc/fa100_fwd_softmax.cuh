@@ -124,13 +124,13 @@ struct RowGeom {
   bool has_rows;
 };
 
-template <bool FP8, bool DUAL, bool SOLO>
-FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row) {
-  const WorkGeom g = make_geom<DUAL, SOLO>(p, w);
+template <bool FP8, bool DUAL, bool SOLO, bool PAIR = false>
+FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row, int rank = 0) {
+  const WorkGeom g = make_geom<DUAL, SOLO, PAIR>(p, w, rank);
   RowGeom r;
   r.has_rows = g.tr[t].has_rows;
   r.n_min = g.tr[t].n_min; r.n_max = g.tr[t].n_max;
-  const int pos = tile_pos0<DUAL || SOLO>(p, g.it, t) + (p.pack > 1 ? row / p.pack : row);
+  const int pos = tile_pos0<DUAL || SOLO, PAIR>(p, g.it, t, rank) + (p.pack > 1 ? row / p.pack : row);
   const int shift = g.seq.sk - g.seq.sq;
   int col_hi = g.seq.sk, col_lo = 0;
   if (p.is_causal) col_hi = min(col_hi, pos + 1 + shift);
@@ -158,19 +158,22 @@ FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row) {
 // on Q tile t = w / 4 and owns TMEM lanes (= query rows) 32*(w%4)..; one thread owns one row, so the row max and the
 // row sum need no shuffles.  The step loop has two bodies: a lean one for interior key blocks (no mask, no softcap; it
 // is the instruction stream tools/ubench/ubench_softmax.cu measures in isolation) and a general one for boundary blocks.
-template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
-FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, uint8_t* sO, FwdBarriers* bar, uint32_t tmem, int warp, int lane) {
+template <int HD, int ELT, bool FP8, bool F16, bool DUAL, bool PAIR = false>
+FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, uint8_t* sO, FwdBarriers* bar, uint32_t tmem, int warp, int lane, int rank = 0) {
   const int t = warp >> 2, q = warp & 3;
   const int row = q * 32 + lane;
   const uint32_t tS = tmem + (uint32_t(q * 32) << 16);  // the score buffer both tiles take turns in
   const uint32_t tP = tS + 128 + t * 64;                // this tile's probabilities (operand dtype)
   const uint32_t tO = tS + 256 + t * 128;
   uint32_t s_it = 0, o_it = 0, pv_n = 0;                // pv_n: P blocks published so far == PV batches requested
+  // the barriers the MMA warps wait on live in the pair's leader: the peer's softmax warps arrive there over the cluster
+  const uint32_t a_s_free = PAIR ? mapa_u32(smem_u32(&bar->s_free), 0) : 0, a_p_full = PAIR ? mapa_u32(smem_u32(&bar->p_full[t]), 0) : 0,
+                 a_o_empty = PAIR ? mapa_u32(smem_u32(&bar->o_empty[t]), 0) : 0;
   FA_PROF_DECL();  // 0 s_full wait, 1 S load, 2 s_free + mask + row max, 3 rescale, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait + publish, 7 rest
 
   const int n_work = total_work(p);
-  for (int wi = 0, w; (w = work_index(wi)) < n_work; ++wi) {
-    const RowGeom rg = row_geom<FP8, DUAL, (HD > 128)>(p, w, t, row);
+  for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
+    const RowGeom rg = row_geom<FP8, DUAL, (HD > 128), PAIR>(p, w, t, row, rank);
     if (!rg.has_rows) continue;
     const float scale_log2 = rg.scale_log2;
     const bool softcap = p.softcap_pre != 0.f;
@@ -193,7 +196,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
       // the scores are in registers: hand S to the other tile's QK
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->s_free);
+      if (lane == 0) { if (PAIR) mbar_arrive_cluster(a_s_free); else mbar_arrive(&bar->s_free); }
       if (q == 3) FA_LAT_STAMP(&bar->ts[2]);
       FA_TRACE_POINT(0xC4);
       // P_t and O_t may be touched again once the previous P_t V has drained; poll now, block only right before the
@@ -363,7 +366,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->p_full[t]);
+      if (lane == 0) { if (PAIR) mbar_arrive_cluster(a_p_full); else mbar_arrive(&bar->p_full[t]); }
       if (q == 3) FA_LAT_STAMP(&bar->ts[4 + t]);
       FA_TRACE_POINT(0xA0 + t);
       ++pv_n;
@@ -373,12 +376,12 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
 
     // ---- epilogue: O / rowsum, LSE (hopper/softmax.h:137-155, epilogue_fwd.hpp:215-481); geometry is recomputed here
     {
-      const WorkGeom g = make_geom<DUAL, (HD > 128)>(p, w);
+      const WorkGeom g = make_geom<DUAL, (HD > 128), PAIR>(p, w, rank);
       const bool split = p.o_accum != nullptr;  // fp32 partials (split-KV, or one hop of ring attention)
       const int part = DUAL ? g.it.split * 2 + t : g.it.split;  // index of this partial
       const bool live = rg.n_max > rg.n_min;
       const int in_tile = p.pack > 1 ? row / p.pack : row;
-      const int pos = tile_pos0<DUAL || (HD > 128)>(p, g.it, t) + in_tile;
+      const int pos = tile_pos0<DUAL || (HD > 128), PAIR>(p, g.it, t, rank) + in_tile;
       const int hq = p.pack > 1 ? g.it.head * p.qheads_per_kv + row % p.pack : g.it.head;
       const bool row_valid = in_tile < p.pos_per_tile && pos < g.seq.sq;
       float out_scale = 1.0f;
@@ -404,7 +407,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
         // swizzle, and one thread sends the box with a bulk tensor store; rows past seqlen_q are clipped by the tensor map.
         // The staging box is free again once the previous store has read it (wait_group.read by the issuing thread,
         // at the top of the next slice or the next work item).
-        uint8_t* stage = sO + t * FwdSmem<HD, ELT>::kOStageBytes;
+        uint8_t* stage = sO + t * FwdSmem<HD, ELT, PAIR>::kOStageBytes;
         const bool issuer = (q == 0 && lane == 0);
 #pragma unroll
         for (int sl = 0; sl < HD / 64; ++sl) {
@@ -476,7 +479,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
       if (live) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bar->o_empty[t]);
+        if (lane == 0) { if (PAIR) mbar_arrive_cluster(a_o_empty); else mbar_arrive(&bar->o_empty[t]); }
       }
     }
   }
@@ -486,53 +489,63 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
 }
 
 // ----------------------------------------------------------------------------- kernel entry
-template <int HD, int ELT, bool FP8, bool F16, bool DUAL>
+template <int HD, int ELT, bool FP8, bool F16, bool DUAL, bool PAIR = false>
 __global__ void __launch_bounds__(kThreads, 1)
 fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constant__ CUtensorMap tmQ,
                  const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                  const __grid_constant__ CUtensorMap tmO, uint32_t fmt) {
-  using L = FwdSmem<HD, ELT>;
+  using L = FwdSmem<HD, ELT, PAIR>;
   extern __shared__ __align__(1024) uint8_t smem[];  // 128-byte swizzle atoms need 1 KB alignment
   uint8_t* sQ = smem;
   uint8_t* sKV = smem + L::kQSlots * L::kQBytes;
   uint8_t* sO = sKV + L::kStages * L::kKVBytes;
   FwdBarriers* bar = reinterpret_cast<FwdBarriers*>(smem + L::kDataBytes);
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int rank = PAIR ? int(cluster_ctarank()) : 0;  // PAIR: launched as clusters of two CTAs; rank 0 issues the MMAs
   FA_TRACE_BEGIN();
   if (smem_u32(smem) & 1023u) __trap();
 
   if (warp == kLoadWarp && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); if (p.o_tma) tma_prefetch_desc(&tmO); }
   if (warp == kMmaWarp && lane == 0) {
+    // PAIR: the softmax warps of both CTAs arrive on the leader's s_free / p_full / o_empty
+    constexpr int kSmxArrivals = PAIR ? 8 : 4;
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
       mbar_init(&bar->q_full[t], 1); mbar_init(&bar->q_empty[t], 1);
-      mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 4); mbar_init(&bar->pv_done[t], 1);
-      mbar_init(&bar->o_full[t], 1); mbar_init(&bar->o_empty[t], 4);
+      mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], kSmxArrivals); mbar_init(&bar->pv_done[t], 1);
+      mbar_init(&bar->o_full[t], 1); mbar_init(&bar->o_empty[t], kSmxArrivals);
     }
-    mbar_init(&bar->s_free, 4);
+    mbar_init(&bar->s_free, kSmxArrivals);
     for (int s = 0; s < 8; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
     fence_mbar_init();
   }
-  if (warp == 0) { tmem_alloc(&bar->tmem_base, 512); tmem_relinquish(); }
+  if (warp == 0) {
+    if (PAIR) { tmem_alloc_2sm(&bar->tmem_base, 512); tmem_relinquish_2sm(); }
+    else { tmem_alloc(&bar->tmem_base, 512); tmem_relinquish(); }
+  }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers exist before anything is sent to them
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
 
   // register pool at launch: 384 threads x 168; warps 8-11 give 112 each to the 8 softmax warps (+56 each)
   if (warp < kSoftmaxWarps) {
     setmaxnreg_inc<224>();
-    softmax_role<HD, ELT, FP8, F16, DUAL>(p, &tmO, sO, bar, tmem, warp, lane);
+    softmax_role<HD, ELT, FP8, F16, DUAL, PAIR>(p, &tmO, sO, bar, tmem, warp, lane, rank);
   } else {
     setmaxnreg_dec<56>();
-    if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL, true>(p, fmt, sQ, sKV, bar, tmem);
-    if (warp == kPvWarp) mma_role<HD, ELT, FP8, DUAL, false>(p, fmt, sQ, sKV, bar, tmem);
-    if (warp == kLoadWarp) producer_role<HD, ELT, DUAL>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar);
+    if (rank == 0) {
+      if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL, true, PAIR>(p, fmt, sQ, sKV, bar, tmem);
+      if (warp == kPvWarp) mma_role<HD, ELT, FP8, DUAL, false, PAIR>(p, fmt, sQ, sKV, bar, tmem);
+    }
+    if (warp == kLoadWarp) producer_role<HD, ELT, DUAL, PAIR>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar, rank);
   }
   FA_TRACE_END();
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
+  if (PAIR) cluster_sync_all();  // nothing of the peer (barriers, K / V halves, tensor memory) may go away while the other CTA still uses it
+  if (warp == 0) { if (PAIR) tmem_dealloc_2sm(tmem, 512); else tmem_dealloc(tmem, 512); }
 }
 
 }  // namespace fa100

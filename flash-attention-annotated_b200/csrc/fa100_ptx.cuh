@@ -66,6 +66,29 @@ FA_DEVICE bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 
+// ------------------------------------------------------------------ CTA pairs (cta_group::2)
+// Encodings follow cute/arch/copy_sm100_tma.hpp (SM100_TMA_2SM_LOAD), cutlass/arch/barrier.h (umma_arrive_multicast_2x1SM,
+// ClusterBarrier::arrive(cta_id)) and cute/arch/tmem_allocator_sm100.hpp (Allocator2Sm).
+FA_DEVICE uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r)); return r; }
+FA_DEVICE void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+// shared::cluster address of the same shared-memory location in CTA `rank` of the cluster
+FA_DEVICE uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// Default semantics (release at CTA scope), as cutlass::arch::ClusterBarrier::arrive(cta_id) does: what the arrival orders
+// here are tensor-memory stores, already fenced by tcgen05.wait::st / fence::before_thread_sync.  A `.release.cluster`
+// arrive costs ~1100 clk per call (cluster-scope release = cache maintenance), measured in profiles/r01c_buckets_pair.log.
+FA_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
+}
+// the pair's leader (even CTA) owns the barriers the MMA warps wait on: clearing the peer bit of a shared::cluster
+// address names the leader's copy
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+
 // Watchdog: a wrong phase/count must never hang the GPU box.  A wait that lasts longer than
 // FA100_WATCHDOG_CYCLES records {tag, block, thread, parity}, raises a device-wide abort flag and returns;
 // every other wait then falls through as well, the kernel ends (with garbage) and the host reads the
@@ -184,6 +207,19 @@ FA_DEVICE void tma_load_5d(void* dst, const CUtensorMap* m, uint64_t* bar, int c
       ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
 }
+// 2-CTA loads: the data lands in this CTA's shared memory, the bytes are counted on the LEADER's mbarrier
+FA_DEVICE void tma_load_4d_2sm(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];\n"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+FA_DEVICE void tma_load_5d_2sm(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];\n"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
 FA_DEVICE void tma_store_4d(const CUtensorMap* m, const void* src, int c0, int c1, int c2, int c3) {
   asm volatile(
       "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];\n"
@@ -202,12 +238,25 @@ FA_DEVICE void tmem_relinquish() { asm volatile("tcgen05.relinquish_alloc_permit
 FA_DEVICE void tmem_dealloc(uint32_t addr, uint32_t ncols) {  // whole warp
   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(addr), "r"(ncols) : "memory");
 }
+FA_DEVICE void tmem_alloc_2sm(uint32_t* smem_dst, uint32_t ncols) {  // the same warp of both CTAs of a pair
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
+}
+FA_DEVICE void tmem_relinquish_2sm() { asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory"); }
+FA_DEVICE void tmem_dealloc_2sm(uint32_t addr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(addr), "r"(ncols) : "memory");
+}
 FA_DEVICE void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 FA_DEVICE void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
 
 // tcgen05.commit: the mbarrier gets one arrival once all MMAs issued so far by this thread are done.
 FA_DEVICE void tc_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// 2-CTA commit: one arrival on the barrier at the same offset in BOTH CTAs of the pair once the MMAs issued so far are done
+FA_DEVICE void tc_commit_2sm(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+               ::"r"(smem_u32(bar)), "h"(uint16_t(3)) : "memory");
 }
 
 // ------------------------------------------------------------------ tcgen05: MMA
@@ -269,6 +318,19 @@ FA_DEVICE void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t 
         "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}\n"
         ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+// cta_group::2 forms (16-bit operands): M = 256 rows over the pair, every CTA supplies its 128 rows of A and half of B
+FA_DEVICE void mma_ss_2sm(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n\t}\n"
+      ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+FA_DEVICE void mma_ts_2sm(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], db, %4, p;\n\t}\n"
+      ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
 }
 // descriptor words for a 128-byte-swizzled operand: hi = SBO >> 4 | version 1 << 14 | SWIZZLE_128B << 29
 __host__ __device__ constexpr uint32_t sdesc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFF) | (1u << 14) | (2u << 29); }

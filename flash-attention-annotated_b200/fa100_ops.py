@@ -195,6 +195,7 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     p.softmax_scale, p.softcap = float(softmax_scale), float(softcap)
     p.is_causal, p.window_left, p.window_right, p.attention_chunk = int(is_causal), window_size_left, window_size_right, attention_chunk
     p.num_splits, p.pack_gqa, p.num_sm = splits, pl.pack_gqa, pl.num_sm
+    p.variant = _variant()
     with torch.cuda.device(q.device):
         if scheduler_metadata is not None and scheduler_metadata.numel() >= META_HEADER + _sched_words(b):
             # the schedule get_scheduler_metadata built ahead of time (CUDA-graphed decode): used as is
@@ -219,6 +220,12 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
 META_HEADER = 8  # host-written words in front of the device-built schedule
 DYN_SPLIT_BOUND = 8  # partials a ragged decode call is sized for when the caller leaves num_splits to the library
 _NO_SCHED = bool(os.environ.get("FA100_NO_SCHED"))  # A/B switch: static schedule for ragged batches too
+
+
+def _variant() -> int:
+    """Fa100FwdParams.variant: FA100_PAIR=1 forces the 2-CTA (cta_group::2) kernel wherever it is eligible, FA100_PAIR=0
+    forbids it; unset, the library's default applies (one CTA per work item: the pair kernel measures within 1 % of it)."""
+    return {"1": 1, "0": 2}.get(os.environ.get("FA100_PAIR", ""), 0)
 
 
 def _sched_words(b: int) -> int:
@@ -361,6 +368,7 @@ def mha_fwd_get_scheduler_metadata(batch_size, max_seqlen_q, max_seqlen_k, num_h
     p.total_q = 1 if cu_seqlens_q is not None else 0  # sizes of the packed tensors play no part in the schedule
     p.is_causal, p.window_left, p.window_right, p.attention_chunk = int(is_causal), window_size_left, window_size_right, attention_chunk
     p.num_splits, p.pack_gqa, p.num_sm = pl.num_splits, pl.pack_gqa, pl.num_sm
+    p.variant = _variant()
     with torch.cuda.device(dev):
         N.check(N.lib().fa100_prepare_scheduler(C.byref(p), _ptr(meta), meta.numel(), _stream()))
     return meta

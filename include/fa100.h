@@ -124,7 +124,12 @@ typedef struct Fa100FwdParams {
   /* Optional device-built schedule for ragged batches: a buffer of fa100_scheduler_metadata_words(b) int32 that
    * fa100_prepare_scheduler has filled for the SAME sizes, lengths, num_splits and pack_gqa.  Null = static schedule. */
   const int32_t* scheduler_metadata;
-  int32_t reserved[8];
+  /* Kernel variant.  The 2-CTA kernel runs CTA pairs with cta_group::2 MMAs (M = 256 over two SMs, each CTA holding half
+   * of every K / V tile); it is eligible for bf16 / fp16, d = dv = 128, K/V not paged, not the dual-stream decode kernel.
+   * 0 = the library's default (today: one CTA per work item), 1 = pairs wherever eligible, 2 = one CTA per work item
+   * always.  fa100_prepare_scheduler must see the same value as fa100_fwd. */
+  int32_t variant;
+  int32_t reserved[7];
 } Fa100FwdParams;
 
 /* LSE-weighted merge of split partials (hopper/flash_fwd_combine_kernel.h:200-483,

@@ -9,6 +9,8 @@ Tolerances (written here as north_star requires):
 """
 import math
 
+import os
+
 import pytest
 import torch
 
@@ -621,7 +623,8 @@ def test_prepare_scheduler_metadata():
                                     cu_seqlens_q=cu_q.to(DEV), causal=False, num_splits=1).cpu()
     assert meta[0].item() == 0xFA100
     body = meta[8:]
-    m_blocks = [(int(x) + 255) // 256 for x in lens_q]                       # 256 query rows per work item (no pack-GQA here)
+    rows_item = 512 if os.environ.get("FA100_PAIR") == "1" else 256              # query rows per work item (no pack-GQA here)
+    m_blocks = [(int(x) + rows_item - 1) // rows_item for x in lens_q]
     # a tile past the end of the sequence has no key blocks: count the real 128-row tiles
     cost = [((int(q) + 127) // 128 if mb else 0) * ((int(k) + 127) // 128) for q, mb, k in zip(lens_q, m_blocks, lens_k)]
     order = sorted(range(b), key=lambda i: (-cost[i], i))
@@ -679,3 +682,22 @@ def test_ragged_decode_dynamic_splits(page_size):
                                                page_table=None if table is None else table.to(DEV), scheduler_metadata=meta.to(DEV),
                                                num_splits=8, return_softmax_lse=True)
     _check(out2, lse2, ref, low, lse_ref)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("sq,sk", [(256, 512), (1024, 1024), (700, 500), (1500, 3000)])
+def test_two_cta_variant(sq, sk, causal, monkeypatch):
+    """The cta_group::2 kernel (Fa100FwdParams.variant = 1 via FA100_PAIR=1): CTA pairs, M = 256 MMAs, each CTA holding half
+    of every K / V tile.  Same oracle, same tolerance; also bitwise equal to the 1-CTA kernel (same per-row arithmetic)."""
+    F = _iface()
+    q, k, v = _qkv(2, sq, sk, 8, 2, 128, torch.bfloat16, seed=5)
+    ref, lse_ref = A.attention_oracle(q, k, v, causal=causal)
+    low, _ = A.attention_oracle(q, k, v, causal=causal, upcast=False, reorder_ops=True)
+    monkeypatch.setenv("FA100_PAIR", "0")
+    base, _ = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), causal=causal, return_attn_probs=True)
+    monkeypatch.setenv("FA100_PAIR", "1")
+    for num_splits in (1, 3):
+        out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), causal=causal, num_splits=num_splits, return_attn_probs=True)
+        _check(out, lse, ref, low, lse_ref)
+        if num_splits == 1:
+            assert torch.equal(out, base)

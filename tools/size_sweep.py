@@ -19,7 +19,8 @@ for b in (int(os.environ.get("SWEEP_B", "0")),) if os.environ.get("SWEEP_B") els
     e0.record(); flash_attn_func(q, k, v, causal=causal); e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     pr = N.prof()
-    items = h * b * (s // 256); grid = min(items, 148)
+    pair = os.environ.get("FA100_PAIR") == "1"  # CTA pairs: 512 rows per work item, 74 pairs walk the list
+    items = h * b * (s // (512 if pair else 256)); grid = min(items, 74 if pair else 148)
     mine = sum(1 for wi in range(items) if (wi * grid + (grid - 1 if wi & 1 else 0)) < items)
     kb = mine * (s // 128)
     w0 = pr[0]
