@@ -82,6 +82,7 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   // falls back to cp.async gathers when the page does not hold whole key blocks, hopper/paged_kv.h:233-283); pages of
   // 128 rows or a multiple are one box per key block, a page of 1 row is 128 boxes.
   kp.kv_box_rows = paged ? std::gcd(128, p->page_size) : 128;
+  kp.merge = p->merge_partial;
   const int G = p->h / p->h_k;
   kp.qheads_per_kv = G;
   kp.pack = plan->pack_gqa ? G : 1;
@@ -228,6 +229,9 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   }
   const int splits = plan->num_splits;
   if (splits > 1) FA_CHECK_ARG(p->o_accum && p->lse_accum, "num_splits > 1 needs o_accum and lse_accum");
+  FA_CHECK_ARG(p->merge_partial >= 0 && p->merge_partial <= 2, "merge_partial must be 0, 1 or 2");
+  if (p->merge_partial) FA_CHECK_ARG(p->o_accum && p->lse_accum && splits == 1 && !plan->dual_stream, "merge_partial needs o_accum / lse_accum and a single partial");
+  if (p->merge_partial == 2) FA_CHECK_ARG(p->o && p->lse, "merge_partial = 2 writes o and lse");
   FA_CHECK_ARG((p->o_accum == nullptr) == (p->lse_accum == nullptr), "o_accum and lse_accum must be given together");
   FA_CHECK_ARG(p->o_accum != nullptr || (p->o != nullptr && p->lse != nullptr), "o and lse are required without o_accum");
 

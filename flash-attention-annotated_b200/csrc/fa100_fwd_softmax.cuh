@@ -392,7 +392,25 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
       if (FP8) l_tot *= exp2f(-kFp8Offset);                        // undo the offset for the LSE
       const float lse_val = dead_row ? -INFINITY : (m_run * scale_log2 + log2f(l_tot)) * kLn2;
       const int64_t row_idx = g.seq.q_off + pos;
-      if (row_valid) {
+      // Fused merge (ring attention): this call's (O_t, LSE_t) joins the running fp32 partial already in o_accum /
+      // lse_accum with the combine arithmetic (hopper/flash_fwd_combine_kernel.h:345-458) instead of going through
+      // memory and a separate combine launch.  w_prev scales the stored row, w_cur the row in tensor memory.
+      float w_prev = 0.f, w_cur = inv;
+      const bool merging = split && p.merge != 0;
+      const bool to_out = merging && p.merge == 2;  // the last hop writes the output dtype
+      if (merging && row_valid) {
+        const int64_t li = g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + row_idx;
+        const float lse_prev = p.lse_accum[li];
+        const float mx = fmaxf(lse_prev, lse_val);
+        float lse_new = -INFINITY;
+        if (mx != -INFINITY) {
+          const float e_prev = __expf(lse_prev - mx), e_cur = __expf(lse_val - mx);
+          lse_new = mx + __logf(e_prev + e_cur);
+          w_prev = __expf(lse_prev - lse_new);
+          w_cur = __expf(lse_val - lse_new) * inv;
+        } else w_cur = 0.f;
+        if (to_out) p.lse[li] = lse_new; else p.lse_accum[li] = lse_new;
+      } else if (row_valid) {
         if (!split) p.lse[g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + row_idx] = lse_val;
         else p.lse_accum[part * p.lseacc_split_stride + g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + row_idx] = lse_val;
       }
@@ -451,7 +469,23 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
 #pragma unroll
           for (int i = 0; i < 32; ++i) o[i] = 0u;
         }
-        if (row_valid) {
+        if (row_valid && merging) {
+#pragma unroll
+          for (int v4 = 0; v4 < 8; ++v4) {
+            if (c * 32 + v4 * 4 < p.dv) {
+              const float4 pr = o32[c * 8 + v4];
+              const float4 mg = make_float4(w_prev * pr.x + w_cur * __uint_as_float(o[v4 * 4]), w_prev * pr.y + w_cur * __uint_as_float(o[v4 * 4 + 1]),
+                                            w_prev * pr.z + w_cur * __uint_as_float(o[v4 * 4 + 2]), w_prev * pr.w + w_cur * __uint_as_float(o[v4 * 4 + 3]));
+              if (!to_out) o32[c * 8 + v4] = mg;
+              else {
+                uint2 u;
+                u.x = F16 ? pack_f16(mg.x, mg.y) : pack_bf16(mg.x, mg.y);
+                u.y = F16 ? pack_f16(mg.z, mg.w) : pack_bf16(mg.z, mg.w);
+                reinterpret_cast<uint2*>(o16)[c * 8 + v4] = u;
+              }
+            }
+          }
+        } else if (row_valid) {
           if (!split) {
 #pragma unroll
             for (int v8 = 0; v8 < 4; ++v8) {

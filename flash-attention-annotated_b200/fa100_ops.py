@@ -55,8 +55,9 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
             page_table=None, kv_batch_idx=None, leftpad_k=None, rotary_cos=None, rotary_sin=None,
             seqlens_rotary=None, q_descale=None, k_descale=None, v_descale=None, softmax_scale=None,
             is_causal=False, window_size_left=-1, window_size_right=-1, attention_chunk=0, softcap=0.0,
-            is_rotary_interleaved=False, scheduler_metadata=None, num_splits=0, pack_gqa=None, sm_margin=0, _partial=None):
-    """torch.ops.flash_attn_3.fwd.  `_partial=(o_accum, lse_accum)` (not part of the schema; used by ring_attention) makes
+            is_rotary_interleaved=False, scheduler_metadata=None, num_splits=0, pack_gqa=None, sm_margin=0, _partial=None, _merge=0):
+    """torch.ops.flash_attn_3.fwd.  `_merge` (with `_partial`): 1 = merge this call's result into the partial already in the
+    buffers, in place; 2 = merge and write `out` / the returned lse in the output dtype (Fa100FwdParams.merge_partial).  `_partial=(o_accum, lse_accum)` (not part of the schema; used by ring_attention) makes
     the kernel write one fp32 partial -- o_accum (1, b, h, sq, dv), lse_accum (1, b, h, sq) -- instead of out / lse."""
     _chk(q.is_cuda and k.is_cuda and v.is_cuda, "q, k, v must be CUDA tensors (there is no CPU path)")
     qt = q.dtype
@@ -123,14 +124,14 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
 
     out_dtype = torch.bfloat16 if qt == torch.float8_e4m3fn else qt
     out_shape = (total_q, h, dv) if varlen_q else (b, seqlen_q, h, dv)
-    if _partial is not None:  # the kernel writes only the fp32 partial
+    if _partial is not None and _merge != 2:  # the kernel writes only the fp32 partial
         out = torch.empty((0,) * len(out_shape), dtype=out_dtype, device=q.device)
     elif out is None:
         out = torch.empty(out_shape, dtype=out_dtype, device=q.device)
     else:
         _chk(out.dtype == out_dtype and tuple(out.shape) == out_shape and out.stride(-1) == 1 and out.device == q.device,
              "out has the wrong dtype / shape / layout")
-    lse = torch.empty(((h, total_q) if varlen_q else (b, h, seqlen_q)) if _partial is None else (0,), dtype=torch.float32, device=q.device)
+    lse = torch.empty(((h, total_q) if varlen_q else (b, h, seqlen_q)) if (_partial is None or _merge == 2) else (0,), dtype=torch.float32, device=q.device)
     empty = torch.empty(0, dtype=torch.float32, device=q.device)
     if _partial is None and (seqlen_k == 0 or out.numel() == 0):  # hopper/flash_api.cpp:1190-1194
         out.zero_()
@@ -196,6 +197,7 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     p.is_causal, p.window_left, p.window_right, p.attention_chunk = int(is_causal), window_size_left, window_size_right, attention_chunk
     p.num_splits, p.pack_gqa, p.num_sm = splits, pl.pack_gqa, pl.num_sm
     p.variant = _variant()
+    p.merge_partial = int(_merge) if _partial is not None else 0
     with torch.cuda.device(q.device):
         if scheduler_metadata is not None and scheduler_metadata.numel() >= META_HEADER + _sched_words(b):
             # the schedule get_scheduler_metadata built ahead of time (CUDA-graphed decode): used as is

@@ -12,8 +12,10 @@ and V, so every rank has the same causal work in every hop.  Hop t uses the K/V 
   s < r           lo rows and hi rows x lo keys of s, unmasked   (hi keys of s lie in the future of both)
   s > r           hi rows x (lo, hi) keys of s, unmasked         (lo rows see nothing of s)
 
-Each launch writes an fp32 partial (O_t, LSE_t); partials are merged into running fp32 (O, LSE) per row group with
-``fa100_combine`` (two-way, in place), the last merge writing the 16-bit output.  K/V travel around the ring as one
+The first launch of a row group writes an fp32 partial (O, LSE); every later hop's launch merges its own result into it in
+the attention kernel's epilogue (``Fa100FwdParams.merge_partial``), the last one writing the 16-bit output -- no separate
+combine launch and no second partial buffer on the CUDA path (the CPU test backend keeps the two-way ``fa100_combine``
+form of the same arithmetic).  K/V travel around the ring as one
 packed buffer with NCCL send/recv on a side stream, double-buffered so hop t+1's transfer overlaps hop t's attention;
 the final O stays sequence-sharded (no gather).  Message per hop: 2 * 2c * h_k * d * 2 B (268 MB at C5 on 8 GPUs).
 
@@ -73,12 +75,24 @@ class Fa100Backend:
         self.scale = softmax_scale
 
     def alloc(self, b, h, rows, dv, device):
-        o = torch.empty((2, b, h, rows, dv), dtype=torch.float32, device=device)  # slot 0 running, slot 1 this hop
-        lse = torch.empty((2, b, h, rows), dtype=torch.float32, device=device)
+        o = torch.empty((1, b, h, rows, dv), dtype=torch.float32, device=device)  # the running partial (later hops merge into it in the kernel)
+        lse = torch.empty((1, b, h, rows), dtype=torch.float32, device=device)
         return o, lse
+
+    fused_merge = True  # the attention epilogue merges into the running partial itself: no combine launch
 
     def partial(self, q, k, v, causal, o_slot, lse_slot):
         self.ops.mha_fwd(q, k, v, softmax_scale=self.scale, is_causal=causal, _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)))
+
+    def partial_merge(self, q, k, v, causal, o_slot, lse_slot, out=None, out_lse=None):
+        """This hop's attention merged into the running fp32 partial in `o_slot` / `lse_slot` by the kernel's epilogue; the
+        last hop (`out` given) writes the 16-bit output (b, rows, h, dv) and the LSE (b, h, rows) instead."""
+        if out is None:
+            self.ops.mha_fwd(q, k, v, softmax_scale=self.scale, is_causal=causal, _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)), _merge=1)
+        else:
+            _, lse, *_ = self.ops.mha_fwd(q, k, v, out=out, softmax_scale=self.scale, is_causal=causal,
+                                          _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)), _merge=2)
+            out_lse.copy_(lse)
 
     def merge(self, o, lse, out=None, out_lse=None):
         """slot 0 <- merge(slot 0, slot 1) in fp32, or into the 16-bit `out` (b, rows, h, dv) / `out_lse` (b, h, rows)."""
@@ -175,9 +189,15 @@ def ring_flash_attn_func(q, k, v, softmax_scale=None, causal=True, group=None, b
             o, lse = acc[g]
             kk = k_t[:, :c] if keys == "lo" else k_t
             vv = v_t[:, :c] if keys == "lo" else v_t
+            final = t == last_use[g]
+            if filled[g] and getattr(be, "fused_merge", False):
+                if final:
+                    be.partial_merge(q[:, groups[g]], kk, vv, is_causal, o[0], lse[0], out[:, groups[g]], out_lse[:, :, groups[g]])
+                else:
+                    be.partial_merge(q[:, groups[g]], kk, vv, is_causal, o[0], lse[0])
+                continue
             slot = 1 if filled[g] else 0
             be.partial(q[:, groups[g]], kk, vv, is_causal, o[slot], lse[slot])
-            final = t == last_use[g]
             if filled[g]:
                 if final:
                     be.merge(o, lse, out[:, groups[g]], out_lse[:, :, groups[g]])

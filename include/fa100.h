@@ -129,7 +129,12 @@ typedef struct Fa100FwdParams {
    * 0 = the library's default (today: one CTA per work item), 1 = pairs wherever eligible, 2 = one CTA per work item
    * always.  fa100_prepare_scheduler must see the same value as fa100_fwd. */
   int32_t variant;
-  int32_t reserved[7];
+  /* Fused merge of a running partial (ring / context-parallel attention): with o_accum / lse_accum set and
+   * num_splits == 1, 1 = read the fp32 partial already in o_accum / lse_accum, merge this call's result into it with the
+   * combine arithmetic (LSE' = logaddexp, O' = e^(LSE-LSE') O + e^(LSE_t-LSE') O_t) and write it back in place;
+   * 2 = the same, but write the merged result to o / lse (output dtype) instead.  0 = plain partial. */
+  int32_t merge_partial;
+  int32_t reserved[6];
 } Fa100FwdParams;
 
 /* LSE-weighted merge of split partials (hopper/flash_fwd_combine_kernel.h:200-483,
