@@ -15,16 +15,8 @@ FA_DEVICE uint32_t pack_f16(float lo, float hi) {
 FA_DEVICE float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 FA_DEVICE float fast_tanh(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-// Packed f32x2 arithmetic (one issue slot for two lanes of the row): (a, b) = (a, b) * sc + m and (acc0, acc1) += (a, b).
-FA_DEVICE void ffma2(float& a, float& b, float sc, float m) {
-  asm("{\n\t.reg .b64 x, s2, m2;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 s2, {%2, %2};\n\tmov.b64 m2, {%3, %3};\n\t"
-      "fma.rn.ftz.f32x2 x, x, s2, m2;\n\tmov.b64 {%0, %1}, x;\n\t}" : "+f"(a), "+f"(b) : "f"(sc), "f"(m));
-}
-FA_DEVICE void fadd2(float& acc0, float& acc1, float a, float b) {
-  asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tadd.rn.ftz.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
-      : "+f"(acc0), "+f"(acc1) : "f"(a), "f"(b));
-}
-// Order-pinned variants for the exp pipeline: the compiler front end keeps volatile asm statements in program order, so
+// Packed f32x2 arithmetic (one issue slot for two scores of the row), order-pinned for the exp pipeline: the compiler
+// front end keeps volatile asm statements in program order, so
 // the PTX carries the software pipeline written in softmax_role (scale-subtract two pairs ahead of the exponentials,
 // row sum and pack three pairs behind them) instead of one burst of FFMA2s followed by stretches with one MUFU per
 // five issue slots (what the scheduler made of the per-chunk loops: a lone warp ran at 12.5 clk per score, not 8).
@@ -51,69 +43,6 @@ FA_DEVICE uint16_t pack8_v(uint32_t lo, uint32_t hi) {
 #ifndef FA100_GARBAGE
 #define FA100_GARBAGE 0  // timing-only experiments (wrong results): 1 half the exponentials, 2 no row sum, 4 no pack, 8 no row max
 #endif
-#ifndef FA100_PREFETCH
-#define FA100_PREFETCH 0  // experiment switch, measured slower (profiles/r01b_ab_prefetch.log): bit 0 early non-blocking look at pv_done (-1..2 %), bit 1 next block's S loads issued behind the P stores (-0.5..2 %), both -2..3 %
-#endif
-#ifndef FA100_PIPE
-#define FA100_PIPE 1   // software-pipelined exp phase with all P stores at the end (0: the per-chunk loops)
-#endif
-// exp2 of two values on the FMA/ALU pipes instead of the MUFU pipe (which both tiles' softmax warps share at 16
-// results/clk/SM): Cody-Waite split with the 1.5 * 2^23 magic add (round toward -inf), degree-3 minimax polynomial of
-// 2^f on [0, 1) (relative error ~1e-4, below the 16-bit rounding of P), exponent spliced with an integer add.
-// Arguments are <= 0 here; below -126 the result is clamped to 2^-126 instead of 0, so this is used only on interior
-// key blocks (a masked -inf score must give an exact 0 for the dead-row test).
-FA_DEVICE void ex2_poly2(float& a, float& b) {
-  asm("{\n\t.reg .b64 x, r, f, pl;\n\t.reg .f32 a0, b0, r0, r1, p0, p1;\n\t.reg .b32 i0, i1, q0, q1;\n\t"
-      "max.ftz.f32 a0, %0, 0fC2FC0000;\n\tmax.ftz.f32 b0, %1, 0fC2FC0000;\n\t"
-      "mov.b64 x, {a0, b0};\n\t"
-      "mov.b64 pl, {0f4B400000, 0f4B400000};\n\t"
-      "add.rm.ftz.f32x2 r, x, pl;\n\t"
-      "sub.rn.ftz.f32x2 f, r, pl;\n\t"
-      "sub.rn.ftz.f32x2 f, x, f;\n\t"
-      "mov.b64 pl, {0f3D9DF09D, 0f3D9DF09D};\n\t"
-      "mov.b64 x, {0f3E6906A4, 0f3E6906A4};\n\t"
-      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
-      "mov.b64 x, {0f3F31F519, 0f3F31F519};\n\t"
-      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
-      "mov.b64 x, {0f3F800000, 0f3F800000};\n\t"
-      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
-      "mov.b64 {p0, p1}, pl;\n\tmov.b64 {r0, r1}, r;\n\t"
-      "mov.b32 i0, r0;\n\tmov.b32 i1, r1;\n\tshl.b32 i0, i0, 23;\n\tshl.b32 i1, i1, 23;\n\t"
-      "mov.b32 q0, p0;\n\tmov.b32 q1, p1;\n\tadd.s32 q0, q0, i0;\n\tadd.s32 q1, q1, i1;\n\t"
-      "mov.b32 %0, q0;\n\tmov.b32 %1, q1;\n\t}"
-      : "+f"(a), "+f"(b));
-}
-// Degree-2 variant for e4m3 P (3 mantissa bits): 2^f on [0, 1) to 1.7e-3 relative, exponent spliced by one IMAD.
-// 9 issue slots per pair of scores and none of them on the MUFU pipe.
-FA_DEVICE void ex2_poly2_deg2(float& a, float& b) {
-  asm("{\n\t.reg .b64 x, r, f, pl;\n\t.reg .f32 a0, b0, r0, r1, p0, p1;\n\t.reg .b32 i0, i1, q0, q1;\n\t"
-      "max.ftz.f32 a0, %0, 0fC2800000;\n\tmax.ftz.f32 b0, %1, 0fC2800000;\n\t"
-      "mov.b64 x, {a0, b0};\n\t"
-      "mov.b64 pl, {0f4B400000, 0f4B400000};\n\t"
-      "add.rm.ftz.f32x2 r, x, pl;\n\t"
-      "sub.rn.ftz.f32x2 f, r, pl;\n\t"
-      "sub.rn.ftz.f32x2 f, x, f;\n\t"
-      "mov.b64 pl, {0f3EACA418, 0f3EACA418};\n\t"
-      "mov.b64 x, {0f3F285ADA, 0f3F285ADA};\n\t"
-      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
-      "mov.b64 x, {0f3F803884, 0f3F803884};\n\t"
-      "fma.rn.ftz.f32x2 pl, pl, f, x;\n\t"
-      "mov.b64 {p0, p1}, pl;\n\tmov.b64 {r0, r1}, r;\n\t"
-      "mov.b32 i0, r0;\n\tmov.b32 i1, r1;\n\tmov.b32 q0, p0;\n\tmov.b32 q1, p1;\n\t"
-      "mad.lo.s32 q0, i0, 8388608, q0;\n\tmad.lo.s32 q1, i1, 8388608, q1;\n\t"
-      "mov.b32 %0, q0;\n\tmov.b32 %1, q1;\n\t}"
-      : "+f"(a), "+f"(b));
-}
-#ifndef FA100_POLY_FP8
-#define FA100_POLY_FP8 0  // of every 8 scores of an interior e4m3 key block, how many take ex2_poly2_deg2
-#endif
-#ifndef FA100_POLY
-#define FA100_POLY 0   // of every 8 scores of an interior key block, how many take the polynomial exp2 (measured slower at full size: 2/8 -> 1217, 4/8 -> 1151 vs 1274 TFLOPS; kept as an experiment switch)
-#endif
-#ifndef FA100_F32X2
-#define FA100_F32X2 1  // packed f32x2 scale-subtract and row sum (measured: C2 1209 -> 1274 TFLOPS, C3 1115 -> 1199)
-#endif
-
 // What one softmax thread needs about its row while it walks the key blocks of a work item.  Kept this small on
 // purpose: with 227 KB of shared memory carved out the L1 is tiny, so a register spill in the step loop costs an L2
 // round trip; everything the epilogue needs is recomputed there instead of being carried across the loop.
@@ -178,19 +107,16 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
     const float scale_log2 = rg.scale_log2;
     const bool softcap = p.softcap_pre != 0.f;
     float m_run = -INFINITY, l_run = 0.f;
-    uint32_t s[4][32];
-    bool s_loaded = false;  // the next block's scores are already on their way into s (loads issued behind the P stores)
     for (int nb = rg.n_max - 1; nb >= rg.n_min; nb -= (DUAL ? 2 : 1)) {
       FA_PROF(7);
-      if (!s_loaded) {
-        mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
-        FA_PROF(0);
-        FA_LAT_ACC(3, &bar->ts[t]);
-        ++s_it;
-        tc_fence_after();
+      mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
+      FA_PROF(0);
+      FA_LAT_ACC(3, &bar->ts[t]);
+      ++s_it;
+      tc_fence_after();
+      uint32_t s[4][32];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
-      }
+      for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
       tmem_ld_wait();
       FA_PROF(1);
       // the scores are in registers: hand S to the other tile's QK
@@ -201,9 +127,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
       FA_TRACE_POINT(0xC4);
       // P_t and O_t may be touched again once the previous P_t V has drained; poll now, block only right before the
       // first write (normally long complete by then)
-      // (a non-blocking look: it costs nothing when the phase is still open, and its latency hides behind the row max)
-      bool pv_drained = pv_n == 0 || (FA100_PIPE ? ((FA100_PREFETCH & 1) && __all_sync(0xffffffffu, mbar_test_wait(&bar->pv_done[t], (pv_n - 1) & 1)))
-                                                 : mbar_try_wait(&bar->pv_done[t], (pv_n - 1) & 1));
+      bool pv_drained = pv_n == 0;
       const int n0 = nb * kBlockN;
       // boundary block for any row of this warp (warp-uniform): softcap first, then the mask (hopper/mainloop...:1073-1077)
       const bool boundary = __any_sync(0xffffffffu, softcap || n0 + kBlockN > rg.col_hi || n0 < rg.col_lo);
@@ -256,7 +180,6 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
       // P = exp2(S * scale - max), packed to the operand dtype and written over S: keys [32c, 32c + 32) of the tile go to
       // columns [16c, +16) (16-bit operands) or [8c, +8) (e4m3)
       float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
-#if FA100_PIPE
       {
         // One straight-line pipeline over the 64 score pairs of the row: pair k + 2 gets its scale-subtract while pair k
         // is in the MUFU pipe and pair k - 3 is summed and packed, so the exponentials issue at an even pace from the
@@ -289,79 +212,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
           if (!FP8) tmem_st16(tP + c * 16, pk + c * 16);
           else tmem_st8(tP + c * 8, pk + c * 8);
         }
-#if (FA100_PREFETCH & 2)
-        // The score registers are free: if this tile's next scores are already in S (the usual case), start copying them
-        // now, so that the 16 KB tensor-memory read per warp, and the hand-over of S to the other tile behind it, overlap
-        // the store wait, the publish and the loop tail instead of following them.
-        s_loaded = false;
-        if (nb - (DUAL ? 2 : 1) >= rg.n_min && __all_sync(0xffffffffu, mbar_test_wait(&bar->s_full[t], s_it & 1))) {
-          ++s_it;
-          tc_fence_after();
-#pragma unroll
-          for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
-          s_loaded = true;
-        }
-#endif
       }
-#else
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        if ((FP8 ? FA100_POLY_FP8 : FA100_POLY) > 0 && !boundary) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float x0 = __uint_as_float(s[c][i]), x1 = __uint_as_float(s[c][i + 1]);
-            if (FA100_F32X2) ffma2(x0, x1, scale_log2, -m_sub);
-            else { x0 = fmaf(x0, scale_log2, -m_sub); x1 = fmaf(x1, scale_log2, -m_sub); }
-            if (FP8 && (i & 7) >= 8 - FA100_POLY_FP8) ex2_poly2_deg2(x0, x1);
-            else if (!FP8 && (i & 7) >= 8 - FA100_POLY) ex2_poly2(x0, x1);
-            else { x0 = ex2_approx(x0); x1 = ex2_approx(x1); }
-            s[c][i] = __float_as_uint(x0); s[c][i + 1] = __float_as_uint(x1);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float x0 = __uint_as_float(s[c][i]), x1 = __uint_as_float(s[c][i + 1]);
-            if (FA100_F32X2) ffma2(x0, x1, scale_log2, -m_sub);
-            else { x0 = fmaf(x0, scale_log2, -m_sub); x1 = fmaf(x1, scale_log2, -m_sub); }
-            s[c][i] = __float_as_uint(ex2_approx(x0)); s[c][i + 1] = __float_as_uint(ex2_approx(x1));
-          }
-        }
-        if (c == 0) {
-          if (!pv_drained) mbar_wait(&bar->pv_done[t], (pv_n - 1) & 1, 0x78 + t);
-          tc_fence_after();
-        }
-        if (!FP8) {
-          uint32_t pk[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float p0 = __uint_as_float(s[c][2 * i]), p1 = __uint_as_float(s[c][2 * i + 1]);
-            pk[i] = F16 ? pack_f16(p0, p1) : pack_bf16(p0, p1);
-          }
-          tmem_st16(tP + c * 16, pk);
-        } else {
-          uint32_t pk[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            uint16_t lo, hi;
-            asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(__uint_as_float(s[c][4 * i + 1])), "f"(__uint_as_float(s[c][4 * i])));
-            asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(__uint_as_float(s[c][4 * i + 3])), "f"(__uint_as_float(s[c][4 * i + 2])));
-            pk[i] = uint32_t(lo) | (uint32_t(hi) << 16);
-          }
-          tmem_st8(tP + c * 8, pk);
-        }
-#pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          if (FA100_F32X2) {
-            fadd2(sum0, sum1, __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
-            fadd2(sum2, sum3, __uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3]));
-          } else {
-            sum0 += __uint_as_float(s[c][i]); sum1 += __uint_as_float(s[c][i + 1]);
-            sum2 += __uint_as_float(s[c][i + 2]); sum3 += __uint_as_float(s[c][i + 3]);
-          }
-        }
-        if (c == 1) FA_PROF(4);
-      }
-#endif
       FA_PROF(5);
       tmem_st_wait();
       tc_fence_before();
