@@ -79,3 +79,35 @@ def test_nccl_ring_two_gpus():
         assert p.exitcode == 0
     for rank, err, lerr in res:
         assert err <= 2e-2 and lerr <= 1e-4, (rank, err, lerr)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_fused_merge_equals_partial_plus_combine(dtype):
+    """Fa100FwdParams.merge_partial: the epilogue's merge (1 = in place, 2 = into the 16-bit output) against the same two
+    partials merged by fa100_combine (hopper/flash_fwd_combine_kernel.h:345-458); rows with no keys on either side."""
+    import fa100_ops as ops
+
+    b, sq, h, hk, d = 2, 300, 4, 2, 128
+    g = torch.Generator(device="cuda").manual_seed(11)
+    mk = lambda *shape: torch.randn(*shape, generator=g, device="cuda", dtype=torch.float32).to(dtype)  # noqa: E731
+    q, k1, v1, k2, v2 = mk(b, sq, h, d), mk(b, 500, hk, d), mk(b, 500, hk, d), mk(b, 260, hk, d), mk(b, 260, hk, d)
+    o = torch.empty((2, b, h, sq, d), dtype=torch.float32, device="cuda")
+    l = torch.empty((2, b, h, sq), dtype=torch.float32, device="cuda")
+    ops.mha_fwd(q, k1, v1, is_causal=True, _partial=(o[:1], l[:1]))   # bottom-right causal: the first rows see few keys
+    ops.mha_fwd(q, k2, v2, is_causal=True, _partial=(o[1:], l[1:]))   # sk < sq: the first 40 rows see no key at all
+    want_o = torch.empty((b, sq, h, d), dtype=dtype, device="cuda")
+    want_l = torch.empty((b, sq, h), dtype=torch.float32, device="cuda")
+    ops._combine_into(o.permute(0, 1, 3, 2, 4), l.permute(0, 1, 3, 2), want_o, want_l)
+    acc_o, acc_l = o[:1].clone(), l[:1].clone()
+    ops.mha_fwd(q, k2, v2, is_causal=True, _partial=(acc_o, acc_l), _merge=1)
+    got_o = torch.empty((b, sq, h, d), dtype=dtype, device="cuda")
+    acc2_o, acc2_l = o[:1].clone(), l[:1].clone()
+    _, got_l, *_ = ops.mha_fwd(q, k2, v2, out=got_o, is_causal=True, _partial=(acc2_o, acc2_l), _merge=2)
+    torch.cuda.synchronize()
+    assert torch.isneginf(l[1, :, :, :40]).all() and torch.isfinite(want_l).all()
+    fp32_want = torch.empty((b, sq, h, d), dtype=torch.float32, device="cuda")
+    ops._combine_into(o.permute(0, 1, 3, 2, 4), l.permute(0, 1, 3, 2), fp32_want, torch.empty_like(want_l))
+    assert torch.allclose(acc_o[0].permute(0, 2, 1, 3), fp32_want, atol=2e-5, rtol=1e-5)
+    assert torch.allclose(acc_l[0].permute(0, 2, 1), want_l, atol=1e-5, rtol=1e-5)
+    assert (got_o.float() - want_o.float()).abs().max().item() <= (8e-3 if dtype == torch.bfloat16 else 1e-3)
+    assert torch.allclose(got_l.permute(0, 2, 1), want_l, atol=1e-5, rtol=1e-5)
