@@ -1,7 +1,12 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the B200-native FlashAttention forward (driver contract).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c3nc|c4] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c3nc|c4|c5] [--impl reference] [--no-extras]
+
+The ONE JSON line is the headline workload (default C2).  So that every north_star config reaches the driver's records,
+the default run attaches the others to the same line: at N = 1 `extra: {c3, c3nc, c4}` (FP8 causal / non-causal against
+an FP8 peak measured in the same run, paged split-KV decode against the HBM peak), at N > 1 `ring_c5` (the 131072-token
+context-parallel prefill over the N ranks: strong scaling, per-hop attention / transfer times, both transports).
 
 Default workload = BASELINE.json configs[1] (C2): bf16, batch 8, 32 Q / 8 KV heads, seqlen 8192, hdim 128, causal.
 A step is one forward over that batch.  `value` times the kernel with inputs resident in HBM (CUDA events on the
@@ -200,78 +205,120 @@ def metric_name(w):
     return f"fwd TFLOPS/GPU {w['dtype']} hdim128 {'causal' if w['causal'] else 'non-causal'}"
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--impl", default="fa100", choices=["fa100", "reference"])
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "fa100" else args.warmup
-    w = WORKLOADS[args.workload]
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.impl == "reference":
-        run_reference(args, w, rank)
-        return
 
-    import fa100_native as N
+
+def fp8_peak(dev):
+    """Dense e4m3 tensor peak of THIS box, measured the way MEASURED_PEAKS.json measures bf16: torch._scaled_mm 8192^3
+    (cuBLASLt), best of 10 after warm-up (burst).  None when the op is not available."""
+    try:
+        n = 8192
+        a = torch.randn(n, n, device=dev, dtype=torch.bfloat16).to(torch.float8_e4m3fn)
+        b = torch.randn(n, n, device=dev, dtype=torch.bfloat16).to(torch.float8_e4m3fn).t()  # column-major B
+        one = torch.ones((), device=dev, dtype=torch.float32)
+        run = lambda: torch._scaled_mm(a, b, scale_a=one, scale_b=one, out_dtype=torch.bfloat16)  # noqa: E731
+        for _ in range(3):
+            run()
+        best = None
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            run()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            best = ms if best is None else min(best, ms)
+        return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    except Exception:  # noqa: BLE001
+        return None
+
+
+class Ctx:
+    """What every measurement needs: ranks, device, barrier."""
+
+    def __init__(self, args):
+        self.args = args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.dist = dist
+
+    def barrier(self):
+        torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, vals):
+        t = torch.tensor(vals, dtype=torch.float64, device=self.dev)
+        if self.dist is not None:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.tolist()
+
+
+def make_step(w, world, ring_kw=None):
+    """The call a user makes for this workload (public API only)."""
     from flash_attn_interface import flash_attn_func, flash_attn_with_kvcache
 
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
+    if w.get("ring"):
+        import ring_attention as R
 
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        kw = dict(ring_kw or {})
+        return lambda t: R.ring_flash_attn_func(t["q"], t["k"], t["v"], causal=True, **kw)
+    if "page" in w:
+        return lambda t: flash_attn_with_kvcache(t["q"], t["k"], t["v"], cache_seqlens=t["cache_seqlens"],
+                                                 page_table=t["page_table"], causal=False)
+
+    def step(t):
+        kw = {n: t[n] for n in ("q_descale", "k_descale", "v_descale") if n in t}
+        return flash_attn_func(t["q"], t["k"], t["v"], causal=w["causal"], **kw)
+    return step
+
+
+def launches_per_step(w, world):
+    if "page" in w:
+        return 2  # forward (dual-stream partials) + combine
+    if w.get("ring"):  # one attention launch per (hop, row group) of this rank's plan; merges are fused into them
+        import ring_attention as R
+
+        return sum(len(work) for _, work in R.hop_plan(0, world))
+    return 1
+
+
+def measure(ctx, w, steps, warmup, do_e2e, ring_kw=None, want_clocks=True):
+    """Device-timed `steps` back-to-back steps (CUDA events on the launching stream, barrier + synchronize on both sides,
+    max over ranks), then the end-to-end variant with HOST inputs / outputs.  Returns a dict of raw numbers."""
+    import fa100_native as N
+
+    rank, world, dev = ctx.rank, ctx.world, ctx.dev
     host = make_inputs(w, dev, seed=1234 + rank, world=world)
     pin = {k_: (v_.pin_memory() if v_.device.type == "cpu" else v_) for k_, v_ in host.items()}
     devt = {k_: v_.to(dev, non_blocking=True) for k_, v_ in pin.items()}
     torch.cuda.synchronize()
-    decode = "page" in w
-
-    ring = bool(w.get("ring"))
-    if ring:
-        import ring_attention as R
-
-    def step(t):
-        if ring:
-            return R.ring_flash_attn_func(t["q"], t["k"], t["v"], causal=True)
-        if decode:
-            return flash_attn_with_kvcache(t["q"], t["k"], t["v"], cache_seqlens=t["cache_seqlens"], page_table=t["page_table"],
-                                           causal=False)
-        kw = {n: t[n] for n in ("q_descale", "k_descale", "v_descale") if n in t}
-        return flash_attn_func(t["q"], t["k"], t["v"], causal=w["causal"], **kw)
-
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
+    step = make_step(w, world, ring_kw)
+    for _ in range(warmup):
         out = step(devt)
-    barrier()
-    sampler = ClockSampler(local)
+    ctx.barrier()
+    sampler = ClockSampler(ctx.local)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    if rank == 0:
+    ctx.barrier()
+    if rank == 0 and want_clocks:
         sampler.start()  # samples only while the timed steps run
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         out = step(devt)
     e1.record()
     torch.cuda.synchronize()
-    clocks = sampler.stop() if rank == 0 else None
-    barrier()
-    ms = e0.elapsed_time(e1) / args.steps
+    clocks = sampler.stop() if (rank == 0 and want_clocks) else None
+    ctx.barrier()
+    ms = e0.elapsed_time(e1) / steps
     hang = N.hang_info()
     assert hang[0] == 0, f"kernel watchdog fired: {hang}"
 
@@ -280,7 +327,7 @@ def main():
     # double-buffered device inputs, so step i+1's upload and step i-1's download overlap step i's kernel (what a serving
     # loop over PCIe does).  Every byte of every step crosses the bus inside the timed region.
     e2e_ms, h2d, d2h = None, 0, 0
-    if not args.no_e2e:
+    if do_e2e:
         host_keys = [k_ for k_, v_ in pin.items() if v_.device.type == "cpu"]
         out_host = [torch.empty(out.shape, dtype=out.dtype).pin_memory() for _ in range(2)]
         h2d = sum(pin[k_].numel() * pin[k_].element_size() for k_ in host_keys)
@@ -315,59 +362,229 @@ def main():
             s_run.wait_stream(s_out)
 
         e2e_steps(2)
-        barrier()
-        n_e2e = max(4, min(args.steps, 10))
+        ctx.barrier()
+        n_e2e = max(4, min(steps, 10))
         with torch.cuda.stream(s_run):
             e0.record(s_run)
             e2e_steps(n_e2e)
             e1.record(s_run)
-        barrier()
+        ctx.barrier()
         e2e_ms = e0.elapsed_time(e1) / n_e2e
-    vals = torch.tensor([ms, e2e_ms or 0.0], dtype=torch.float64, device=dev)
-    if dist is not None:
-        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
-    ms, e2e_ms = vals[0].item(), (vals[1].item() if e2e_ms is not None else None)
+    ms_max, e2e_max = ctx.max_over_ranks([ms, e2e_ms or 0.0])
+    res = dict(ms=ms_max, e2e_ms=(e2e_max if e2e_ms is not None else None), h2d=h2d, d2h=d2h, clocks=clocks,
+               launches=launches_per_step(w, world))
+    if e2e_ms is not None:
+        # per-rank bus rate of the e2e loop (copies of all ranks share the host's memory system and PCIe switches)
+        gbs = ctx.max_over_ranks([-(h2d + d2h) / (e2e_ms * 1e-3) / 1e9])
+        res["e2e_copy_gbs_slowest_rank"] = -gbs[0]
+    del devt, out
+    torch.cuda.empty_cache()
+    return res
 
-    launches_per_step = 2 if decode else 1
-    if ring:  # partial-attention launches of this rank's hop plan + one merge per partial after the first of a row group
-        n_part = sum(len(work) for _, work in R.hop_plan(0, world))
-        launches_per_step = n_part + max(0, n_part - 2)
-    if rank == 0:
-        peaks = measured_peaks()
-        if decode:
-            per_gpu = decode_bytes(w) / (ms * 1e-3) / 1e9
-            unit, bound, peak = "GB/s", "hbm", peaks["hbm"]
-            e2e_val = decode_bytes(w) * world / (e2e_ms * 1e-3) / 1e9 if e2e_ms else None
-        else:
-            share = 1.0 / world if ring else 1.0  # ring: the ranks split ONE problem
-            per_gpu = flops(w) * share / (ms * 1e-3) / 1e12
-            unit, bound, peak = "TFLOP/s", "tensor", peaks["tensor"] * (2.0 if w["dtype"] == "e4m3" else 1.0)
-            e2e_val = flops(w) * share * world / (e2e_ms * 1e-3) / 1e12 if e2e_ms else None
-        line = dict(metric=metric_name(w), value=per_gpu * world, unit=unit, n_gpus=world, steps=args.steps, warmup=args.warmup,
-                    ms_per_step=ms, higher_is_better=True, scaling="strong" if ring else "weak", vs_baseline=None,
-                    dtype={"bf16": "bf16", "e4m3": "fp8_e4m3"}[w["dtype"]], data="synthetic",
-                    config=dict(workload=w["desc"], per_gpu=("1/N of the sequence per GPU, K/V ring over NCCL send/recv" if ring else
-                                                            "full workload on every GPU (batch x heads sharding, no communication)"),
-                                l2="inputs (>= 0.67 GB) exceed the 126 MB L2; no flush between steps"),
-                    clocks=clocks, gpu_launches=args.steps * launches_per_step,
-                    e2e=dict(value=e2e_val, unit=unit, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h),
-                    roofline=dict(bound=bound, achieved=per_gpu, peak=peak, unit=unit, frac=per_gpu / peak, traffic=ncu_traffic(args.workload),
-                                  peak_source=peaks["source"] + (" (bf16 burst x2 for fp8)" if w["dtype"] == "e4m3" and not decode else ""),
-                                  frac_of_sustained=(per_gpu / (peaks["tensor_sustained"] * (2.0 if w["dtype"] == "e4m3" else 1.0))
-                                                     if bound == "tensor" and peaks["tensor_sustained"] else None),
-                                  kernel="fa100_fwd_kernel"))
-        if not args.no_cpu_baseline and world == 1:
-            threads = os.cpu_count() or 1
-            dt, fl, slices = cpu_sample(w, threads, 4, min_seconds=12.0)
-            line["cpu_baseline"] = dict(value=fl / dt / 1e12, unit="TFLOP/s", cores=threads, kind="port",
-                                        sample=f"{slices} (batch, kv-group) slices ({slices * (w['h'] // w['hk'])} of "
-                                               f"{w['b'] * w['h']} q-head rows), seq capped at 8192, {dt:.1f} s")
-        else:
-            line["cpu_baseline"] = None
-        print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+
+def roofline_of(w, per_gpu, peaks, name, fp8_tflops=None):
+    decode = "page" in w
+    if decode:
+        return dict(bound="hbm", achieved=per_gpu, peak=peaks["hbm"], unit="GB/s", frac=per_gpu / peaks["hbm"],
+                    traffic=ncu_traffic(name), peak_source=peaks["source"] + " (copy)", kernel="fa100_fwd_kernel")
+    fp8 = w["dtype"] == "e4m3"
+    if fp8 and fp8_tflops:
+        peak, src = fp8_tflops, "measured in this run: torch._scaled_mm e4m3 8192^3 best of 10 (burst)"
+    elif fp8:
+        peak, src = peaks["tensor"] * 2.0, peaks["source"] + " (bf16 burst x2: no fp8 GEMM on this box)"
+    else:
+        peak, src = peaks["tensor"], peaks["source"] + " (cuBLAS bf16 burst)"
+    r = dict(bound="tensor", achieved=per_gpu, peak=peak, unit="TFLOP/s", frac=per_gpu / peak, traffic=ncu_traffic(name),
+             peak_source=src, kernel="fa100_fwd_kernel")
+    if peaks.get("tensor_sustained") and not fp8:
+        r["frac_of_sustained"] = per_gpu / peaks["tensor_sustained"]
+    if fp8:
+        r["frac_of_2x_bf16_burst"] = per_gpu / (peaks["tensor"] * 2.0)
+    return r
+
+
+def measure_ring(ctx, steps, warmup):
+    """C5 over the N ranks of this job: one 131072-token causal sequence, zig-zag sharded; strong scaling.  Both transports
+    are timed (NCCL send/recv ring with SMs left free for its copy kernels; copy-engine pushes into peer memory), then one
+    instrumented step per transport gives the per-hop attention / transfer times.  Every rank also runs the WHOLE problem
+    alone (N = 1 arithmetic, no communication) so that the strong-scaling efficiency is measured inside one record."""
+    import ring_attention as R
+
+    w = WORKLOADS["c5"]
+    world, rank, dev = ctx.world, ctx.rank, ctx.dev
+    total = flops(w)
+    out = dict(n_gpus=world, workload=w["desc"], unit="TFLOP/s", scaling="strong")
+    # ---- N = 1 reference time of the same problem on one GPU (each rank, concurrently, no communication)
+    g = torch.Generator(device="cpu").manual_seed(7)
+    full = {n: torch.randn(1, w["sq"], w["h"] if n == "q" else w["hk"], w["d"], dtype=torch.bfloat16, device=dev) for n in ("q", "k", "v")}
+    one = lambda: R.ring_flash_attn_func(full["q"], full["k"], full["v"], causal=True, _rank_world=(0, 1))  # noqa: E731
+    for _ in range(2):
+        one()
+    ctx.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    n1_steps = 3
+    for _ in range(n1_steps):
+        one()
+    e1.record()
+    torch.cuda.synchronize()
+    (t1,) = ctx.max_over_ranks([e0.elapsed_time(e1) / n1_steps])
+    out["n1_ms_per_step"] = t1
+    out["n1_tflops"] = total / (t1 * 1e-3) / 1e12
+    del full
+    torch.cuda.empty_cache()
+    # ---- the ring, per transport
+    rows = w["sq"] // world
+    kv_bytes = 2 * w["b"] * rows * w["hk"] * w["d"] * 2
+    results = {}
+    for transport, kw in (("nccl", dict(transport="nccl", sm_margin=ctx.args.ring_sm_margin)), ("ce_push", dict(transport="ce_push"))):
+        try:
+            m = measure(ctx, w, steps, warmup, do_e2e=False, ring_kw=kw, want_clocks=(transport == "nccl"))
+            ms = m["ms"]
+            r = dict(value=total / (ms * 1e-3) / 1e12, ms_per_step=ms, gpu_launches_per_step=m["launches"],
+                     strong_efficiency_vs_n1=(t1 / world) / ms, clocks=m["clocks"])
+            if transport == "nccl":
+                r["sm_margin"] = ctx.args.ring_sm_margin
+            # one instrumented step: events around every hop's attention launches and every transfer
+            host = make_inputs(w, dev, seed=1234 + rank, world=world)
+            t = {k_: v_.to(dev) for k_, v_ in host.items()}
+            ev = []
+            ctx.barrier()
+            R.ring_flash_attn_func(t["q"], t["k"], t["v"], causal=True, _events=ev, **kw)
+            ctx.barrier()
+            attn = [0.0] * world
+            comm = [0.0] * world
+            for kind, hop, a, b in ev:
+                (attn if kind == "attn" else comm)[hop] += a.elapsed_time(b)
+            attn = ctx.max_over_ranks(attn)
+            comm = ctx.max_over_ranks(comm)
+            r["per_hop"] = dict(attn_ms=[round(x, 3) for x in attn], transfer_ms=[round(x, 3) for x in comm[:-1]],
+                                bytes_per_hop=kv_bytes, exposed_comm_ms=round(ms - sum(attn), 3),
+                                note="transfer_ms[t]: the copy issued at hop t (needed by hop t+1; ce_push: the push to rank r+t+1); "
+                                     "exposed_comm_ms = step time - sum of the hops' attention time")
+            r["merge_launches"] = 0  # merges run in the attention epilogue (Fa100FwdParams.merge_partial)
+            results[transport] = r
+            del t
+        except Exception as e:  # noqa: BLE001
+            import traceback
+
+            results[transport] = "unavailable: " + traceback.format_exc()[-900:]
+            if transport == "nccl":
+                raise
+        torch.cuda.empty_cache()
+    ok = {k_: v_ for k_, v_ in results.items() if isinstance(v_, dict)}
+    best = max(ok, key=lambda k_: ok[k_]["value"])
+    out.update(ok[best])
+    out["transport"] = best
+    out["transports"] = {k_: (dict(value=v_["value"], ms_per_step=v_["ms_per_step"], strong_efficiency_vs_n1=v_["strong_efficiency_vs_n1"],
+                                   per_hop=v_["per_hop"]) if isinstance(v_, dict) else v_) for k_, v_ in results.items()}
+    peaks = measured_peaks()
+    out["roofline"] = dict(bound="tensor", achieved=out["value"] / world, peak=peaks["tensor"], unit="TFLOP/s per GPU",
+                           frac=out["value"] / world / peaks["tensor"], peak_source=peaks["source"] + " (cuBLAS bf16 burst)",
+                           nvlink_bytes_per_gpu_per_step=kv_bytes * (world - 1))
+    return out
+
+
+def line_for(ctx, name, m, peaks, fp8_tflops=None):
+    """Fields of a bench line (or of an `extra` entry) for one measured workload."""
+    w, world = WORKLOADS[name], ctx.world
+    decode, ring = "page" in w, bool(w.get("ring"))
+    ms, e2e_ms = m["ms"], m["e2e_ms"]
+    if decode:
+        per_gpu = decode_bytes(w) / (ms * 1e-3) / 1e9
+        unit = "GB/s"
+        e2e_val = decode_bytes(w) * world / (e2e_ms * 1e-3) / 1e9 if e2e_ms else None
+    else:
+        share = 1.0 / world if ring else 1.0  # ring: the ranks split ONE problem
+        per_gpu = flops(w) * share / (ms * 1e-3) / 1e12
+        unit = "TFLOP/s"
+        e2e_val = flops(w) * share * world / (e2e_ms * 1e-3) / 1e12 if e2e_ms else None
+    d = dict(metric=metric_name(w), value=per_gpu * world, unit=unit, ms_per_step=ms,
+             dtype={"bf16": "bf16", "e4m3": "fp8_e4m3"}[w["dtype"]],
+             config=dict(workload=w["desc"]),
+             notes=dict(per_gpu=("1/N of the sequence per GPU, K/V exchanged between the ranks" if ring else
+                                 "full workload on every GPU (batch x heads sharding, no communication)"),
+                        l2="inputs (>= 0.67 GB) exceed the 126 MB L2; no flush between steps"),
+             clocks=m["clocks"], gpu_launches=ctx.args.steps * m["launches"],
+             e2e=dict(value=e2e_val, unit=unit, h2d_bytes_per_step=m["h2d"], d2h_bytes_per_step=m["d2h"],
+                      copy_gbs_slowest_rank=m.get("e2e_copy_gbs_slowest_rank")),
+             roofline=roofline_of(w, per_gpu, peaks, name, fp8_tflops))
+    return d
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="fa100", choices=["fa100", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="only the headline workload (no extra / ring_c5 attachments)")
+    ap.add_argument("--ring-sm-margin", type=int, default=8, help="SMs the attention kernel leaves to NCCL's send/recv kernels in the ring")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "fa100" else args.warmup
+    w = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, w, int(os.environ.get("RANK", "0")))
+        return
+
+    import fa100_native  # noqa: F401  (fails loudly when libfa100.so is missing: there is no fallback)
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    ctx = Ctx(args)
+    rank, world = ctx.rank, ctx.world
+    peaks = measured_peaks()
+    ring = bool(w.get("ring"))
+    fp8_tflops = fp8_peak(ctx.dev) if (w["dtype"] == "e4m3" or (world == 1 and not args.no_extras)) else None
+
+    if ring and world > 1:
+        r = measure_ring(ctx, args.steps, args.warmup)
+        if rank == 0:
+            line = dict(metric=metric_name(w), value=r["value"], unit="TFLOP/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+                        ms_per_step=r["ms_per_step"], higher_is_better=True, scaling="strong", vs_baseline=None, dtype="bf16",
+                        data="synthetic", config=dict(workload=w["desc"], transport=r["transport"]), clocks=r.get("clocks"),
+                        gpu_launches=args.steps * r["gpu_launches_per_step"], e2e=None, roofline=r["roofline"], cpu_baseline=None, ring_c5=r)
+            print(json.dumps(line), flush=True)
+    else:
+        m = measure(ctx, w, args.steps, args.warmup, do_e2e=not args.no_e2e)
+        line = line_for(ctx, args.workload, m, peaks, fp8_tflops)
+        line.update(n_gpus=world, steps=args.steps, warmup=args.warmup, higher_is_better=True, scaling="strong" if ring else "weak",
+                    vs_baseline=None, data="synthetic")
+        if fp8_tflops is not None:
+            line["fp8_peak_tflops_measured"] = fp8_tflops
+        if not args.no_extras and args.workload == "c2":
+            if world == 1:
+                # the other single-GPU north_star configs, each with its own roofline, on the same line
+                extra = {}
+                for name in ("c3", "c3nc", "c4"):
+                    try:
+                        mx = measure(ctx, WORKLOADS[name], args.steps, args.warmup, do_e2e=False, want_clocks=True)
+                        ex = line_for(ctx, name, mx, peaks, fp8_tflops)
+                        extra[name] = {k_: ex[k_] for k_ in ("metric", "value", "unit", "ms_per_step", "dtype", "clocks", "gpu_launches", "roofline")}
+                        extra[name]["workload"] = WORKLOADS[name]["desc"]
+                    except Exception as e:  # noqa: BLE001
+                        extra[name] = "failed: " + repr(e)[:300]
+                line["extra"] = extra
+            else:
+                line["ring_c5"] = measure_ring(ctx, max(3, min(args.steps, 10)), args.warmup)
+        if rank == 0:
+            if not args.no_cpu_baseline and world == 1:
+                threads = os.cpu_count() or 1
+                dt, fl, slices = cpu_sample(w, threads, 4, min_seconds=12.0)
+                line["cpu_baseline"] = dict(value=fl / dt / 1e12, unit="TFLOP/s", cores=threads, kind="port",
+                                            sample=f"{slices} (batch, kv-group) slices ({slices * (w['h'] // w['hk'])} of "
+                                                   f"{w['b'] * w['h']} q-head rows), seq capped at 8192, {dt:.1f} s")
+            else:
+                line["cpu_baseline"] = None
+            order = ["metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+                     "dtype", "data", "config", "clocks", "gpu_launches", "e2e", "roofline", "cpu_baseline"]
+            line = {**{k_: line[k_] for k_ in order if k_ in line}, **{k_: v_ for k_, v_ in line.items() if k_ not in order}}
+            print(json.dumps(line), flush=True)
+    if ctx.dist is not None:
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

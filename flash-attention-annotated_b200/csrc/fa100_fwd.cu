@@ -2,9 +2,10 @@
 // Role of set_params_fprop + run_mha_fwd + run_flash_fwd (hopper/flash_api.cpp:50-168,367-385,
 // hopper/flash_fwd_launch_template.h:30-198) for the sm_100a kernel in fa100_fwd_softmax.cuh.
 #include "fa100_host.h"
-#include "fa100_fwd_softmax.cuh"
+#include "fa100_fwd2.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
@@ -16,10 +17,15 @@ static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, co
                            const CUtensorMap& tmV, const CUtensorMap& tmO, uint32_t fmt, int grid, cudaStream_t stream) {
   using L = FwdSmem<HD, ELT, PAIR>;
   auto kernel = fa100_fwd_kernel<HD, ELT, FP8, F16, DUAL, PAIR>;
-  static bool attr_set = false;  // benign race: the call is idempotent
-  if (!attr_set) {
+  // the opt-in is per device (per context), not per process: one flag per device ordinal and kernel instance
+  // (the reference sets the attribute on every launch, hopper/flash_fwd_launch_template.h:183-193)
+  static std::atomic<uint64_t> attr_set[2] = {{0}, {0}};  // devices 0..127; benign race: the call is idempotent
+  int dev = 0;
+  FA_CUDA(cudaGetDevice(&dev));
+  const bool tracked = dev >= 0 && dev < 128;
+  if (!tracked || !((attr_set[dev >> 6].load(std::memory_order_relaxed) >> (dev & 63)) & 1)) {
     FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes));
-    attr_set = true;
+    if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
   }
   if (PAIR) {
     // clusters of two CTAs: the pair shares every K / V tile (cta_group::2 MMAs); grid = 2 x pairs
@@ -37,6 +43,25 @@ static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, co
   return FA100_OK;
 }
 
+// The prefill mainloop of fa100_fwd2.cuh (one MMA warp, correction warpgroup; 512 threads).
+template <int HD, int ELT, bool FP8, bool F16>
+static int launch_instance2(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                            const CUtensorMap& tmO, uint32_t fmt, int grid, cudaStream_t stream) {
+  using L2 = FwdSmem2<HD, ELT>;
+  auto kernel = fa100_fwd2_kernel<HD, ELT, FP8, F16>;
+  static std::atomic<uint64_t> attr_set[2] = {{0}, {0}};
+  int dev = 0;
+  FA_CUDA(cudaGetDevice(&dev));
+  const bool tracked = dev >= 0 && dev < 128;
+  if (!tracked || !((attr_set[dev >> 6].load(std::memory_order_relaxed) >> (dev & 63)) & 1)) {
+    FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L2::kTotalBytes));
+    if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
+  }
+  kernel<<<grid, kThreads2, L2::kTotalBytes, stream>>>(kp, tmQ, tmK, tmV, tmO, fmt);
+  FA_CUDA(cudaGetLastError());
+  return FA100_OK;
+}
+
 // The 2-CTA variant (cta_group::2; the second MMA form SURVEY 8(a) a2 names): bf16 / fp16, head dims of exactly 128,
 // dense or packed K/V (not paged), not the dual-stream decode kernel.  Parity-green on the whole GPU suite when forced on
 // and bitwise equal to the 1-CTA kernel.  Interleaved bursts in one process (tools/pair_ab.py, profiles/r01c_pair_ab.log):
@@ -46,7 +71,7 @@ static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, co
 // chain is shorter with pairs, but the softmax chain is co-critical, so nothing is gained yet and the
 // default stays one CTA per work item.  Fa100FwdParams.variant: 0 / 2 = one CTA per work item, 1 = pairs where eligible.
 static bool use_pair(const Fa100FwdParams* p, const Fa100Plan* plan) {
-  return p->variant == 1 && p->dtype != FA100_E4M3 && p->d == 128 && p->dv == 128 && p->page_table == nullptr && !plan->dual_stream &&
+  return (p->variant & 3) == 1 && p->dtype != FA100_E4M3 && p->d == 128 && p->dv == 128 && p->page_table == nullptr && !plan->dual_stream &&
          plan->num_sm >= 2;
 }
 
@@ -184,7 +209,12 @@ fa100_schedule_kernel(const FwdKernelParams p, int32_t* __restrict__ meta, int32
   }
   int acc = run_total[threadIdx.x] - sum;
   for (int r = lo; r < hi; ++r) { prefix[r] = acc; acc += mblk[order[r]] * p.heads_work * nsplit[r]; }
-  if (threadIdx.x == blockDim.x - 1) { prefix[p.b] = run_total[threadIdx.x]; meta[0] = run_total[threadIdx.x]; meta[1] = p.b; }
+  if (threadIdx.x == blockDim.x - 1) {
+    prefix[p.b] = run_total[threadIdx.x]; meta[0] = run_total[threadIdx.x]; meta[1] = p.b;
+    // the plan this schedule was built for; the forward kernel checks it (sched_matches)
+    int32_t* header = meta - kSchedHeaderWords;
+    header[0] = kSchedMagic; header[3] = p.num_sm; header[5] = p.tiles_per_item; header[6] = p.num_splits; header[7] = p.pack;
+  }
 }
 
 // splits a batch element does not use must read as empty in the combine pass
@@ -218,7 +248,6 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   if (fp8) FA_CHECK_ARG(p->d % 16 == 0 && p->dv % 16 == 0, "fp8 head dims must be multiples of 16");
   FA_UNSUPPORTED(p->d > 256 || p->dv > 256, "head dim > 256 is not supported (d=%d dv=%d)", p->d, p->dv);
   FA_UNSUPPORTED(p->k_new || p->v_new || p->rotary_cos, "append-KV / rotary handled by the caller-side kernel, not fa100_fwd");
-  FA_UNSUPPORTED(fp8 && p->softcap > 0.f, "softcap with fp8 not supported");
   const bool varlen_q = p->cu_seqlens_q != nullptr;
   const bool varlen_k = p->cu_seqlens_k != nullptr;
   const bool paged = p->page_table != nullptr;
@@ -273,8 +302,7 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   // into the next sequence), no seqused_q, no pack-GQA (rows interleave heads), no fp32 partials; hdim <= 128.
   CUtensorMap tmO = tmQ;
   {
-    static const bool no_tma_store = getenv("FA100_NO_TMA_STORE") != nullptr;  // A/B switch: register stores everywhere
-    const bool o_tma = !no_tma_store && p->o_accum == nullptr && !varlen_q && !p->seqused_q && kp.pack == 1 &&
+    const bool o_tma = !(p->variant & FA100_VARIANT_NO_TMA_STORE) && p->o_accum == nullptr && !varlen_q && !p->seqused_q && kp.pack == 1 &&
                        std::max(p->d, p->dv) <= 128 && (p->o_row_stride * 2) % 16 == 0 && (p->o_head_stride * 2) % 16 == 0 &&
                        (p->o_batch_stride * 2) % 16 == 0 && reinterpret_cast<uintptr_t>(p->o) % 16 == 0;
     if (o_tma) {
@@ -307,6 +335,14 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)                 \
         : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream))
   if (fp8 && hd == 256) return launch_instance<256, 1, true, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+  // prefill (two Q tiles per work item, head dims <= 128, one CTA per item): the four-role mainloop of fa100_fwd2.cuh
+  if (!dual && !solo && !pair && !(p->variant & FA100_VARIANT_LEGACY_MAINLOOP)) {
+    if (fp8) return launch_instance2<128, 1, true, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+    if (hd == 64) return f16 ? launch_instance2<64, 2, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
+                             : launch_instance2<64, 2, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+    return f16 ? launch_instance2<128, 2, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
+               : launch_instance2<128, 2, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+  }
   if (fp8) return FA_LAUNCH(128, 1, true, false);
   if (hd == 256)
     return f16 ? launch_instance<256, 2, false, true, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)

@@ -116,7 +116,15 @@ FA_DEVICE int work_index(int round) {
   return round * grid + ((round & 1) ? grid - 1 - cta : cta);
 }
 
-constexpr int kSchedHeaderWords = 8;  // [magic, num_splits, pack_gqa, num_sm, num_work bound, 0, 0, 0] written by the host (get_scheduler_metadata)
+// Header in front of the device-built schedule: [magic, num_splits, pack_gqa, num_sm, num_work bound] from the host
+// (get_scheduler_metadata; informational) and [magic, .., .., num_sm, .., tiles_per_item, CTA-level splits, pack] from
+// fa100_schedule_kernel: the forward kernel refuses a schedule built for another plan (sched_matches).
+constexpr int kSchedHeaderWords = 8;
+constexpr int32_t kSchedMagic = 0xFA100;
+FA_DEVICE bool sched_matches(const FwdKernelParams& p) {
+  const int32_t* h = p.sched - kSchedHeaderWords;
+  return h[0] == kSchedMagic && h[3] == p.num_sm && h[5] == p.tiles_per_item && h[6] == p.num_splits && h[7] == p.pack && p.sched[1] == p.b;
+}
 FA_DEVICE int total_work(const FwdKernelParams& p) { return p.sched ? p.sched[0] : p.num_work; }
 
 FA_DEVICE WorkItem decode_work(const FwdKernelParams& p, int w) {
@@ -135,7 +143,7 @@ FA_DEVICE WorkItem decode_work(const FwdKernelParams& p, int w) {
     int lo = 0, hi = p.b - 1;  // largest r with prefix[r] <= w
     while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (prefix[mid] <= w) lo = mid; else hi = mid - 1; }
     const int per_batch = prefix[lo + 1] - prefix[lo];
-    it.nsplits = prefix[p.b + 1 + lo];
+    it.nsplits = min(prefix[p.b + 1 + lo], p.num_splits);  // never past the partials the caller allocated
     const int m_blocks = per_batch / (p.heads_work * it.nsplits);
     w -= prefix[lo];
     it.bi = order[lo];

@@ -87,9 +87,9 @@ template <int STAGES> FA_DEVICE void ring_advance(RingState& r) { if (++r.stage 
 // ----------------------------------------------------------------------------- TMA producer
 // The whole warp walks the schedule (warp-uniform control flow keeps descriptors and coordinates in uniform
 // registers); one elected lane issues the bulk copies.
-template <int HD, int ELT, bool DUAL, bool PAIR = false>
+template <int HD, int ELT, bool DUAL, bool PAIR = false, typename Bar = FwdBarriers>
 FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, const CUtensorMap* tmK,
-                             const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar, int rank = 0) {
+                             const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, Bar* bar, int rank = 0) {
   using L = FwdSmem<HD, ELT, PAIR>;
   constexpr int kRowBytes = 128;                       // 128B-swizzled rows
   constexpr int kColsPerBox = kRowBytes / ELT;         // 64 (16-bit) or 128 (8-bit)
@@ -262,7 +262,19 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
     FA_PROF(3);
   };
   // O_t (+)= P_t V(stage)
-  auto pv_op = [&](int t, int stage, bool first, bool last) {
+  auto pv_op = [&](int t, int stage, bool first, bool last, int valid_rows) {
+    // Key rows of the block past the end of the sequence are real memory (the tail of a dense cache, the rest of a page),
+    // not TMA zero fill: their probabilities are 0, but 0 x NaN / Inf from an uninitialised cache would poison every row
+    // of the tile.  Zero them in the V stage before the product (once per work item at most; PAIR: the peer's half is out
+    // of reach of this warp, the variant requires finite cache tails).
+    if (!PAIR && valid_rows < kBlockN) {
+      uint8_t* vs = sKV + stage * L::kKVBytes;
+      const int r0 = max(valid_rows, 0);
+      for (int i = r0 * 8 + int(threadIdx.x & 31); i < kBlockN * 8; i += 32)
+        for (int hb = 0; hb < p.v_boxes; ++hb) *reinterpret_cast<uint4*>(vs + hb * kHalfBytes + i * 16) = make_uint4(0u, 0u, 0u, 0u);
+      fence_proxy_async_smem();
+      __syncwarp();
+    }
     if (first) mbar_wait(&bar->o_empty[t], (o_it[t] & 1) ^ 1, 0x50 + t);  // epilogue of the previous work item
     mbar_wait(&bar->p_full[t], p_it[t] & 1, 0x60 + t);
     ++p_it[t];
@@ -302,10 +314,10 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
 
   const int n_work = total_work(p);
   for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
-    int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi;
+    int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi, seq_k;
     {
       const WorkGeom g = make_geom<DUAL, (HD > 128), PAIR>(p, w, 0);
-      n_lo = g.n_lo; n_hi = g.n_hi;
+      n_lo = g.n_lo; n_hi = g.n_hi; seq_k = g.seq.sk;
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) { n_min[t] = g.tr[t].n_min; n_max[t] = g.tr[t].n_max; }
     }
@@ -339,7 +351,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
             if (kIsQK) { qk_op(t, sk, left[t] == 1); release(sk); }
             --left[t];
           }
-          if (!kIsQK) { pv_op(t, sv, j == 0, nb - 2 < n_min[t]); release(sv); }
+          if (!kIsQK) { pv_op(t, sv, j == 0, nb - 2 < n_min[t], seq_k - nb * kBlockN); release(sv); }
         }
       }
     } else {
@@ -367,7 +379,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
         } else {
 #pragma unroll
           for (int t = 0; t < kQTiles; ++t)
-            if (nb >= n_min[t] && nb < n_max[t]) pv_op(t, sv, nb == n_max[t] - 1, nb == n_min[t]);
+            if (nb >= n_min[t] && nb < n_max[t]) pv_op(t, sv, nb == n_max[t] - 1, nb == n_min[t], seq_k - nb * kBlockN);
           release(sv);
         }
       }

@@ -50,6 +50,7 @@ struct RowGeom {
   int n_min, n_max;    // key blocks [n_min, n_max) of this Q tile
   int col_lo, col_hi;  // visible key columns [col_lo, col_hi) of this row
   float scale_log2;
+  float softcap_pre;   // softmax_scale / softcap (x q_descale x k_descale for e4m3); 0 = no softcap
   bool has_rows;
 };
 
@@ -57,8 +58,9 @@ template <bool FP8, bool DUAL, bool SOLO, bool PAIR = false>
 FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row, int rank = 0) {
   const WorkGeom g = make_geom<DUAL, SOLO, PAIR>(p, w, rank);
   RowGeom r;
-  r.has_rows = g.tr[t].has_rows;
-  r.n_min = g.tr[t].n_min; r.n_max = g.tr[t].n_max;
+  const TileRange tr = t == 0 ? g.tr[0] : g.tr[1];  // no dynamic indexing: that would put the struct in local memory
+  r.has_rows = tr.has_rows;
+  r.n_min = tr.n_min; r.n_max = tr.n_max;
   const int pos = tile_pos0<DUAL || SOLO, PAIR>(p, g.it, t, rank) + (p.pack > 1 ? row / p.pack : row);
   const int shift = g.seq.sk - g.seq.sq;
   int col_hi = g.seq.sk, col_lo = 0;
@@ -74,10 +76,13 @@ FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row, int 
   }
   r.col_lo = col_lo; r.col_hi = col_hi;
   r.scale_log2 = p.scale_log2;
-  if (FP8) {  // q and k descales fold into the softmax scale (hopper/flash_fwd_kernel_sm90.h:409-415); softcap + fp8 is rejected on the host
+  r.softcap_pre = p.softcap_pre;
+  if (FP8) {
+    // q and k descales fold into the softmax scale (hopper/flash_fwd_kernel_sm90.h:409-415); with softcap they fold into
+    // the factor in front of tanh instead (the scores leave tanh in true units; same place the reference puts them)
     const float qd = p.q_descale ? p.q_descale[g.it.bi * p.q_descale_batch_stride + g.hk * p.q_descale_head_stride] : 1.f;
     const float kd = p.k_descale ? p.k_descale[g.it.bi * p.k_descale_batch_stride + g.hk * p.k_descale_head_stride] : 1.f;
-    r.scale_log2 *= qd * kd;
+    if (p.softcap_pre != 0.f) r.softcap_pre *= qd * kd; else r.scale_log2 *= qd * kd;
   }
   return r;
 }
@@ -136,7 +141,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
 #pragma unroll
           for (int c = 0; c < 4; ++c)
 #pragma unroll
-            for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(fast_tanh(__uint_as_float(s[c][i]) * p.softcap_pre));
+            for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(fast_tanh(__uint_as_float(s[c][i]) * rg.softcap_pre));
         }
 #pragma unroll
         for (int c = 0; c < 4; ++c)
@@ -389,6 +394,12 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
   const int rank = PAIR ? int(cluster_ctarank()) : 0;  // PAIR: launched as clusters of two CTAs; rank 0 issues the MMAs
   FA_TRACE_BEGIN();
   if (smem_u32(smem) & 1023u) __trap();
+  if (p.sched && !sched_matches(p)) {
+    // a schedule built for other sizes / num_splits / pack_gqa / sm_margin / kernel variant would index partials and
+    // row blocks that do not exist: fail the launch loudly (tag 0x5C4ED in fa100_debug_hang_info)
+    if (threadIdx.x == 0 && blockIdx.x == 0) { g_fa100_hang_info[0] = 0xDEAD0000u | 0x5CEDu; g_fa100_hang_info[1] = 0; g_fa100_hang_info[2] = 0; g_fa100_hang_info[3] = 0; __threadfence(); }
+    __trap();
+  }
 
   if (warp == kLoadWarp && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); if (p.o_tma) tma_prefetch_desc(&tmO); }
   if (warp == kMmaWarp && lane == 0) {

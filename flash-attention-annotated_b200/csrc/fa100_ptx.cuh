@@ -90,9 +90,9 @@ FA_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
 
 // Watchdog: a wrong phase/count must never hang the GPU box.  A wait that lasts longer than
-// FA100_WATCHDOG_CYCLES records {tag, block, thread, parity}, raises a device-wide abort flag and returns;
-// every other wait then falls through as well, the kernel ends (with garbage) and the host reads the
-// record through fa100_debug_hang_info().
+// FA100_WATCHDOG_CYCLES records {tag, block, thread, parity} (read by fa100_debug_hang_info()) and TRAPS: the launch
+// fails with a CUDA error at the caller's next synchronisation instead of finishing with garbage.  The abort flag makes
+// the other CTAs' waits fall through so that the grid drains quickly.
 #ifndef FA100_WATCHDOG_CYCLES
 #define FA100_WATCHDOG_CYCLES (4000000000ll)
 #endif
@@ -106,7 +106,7 @@ static __device__ volatile unsigned int g_fa100_abort;
 #ifndef FA100_TRACE_BLOCK
 #define FA100_TRACE_BLOCK 0
 #endif
-constexpr int kTraceWarps = 12, kTracePerWarp = 4096;
+constexpr int kTraceWarps = 16, kTracePerWarp = 4096;
 static __device__ unsigned int g_fa100_trace[kTraceWarps * kTracePerWarp * 3];
 static __device__ unsigned int g_fa100_trace_cnt[kTraceWarps];
 #ifndef FA100_TRACE_MAXWARP
@@ -175,7 +175,8 @@ FA_DEVICE void mbar_wait_slow(uint64_t* bar, uint32_t parity, int tag) {
         g_fa100_hang_info[2] = threadIdx.x;
         g_fa100_hang_info[3] = parity;
         g_fa100_abort = 1;
-        return;
+        __threadfence();
+        __trap();
       }
     }
   }

@@ -227,7 +227,12 @@ _NO_SCHED = bool(os.environ.get("FA100_NO_SCHED"))  # A/B switch: static schedul
 def _variant() -> int:
     """Fa100FwdParams.variant: FA100_PAIR=1 forces the 2-CTA (cta_group::2) kernel wherever it is eligible, FA100_PAIR=0
     forbids it; unset, the library's default applies (one CTA per work item: the pair kernel measures within 1 % of it)."""
-    return {"1": 1, "0": 2}.get(os.environ.get("FA100_PAIR", ""), 0)
+    v = {"1": 1, "0": 2}.get(os.environ.get("FA100_PAIR", ""), 0)
+    if os.environ.get("FA100_NO_TMA_STORE"):   # A/B switches live in the Python layer; the C library reads no environment
+        v |= 16
+    if os.environ.get("FA100_LEGACY_MAINLOOP"):
+        v |= 32
+    return v
 
 
 def _sched_words(b: int) -> int:

@@ -68,11 +68,12 @@ def hop_plan(rank: int, world: int) -> List[Tuple[int, List[Tuple[str, str, bool
 class Fa100Backend:
     """Partial attention = fa100_fwd in partial mode; merge = fa100_combine.  CUDA only."""
 
-    def __init__(self, softmax_scale: Optional[float] = None):
+    def __init__(self, softmax_scale: Optional[float] = None, sm_margin: int = 0):
         import fa100_ops as ops  # raises if the library is missing; no fallback
 
         self.ops = ops
         self.scale = softmax_scale
+        self.sm_margin = sm_margin  # SMs left to the NCCL send/recv kernels while a transfer overlaps the hop
 
     def alloc(self, b, h, rows, dv, device):
         o = torch.empty((1, b, h, rows, dv), dtype=torch.float32, device=device)  # the running partial (later hops merge into it in the kernel)
@@ -82,15 +83,15 @@ class Fa100Backend:
     fused_merge = True  # the attention epilogue merges into the running partial itself: no combine launch
 
     def partial(self, q, k, v, causal, o_slot, lse_slot):
-        self.ops.mha_fwd(q, k, v, softmax_scale=self.scale, is_causal=causal, _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)))
+        self.ops.mha_fwd(q, k, v, softmax_scale=self.scale, is_causal=causal, sm_margin=self.sm_margin, _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)))
 
     def partial_merge(self, q, k, v, causal, o_slot, lse_slot, out=None, out_lse=None):
         """This hop's attention merged into the running fp32 partial in `o_slot` / `lse_slot` by the kernel's epilogue; the
         last hop (`out` given) writes the 16-bit output (b, rows, h, dv) and the LSE (b, h, rows) instead."""
         if out is None:
-            self.ops.mha_fwd(q, k, v, softmax_scale=self.scale, is_causal=causal, _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)), _merge=1)
+            self.ops.mha_fwd(q, k, v, softmax_scale=self.scale, is_causal=causal, sm_margin=self.sm_margin, _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)), _merge=1)
         else:
-            _, lse, *_ = self.ops.mha_fwd(q, k, v, out=out, softmax_scale=self.scale, is_causal=causal,
+            _, lse, *_ = self.ops.mha_fwd(q, k, v, out=out, softmax_scale=self.scale, is_causal=causal, sm_margin=self.sm_margin,
                                           _partial=(o_slot.unsqueeze(0), lse_slot.unsqueeze(0)), _merge=2)
             out_lse.copy_(lse)
 
@@ -110,38 +111,156 @@ class Fa100Backend:
 
 # --------------------------------------------------------------------------- K/V exchange
 class _RingExchange:
-    """K and V travel as one buffer; two buffers alternate so the next hop's transfer overlaps this hop's attention."""
+    """NCCL send/recv ring (north_star's transport).  K and V are two messages of one grouped send/recv, so d != dv and
+    GQA shards need no packing; hop 0 uses the caller's tensors as they are (no staging copy), later hops alternate
+    between two receive buffers so that hop t+1's transfer overlaps hop t's attention."""
 
-    def __init__(self, k, v, rank, world, group):
-        assert k.shape == v.shape, "ring exchange packs K and V in one message: d must equal dv"
-        self.kv = [torch.stack((k, v)), torch.empty((2,) + tuple(k.shape), dtype=k.dtype, device=k.device) if world > 1 else None]
+    name = "nccl"
+
+    def __init__(self, k, v, rank, world, group, events=None):
+        self.cur = (k, v)
+        self.bufs = [(torch.empty_like(k), torch.empty_like(v)) for _ in range(2)] if world > 1 else []
         self.world, self.group, self.dev = world, group, k.device
         self.comm_stream = torch.cuda.Stream(device=k.device) if (k.is_cuda and world > 1) else None
         self.nxt, self.prv = (rank + 1) % world, (rank - 1) % world
         if group is not None and world > 1:
             self.nxt, self.prv = dist.get_global_rank(group, self.nxt), dist.get_global_rank(group, self.prv)
-        self.reqs = []
+        self.reqs, self.events = [], events
 
     def begin(self, t):
         """Start moving the buffer of hop t on to the next rank (and receiving hop t+1's); return hop t's (K, V)."""
-        cur = self.kv[t % 2]
+        cur = self.cur
         if t + 1 < self.world:
-            recv = self.kv[(t + 1) % 2]
-            ops = [dist.P2POp(dist.isend, cur, self.nxt, self.group), dist.P2POp(dist.irecv, recv, self.prv, self.group)]
+            recv = self.bufs[(t + 1) % 2]
+            ops = [dist.P2POp(dist.isend, cur[0], self.nxt, self.group), dist.P2POp(dist.isend, cur[1], self.nxt, self.group),
+                   dist.P2POp(dist.irecv, recv[0], self.prv, self.group), dist.P2POp(dist.irecv, recv[1], self.prv, self.group)]
             if self.comm_stream is not None:
                 self.comm_stream.wait_stream(torch.cuda.current_stream(self.dev))  # recv's last readers (hop t-1) are done
                 with torch.cuda.stream(self.comm_stream):
+                    e0 = _mark(self.events, self.comm_stream)
                     self.reqs = dist.batch_isend_irecv(ops)
+                    e1 = _mark(self.events, self.comm_stream)
+                if self.events is not None:
+                    self.events.append(("comm", t, e0, e1))
             else:
                 self.reqs = dist.batch_isend_irecv(ops)
-        return cur[0], cur[1]
+            self.nxt_cur = recv
+        return cur
 
     def end(self, t):
         for r in self.reqs:
             r.wait()
         if self.comm_stream is not None and self.reqs:
             torch.cuda.current_stream(self.dev).wait_stream(self.comm_stream)
+        if self.reqs:
+            self.cur = self.nxt_cur
         self.reqs = []
+
+    def finish(self):
+        pass
+
+
+def _mark(events, stream):
+    if events is None:
+        return None
+    e = torch.cuda.Event(enable_timing=True)
+    e.record(stream)
+    return e
+
+
+class _PushExchange:
+    """Copy-engine transport over NVSwitch peer memory: no SM is taken from the attention kernel.
+
+    NVSwitch gives every GPU full bandwidth to every peer, so nothing has to be forwarded around a ring: each rank PUSHES
+    its K/V shard straight into a receive slot in every peer's memory (symmetric-memory buffer, peer-mapped), in the order
+    the peers need it (peer r+t uses it at its hop t).  The copies are cudaMemcpyAsync on a side stream -> DMA engines; the
+    hand-shakes are stream memory operations (cuStreamWriteValue32 on the peer's signal pad after the copy,
+    cuStreamWaitValue32 on the local pad in front of the hop), so neither side launches a kernel for communication and the
+    persistent attention kernel keeps all 148 SMs.  The NCCL send/recv kernels of _RingExchange need SMs of their own while
+    the attention kernel's 384 threads x 168 registers fill every SM it runs on.
+
+    Flow control across calls: before overwriting its slot on peer p a rank waits until p has signalled "consumed" for the
+    previous call (written by p's compute stream after its last hop).  Buffers and handles are cached per shape."""
+
+    name = "ce_push"
+    _cache = {}
+
+    def __init__(self, k, v, rank, world, group, events=None):
+        import torch.distributed._symmetric_memory as symm
+        from cuda.bindings import driver as cu
+
+        self.cu, self.rank, self.world, self.dev, self.events = cu, rank, world, k.device, events
+        self.k, self.v = k, v
+        kb, vb = k.numel() * k.element_size(), v.numel() * v.element_size()
+        self.kb, self.vb = kb, vb
+        slot = (kb + vb + 255) // 256 * 256
+        gname = (group if group is not None else dist.group.WORLD).group_name
+        key = (gname, slot, k.device.index)
+        st = _PushExchange._cache.get(key)
+        if st is None:
+            buf = symm.empty(world * slot, dtype=torch.uint8, device=k.device)
+            hdl = symm.rendezvous(buf, gname)
+            peers = [hdl.get_buffer(p, (world * slot,), torch.uint8) for p in range(world)]
+            pads = [int(x) + 4096 for x in hdl.signal_pad_ptrs]  # second half of the pad: clear of torch's own barrier channels
+            st = dict(buf=buf, hdl=hdl, peers=peers, pads=pads, epoch=0, stream=torch.cuda.Stream(device=k.device))
+            hdl.barrier(channel=0)  # one-time: every rank's pads are zeroed and mapped before the first signal
+            torch.cuda.synchronize(k.device)
+            _PushExchange._cache[key] = st
+        self.st, self.slot = st, slot
+        st["epoch"] += 1
+        self.epoch = st["epoch"]
+        self.comm_stream = st["stream"]
+        # signal pad words (uint32) on every rank: [src] = epoch of the data src pushed here; [world + dst] = epoch dst has consumed
+        main = torch.cuda.current_stream(self.dev)
+        self.comm_stream.wait_stream(main)  # K/V are ready
+        with torch.cuda.stream(self.comm_stream):
+            for t in range(1, world):
+                dst = (rank + t) % world
+                e0 = _mark(events, self.comm_stream)
+                self._wait(self.comm_stream, st["pads"][rank] + 4 * (world + dst), self.epoch - 1)
+                peer = st["peers"][dst]
+                off = rank * slot
+                peer[off:off + kb].copy_(k.reshape(-1).view(torch.uint8), non_blocking=True)
+                peer[off + kb:off + kb + vb].copy_(v.reshape(-1).view(torch.uint8), non_blocking=True)
+                self._write(self.comm_stream, st["pads"][dst] + 4 * rank, self.epoch)
+                e1 = _mark(events, self.comm_stream)
+                if events is not None:
+                    events.append(("comm", t, e0, e1))
+
+    def _check(self, res):
+        err = res[0] if isinstance(res, tuple) else res
+        if int(err) != 0:
+            raise RuntimeError(f"CUDA driver call failed in _PushExchange: {err}")
+
+    def _wait(self, stream, addr, value):
+        self._check(self.cu.cuStreamWaitValue32(stream.cuda_stream, addr, value & 0xFFFFFFFF, self.cu.CUstreamWaitValue_flags.CU_STREAM_WAIT_VALUE_GEQ))
+
+    def _write(self, stream, addr, value):
+        self._check(self.cu.cuStreamWriteValue32(stream.cuda_stream, addr, value & 0xFFFFFFFF, 0))
+
+    def begin(self, t):
+        if t == 0:
+            return self.k, self.v
+        src = (self.rank - t) % self.world
+        main = torch.cuda.current_stream(self.dev)
+        self._wait(main, self.st["pads"][self.rank] + 4 * src, self.epoch)
+        mine = self.st["buf"]
+        off = src * self.slot
+        kk = mine[off:off + self.kb].view(self.k.dtype).view(self.k.shape)
+        vv = mine[off + self.kb:off + self.kb + self.vb].view(self.v.dtype).view(self.v.shape)
+        return kk, vv
+
+    def end(self, t):
+        pass
+
+    def finish(self):
+        # tell every source that its slot here may be overwritten by the next call; the caller's K/V stay in use by the
+        # side stream until its pushes are done
+        main = torch.cuda.current_stream(self.dev)
+        for t in range(1, self.world):
+            src = (self.rank - t) % self.world
+            self._write(main, self.st["pads"][src] + 4 * (self.world + self.rank), self.epoch)
+        main.wait_stream(self.comm_stream)
 
 
 class _LocalExchange:
@@ -157,19 +276,28 @@ class _LocalExchange:
     def end(self, t):
         pass
 
+    def finish(self):
+        pass
+
 
 # --------------------------------------------------------------------------- the ring
+TRANSPORTS = ("nccl", "ce_push")
+
+
 def ring_flash_attn_func(q, k, v, softmax_scale=None, causal=True, group=None, backend=None, return_lse=False, _exchange=None,
-                         _rank_world=None):
+                         _rank_world=None, transport="nccl", sm_margin=0, _events=None):
     """q, k, v: this rank's zig-zag shard, (b, 2c, h, d) / (b, 2c, h_k, d) / (b, 2c, h_k, dv), contiguous.
-    Returns this rank's shard of the output (b, 2c, h, dv) [and LSE (b, h, 2c)]."""
+    Returns this rank's shard of the output (b, 2c, h, dv) [and LSE (b, h, 2c)].
+    transport: "nccl" = K/V ring over NCCL send/recv (needs SMs for its copy kernels: `sm_margin` SMs are left free for
+    them); "ce_push" = direct pushes into every peer's memory by the copy engines (no SMs, CUDA only).
+    _events: a list that receives ("attn" | "comm", hop, start_event, end_event) for per-hop timing."""
     assert causal, "ring attention is built for the causal C5 case (non-causal needs no zig-zag; use flash_attn_func per hop)"
     if _rank_world is not None:
         rank, world = _rank_world
     else:
         world = dist.get_world_size(group) if dist.is_initialized() else 1
         rank = dist.get_rank(group) if dist.is_initialized() else 0
-    be = backend if backend is not None else Fa100Backend(softmax_scale)
+    be = backend if backend is not None else Fa100Backend(softmax_scale, sm_margin if (world > 1 and transport == "nccl") else 0)
     b, rows2, h, d = q.shape
     c = rows2 // 2
     dv = v.shape[-1]
@@ -181,10 +309,18 @@ def ring_flash_attn_func(q, k, v, softmax_scale=None, causal=True, group=None, b
     filled = {g: False for g in groups}
     plan = hop_plan(rank, world)
     last_use = {g: max(t for t, (_, work) in enumerate(plan) if any(w[0] == g for w in work)) for g in groups}
-    ex = _exchange if _exchange is not None else _RingExchange(k, v, rank, world, group)
+    if _exchange is not None:
+        ex = _exchange
+    elif transport == "ce_push" and world > 1 and k.is_cuda:
+        ex = _PushExchange(k, v, rank, world, group, _events)
+    else:
+        assert transport in TRANSPORTS, transport
+        ex = _RingExchange(k, v, rank, world, group, _events)
+    timed = _events is not None and q.is_cuda
 
     for t, (src, work) in enumerate(plan):
         k_t, v_t = ex.begin(t)
+        a0 = _mark(_events, torch.cuda.current_stream(q.device)) if timed else None
         for g, keys, is_causal in work:
             o, lse = acc[g]
             kk = k_t[:, :c] if keys == "lo" else k_t
@@ -206,7 +342,10 @@ def ring_flash_attn_func(q, k, v, softmax_scale=None, causal=True, group=None, b
             elif final:
                 be.finish_single(o, lse, out[:, groups[g]], out_lse[:, :, groups[g]])
             filled[g] = True
+        if timed:
+            _events.append(("attn", t, a0, _mark(_events, torch.cuda.current_stream(q.device))))
         ex.end(t)
+    ex.finish()
     return (out, out_lse) if return_lse else out
 
 

@@ -42,6 +42,9 @@ typedef void* fa100_stream_t; /* cudaStream_t */
  * Layouts: q (b, sq, h, d) or packed (total_q, h, d) with cu_seqlens_q;
  * k/v (b_k, sk, h_k, d|dv), packed (total_k, h_k, d), or paged (num_pages, page_size, h_k, d);
  * o like q with dv; lse fp32 (b, h, sq) or (h, total_q). */
+#define FA100_VARIANT_NO_TMA_STORE 16
+#define FA100_VARIANT_LEGACY_MAINLOOP 32
+
 typedef struct Fa100FwdParams {
   /* tensors */
   const void* q;
@@ -127,7 +130,9 @@ typedef struct Fa100FwdParams {
   /* Kernel variant.  The 2-CTA kernel runs CTA pairs with cta_group::2 MMAs (M = 256 over two SMs, each CTA holding half
    * of every K / V tile); it is eligible for bf16 / fp16, d = dv = 128, K/V not paged, not the dual-stream decode kernel.
    * 0 = the library's default (today: one CTA per work item), 1 = pairs wherever eligible, 2 = one CTA per work item
-   * always.  fa100_prepare_scheduler must see the same value as fa100_fwd. */
+   * always (low two bits).  fa100_prepare_scheduler must see the same value as fa100_fwd.
+   * Flag bits for A/B measurements: FA100_VARIANT_NO_TMA_STORE = O leaves through register stores everywhere,
+   * FA100_VARIANT_LEGACY_MAINLOOP = the round-1 mainloop (shared score buffer, softmax warps own rescale + epilogue). */
   int32_t variant;
   /* Fused merge of a running partial (ring / context-parallel attention): with o_accum / lse_accum set and
    * num_splits == 1, 1 = read the fp32 partial already in o_accum / lse_accum, merge this call's result into it with the

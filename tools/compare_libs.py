@@ -75,10 +75,23 @@ def main():
     attempt(c2, "torch SDPA flash TFLOP/s", lambda: sdpa(SDPBackend.FLASH_ATTENTION))
     attempt(c2, "flash_attn 2.8 (FA2 kernels) TFLOP/s", fa2)
     attempt(c2, "flashinfer single_prefill TFLOP/s", flashinfer_prefill)
-    c2["reference CuTe-DSL FlashAttentionForwardSm100"] = ("unavailable: /root/reference is not present on the GPU box and its "
-                                                           "pinned nvidia-cutlass-dsl 4.3.0.dev0 is not installed (4.5.0 is)")
     out["C2 bf16 b8 32q/8kv s8192 d128 causal"] = c2
     del q, k, v
+    torch.cuda.empty_cache()
+
+    # ---- the reference's own Blackwell kernel (CuTe-DSL FlashAttentionForwardSm100, flash_attn/cute/interface.py), installed
+    # unmodified by tools/install_ref_cute.sh; a subprocess so that its `flash_attn` package does not collide with the FA2 wheel
+    import subprocess
+    ref_dir = os.path.join(ROOT, "baseline", "_ref", "flash_attn", "cute")
+    if not os.path.isdir(ref_dir):
+        out["reference CuTe-DSL FlashAttentionForwardSm100"] = "unavailable: baseline/_ref/flash_attn/cute missing (run tools/install_ref_cute.sh)"
+    else:
+        try:
+            r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "time_ref_cute.py")], capture_output=True, text=True, timeout=900)
+            last = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+            out["reference CuTe-DSL FlashAttentionForwardSm100"] = json.loads(last[-1]) if last else "unavailable: rc=%d %s" % (r.returncode, r.stderr[-1500:])
+        except Exception as e:  # noqa: BLE001
+            out["reference CuTe-DSL FlashAttentionForwardSm100"] = "unavailable: " + repr(e)[:300]
 
     # ---- C4: decode b64 32q/8kv sq1 sk32768 d128 page 256
     b, sk, h, hk, d, ps = 64, 32768, 32, 8, 128, 256
