@@ -38,7 +38,7 @@ def test_simulated_ring_matches_single_pass(world, s, h, hk):
     assert torch.allclose(lse[:1, :h // hk].cpu(), lref, atol=1e-3, rtol=1e-3)
 
 
-def _nccl_worker(rank, world, port, q_out):
+def _nccl_worker(rank, world, port, q_out, transport="nccl"):
     sys.path[:0] = [os.path.join(ROOT, "flash-attention-annotated_b200"), os.path.join(ROOT, "oracle")]
     import torch.distributed as dist
     import ring_attention as R
@@ -50,12 +50,15 @@ def _nccl_worker(rank, world, port, q_out):
     try:
         g = torch.Generator(device="cuda").manual_seed(77)  # same full problem on every rank
         mk = lambda *shape: torch.randn(*shape, generator=g, device="cuda", dtype=torch.bfloat16)  # noqa: E731
-        q, k, v = mk(1, 8192, 8, 128), mk(1, 8192, 8, 128), mk(1, 8192, 8, 128)
-        out, lse = R.ring_flash_attn_func(R.zigzag_shard(q, rank, world), R.zigzag_shard(k, rank, world),
-                                          R.zigzag_shard(v, rank, world), causal=True, return_lse=True)
+        q, k, v = mk(1, 8192, 8, 128), mk(1, 8192, 2, 128), mk(1, 8192, 2, 128)  # GQA shards: K / V messages smaller than Q
         ref_o, ref_lse = flash_attn_func(q, k, v, causal=True, return_attn_probs=True)
-        err = (out.float() - R.zigzag_shard(ref_o, rank, world).float()).abs().max().item()
-        lerr = (lse - R.zigzag_shard(ref_lse, rank, world, dim=2)).abs().max().item()
+        err = lerr = 0.0
+        for _ in range(3):  # repeated calls reuse the transport's buffers (flow control across calls)
+            out, lse = R.ring_flash_attn_func(R.zigzag_shard(q, rank, world), R.zigzag_shard(k, rank, world),
+                                              R.zigzag_shard(v, rank, world), causal=True, return_lse=True, transport=transport,
+                                              sm_margin=8 if transport == "nccl" else 0)
+            err = max(err, (out.float() - R.zigzag_shard(ref_o, rank, world).float()).abs().max().item())
+            lerr = max(lerr, (lse - R.zigzag_shard(ref_lse, rank, world, dim=2)).abs().max().item())
         torch.cuda.synchronize()
         q_out.put((rank, err, lerr))
     finally:
@@ -63,14 +66,17 @@ def _nccl_worker(rank, world, port, q_out):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (run with gpurun --gpus 2)")
-def test_nccl_ring_two_gpus():
+@pytest.mark.parametrize("transport", ["nccl", "ce_push"])
+def test_nccl_ring_two_gpus(transport):
+    """The real ring over NVLink on 2 (or 4 / 8 when visible) GPUs, one process per GPU: NCCL send/recv ring, and the
+    copy-engine push transport (peer memory + stream memory operations, no communication kernels)."""
     import torch.multiprocessing as mp
 
-    world = min(torch.cuda.device_count(), 4)
-    world = 2 if world < 4 else 4
+    world = torch.cuda.device_count()
+    world = 8 if world >= 8 else (4 if world >= 4 else 2)
     ctx = mp.get_context("spawn")
     q_out = ctx.Queue()
-    procs = [ctx.Process(target=_nccl_worker, args=(r, world, 29871, q_out)) for r in range(world)]
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, 29871 + (transport == "ce_push"), q_out, transport)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q_out.get(timeout=300) for _ in range(world)]
