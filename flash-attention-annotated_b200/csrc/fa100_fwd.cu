@@ -335,8 +335,9 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)                 \
         : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream))
   if (fp8 && hd == 256) return launch_instance<256, 1, true, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
-  // prefill (two Q tiles per work item, head dims <= 128, one CTA per item): the four-role mainloop of fa100_fwd2.cuh
-  if (!dual && !solo && !pair && !(p->variant & FA100_VARIANT_LEGACY_MAINLOOP)) {
+  // opt-in (Fa100FwdParams.variant & FA100_VARIANT_FOUR_ROLE): the four-role prefill mainloop of fa100_fwd2.cuh for two Q tiles
+  // per work item, head dims <= 128, one CTA per item
+  if (!dual && !solo && !pair && (p->variant & FA100_VARIANT_FOUR_ROLE)) {
     if (fp8) return launch_instance2<128, 1, true, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
     if (hd == 64) return f16 ? launch_instance2<64, 2, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
                              : launch_instance2<64, 2, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);

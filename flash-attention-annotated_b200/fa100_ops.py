@@ -230,7 +230,7 @@ def _variant() -> int:
     v = {"1": 1, "0": 2}.get(os.environ.get("FA100_PAIR", ""), 0)
     if os.environ.get("FA100_NO_TMA_STORE"):   # A/B switches live in the Python layer; the C library reads no environment
         v |= 16
-    if os.environ.get("FA100_LEGACY_MAINLOOP"):
+    if os.environ.get("FA100_FOUR_ROLE") == "1":  # the four-role prefill mainloop (csrc/fa100_fwd2.cuh)
         v |= 32
     return v
 

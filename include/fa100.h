@@ -43,7 +43,7 @@ typedef void* fa100_stream_t; /* cudaStream_t */
  * k/v (b_k, sk, h_k, d|dv), packed (total_k, h_k, d), or paged (num_pages, page_size, h_k, d);
  * o like q with dv; lse fp32 (b, h, sq) or (h, total_q). */
 #define FA100_VARIANT_NO_TMA_STORE 16
-#define FA100_VARIANT_LEGACY_MAINLOOP 32
+#define FA100_VARIANT_FOUR_ROLE 32
 
 typedef struct Fa100FwdParams {
   /* tensors */
@@ -132,7 +132,10 @@ typedef struct Fa100FwdParams {
    * 0 = the library's default (today: one CTA per work item), 1 = pairs wherever eligible, 2 = one CTA per work item
    * always (low two bits).  fa100_prepare_scheduler must see the same value as fa100_fwd.
    * Flag bits for A/B measurements: FA100_VARIANT_NO_TMA_STORE = O leaves through register stores everywhere,
-   * FA100_VARIANT_LEGACY_MAINLOOP = the round-1 mainloop (shared score buffer, softmax warps own rescale + epilogue). */
+   * FA100_VARIANT_FOUR_ROLE = the four-role prefill mainloop of csrc/fa100_fwd2.cuh (one MMA warp issuing PV_t, QK_t in order
+   * with P_t overlaid on S_t, separate softmax and correction warpgroups, P published in two pieces) instead of the default
+   * (score buffer shared by the two Q tiles, QK and PV issuing warps, softmax warps own rescale + epilogue).  Parity-green on
+   * the whole suite; measured 12 % slower on C2, hence opt-in. */
   int32_t variant;
   /* Fused merge of a running partial (ring / context-parallel attention): with o_accum / lse_accum set and
    * num_splits == 1, 1 = read the fp32 partial already in o_accum / lse_accum, merge this call's result into it with the

@@ -3,7 +3,7 @@
 set -u
 mkdir -p gpurun_out
 TAG=${1:-r02a}; shift || true
-LIBS=${*:-"libfa100.so libfa100.so:FA100_LEGACY_MAINLOOP=1"}
+LIBS=${*:-"libfa100.so libfa100.so:FA100_FOUR_ROLE=1"}
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi_$TAG.csv 2>&1
 timeout 900 python -m pytest tests -m gpu -q -x --maxfail=1 > gpurun_out/pytest_gpu_$TAG.log 2>&1; echo "pytest rc=$?"; tail -6 gpurun_out/pytest_gpu_$TAG.log
 AB_ROUNDS=3 timeout 900 python tools/ab_time.py $LIBS > gpurun_out/ab_$TAG.log 2>&1; echo "ab rc=$?"; cat gpurun_out/ab_$TAG.log
