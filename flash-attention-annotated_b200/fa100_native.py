@@ -70,7 +70,7 @@ class Plan(C.Structure):
 
 
 EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_prepare_scheduler",
-           "fa100_scheduler_metadata_words", "fa100_debug_hang_info",
+           "fa100_scheduler_metadata_words", "fa100_fwd_splitkv_noalloc", "fa100_noalloc_scratch_bytes", "fa100_debug_hang_info",
            "fa100_debug_trace", "fa100_debug_prof")
 
 _lib = None
@@ -102,6 +102,9 @@ def lib() -> C.CDLL:
         l.fa100_prepare_scheduler.argtypes = [C.POINTER(FwdParams), vp, i64, vp]
         l.fa100_scheduler_metadata_words.argtypes = [i32]
         l.fa100_scheduler_metadata_words.restype = i64
+        l.fa100_fwd_splitkv_noalloc.argtypes = [C.POINTER(FwdParams), vp]
+        l.fa100_fwd_splitkv_noalloc.restype = C.c_int
+        l.fa100_noalloc_scratch_bytes.restype = i64
         l.fa100_debug_hang_info.argtypes = [C.POINTER(C.c_uint32 * 4)]
         l.fa100_debug_trace.argtypes = [C.POINTER(C.c_uint32), C.c_int]
         l.fa100_debug_prof.argtypes = [C.POINTER(C.c_uint32), C.c_int]

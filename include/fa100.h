@@ -194,6 +194,22 @@ int fa100_plan(const Fa100Shape* shape, Fa100Plan* out);
 int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream);
 int fa100_combine(const Fa100CombineParams* p, fa100_stream_t stream);
 
+/* Split-KV forward + combine with NO memory allocation anywhere: the fp32 partials (the only scratch memory the forward
+ * uses) live in a static device array inside the library instead of caller-supplied o_accum / lse_accum.
+ * No counterpart in the reference: added for callers that cannot allocate device
+ * memory (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ *   - p as for fa100_fwd, with o and lse set, o_accum = lse_accum = NULL, num_splits in [2, 256], dense (not packed) q;
+ *     result = fa100_fwd with partials followed by fa100_combine into o (bf16 / fp16) and lse (b, h, seqlen_q).
+ *   - limit: num_splits * b * h * seqlen_q * (dv + 1) * 4 bytes <= FA100_NOALLOC_SCRATCH_BYTES (16 MiB); beyond it the call
+ *     returns FA100_ERR_INVALID with a message and launches nothing.  Every GPU that loads the library holds the array
+ *     until the process exits.
+ *   - all calls share the array and it keeps the previous call's contents (the LSE slots are reset at the start of each
+ *     call); calls that overlap on the GPU (several streams, concurrent graph replays) RACE on it: serialise them.
+ *   - calls no cudaMalloc / cudaFree / allocating routine; stream-ordered, no host synchronisation. */
+#define FA100_NOALLOC_SCRATCH_BYTES (16 * 1024 * 1024)
+int fa100_fwd_splitkv_noalloc(const Fa100FwdParams* p, fa100_stream_t stream);
+int64_t fa100_noalloc_scratch_bytes(void);
+
 /* Device-side schedule for ragged batches: the role of prepare_varlen_num_blocks (hopper/flash.h:220,
  * hopper/flash_prepare_scheduler.cu:43-215) and of the metadata tensor mha_fwd_get_scheduler_metadata returns
  * (hopper/flash_api.cpp:521-662, layout :996-1025).  One small kernel on `stream` reads cu_seqlens / seqused / leftpad
