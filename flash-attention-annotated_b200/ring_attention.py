@@ -139,17 +139,19 @@ class _RingExchange:
                 with torch.cuda.stream(self.comm_stream):
                     e0 = _mark(self.events, self.comm_stream)
                     self.reqs = dist.batch_isend_irecv(ops)
+                    for r in self.reqs:
+                        r.wait()  # stream-level: the side stream waits for NCCL's own stream, the host does not block
                     e1 = _mark(self.events, self.comm_stream)
                 if self.events is not None:
                     self.events.append(("comm", t, e0, e1))
             else:
                 self.reqs = dist.batch_isend_irecv(ops)
+                for r in self.reqs:
+                    r.wait()
             self.nxt_cur = recv
         return cur
 
     def end(self, t):
-        for r in self.reqs:
-            r.wait()
         if self.comm_stream is not None and self.reqs:
             torch.cuda.current_stream(self.dev).wait_stream(self.comm_stream)
         if self.reqs:
