@@ -422,12 +422,17 @@ def measure_ring(ctx, steps, warmup):
         one()
     ctx.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(ctx.local)
+    if rank == 0:
+        sampler.start()
     e0.record()
     n1_steps = 3
     for _ in range(n1_steps):
         one()
     e1.record()
     torch.cuda.synchronize()
+    if rank == 0:
+        out["n1_clocks"] = sampler.stop()
     (t1,) = ctx.max_over_ranks([e0.elapsed_time(e1) / n1_steps])
     out["n1_ms_per_step"] = t1
     out["n1_tflops"] = total / (t1 * 1e-3) / 1e12
@@ -437,31 +442,51 @@ def measure_ring(ctx, steps, warmup):
     rows = w["sq"] // world
     kv_bytes = 2 * w["b"] * rows * w["hk"] * w["d"] * 2
     results = {}
-    for transport, kw in (("nccl", dict(transport="nccl", sm_margin=ctx.args.ring_sm_margin)), ("ce_push", dict(transport="ce_push"))):
+    ring_group = R.nccl_ring_group(ctx.args.ring_sm_margin) if not ctx.args.ring_default_comm else None
+    for transport, kw in (("nccl", dict(transport="nccl", sm_margin=ctx.args.ring_sm_margin, group=ring_group)), ("ce_push", dict(transport="ce_push"))):
         try:
-            m = measure(ctx, w, steps, warmup, do_e2e=False, ring_kw=kw, want_clocks=(transport == "nccl"))
+            m = measure(ctx, w, steps, warmup, do_e2e=False, ring_kw=kw, want_clocks=True)
             ms = m["ms"]
             r = dict(value=total / (ms * 1e-3) / 1e12, ms_per_step=ms, gpu_launches_per_step=m["launches"],
                      strong_efficiency_vs_n1=(t1 / world) / ms, clocks=m["clocks"])
             if transport == "nccl":
                 r["sm_margin"] = ctx.args.ring_sm_margin
+                r["nccl_comm"] = "default" if ring_group is None else f"dedicated: max_ctas={ctx.args.ring_sm_margin}, high-priority stream"
             # one instrumented step: events around every hop's attention launches and every transfer
             host = make_inputs(w, dev, seed=1234 + rank, world=world)
             t = {k_: v_.to(dev) for k_, v_ in host.items()}
             ev = []
+            R.ring_flash_attn_func(t["q"], t["k"], t["v"], causal=True, **kw)  # warm: the instrumented step must not pay first-use costs
             ctx.barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
             R.ring_flash_attn_func(t["q"], t["k"], t["v"], causal=True, _events=ev, **kw)
+            s1.record()
             ctx.barrier()
             attn = [0.0] * world
             comm = [0.0] * world
             for kind, hop, a, b in ev:
                 (attn if kind == "attn" else comm)[hop] += a.elapsed_time(b)
+            (step_ms, not_attn) = ctx.max_over_ranks([s0.elapsed_time(s1), s0.elapsed_time(s1) - sum(attn)])
+            # the same step repeated with a barrier in front of each: separates rank drift / coupling (gone with barriers)
+            # from clock effects of a long run (still there)
+            tot = 0.0
+            for _ in range(5):
+                ctx.barrier()
+                s0.record()
+                R.ring_flash_attn_func(t["q"], t["k"], t["v"], causal=True, **kw)
+                s1.record()
+                torch.cuda.synchronize()
+                tot += s0.elapsed_time(s1)
+            (barriered_ms,) = ctx.max_over_ranks([tot / 5])
             attn = ctx.max_over_ranks(attn)
             comm = ctx.max_over_ranks(comm)
             r["per_hop"] = dict(attn_ms=[round(x, 3) for x in attn], transfer_ms=[round(x, 3) for x in comm[:-1]],
-                                bytes_per_hop=kv_bytes, exposed_comm_ms=round(ms - sum(attn), 3),
-                                note="transfer_ms[t]: the copy issued at hop t (needed by hop t+1; ce_push: the push to rank r+t+1); "
-                                     "exposed_comm_ms = step time - sum of the hops' attention time")
+                                bytes_per_hop=kv_bytes, instrumented_step_ms=round(step_ms, 3), barriered_step_ms=round(barriered_ms, 3),
+                                exposed_comm_ms=round(not_attn, 3),
+                                note="one instrumented step, max over ranks.  transfer_ms[t]: the K/V copy that hop t+1 needs (nccl: "
+                                     "send/recv issued at hop t; ce_push: the push whose data the receiver uses at its hop t+1); "
+                                     "exposed_comm_ms = that step's time - the sum of its hops' attention time (waits for K/V + launch gaps)")
             r["merge_launches"] = 0  # merges run in the attention epilogue (Fa100FwdParams.merge_partial)
             results[transport] = r
             del t
@@ -477,7 +502,8 @@ def measure_ring(ctx, steps, warmup):
     out.update(ok[best])
     out["transport"] = best
     out["transports"] = {k_: (dict(value=v_["value"], ms_per_step=v_["ms_per_step"], strong_efficiency_vs_n1=v_["strong_efficiency_vs_n1"],
-                                   per_hop=v_["per_hop"]) if isinstance(v_, dict) else v_) for k_, v_ in results.items()}
+                                   clocks=v_["clocks"], per_hop=v_["per_hop"], **({"sm_margin": v_["sm_margin"], "nccl_comm": v_["nccl_comm"]} if "nccl_comm" in v_ else {}))
+                             if isinstance(v_, dict) else v_) for k_, v_ in results.items()}
     peaks = measured_peaks()
     out["roofline"] = dict(bound="tensor", achieved=out["value"] / world, peak=peaks["tensor"], unit="TFLOP/s per GPU",
                            frac=out["value"] / world / peaks["tensor"], peak_source=peaks["source"] + " (cuBLAS bf16 burst)",
@@ -522,7 +548,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="only the headline workload (no extra / ring_c5 attachments)")
-    ap.add_argument("--ring-sm-margin", type=int, default=8, help="SMs the attention kernel leaves to NCCL's send/recv kernels in the ring")
+    ap.add_argument("--ring-default-comm", action="store_true", help="NCCL ring over the default communicator instead of the max_ctas-capped one")
+    ap.add_argument("--ring-sm-margin", type=int, default=16, help="SMs the attention kernel leaves to NCCL's send/recv kernels in the ring")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "fa100" else args.warmup
     w = WORKLOADS[args.workload]
