@@ -101,6 +101,8 @@ __device__ __forceinline__ void move_vec(const AppendParams& a, const uint8_t* s
 // first the K_new rows, then the V_new rows, then (rotary only) the Q rows.
 template <typename T>
 __global__ void __launch_bounds__(256) fa100_append_kernel(const AppendParams a) {
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");               // PDL (see fa100_ptx.cuh): no global access before this
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
   const int bi = blockIdx.y;
   constexpr int vec_elems = kVec;
   const int new0 = a.cu_seqlens_knew ? a.cu_seqlens_knew[bi] : 0;
@@ -204,9 +206,9 @@ extern "C" int fa100_append_kv(const Fa100FwdParams* p, void* q_rotated, int64_t
   const int64_t vecs = max_new * p->h_k * ((p->d + p->dv) / vec) + (rotary ? int64_t(p->seqlen_q) * p->h * (p->d / vec) : 0);
   const int chunks = int(std::max<int64_t>(1, std::min<int64_t>((vecs + 255) / 256, 148 * 8 / std::max(1, p->b) + 1)));
   const dim3 grid(chunks, p->b);
-  if (fp8) fa100_append_kernel<__nv_fp8_e4m3><<<grid, 256, 0, stream>>>(a);
-  else if (p->dtype == FA100_FP16) fa100_append_kernel<__half><<<grid, 256, 0, stream>>>(a);
-  else fa100_append_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(a);
+  if (fp8) FA_CUDA(launch_pdl(fa100_append_kernel<__nv_fp8_e4m3>, grid, dim3(256), size_t(0), stream, 1, a));
+  else if (p->dtype == FA100_FP16) FA_CUDA(launch_pdl(fa100_append_kernel<__half>, grid, dim3(256), size_t(0), stream, 1, a));
+  else FA_CUDA(launch_pdl(fa100_append_kernel<__nv_bfloat16>, grid, dim3(256), size_t(0), stream, 1, a));
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }

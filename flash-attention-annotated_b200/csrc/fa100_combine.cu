@@ -15,6 +15,8 @@ constexpr int kCombineWarps = 4;
 
 template <int OUT>  // FA100_BF16 / FA100_FP16 / FA100_FP32
 __global__ void __launch_bounds__(kCombineWarps * 32) fa100_combine_kernel(const Fa100CombineParams p) {
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");               // PDL: the partials come from the forward kernel in front
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int64_t rows_total = int64_t(p.b) * p.s * p.h;
   for (int64_t r = int64_t(blockIdx.x) * kCombineWarps + warp; r < rows_total; r += int64_t(gridDim.x) * kCombineWarps) {
@@ -80,9 +82,9 @@ int launch_combine(const Fa100CombineParams* p, cudaStream_t stream) {
   if (rc) return rc;
   const int64_t blocks_needed = (rows + kCombineWarps - 1) / kCombineWarps;
   const int grid = int(blocks_needed < int64_t(num_sm) * 16 ? blocks_needed : int64_t(num_sm) * 16);
-  if (p->out_dtype == FA100_FP32) fa100_combine_kernel<FA100_FP32><<<grid, kCombineWarps * 32, 0, stream>>>(*p);
-  else if (p->out_dtype == FA100_BF16) fa100_combine_kernel<FA100_BF16><<<grid, kCombineWarps * 32, 0, stream>>>(*p);
-  else if (p->out_dtype == FA100_FP16) fa100_combine_kernel<FA100_FP16><<<grid, kCombineWarps * 32, 0, stream>>>(*p);
+  if (p->out_dtype == FA100_FP32) FA_CUDA(launch_pdl(fa100_combine_kernel<FA100_FP32>, dim3(grid), dim3(kCombineWarps * 32), size_t(0), stream, 1, *p));
+  else if (p->out_dtype == FA100_BF16) FA_CUDA(launch_pdl(fa100_combine_kernel<FA100_BF16>, dim3(grid), dim3(kCombineWarps * 32), size_t(0), stream, 1, *p));
+  else if (p->out_dtype == FA100_FP16) FA_CUDA(launch_pdl(fa100_combine_kernel<FA100_FP16>, dim3(grid), dim3(kCombineWarps * 32), size_t(0), stream, 1, *p));
   else return set_error(FA100_ERR_INVALID, "bad out_dtype %d", p->out_dtype);
   FA_CUDA(cudaGetLastError());
   return FA100_OK;

@@ -27,18 +27,9 @@ static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, co
     FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes));
     if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
   }
-  if (PAIR) {
-    // clusters of two CTAs: the pair shares every K / V tile (cta_group::2 MMAs); grid = 2 x pairs
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = L::kTotalBytes; cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    FA_CUDA(cudaLaunchKernelEx(&cfg, kernel, kp, tmQ, tmK, tmV, tmO, fmt));
-  } else {
-    kernel<<<grid, kThreads, L::kTotalBytes, stream>>>(kp, tmQ, tmK, tmV, tmO, fmt);
-  }
+  // PAIR: clusters of two CTAs (the pair shares every K / V tile, cta_group::2 MMAs; grid = 2 x pairs).  Always with PDL:
+  // prologue and launch latency overlap the tail of the schedule / append-KV kernel in front (hopper/flash_fwd_launch_template.h:195-196)
+  FA_CUDA(launch_pdl(kernel, dim3(grid), dim3(kThreads), size_t(L::kTotalBytes), stream, PAIR ? 2 : 1, kp, tmQ, tmK, tmV, tmO, fmt));
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
@@ -57,7 +48,7 @@ static int launch_instance2(const FwdKernelParams& kp, const CUtensorMap& tmQ, c
     FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L2::kTotalBytes));
     if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
   }
-  kernel<<<grid, kThreads2, L2::kTotalBytes, stream>>>(kp, tmQ, tmK, tmV, tmO, fmt);
+  FA_CUDA(launch_pdl(kernel, dim3(grid), dim3(kThreads2), size_t(L2::kTotalBytes), stream, 1, kp, tmQ, tmK, tmV, tmO, fmt));
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
@@ -153,7 +144,15 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
 // `:150-190`) and writes the prefix of work items over that order.  The forward kernel then walks a list without
 // entries for rows past a sequence's end, with the expensive sequences at the front of every CTA's walk.
 __global__ void __launch_bounds__(1024, 1)
-fa100_schedule_kernel(const FwdKernelParams p, int32_t* __restrict__ meta, int32_t* __restrict__ scratch) {
+fa100_schedule_kernel(const FwdKernelParams p, int32_t* __restrict__ meta, int32_t* __restrict__ scratch, float* __restrict__ fill, int64_t fill_n) {
+  pdl_wait();               // the lengths may come from the kernel in front (append-KV, the caller's producer)
+  pdl_launch_dependents();  // the forward's prologue may start; it waits for this grid before reading the schedule
+  if (blockIdx.x > 0) {
+    // CTAs 1.. : with per-batch split counts some partials are never written -- make every LSE slot read as an empty
+    // partial (-inf) for the combine pass (was a separate launch)
+    for (int64_t i = int64_t(blockIdx.x - 1) * blockDim.x + threadIdx.x; i < fill_n; i += int64_t(gridDim.x - 1) * blockDim.x) fill[i] = -INFINITY;
+    return;
+  }
   int32_t* order = meta + 2;
   int32_t* prefix = order + p.b;
   int32_t* nsplit = prefix + p.b + 1;  // per ordered batch element
@@ -219,6 +218,8 @@ fa100_schedule_kernel(const FwdKernelParams p, int32_t* __restrict__ meta, int32
 
 // splits a batch element does not use must read as empty in the combine pass
 __global__ void fa100_fill_neg_inf_kernel(float* __restrict__ x, int64_t n) {
+  pdl_wait();
+  pdl_launch_dependents();
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) x[i] = -INFINITY;
 }
 
@@ -232,7 +233,12 @@ int launch_prepare_scheduler(const Fa100FwdParams* p, const Fa100Plan* plan, int
   FwdKernelParams kp;
   fill_kernel_params(p, plan, kp);
   int32_t* body = metadata + kSchedHeaderWords;
-  fa100_schedule_kernel<<<1, 1024, 0, stream>>>(kp, body, body + 2 + p->b + (p->b + 1) + p->b);
+  // the LSE partials of a split call are pre-filled here (Fa100FwdParams.lse_accum given): the forward then skips its own fill
+  float* fill = nullptr;
+  int64_t fill_n = 0;
+  if (p->lse_accum != nullptr && plan->num_splits > 1 && p->merge_partial == 0) { fill = p->lse_accum; fill_n = kp.lseacc_split_stride * plan->num_splits; }
+  const int fill_ctas = fill_n > 0 ? int(std::min<int64_t>((fill_n + 4095) / 4096, 147)) : 0;
+  FA_CUDA(launch_pdl(fa100_schedule_kernel, dim3(1 + fill_ctas), dim3(1024), size_t(0), stream, 1, kp, body, body + 2 + p->b + (p->b + 1) + p->b, fill, fill_n));
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
@@ -320,10 +326,12 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
                  "o must be 16-byte aligned with strides that are multiples of 8 elements");
   }
 
-  if (kp.sched && splits > 1) {
-    // with per-batch split counts some partials are never written: make them read as empty (LSE = -inf) for fa100_combine
+  if (kp.sched && splits > 1 && !p->lse_accum_prefilled) {
+    // with per-batch split counts some partials are never written: make them read as empty (LSE = -inf) for fa100_combine.
+    // fa100_prepare_scheduler does this itself when it is given lse_accum (the caller then sets lse_accum_prefilled); this
+    // launch remains for a schedule built ahead of time (get_scheduler_metadata)
     const int64_t n = kp.lseacc_split_stride * splits;
-    fa100_fill_neg_inf_kernel<<<int(std::min<int64_t>((n + 255) / 256, 1184)), 256, 0, stream>>>(p->lse_accum, n);
+    FA_CUDA(launch_pdl(fa100_fill_neg_inf_kernel, dim3(int(std::min<int64_t>((n + 255) / 256, 1184))), dim3(256), size_t(0), stream, 1, p->lse_accum, n));
     FA_CUDA(cudaGetLastError());
   }
   int num_sm = plan->num_sm;

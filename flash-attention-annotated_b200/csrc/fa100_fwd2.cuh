@@ -208,35 +208,6 @@ FA_DEVICE void mma2_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, ui
 #ifndef FA100_PUBLISH_AT
 #define FA100_PUBLISH_AT 52  // pair index (0..63, in pack order) after which the first 3/4 of P is published
 #endif
-#ifndef FA100_E2E_MOD
-#define FA100_E2E_MOD 0      // >0: every FA100_E2E_MOD-th score pair of the first three chunks takes the polynomial exp2
-#endif
-
-// exp2 of two scores on the FMA pipe instead of the MUFU (Cody-Waite split + degree-3 polynomial on [0, 1), the scheme of
-// the reference's Blackwell kernel, flash_attn/cute/utils.py:601-681): x <= 0 here, clamped at -127; relative error ~1e-4,
-// far below the bf16 / e4m3 rounding of P that follows.
-FA_DEVICE void ex2_poly2_v(uint32_t& a, uint32_t& b) {
-  asm volatile(
-      "{\n\t.reg .f32 x0, x1, c;\n\t.reg .b64 x, r, rb, f, pl, k;\n\t.reg .b32 r0, r1, p0, p1;\n\t"
-      "mov.b32 x0, %0;\n\tmov.b32 x1, %1;\n\t"
-      "max.ftz.f32 x0, x0, 0fC2FE0000;\n\tmax.ftz.f32 x1, x1, 0fC2FE0000;\n\t"
-      "mov.b64 x, {x0, x1};\n\t"
-      "mov.f32 c, 0f4B400000;\n\tmov.b64 k, {c, c};\n\t"        // 2^23 + 2^22
-      "add.rm.ftz.f32x2 r, x, k;\n\t"                               // floor(x) in the low mantissa bits
-      "sub.rn.ftz.f32x2 rb, r, k;\n\t"
-      "sub.rn.ftz.f32x2 f, x, rb;\n\t"                              // fractional part in [0, 1)
-      "mov.f32 c, 0f3D9DF09D;\n\tmov.b64 pl, {c, c};\n\t"         // 0.077119089663
-      "mov.f32 c, 0f3E6906A4;\n\tmov.b64 k, {c, c};\n\t"          // 0.227564394474
-      "fma.rn.ftz.f32x2 pl, pl, f, k;\n\t"
-      "mov.f32 c, 0f3F31F519;\n\tmov.b64 k, {c, c};\n\t"          // 0.695146143436
-      "fma.rn.ftz.f32x2 pl, pl, f, k;\n\t"
-      "mov.f32 c, 0f3F800000;\n\tmov.b64 k, {c, c};\n\t"          // 1.0
-      "fma.rn.ftz.f32x2 pl, pl, f, k;\n\t"
-      "mov.b64 {r0, r1}, r;\n\tmov.b64 {p0, p1}, pl;\n\t"
-      "shl.b32 r0, r0, 23;\n\tshl.b32 r1, r1, 23;\n\t"
-      "add.s32 %0, r0, p0;\n\tadd.s32 %1, r1, p1;\n\t}"
-      : "+r"(a), "+r"(b));
-}
 
 template <int HD, int ELT, bool FP8, bool F16>
 FA_DEVICE void softmax2_role(const FwdKernelParams& p, float* sMsg, FwdBarriers2* bar, uint32_t tmem, int warp, int lane) {
@@ -618,11 +589,6 @@ fa100_fwd2_kernel(const __grid_constant__ FwdKernelParams p, const __grid_consta
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   FA_TRACE_BEGIN();
   if (smem_u32(smem) & 1023u) __trap();
-  if (p.sched && !sched_matches(p)) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) { g_fa100_hang_info[0] = 0xDEAD0000u | 0x5CEDu; g_fa100_hang_info[1] = 0; g_fa100_hang_info[2] = 0; g_fa100_hang_info[3] = 0; __threadfence(); }
-    __trap();
-  }
-
   if (warp == kLoadWarp2 && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); if (p.o_tma) tma_prefetch_desc(&tmO); }
   if (warp == kMmaWarp2 && lane == 0) {
 #pragma unroll
@@ -639,6 +605,13 @@ fa100_fwd2_kernel(const __grid_constant__ FwdKernelParams p, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
+  pdl_wait();  // PDL: global memory is read only from here on (see fa100_ptx.cuh)
+  pdl_launch_dependents();
+  if (p.sched && !sched_matches(p)) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) { g_fa100_hang_info[0] = 0xDEAD0000u | 0x5CEDu; g_fa100_hang_info[1] = 0; g_fa100_hang_info[2] = 0; g_fa100_hang_info[3] = 0; __threadfence(); }
+    __trap();
+  }
+
 
   // register pool at launch: 512 threads x 128; the correction warps give 48 each, the last warpgroup 80 each, to the softmax warps (+64 each)
   if (warp < kSoftmaxWarps) {

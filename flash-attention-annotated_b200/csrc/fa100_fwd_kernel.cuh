@@ -11,11 +11,12 @@
 //   warp  10    PV issuer (elected lane): O_t += P_t V (TS form, P in TMEM)
 //   warp  11    idle (completes the third warpgroup for setmaxnreg: softmax warps run with 224 registers, the rest 56)
 //
-// TMEM (512 columns): S0 @0, S1 @128, O0 @256, O1 @384; P_t (16-bit) overwrites columns [0,64) of S_t.
-// Two 128-row Q tiles per CTA ping-pong through the tensor pipe: while the softmax warps turn S_t into P_t the
-// MMAs of the other tile run.  O is only rescaled when the running row max grew by more than 2^8 (exact: the
-// final 1/rowsum and LSE use the same stale max); the rescale is done in place in TMEM by the softmax warps,
-// which also run the epilogue (normalise, convert, store O and LSE).
+// TMEM (512 columns): S @0 (fp32 scores; ONE buffer the two Q tiles take turns in), P_0 @128, P_1 @192 (operand dtype: 64
+// columns at 16 bit, 32 at e4m3), O_0 @256, O_1 @384.  Two 128-row Q tiles per CTA ping-pong through the tensor pipe: a
+// softmax warpgroup copies its scores into registers and hands S to the other tile at once, so the next S_t never waits for
+// P_t V.  O is only rescaled when the running row max grew by more than 2^8 (exact: the final 1/rowsum and LSE use the
+// same stale max); the rescale is done in place in TMEM by the softmax warps, which also run the epilogue (normalise,
+// convert, store O and LSE).  The opt-in four-role mainloop with a separate correction warpgroup is csrc/fa100_fwd2.cuh.
 #pragma once
 #include "fa100_ptx.cuh"
 

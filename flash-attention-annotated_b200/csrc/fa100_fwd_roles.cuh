@@ -2,10 +2,6 @@
 #pragma once
 #include "fa100_fwd_kernel.cuh"
 
-#ifndef FA100_GARBAGE
-#define FA100_GARBAGE 0
-#endif
-
 namespace fa100 {
 
 // Work-item geometry every role derives identically (no communication needed).
@@ -69,7 +65,6 @@ FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w, int rank = 0) {
 #pragma unroll
   for (int t = 0; t < kQTiles; ++t) {
     g.tr[t] = tile_range(p, g.seq, (g.it.m_blk * kQTiles + t) * p.pos_per_tile, g.it.split, g.it.nsplits);
-    if ((FA100_GARBAGE & 128) && t == 1) { g.tr[t].has_rows = false; g.tr[t].n_min = g.tr[t].n_max = 0; }  // timing only: tile 1 idle
     if (g.tr[t].n_max > g.tr[t].n_min) { g.n_lo = min(g.n_lo, g.tr[t].n_min); g.n_hi = max(g.n_hi, g.tr[t].n_max); }
   }
   return g;
@@ -149,8 +144,7 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
             tma_load_4d_2sm(dst, tm, &bar->kv_full[stage], rank * kColsPerBox, g.seq.k_off + nb * kBlockN, g.hk, g.seq.bk);
           }
         }
-      } else if (FA100_GARBAGE & 16) { if (elect_one()) mbar_arrive(&bar->kv_full[stage]); }  // timing only: no K/V traffic into shared memory
-      else if (p.page_size == 0) {
+      } else if (p.page_size == 0) {
         if (elect_one()) {
           mbar_arrive_expect_tx(&bar->kv_full[stage], boxes * kHalfBytes);
 #pragma unroll
@@ -249,7 +243,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
         const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
         // PAIR: this CTA's K boxes hold 64 keys, so the next 64 head-dim columns are half as far away
         const uint32_t off_b = PAIR ? (ks / kSlicesPerBox) * (kHalfBytes >> 5) + (ks % kSlicesPerBox) * 2 : off;
-        if (ks < p.qk_slices && !(FA100_GARBAGE & 64)) {
+        if (ks < p.qk_slices) {
           if (PAIR) mma_ss_2sm(tmem, a_lo + off, b_lo + off_b, kHi, idesc, ks > 0);
           else mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
         }
@@ -284,8 +278,7 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
     if (elect_one()) {
       const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboV;
 #pragma unroll
-      for (int ks = 0; ks < kPVSlices; ++ks)
-        if (!(FA100_GARBAGE & 32)) {
+      for (int ks = 0; ks < kPVSlices; ++ks) {
           if (PAIR) mma_ts_2sm(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc, (!first || ks > 0));
           else mma_ts<FP8>(tmem + 256 + t * 128, tmem + 128 + t * 64 + ks * 8, b_lo + ks * (kKPerMma * 128 >> 4), kHi, idesc, (!first || ks > 0));
         }

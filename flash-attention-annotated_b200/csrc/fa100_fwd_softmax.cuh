@@ -40,9 +40,40 @@ FA_DEVICE uint16_t pack8_v(uint32_t lo, uint32_t hi) {
   asm volatile("cvt.rn.satfinite.e4m3x2.f32 %0, %2, %1;" : "=h"(r) : "r"(lo), "r"(hi));
   return r;
 }
-#ifndef FA100_GARBAGE
-#define FA100_GARBAGE 0  // timing-only experiments (wrong results): 1 half the exponentials, 2 no row sum, 4 no pack, 8 no row max
+// Build-time experiment switches (default off = the product kernel): every FA100_E2E_MOD-th score pair of the first three
+// chunks of a row (FA100_E2E_MOD_FP8 for the e4m3 kernels) takes the polynomial exp2 below instead of the MUFU.
+#ifndef FA100_E2E_MOD
+#define FA100_E2E_MOD 0
 #endif
+#ifndef FA100_E2E_MOD_FP8
+#define FA100_E2E_MOD_FP8 FA100_E2E_MOD
+#endif
+// exp2 of two scores on the FMA pipe instead of the MUFU (Cody-Waite split + degree-3 polynomial on [0, 1), the scheme of
+// the reference's Blackwell kernel, flash_attn/cute/utils.py:601-681): x <= 0 here, clamped at -127; relative error ~1e-4,
+// far below the bf16 / e4m3 rounding of P that follows.
+FA_DEVICE void ex2_poly2_v(uint32_t& a, uint32_t& b) {
+  asm volatile(
+      "{\n\t.reg .f32 x0, x1, c;\n\t.reg .b64 x, r, rb, f, pl, k;\n\t.reg .b32 r0, r1, p0, p1;\n\t"
+      "mov.b32 x0, %0;\n\tmov.b32 x1, %1;\n\t"
+      "max.ftz.f32 x0, x0, 0fC2FE0000;\n\tmax.ftz.f32 x1, x1, 0fC2FE0000;\n\t"
+      "mov.b64 x, {x0, x1};\n\t"
+      "mov.f32 c, 0f4B400000;\n\tmov.b64 k, {c, c};\n\t"        // 2^23 + 2^22
+      "add.rm.ftz.f32x2 r, x, k;\n\t"                               // floor(x) in the low mantissa bits
+      "sub.rn.ftz.f32x2 rb, r, k;\n\t"
+      "sub.rn.ftz.f32x2 f, x, rb;\n\t"                              // fractional part in [0, 1)
+      "mov.f32 c, 0f3D9DF09D;\n\tmov.b64 pl, {c, c};\n\t"         // 0.077119089663
+      "mov.f32 c, 0f3E6906A4;\n\tmov.b64 k, {c, c};\n\t"          // 0.227564394474
+      "fma.rn.ftz.f32x2 pl, pl, f, k;\n\t"
+      "mov.f32 c, 0f3F31F519;\n\tmov.b64 k, {c, c};\n\t"          // 0.695146143436
+      "fma.rn.ftz.f32x2 pl, pl, f, k;\n\t"
+      "mov.f32 c, 0f3F800000;\n\tmov.b64 k, {c, c};\n\t"          // 1.0
+      "fma.rn.ftz.f32x2 pl, pl, f, k;\n\t"
+      "mov.b64 {r0, r1}, r;\n\tmov.b64 {p0, p1}, pl;\n\t"
+      "shl.b32 r0, r0, 23;\n\tshl.b32 r1, r1, 23;\n\t"
+      "add.s32 %0, r0, p0;\n\tadd.s32 %1, r1, p1;\n\t}"
+      : "+r"(a), "+r"(b));
+}
+
 // What one softmax thread needs about its row while it walks the key blocks of a work item.  Kept this small on
 // purpose: with 227 KB of shared memory carved out the L1 is tiny, so a register spill in the step loop costs an L2
 // round trip; everything the epilogue needs is recomputed there instead of being carried across the loop.
@@ -159,7 +190,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
           mx0 = fmaxf(mx0, __uint_as_float(s[c][i])); mx1 = fmaxf(mx1, __uint_as_float(s[c][i + 1]));
           mx2 = fmaxf(mx2, __uint_as_float(s[c][i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[c][i + 3]));
         }
-      const float m_blk = (FA100_GARBAGE & 8) ? __uint_as_float(s[0][0]) + 4.f : fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
       FA_PROF(2);
       const float m_cand = fmaxf(m_run, m_blk);
       // lazy rescale: keep the stale max unless it grew by more than 2^8 (NaN from -inf - -inf compares false)
@@ -197,12 +228,16 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
 #pragma unroll
         for (int k = -kAhead; k < 64 + kBehind; ++k) {
           if (k + kAhead < 64) { const int a = k + kAhead; ffma2_v(s[a >> 4][(a & 15) * 2], s[a >> 4][(a & 15) * 2 + 1], scale_log2, neg_m); }
-          if (k >= 0 && k < 64 && !((FA100_GARBAGE & 1) && (k & 1))) { ex2_v(s[k >> 4][(k & 15) * 2]); ex2_v(s[k >> 4][(k & 15) * 2 + 1]); }
+          if (k >= 0 && k < 64) {
+            constexpr int kMod = FP8 ? FA100_E2E_MOD_FP8 : FA100_E2E_MOD;
+            if (kMod > 0 && k < 48 && (k % (kMod > 0 ? kMod : 1)) == (kMod > 0 ? kMod : 1) - 1) ex2_poly2_v(s[k >> 4][(k & 15) * 2], s[k >> 4][(k & 15) * 2 + 1]);
+            else { ex2_v(s[k >> 4][(k & 15) * 2]); ex2_v(s[k >> 4][(k & 15) * 2 + 1]); }
+          }
           if (k - kBehind >= 0) {
             const int c = k - kBehind;
             const uint32_t p0 = s[c >> 4][(c & 15) * 2], p1 = s[c >> 4][(c & 15) * 2 + 1];
-            if (!(FA100_GARBAGE & 2)) { if (c & 1) fadd2_v(sum2, sum3, p0, p1); else fadd2_v(sum0, sum1, p0, p1); }
-            if (!FP8) pk[c] = (FA100_GARBAGE & 4) ? p0 : pack16_v<F16>(p0, p1);
+            if (c & 1) fadd2_v(sum2, sum3, p0, p1); else fadd2_v(sum0, sum1, p0, p1);
+            if (!FP8) pk[c] = pack16_v<F16>(p0, p1);
             else {
               h8[c] = pack8_v(p0, p1);
               if (c & 1) pk[c >> 1] = uint32_t(h8[c - 1]) | (uint32_t(h8[c]) << 16);
@@ -394,13 +429,6 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
   const int rank = PAIR ? int(cluster_ctarank()) : 0;  // PAIR: launched as clusters of two CTAs; rank 0 issues the MMAs
   FA_TRACE_BEGIN();
   if (smem_u32(smem) & 1023u) __trap();
-  if (p.sched && !sched_matches(p)) {
-    // a schedule built for other sizes / num_splits / pack_gqa / sm_margin / kernel variant would index partials and
-    // row blocks that do not exist: fail the launch loudly (tag 0x5C4ED in fa100_debug_hang_info)
-    if (threadIdx.x == 0 && blockIdx.x == 0) { g_fa100_hang_info[0] = 0xDEAD0000u | 0x5CEDu; g_fa100_hang_info[1] = 0; g_fa100_hang_info[2] = 0; g_fa100_hang_info[3] = 0; __threadfence(); }
-    __trap();
-  }
-
   if (warp == kLoadWarp && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); if (p.o_tma) tma_prefetch_desc(&tmO); }
   if (warp == kMmaWarp && lane == 0) {
     // PAIR: the softmax warps of both CTAs arrive on the leader's s_free / p_full / o_empty
@@ -424,6 +452,17 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
   if (PAIR) cluster_sync_all();  // the peer's barriers exist before anything is sent to them
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
+  // PDL: everything above touched only shared / tensor memory and kernel parameters; global memory written by the kernels
+  // in front of this one (schedule, append-KV, the caller's producers) is read only from here on
+  pdl_wait();
+  pdl_launch_dependents();
+  if (p.sched && !sched_matches(p)) {
+    // a schedule built for other sizes / num_splits / pack_gqa / sm_margin / kernel variant would index partials and
+    // row blocks that do not exist: fail the launch loudly (tag 0x5C4ED in fa100_debug_hang_info)
+    if (threadIdx.x == 0 && blockIdx.x == 0) { g_fa100_hang_info[0] = 0xDEAD0000u | 0x5CEDu; g_fa100_hang_info[1] = 0; g_fa100_hang_info[2] = 0; g_fa100_hang_info[3] = 0; __threadfence(); }
+    __trap();
+  }
+
 
   // register pool at launch: 384 threads x 168; warps 8-11 give 112 each to the 8 softmax warps (+56 each)
   if (warp < kSoftmaxWarps) {

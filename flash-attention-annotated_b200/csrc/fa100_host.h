@@ -33,6 +33,28 @@ int encode_tensor_map(CUtensorMap* out, int dtype, int rank, const void* base, c
 
 int device_sm_count(int* out);
 
+// Launch with programmatic stream serialization (PDL): the kernel may start while the previous kernel of the stream is
+// still draining; every fa100 kernel executes griddepcontrol.wait before its first global-memory access (fa100_ptx.cuh).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, int cluster_x, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+#ifndef FA100_NO_PDL  // A/B switch of the build (tools/build_variant.sh): plain stream-ordered launches
+  attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[n].val.programmaticStreamSerializationAllowed = 1;
+  ++n;
+#endif
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster_x; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = attr; cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stream);
 int launch_combine(const Fa100CombineParams* p, cudaStream_t stream);
 int launch_prepare_scheduler(const Fa100FwdParams* p, const Fa100Plan* plan, int32_t* metadata, int64_t words, cudaStream_t stream);

@@ -28,6 +28,16 @@ template <int N> FA_DEVICE void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.
 
 FA_DEVICE void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory"); }
 
+// ------------------------------------------------------------------ programmatic dependent launch (PDL)
+// Role of cutlass::arch::wait_on_dependent_grids / launch_dependent_grids in the reference (hopper/flash_fwd_kernel_sm90.h,
+// flash_fwd_combine_kernel.h, flash_prepare_scheduler.cu).  Contract in this library: every kernel executes pdl_wait() in
+// all of its threads BEFORE its first global-memory access, so a kernel launched with the programmatic-serialization
+// attribute only overlaps its prologue (barrier init, TMEM allocation, descriptor prefetch) and its launch latency with the
+// previous kernel's tail, and completion of a kernel implies completion of everything before it in the stream.  Both
+// instructions are no-ops in a kernel launched without the attribute.
+FA_DEVICE void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
+FA_DEVICE void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
+
 // ------------------------------------------------------------------ mbarrier
 FA_DEVICE void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count) : "memory");

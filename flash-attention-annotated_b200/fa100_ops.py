@@ -39,15 +39,52 @@ def _i32(t, name, n=None):
         _chk(t.numel() == n, f"{name} must have shape ({n},)")
 
 
+_SM_COUNT = {}
+_PLAN_CACHE = {}
+
+
+def _sm_count(device) -> int:
+    idx = torch.cuda.current_device() if device is None else (device.index if isinstance(device, torch.device) and device.index is not None
+                                                              else torch.cuda.current_device() if isinstance(device, torch.device) else int(device))
+    n = _SM_COUNT.get(idx)
+    if n is None:
+        n = _SM_COUNT[idx] = torch.cuda.get_device_properties(idx).multi_processor_count
+    return n
+
+
 def plan(b, seqlen_q, seqlen_k, h, h_k, d, dv, dtype, causal, local, num_splits, pack_gqa, sm_margin, device=None):
-    """Sizes-only policy (num_splits, pack_gqa, #work items); the role of get_num_splits/get_pack_gqa."""
-    num_sm = torch.cuda.get_device_properties(device if device is not None else torch.cuda.current_device()).multi_processor_count
-    s = N.Shape(b=b, seqlen_q=seqlen_q, seqlen_k=seqlen_k, h=h, h_k=h_k, d=d, dv=dv, dtype=_DT[dtype],
-                is_causal=int(causal), is_local=int(local), num_splits=int(num_splits),
-                pack_gqa=-1 if pack_gqa is None else int(bool(pack_gqa)), num_sm=max(1, num_sm - sm_margin))
-    p = N.Plan()
-    N.check(N.lib().fa100_plan(C.byref(s), C.byref(p)))
+    """Sizes-only policy (num_splits, pack_gqa, #work items); the role of get_num_splits/get_pack_gqa.  A pure function of
+    its arguments, so results are cached (a decode loop asks the same question every step; measured host cost of a call:
+    profiles/r02_host_latency_*.json)."""
+    num_sm = max(1, _sm_count(device) - sm_margin)
+    key = (b, seqlen_q, seqlen_k, h, h_k, d, dv, dtype, bool(causal), bool(local), int(num_splits), pack_gqa, num_sm)
+    p = _PLAN_CACHE.get(key)
+    if p is None:
+        s = N.Shape(b=b, seqlen_q=seqlen_q, seqlen_k=seqlen_k, h=h, h_k=h_k, d=d, dv=dv, dtype=_DT[dtype],
+                    is_causal=int(causal), is_local=int(local), num_splits=int(num_splits),
+                    pack_gqa=-1 if pack_gqa is None else int(bool(pack_gqa)), num_sm=num_sm)
+        p = N.Plan()
+        N.check(N.lib().fa100_plan(C.byref(s), C.byref(p)))
+        if len(_PLAN_CACHE) > 4096:
+            _PLAN_CACHE.clear()
+        _PLAN_CACHE[key] = p
     return p
+
+
+class _on_device:
+    """torch.cuda.device(dev) only when dev is not already current (the context manager costs ~5 us of host time per call)."""
+
+    def __init__(self, dev):
+        self.ctx = None if dev.index is None or dev.index == torch.cuda.current_device() else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            return self.ctx.__exit__(*exc)
+        return False
 
 
 def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=None, cu_seqlens_k=None,
@@ -198,7 +235,7 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     p.num_splits, p.pack_gqa, p.num_sm = splits, pl.pack_gqa, pl.num_sm
     p.variant = _variant()
     p.merge_partial = int(_merge) if _partial is not None else 0
-    with torch.cuda.device(q.device):
+    with _on_device(q.device):
         if scheduler_metadata is not None and scheduler_metadata.numel() >= META_HEADER + _sched_words(b):
             # the schedule get_scheduler_metadata built ahead of time (CUDA-graphed decode): used as is
             _chk(int(scheduler_metadata.numel()) >= META_HEADER, "scheduler_metadata is too short")
@@ -208,6 +245,7 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
             meta = torch.empty(META_HEADER + _sched_words(b), dtype=torch.int32, device=q.device)
             N.check(N.lib().fa100_prepare_scheduler(C.byref(p), _ptr(meta), meta.numel(), _stream()))
             p.scheduler_metadata = _ptr(meta)
+            p.lse_accum_prefilled = int(lse_accum is not None and splits > 1 and p.merge_partial == 0)  # filled by that launch
         N.check(N.lib().fa100_fwd(C.byref(p), _stream()))
         if _partial is None and splits > 1:
             if varlen_q:  # (splits, h, total_q, dv) viewed as (splits, b=1, s=total_q, h, dv)
@@ -297,7 +335,7 @@ def _append_kv(q, k, v, k_new, v_new, cu_seqlens_q, cu_seqlens_k_new, seqused_q,
     new_lens = torch.empty(b, dtype=torch.int32, device=q.device)
     qs = (0, q_rot.stride(0), q_rot.stride(1)) if (q_rot is not None and varlen_q) else (
         (q_rot.stride(0), q_rot.stride(1), q_rot.stride(2)) if q_rot is not None else (0, 0, 0))
-    with torch.cuda.device(q.device):
+    with _on_device(q.device):
         N.check(N.lib().fa100_append_kv(C.byref(pa), _ptr(q_rot), qs[0], qs[1], qs[2], _ptr(new_lens), _stream()))
     return (q_rot if q_rot is not None else q), new_lens
 
@@ -337,7 +375,7 @@ def mha_combine(out_partial, lse_partial, out=None, out_dtype=None):
         _chk(tuple(out.shape) == (b, s, h, d) and out.dtype == out_dtype and out.stride(-1) == 1, "out has the wrong shape/dtype")
         out_p = out if d4 == d and all(st % 4 == 0 for st in out.stride()[:-1]) else torch.empty((b, s, h, d4), dtype=out_dtype, device=op.device)
     lse = torch.empty((b, h, s), dtype=torch.float32, device=op.device).transpose(1, 2)  # (b, s, h) view, s contiguous
-    with torch.cuda.device(op.device):
+    with _on_device(op.device):
         _combine_into(op, lse_partial, out_p, lse)
     if out is None:
         out = out_p[..., :d] if d4 != d else out_p
@@ -376,7 +414,7 @@ def mha_fwd_get_scheduler_metadata(batch_size, max_seqlen_q, max_seqlen_k, num_h
     p.is_causal, p.window_left, p.window_right, p.attention_chunk = int(is_causal), window_size_left, window_size_right, attention_chunk
     p.num_splits, p.pack_gqa, p.num_sm = pl.num_splits, pl.pack_gqa, pl.num_sm
     p.variant = _variant()
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         N.check(N.lib().fa100_prepare_scheduler(C.byref(p), _ptr(meta), meta.numel(), _stream()))
     return meta
 

@@ -142,7 +142,11 @@ typedef struct Fa100FwdParams {
    * combine arithmetic (LSE' = logaddexp, O' = e^(LSE-LSE') O + e^(LSE_t-LSE') O_t) and write it back in place;
    * 2 = the same, but write the merged result to o / lse (output dtype) instead.  0 = plain partial. */
   int32_t merge_partial;
-  int32_t reserved[6];
+  /* 1 = fa100_prepare_scheduler was called for THIS call with lse_accum set (it pre-fills the LSE partials with -inf, the
+   * "empty partial" marker, in the same launch that builds the schedule): fa100_fwd then skips its own fill launch.
+   * Leave 0 with a schedule built ahead of time (get_scheduler_metadata). */
+  int32_t lse_accum_prefilled;
+  int32_t reserved[5];
 } Fa100FwdParams;
 
 /* LSE-weighted merge of split partials (hopper/flash_fwd_combine_kernel.h:200-483,
