@@ -45,7 +45,22 @@ FA_DEVICE void mbar_init(uint64_t* bar, uint32_t count) {
 FA_DEVICE void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
 FA_DEVICE void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 
+// Jitter build (-DFA100_JITTER, libfa100_jitter.so; never the product library): a pseudo-random pause of 0 .. ~2 us in
+// front of every barrier wait and arrive of every role, so that the roles interleave differently in every key block.  The
+// parity and bitwise-repeat tests must still pass on it: a hand-off that only works by timing breaks (our stand-in for
+// compute-sanitizer racecheck, which is closed on this pool -- profiles/r02_sanitizer_closed_on_pool.log).
+#ifdef FA100_JITTER
+FA_DEVICE void fa_jitter() {
+  uint32_t x = uint32_t(clock()) * 2654435761u + (threadIdx.x >> 5) * 40503u + blockIdx.x * 9176u;
+  x ^= x >> 15; x *= 2246822519u; x ^= x >> 13;
+  if ((x & 3u) == 0u) __nanosleep((x >> 8) & 2047u);  // one time in four; warp-uniform enough: lanes of a warp read nearly the same clock
+}
+#else
+FA_DEVICE void fa_jitter() {}
+#endif
+
 FA_DEVICE void mbar_arrive(uint64_t* bar) {
+  fa_jitter();
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");
 }
 FA_DEVICE void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
@@ -93,6 +108,7 @@ FA_DEVICE uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
 // here are tensor-memory stores, already fenced by tcgen05.wait::st / fence::before_thread_sync.  A `.release.cluster`
 // arrive costs ~1100 clk per call (cluster-scope release = cache maintenance), measured in profiles/r01c_buckets_pair.log.
 FA_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {
+  fa_jitter();
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
 }
 // the pair's leader (even CTA) owns the barriers the MMA warps wait on: clearing the peer bit of a shared::cluster
@@ -193,6 +209,7 @@ FA_DEVICE void mbar_wait_slow(uint64_t* bar, uint32_t parity, int tag) {
 }
 
 FA_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
+  fa_jitter();
 #if defined(FA100_TRACE) && !defined(FA100_TRACE_NOEVENTS)
   const long long tb_ = clock64();
 #endif
@@ -261,6 +278,7 @@ FA_DEVICE void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync
 
 // tcgen05.commit: the mbarrier gets one arrival once all MMAs issued so far by this thread are done.
 FA_DEVICE void tc_commit(uint64_t* bar) {
+  fa_jitter();
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(smem_u32(bar)) : "memory");
 }
 
