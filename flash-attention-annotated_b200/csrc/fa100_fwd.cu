@@ -14,7 +14,7 @@ namespace fa100 {
 
 template <int HD, int ELT, bool FP8, bool F16, bool DUAL, bool PAIR = false>
 static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK,
-                           const CUtensorMap& tmV, const CUtensorMap& tmO, uint32_t fmt, int grid, cudaStream_t stream) {
+                           const CUtensorMap& tmV, const CUtensorMap& tmO, const CUtensorMap& tmQv, uint32_t fmt, int grid, cudaStream_t stream) {
   using L = FwdSmem<HD, ELT, PAIR>;
   auto kernel = fa100_fwd_kernel<HD, ELT, FP8, F16, DUAL, PAIR>;
   // the opt-in is per device (per context), not per process: one flag per device ordinal and kernel instance
@@ -29,7 +29,7 @@ static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, co
   }
   // PAIR: clusters of two CTAs (the pair shares every K / V tile, cta_group::2 MMAs; grid = 2 x pairs).  Always with PDL:
   // prologue and launch latency overlap the tail of the schedule / append-KV kernel in front (hopper/flash_fwd_launch_template.h:195-196)
-  FA_CUDA(launch_pdl(kernel, dim3(grid), dim3(kThreads), size_t(L::kTotalBytes), stream, PAIR ? 2 : 1, kp, tmQ, tmK, tmV, tmO, fmt));
+  FA_CUDA(launch_pdl(kernel, dim3(grid), dim3(kThreads), size_t(L::kTotalBytes), stream, PAIR ? 2 : 1, kp, tmQ, tmK, tmV, tmO, tmQv, fmt));
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
@@ -107,6 +107,7 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   kp.v_boxes = (p->dv * elt + 127) / 128;
   kp.qk_slices = (p->d * elt + 31) / 32;
   kp.pv_n = (p->dv + 15) / 16 * 16;
+  kp.qv_slices = p->qv ? (p->dv + 15) / 16 : 0;
   const bool dual = plan->dual_stream != 0;  // two partials per CTA-level split (make_geom<DUAL>)
   const int cta_splits = dual ? splits / 2 : splits;
   const bool solo = std::max(p->d, p->dv) > 128;  // one Q tile per work item (make_geom<.., SOLO>)
@@ -254,6 +255,12 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   if (fp8) FA_CHECK_ARG(p->d % 16 == 0 && p->dv % 16 == 0, "fp8 head dims must be multiples of 16");
   FA_UNSUPPORTED(p->d > 256 || p->dv > 256, "head dim > 256 is not supported (d=%d dv=%d)", p->d, p->dv);
   FA_UNSUPPORTED(p->k_new || p->v_new || p->rotary_cos, "append-KV / rotary handled by the caller-side kernel, not fa100_fwd");
+  if (p->qv) {  // hopper/flash_api.cpp:1028-1050
+    FA_CHECK_ARG(p->d <= 64, "q_v is only supported for head_size <= 64");
+    FA_CHECK_ARG(p->dv >= 256, "q_v is only supported for hdim_v >= 256.");
+    FA_CHECK_ARG(!fp8, "q_v is only supported for fp16 and bf16 data type");
+    FA_UNSUPPORTED(p->dv > 256, "q_v with hdim_v > 256 is not supported (hdim_v=%d)", p->dv);
+  }
   const bool varlen_q = p->cu_seqlens_q != nullptr;
   const bool varlen_k = p->cu_seqlens_k != nullptr;
   const bool paged = p->page_table != nullptr;
@@ -280,7 +287,7 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
 
   // ---- tensor maps
   const int cols_per_box = 128 / elt;
-  CUtensorMap tmQ, tmK, tmV;
+  CUtensorMap tmQ, tmK, tmV, tmQv;
   {
     const uint64_t heads3 = plan->pack_gqa ? p->h_k : p->h;
     uint64_t dims[5] = {uint64_t(p->d), uint64_t(kp.pack), uint64_t(rows_q), heads3, uint64_t(varlen_q ? 1 : p->b)};
@@ -289,6 +296,14 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
     uint32_t box[5] = {uint32_t(cols_per_box), uint32_t(kp.pack), uint32_t(kp.pos_per_tile), 1, 1};
     int rc = encode_tensor_map(&tmQ, p->dtype, 5, p->q, dims, str, box);
     if (rc) return rc;
+    tmQv = tmQ;
+    if (p->qv) {  // same rows / heads / packing as q, dv columns
+      uint64_t dimsv[5] = {uint64_t(p->dv), uint64_t(kp.pack), uint64_t(rows_q), heads3, uint64_t(varlen_q ? 1 : p->b)};
+      uint64_t strv[5] = {0, uint64_t(p->qv_head_stride) * elt, uint64_t(p->qv_row_stride) * elt,
+                          uint64_t(p->qv_head_stride) * kp.pack * elt, uint64_t(p->qv_batch_stride) * elt};
+      rc = encode_tensor_map(&tmQv, p->dtype, 5, p->qv, dimsv, strv, box);
+      if (rc) return rc;
+    }
   }
   {
     const uint64_t rows_k = paged ? uint64_t(p->page_size) : uint64_t(varlen_k ? p->total_k : p->seqlen_k);
@@ -340,9 +355,9 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   const int hd = solo ? 256 : ((p->d <= 64 && p->dv <= 64 && !fp8) ? 64 : 128);
   const bool f16 = p->dtype == FA100_FP16;
 #define FA_LAUNCH(HD_, ELT_, FP8_, F16_)                                                                      \
-  (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)                 \
-        : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream))
-  if (fp8 && hd == 256) return launch_instance<256, 1, true, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+  (dual ? launch_instance<HD_, ELT_, FP8_, F16_, true>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream)                 \
+        : launch_instance<HD_, ELT_, FP8_, F16_, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream))
+  if (fp8 && hd == 256) return launch_instance<256, 1, true, false, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);
   // opt-in (Fa100FwdParams.variant & FA100_VARIANT_FOUR_ROLE): the four-role prefill mainloop of fa100_fwd2.cuh for two Q tiles
   // per work item, head dims <= 128, one CTA per item
   if (!dual && !solo && !pair && (p->variant & FA100_VARIANT_FOUR_ROLE)) {
@@ -354,12 +369,12 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   }
   if (fp8) return FA_LAUNCH(128, 1, true, false);
   if (hd == 256)
-    return f16 ? launch_instance<256, 2, false, true, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
-               : launch_instance<256, 2, false, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+    return f16 ? launch_instance<256, 2, false, true, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream)
+               : launch_instance<256, 2, false, false, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);
   if (hd == 64) return f16 ? FA_LAUNCH(64, 2, false, true) : FA_LAUNCH(64, 2, false, false);
   if (pair)
-    return f16 ? launch_instance<128, 2, false, true, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
-               : launch_instance<128, 2, false, false, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+    return f16 ? launch_instance<128, 2, false, true, false, true>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream)
+               : launch_instance<128, 2, false, false, false, true>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);
   return f16 ? FA_LAUNCH(128, 2, false, true) : FA_LAUNCH(128, 2, false, false);
 #undef FA_LAUNCH
 }

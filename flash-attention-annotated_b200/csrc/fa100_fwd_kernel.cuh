@@ -73,6 +73,7 @@ struct FwdKernelParams {
   int32_t v_boxes;        // same for V: ceil(dv * elt / 128)
   int32_t qk_slices;      // MMA k-slices of S = Q K^T actually issued: ceil(d / (32 / elt))
   int32_t pv_n;           // N of O += P V: dv rounded up to 16
+  int32_t qv_slices;      // qv (hdim-256 instance only): MMA k-slices of the extra score term Qv V^T = ceil(dv / 16); 0 = off
   int32_t qheads_per_kv;  // G
   int32_t pack;           // Gp: G when pack_gqa else 1
   int32_t pos_per_tile;   // 128 / Gp query positions per Q tile

@@ -84,7 +84,7 @@ template <int STAGES> FA_DEVICE void ring_advance(RingState& r) { if (++r.stage 
 // registers); one elected lane issues the bulk copies.
 template <int HD, int ELT, bool DUAL, bool PAIR = false, typename Bar = FwdBarriers>
 FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, const CUtensorMap* tmK,
-                             const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, Bar* bar, int rank = 0) {
+                             const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, Bar* bar, int rank = 0, const CUtensorMap* tmQv = nullptr) {
   using L = FwdSmem<HD, ELT, PAIR>;
   constexpr int kRowBytes = 128;                       // 128B-swizzled rows
   constexpr int kColsPerBox = kRowBytes / ELT;         // 64 (16-bit) or 128 (8-bit)
@@ -97,7 +97,10 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   RingState rings[2];
   uint32_t q_it[kQTiles] = {0, 0};
   // only the boxes that hold real head-dim columns are loaded (d = 192 in the 256 instance: 3 of 4)
-  const uint32_t q_tx = uint32_t(p.qk_boxes * kRowBytes) * p.pack * p.pos_per_tile;
+  // qv (hdim-256 instance, d <= 64): the Q slot holds the Qv tile (dv columns) and the Q tile moves into box 1 of the K
+  // stage, which K tiles of d <= 64 never touch (they fill box 0 only); see mma_role
+  const bool with_qv = HD > 128 && p.qv_slices > 0;
+  const uint32_t q_tx = uint32_t((p.qk_boxes + (with_qv ? p.v_boxes : 0)) * kRowBytes) * p.pack * p.pos_per_tile;
   const int n_work = total_work(p);
   for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
     const WorkGeom g = make_geom<DUAL, (HD > 128), PAIR>(p, w, rank);
@@ -110,6 +113,12 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
       if (elect_one()) {
         // PAIR: both CTAs' Q tiles are counted on the leader's barrier; the leader announces the bytes of both
         if (!PAIR || rank == 0) mbar_arrive_expect_tx(&bar->q_full[t], PAIR ? 2 * q_tx : q_tx);
+        if (with_qv) {
+          tma_load_5d(sKV + kHalfBytes, tmQ, &bar->q_full[t], 0, 0, g.seq.q_off + pos0, g.it.head, g.seq.bq);
+#pragma unroll
+          for (int hb = 0; hb < kBoxesD; ++hb)
+            if (hb < p.v_boxes) tma_load_5d(sQ + hb * kHalfBytes, tmQv, &bar->q_full[t], hb * kColsPerBox, 0, g.seq.q_off + pos0, g.it.head, g.seq.bq);
+        } else
 #pragma unroll
         for (int hb = 0; hb < kBoxesD; ++hb)
           if (hb < p.qk_boxes) {
@@ -225,6 +234,8 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   // warps wait on their own copies)
   auto commit = [&](uint64_t* b) { if (PAIR) tc_commit_2sm(b); else tc_commit(b); };
   RingState ring;
+  RingState ring_v_qk;  // qv: the QK warp also reads the V stages (score term Qv V^T); it only waits for them, the PV warp releases
+  const bool with_qv = kIsQK && HD > 128 && p.qv_slices > 0;
   uint32_t q_it[kQTiles] = {0, 0}, p_it[kQTiles] = {0, 0}, o_it[kQTiles] = {0, 0};
   uint32_t qk_n = 0;  // QK batches issued so far == phases of s_free consumed + 1
   FA_PROF_DECL();     // 0 kv_full waits, 1 s_free waits, 2 p_full / o_empty waits, 3 issue, 4 everything else
@@ -233,10 +244,19 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   auto qk_op = [&](int t, int stage, bool last_use_of_q) {
     if (qk_n > 0) mbar_wait(&bar->s_free, (qk_n - 1) & 1, 0x48 + t);
     ++qk_n;
+    int v_stage = 0;
+    if (HD > 128 && with_qv) {
+      // V(nb) must have landed before its K-major reading below; QK(nb) completes before softmax(nb), hence before the
+      // PV(nb) whose commit releases the stage, so no release is needed here
+      v_stage = L::kStages / 2 + ring_v_qk.stage;
+      mbar_wait(&bar->kv_full[v_stage], ring_v_qk.phase, 0x43);
+      ring_advance<L::kStages / 2>(ring_v_qk);
+    }
     tc_fence_after();
     FA_PROF(1);
     if (elect_one()) {
-      const uint32_t a_lo = q_lo + t * (L::kQBytes >> 4);
+      // qv: the Q tile sits in box 1 of the (single) K stage, the Q slot holds Qv
+      const uint32_t a_lo = (HD > 128 && with_qv) ? (((smem_u32(sKV) + kHalfBytes) >> 4) | kLboK) : q_lo + t * (L::kQBytes >> 4);
       const uint32_t b_lo = (kv_lo + stage * (L::kKVBytes >> 4)) | kLboK;
 #pragma unroll
       for (int ks = 0; ks < kQKSlices; ++ks) {
@@ -246,6 +266,16 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
         if (ks < p.qk_slices) {
           if (PAIR) mma_ss_2sm(tmem, a_lo + off, b_lo + off_b, kHi, idesc, ks > 0);
           else mma_ss<FP8>(tmem, a_lo + off, b_lo + off, kHi, idesc, ks > 0);
+        }
+      }
+      if (HD > 128 && with_qv) {
+        // S += Qv V^T: A = the Qv tile (Q slot), B = the V tile read K-major (rows = keys, 64 dv columns per box: the layout of
+        // a K tile of head dim dv), contraction over dv
+        const uint32_t v_lo = (kv_lo + v_stage * (L::kKVBytes >> 4)) | kLboK;
+#pragma unroll
+        for (int ks = 0; ks < kQKSlices; ++ks) {
+          const uint32_t off = (ks / kSlicesPerBox) * (kHalfBytes >> 4) + (ks % kSlicesPerBox) * 2;
+          if (ks < p.qv_slices) mma_ss<FP8>(tmem, q_lo + off, v_lo + off, kHi, idesc, 1u);
         }
       }
       commit(&bar->s_full[t]);

@@ -418,7 +418,7 @@ template <int HD, int ELT, bool FP8, bool F16, bool DUAL, bool PAIR = false>
 __global__ void __launch_bounds__(kThreads, 1)
 fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constant__ CUtensorMap tmQ,
                  const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-                 const __grid_constant__ CUtensorMap tmO, uint32_t fmt) {
+                 const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmQv, uint32_t fmt) {
   using L = FwdSmem<HD, ELT, PAIR>;
   extern __shared__ __align__(1024) uint8_t smem[];  // 128-byte swizzle atoms need 1 KB alignment
   uint8_t* sQ = smem;
@@ -474,7 +474,7 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
       if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL, true, PAIR>(p, fmt, sQ, sKV, bar, tmem);
       if (warp == kPvWarp) mma_role<HD, ELT, FP8, DUAL, false, PAIR>(p, fmt, sQ, sKV, bar, tmem);
     }
-    if (warp == kLoadWarp) producer_role<HD, ELT, DUAL, PAIR>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar, rank);
+    if (warp == kLoadWarp) producer_role<HD, ELT, DUAL, PAIR>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar, rank, &tmQv);
   }
   FA_TRACE_END();
   tc_fence_before();

@@ -42,6 +42,7 @@ class FwdParams(C.Structure):
         + [(n, i32) for n in ("is_causal", "window_left", "window_right", "attention_chunk")]
         + [(n, i32) for n in ("num_splits", "pack_gqa", "num_sm")]
         + [("scheduler_metadata", vp), ("variant", i32), ("merge_partial", i32), ("lse_accum_prefilled", i32), ("reserved", i32 * 5)]
+        + [("qv", vp), ("qv_batch_stride", i64), ("qv_row_stride", i64), ("qv_head_stride", i64)]
     )
 
 
@@ -111,7 +112,7 @@ def lib() -> C.CDLL:
         for n in ("fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_prepare_scheduler", "fa100_debug_hang_info",
            "fa100_debug_trace", "fa100_debug_prof"):
             getattr(l, n).restype = C.c_int
-        if l.fa100_abi_version() != 1:
+        if l.fa100_abi_version() != 2:
             raise RuntimeError("libfa100.so ABI version mismatch")
         _lib = l
     return _lib

@@ -101,8 +101,6 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     _chk(qt in (torch.bfloat16, torch.float16, torch.float8_e4m3fn), "FlashAttention only supports fp16, bf16, and fp8_e4m3 data type")
     _chk(k.dtype == qt and v.dtype == qt, "query, key and value must have the same dtype")
     _chk(q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Input tensor must have contiguous last dimension")
-    if q_v is not None:
-        raise NotImplementedError("fa100: qv (MLA-style absorbed heads) is not built yet")
     paged = page_table is not None
     varlen_q = cu_seqlens_q is not None
     varlen_k = cu_seqlens_k is not None
@@ -143,6 +141,15 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
             _i32(t, nm, b)
     if leftpad_k is not None:
         _chk(not paged, "leftpad_k is not supported with paged KV")
+    if q_v is not None:  # hopper/flash_api.cpp:1028-1050
+        _chk(d <= 64, "q_v is only supported for head_size <= 64")
+        _chk(dv >= 256, "q_v is only supported for hdim_v >= 256.")
+        _chk(qt in (torch.float16, torch.bfloat16), "q_v is only supported for fp16 and bf16 data type")
+        _chk(q_v.dtype == qt, "q_v must have the same dtype as query")
+        _chk(q_v.is_cuda and q_v.stride(-1) == 1, "q_v tensor must have contiguous last dimension")
+        _chk(tuple(q_v.shape) == ((total_q, h, dv) if varlen_q else (b, seqlen_q, h, dv)), "q_v has the wrong shape")
+        if dv > 256:
+            raise NotImplementedError("fa100: q_v with hdim_v > 256 is not supported")
     align = 16 if qt == torch.float8_e4m3fn else 8
     _chk(d % align == 0 and dv % align == 0, f"head dims must be multiples of {align} for {qt}")
     if rotary_cos is not None:
@@ -215,6 +222,10 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     else:
         p.k_batch_stride, p.k_row_stride, p.k_head_stride = k.stride(0), k.stride(1), k.stride(2)
         p.v_batch_stride, p.v_row_stride, p.v_head_stride = v.stride(0), v.stride(1), v.stride(2)
+    if q_v is not None:
+        p.qv = _ptr(q_v)
+        p.qv_batch_stride, p.qv_row_stride, p.qv_head_stride = ((0, q_v.stride(0), q_v.stride(1)) if varlen_q else
+                                                                (q_v.stride(0), q_v.stride(1), q_v.stride(2)))
     p.o_accum, p.lse_accum = _ptr(out_accum), _ptr(lse_accum)
     p.b, p.b_k, p.seqlen_q, p.seqlen_k, p.total_q, p.total_k = b, b_k, seqlen_q, seqlen_k, total_q, total_k
     p.h, p.h_k, p.d, p.dv, p.dtype = h, h_k, d, dv, _DT[qt]

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define FA100_ABI_VERSION 1
+#define FA100_ABI_VERSION 2  /* 2: Fa100FwdParams grew the qv fields at its end */
 
 enum {
   FA100_OK = 0,
@@ -147,6 +147,11 @@ typedef struct Fa100FwdParams {
    * Leave 0 with a schedule built ahead of time (get_scheduler_metadata). */
   int32_t lse_accum_prefilled;
   int32_t reserved[5];
+  /* ABI version 2.  qv (hopper/flash_api.cpp:1028-1050, params.qv_ptr): a second query tensor (b, sq, h, dv) or packed
+   * (total_q, h, dv), same dtype and layout rules as q; the scores become (q k^T + qv v^T) * softmax_scale.  Like the
+   * reference: 16-bit dtypes, d <= 64, dv >= 256 (this library: dv == 256).  Null = off. */
+  const void* qv;
+  int64_t qv_batch_stride, qv_row_stride, qv_head_stride;
 } Fa100FwdParams;
 
 /* LSE-weighted merge of split partials (hopper/flash_fwd_combine_kernel.h:200-483,

@@ -122,6 +122,7 @@ def attention_oracle(
     upcast: bool = True,
     reorder_ops: bool = False,
     intermediate_dtype: Optional[torch.dtype] = None,
+    qv: Optional[torch.Tensor] = None,  # (b, sq, h, dv): scores += qv v^T (hopper/test_util.py:287-293)
 ) -> Tuple[torch.Tensor, torch.Tensor]:
     """Returns ``(out (b,sq,h,dv) in q's dtype, lse (b,h,sq) fp32)``.
 
@@ -137,19 +138,24 @@ def attention_oracle(
     g = h // hk
     if upcast:
         q, k, v = q.float(), k.float(), v.float()
+        qv = qv.float() if qv is not None else None
     if q_descale is not None:
         q = (q.float() * q_descale.repeat_interleave(g, dim=1).view(b, 1, h, 1)).to(q.dtype)
+        qv = (qv.float() * q_descale.repeat_interleave(g, dim=1).view(b, 1, h, 1)).to(qv.dtype) if qv is not None else None
     if k_descale is not None:
         k = (k.float() * k_descale.view(b, 1, hk, 1)).to(k.dtype)
     if v_descale is not None:
         v = (v.float() * v_descale.view(b, 1, hk, 1)).to(v.dtype)
     k = k.repeat_interleave(g, dim=2)
     v = v.repeat_interleave(g, dim=2)
-    scale = 1.0 / math.sqrt(d) if softmax_scale is None else softmax_scale
+    # default scale with qv: 1 / sqrt(d + dv) (hopper/test_util.py:287)
+    scale = 1.0 / math.sqrt(d if qv is None else d + v.shape[-1]) if softmax_scale is None else softmax_scale
     if reorder_ops:
         s = torch.einsum("bthd,bshd->bhts", q, k * scale)
     else:
         s = torch.einsum("bthd,bshd->bhts", q * scale, k)
+    if qv is not None:
+        s = s + torch.einsum("bthd,bshd->bhts", qv * scale, v)
     if softcap > 0:
         s = torch.tanh(s / softcap) * softcap
     kmask = _padding_mask(k_lens, sk, b, key_leftpad)

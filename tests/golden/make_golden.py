@@ -38,6 +38,9 @@ CASES = [
     ("fp8_descale", (2, 32, 48, 4, 2, 64, 64), torch.bfloat16,
      dict(causal=True, _descale=True, upcast=False, reorder_ops=True, intermediate_dtype=torch.float8_e4m3fn)),
     ("fp8_descale_fp32", (2, 32, 48, 4, 2, 64, 64), torch.bfloat16, dict(causal=True, _descale=True)),
+    # qv (scores += qv v^T, default scale 1/sqrt(d + dv)): appended after the round-1 cases so their seeds do not move
+    ("qv_causal_gqa", (2, 24, 40, 4, 2, 64, 256), torch.bfloat16, dict(causal=True, _qv=True)),
+    ("qv_lowprec", (1, 16, 33, 2, 1, 64, 256), torch.bfloat16, dict(_qv=True, upcast=False, reorder_ops=True)),
 ]
 
 
@@ -50,6 +53,9 @@ def main():
         v = torch.randn(b, sk, hk, dv, generator=g).to(dtype)
         kw = dict(kw)
         rec = dict(q=q, k=k, v=v, dtype=str(dtype))
+        if kw.pop("_qv", False):
+            kw["qv"] = torch.randn(b, sq, h, dv, generator=g).to(dtype)
+            rec["qv"] = kw["qv"]
         if kw.pop("_descale", False):
             q = q.to(torch.float8_e4m3fn).to(dtype)
             k = k.to(torch.float8_e4m3fn).to(dtype)

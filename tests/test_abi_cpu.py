@@ -29,7 +29,7 @@ def test_exports_match_header(native):
     lib = native.lib()
     for name in declared:
         assert getattr(lib, name) is not None
-    assert lib.fa100_abi_version() == 1
+    assert lib.fa100_abi_version() == 2  # 2: Fa100FwdParams grew the qv fields
 
 
 def test_struct_sizes_match_c(native, tmp_path):

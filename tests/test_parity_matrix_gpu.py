@@ -490,3 +490,71 @@ def test_scheduler_metadata_mismatch_is_clamped_on_device():
         ref, lse_ref = A.attention_oracle(q, kc, vc, k_lens=lens)
         low, _ = A.attention_oracle(q, kc, vc, k_lens=lens, upcast=False, reorder_ops=True)
         _check(out, lse, ref, low, lse_ref)
+
+
+# ----------------------------------------------------------------------------- qv
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("mha_type", ["mha", "mqa", "gqa"])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("sq,sk", [(1, 1), (1, 1024), (3, 799), (64, 128), (128, 128), (113, 203), (300, 411), (1023, 1024)])
+def test_qv(sq, sk, causal, mha_type, dtype):
+    """qv: scores = (q k^T + qv v^T) * softmax_scale with d = 64, d_v = 256 and the default scale 1/sqrt(d + d_v)
+    (hopper/flash_api.cpp:1028-1050, mainloop_fwd_sm90_tma_gmma_ws.hpp:1144-1148; the reference tests it with d = 64,
+    d_v in {256, 512}: hopper/test_flash_attn.py:116-127).  Here V is read twice from its shared-memory stage: K-major for
+    the score term, MN-major for P V."""
+    F = _iface()
+    h = 6
+    hk = {"mha": 6, "mqa": 1, "gqa": 2}[mha_type]
+    g = torch.Generator().manual_seed(71)
+    mk = lambda *s: torch.randn(*s, generator=g).to(dtype)  # noqa: E731
+    q, k, v, qv = mk(2, sq, h, 64), mk(2, sk, hk, 64), mk(2, sk, hk, 256), mk(2, sq, h, 256)
+    ref, lse_ref = A.attention_oracle(q, k, v, qv=qv, causal=causal)
+    low, _ = A.attention_oracle(q, k, v, qv=qv, causal=causal, upcast=False, reorder_ops=True)
+    for pack_gqa, num_splits in ((False, 1), (True, 1), (None, 3)):
+        out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), qv=qv.to(DEV), causal=causal, pack_gqa=pack_gqa, num_splits=num_splits,
+                                     return_attn_probs=True)
+        _check(out, lse, ref, low, lse_ref)
+
+
+def test_qv_varlen_and_paged_decode():
+    """qv through the varlen entry point and through the paged KV cache with MLA-like head counts (16 query heads on one
+    KV head, packed into the M dimension)."""
+    F = _iface()
+    g = torch.Generator().manual_seed(72)
+    dt = torch.bfloat16
+    lens_q, lens_k = [5, 200, 131], [64, 333, 131]
+    cq = torch.tensor([0] + torch.tensor(lens_q).cumsum(0).tolist(), dtype=torch.int32)
+    ck = torch.tensor([0] + torch.tensor(lens_k).cumsum(0).tolist(), dtype=torch.int32)
+    h, hk = 4, 2
+    q, qv = torch.randn(int(cq[-1]), h, 64, generator=g).to(dt), torch.randn(int(cq[-1]), h, 256, generator=g).to(dt)
+    k, v = torch.randn(int(ck[-1]), hk, 64, generator=g).to(dt), torch.randn(int(ck[-1]), hk, 256, generator=g).to(dt)
+    out, lse = F.flash_attn_varlen_func(q.to(DEV), k.to(DEV), v.to(DEV), cq.to(DEV), ck.to(DEV), max(lens_q), max(lens_k), qv=qv.to(DEV),
+                                        causal=True, return_attn_probs=True)
+    for i in range(3):
+        qs, ks = slice(int(cq[i]), int(cq[i + 1])), slice(int(ck[i]), int(ck[i + 1]))
+        ref, lse_ref = A.attention_oracle(q[qs][None], k[ks][None], v[ks][None], qv=qv[qs][None], causal=True)
+        low, _ = A.attention_oracle(q[qs][None], k[ks][None], v[ks][None], qv=qv[qs][None], causal=True, upcast=False, reorder_ops=True)
+        _check(out[qs][None], lse[:, qs][None], ref, low, lse_ref)
+    # decode: b 3, 16 query heads / 1 KV head, paged cache, ragged lengths, library-chosen and forced splits
+    b, h, hk, ps, cap = 3, 16, 1, 64, 1024
+    q, qv = torch.randn(b, 1, h, 64, generator=g).to(dt), torch.randn(b, 1, h, 256, generator=g).to(dt)
+    kd, vd, table, kp, vp = A.paged_kvcache(cap, ps, b, hk, 64, 256, dt, generator=g)
+    lens = torch.tensor([1024, 517, 1], dtype=torch.int32)
+    ref, lse_ref = A.attention_oracle(q, kd, vd, qv=qv, k_lens=lens)
+    low, _ = A.attention_oracle(q, kd, vd, qv=qv, k_lens=lens, upcast=False, reorder_ops=True)
+    for num_splits in (0, 1, 4):
+        out, lse, *_ = F.flash_attn_with_kvcache(q.to(DEV), kp.to(DEV), vp.to(DEV), qv=qv.to(DEV), cache_seqlens=lens.to(DEV),
+                                                 page_table=table.to(DEV), num_splits=num_splits, return_softmax_lse=True)
+        _check(out, lse, ref, low, lse_ref)
+
+
+def test_qv_rules():
+    """The reference's argument rules for qv (hopper/flash_api.cpp:1028-1050) raise the same way."""
+    F = _iface()
+    mk = lambda *s, dt=torch.bfloat16: torch.zeros(*s, dtype=dt, device=DEV)  # noqa: E731
+    with pytest.raises(RuntimeError, match="head_size <= 64"):
+        F.flash_attn_func(mk(1, 8, 2, 128), mk(1, 8, 2, 128), mk(1, 8, 2, 256), qv=mk(1, 8, 2, 256))
+    with pytest.raises(RuntimeError, match="hdim_v >= 256"):
+        F.flash_attn_func(mk(1, 8, 2, 64), mk(1, 8, 2, 64), mk(1, 8, 2, 128), qv=mk(1, 8, 2, 128))
+    with pytest.raises(RuntimeError, match="wrong shape"):
+        F.flash_attn_func(mk(1, 8, 2, 64), mk(1, 8, 2, 64), mk(1, 8, 2, 256), qv=mk(1, 9, 2, 256))
