@@ -31,3 +31,16 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+# The FA2-style public signatures (names, order, defaults) of /root/reference/flash_attn/flash_attn_interface.py are stored
+# the same way (ast, because that module imports its CUDA extension at import time) in tests/golden/fa2_signatures.json:
+#   python - <<'PY'
+#   import ast, json
+#   out = {}
+#   for n in ast.parse(open('/root/reference/flash_attn/flash_attn_interface.py').read()).body:
+#       if isinstance(n, ast.FunctionDef) and n.name.startswith('flash_attn'):
+#           a = n.args; names = [x.arg for x in a.args]; d = [ast.unparse(x) for x in a.defaults]
+#           out[n.name] = [[x, y] for x, y in zip(names, [None] * (len(names) - len(d)) + d)]
+#   json.dump(out, open('tests/golden/fa2_signatures.json', 'w'), indent=1)
+#   PY

@@ -152,3 +152,23 @@ def test_meta_kernels_trace_shapes():
     lp = torch.empty(5, 2, 100, 4, device="meta")
     o, l = torch.ops.flash_attn_3.fwd_combine(op, lp, None, torch.bfloat16)
     assert o.shape == (2, 100, 4, 64) and o.dtype == torch.bfloat16 and l.shape == (2, 100, 4)
+
+
+def test_fa2_compat_signatures_match_reference():
+    """Names, order and defaults of the FA2-style entry points (compat/flash_attn/flash_attn_interface.py) equal the
+    reference's flash_attn/flash_attn_interface.py:1003-1590 (tests/golden/fa2_signatures.json, extracted with ast)."""
+    import ast
+    import json
+
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fa2_signatures.json")))
+    src = open(os.path.join(ROOT, "flash-attention-annotated_b200", "compat", "flash_attn", "flash_attn_interface.py")).read()
+    mine = {}
+    for n in ast.parse(src).body:
+        if isinstance(n, ast.FunctionDef) and n.name.startswith("flash_attn"):
+            a = n.args
+            names = [x.arg for x in a.args]
+            d = [ast.unparse(x) for x in a.defaults]
+            mine[n.name] = [[x, y] for x, y in zip(names, [None] * (len(names) - len(d)) + d)]
+    assert set(mine) == set(gold)
+    for name in gold:
+        assert mine[name] == gold[name], name
