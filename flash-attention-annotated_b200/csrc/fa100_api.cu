@@ -49,6 +49,11 @@ int encode_tensor_map(CUtensorMap* out, int dtype, int rank, const void* base, c
                       const uint64_t* strides_bytes, const uint32_t* box) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return set_error(FA100_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  // cuTensorMapEncodeTiled is a driver-API call: it needs the device's primary context current in THIS thread.  A thread that
+  // has only inherited the device ordinal (e.g. torch's autograd engine threads, which run the backward) may not have it
+  // bound yet (CUDA_ERROR_INVALID_CONTEXT); one runtime call binds it.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) { FA_CUDA(cudaFree(nullptr)); ctx_bound = true; }
   CUtensorMapDataType dt = dtype == FA100_BF16   ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                            : dtype == FA100_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
                                                  : CU_TENSOR_MAP_DATA_TYPE_UINT8;

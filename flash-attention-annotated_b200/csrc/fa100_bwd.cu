@@ -1,0 +1,487 @@
+// fa100_bwd.cu -- backward pass of the attention forward, first version.
+//
+// Role of hopper/flash_bwd_launch_template.h + mainloop_bwd_sm90_tma_gmma_ws.hpp + flash_bwd_preprocess_kernel.h (and of
+// flash_attn/cute/flash_bwd_sm100.py) re-designed around tensor memory, with the same math:
+//   D_i  = sum_j dO_ij O_ij                      (preprocess; "softmax_d")
+//   P    = exp(S * scale - LSE),  S = Q K^T       (recomputed, never stored)
+//   dP   = dO V^T,   dS = P o (dP - D)
+//   dV   = P^T dO,   dK = scale * dS^T Q,   dQ = scale * dS K
+// Three launches, no atomics, bitwise deterministic:
+//   fa100_bwd_dot_kernel     one warp per query row: D
+//   fa100_bwd_dq_kernel      one CTA per (128-row query block, head, batch) walks the key blocks: S and dP in TMEM (fp32), one
+//                            thread per query row turns them into dS (16 bit, written over S's columns), dQ += dS K with dS as
+//                            the TMEM A operand -- the forward's P V form
+//   fa100_bwd_dkdv_kernel    one CTA per (128-key block, KV head, batch) walks the query blocks of every query head of the
+//                            group: S^T = K Q^T and dP^T = V dO^T (keys on the TMEM lanes), one thread per key row makes P^T
+//                            and dS^T, dV += P^T dO and dK += dS^T Q, again in the forward's P V form; the GQA sum over the
+//                            group's heads happens in the accumulators
+// Recomputing S and dP in both kernels costs 7 instead of 5 MMAs per (query block, key block) pair and buys: no dQ atomics,
+// no transposes, only operand forms the forward kernel already uses (SS K-major x K-major, TS with an MN-major B).
+// Simple CTAs (128 threads, one issuing thread, two-stage TMA prefetch); the tensor pipe and the elementwise work of a step
+// are serialised -- this is the functional first version, not the tuned one.
+#include "fa100_host.h"
+#include "fa100_ptx.cuh"
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+
+namespace fa100 {
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr int kBwdThreads = 128;
+constexpr int kBwdTile = 128;                 // query rows / keys per tile
+constexpr int kBwdTileBytes = 128 * 128 * 2;  // one [128][128] 16-bit tile (two 64-column boxes)
+constexpr int kBwdBoxBytes = 128 * 128;       // one [128 rows][128 B] box
+
+struct BwdKernelParams {
+  void* dq; void* dk; void* dv;
+  const float* lse; const float* dsum;  // (b, h, seqlen_q) and (b, h, seqlen_q_rounded)
+  int64_t dq_batch_stride, dq_row_stride, dq_head_stride;
+  int64_t dk_batch_stride, dk_row_stride, dk_head_stride;
+  int64_t dv_batch_stride, dv_row_stride, dv_head_stride;
+  int32_t b, h, h_k, seqlen_q, seqlen_k, seqlen_q_rounded, d;
+  int32_t boxes;       // 64-column boxes per tile actually loaded: ceil(d / 64)
+  int32_t slices;      // MMA k-slices over the head dim: ceil(d / 16)
+  int32_t n16;         // d rounded up to 16: N of the products whose result has d columns
+  int32_t is_causal, f16;
+  float scale, scale_log2;
+};
+
+struct BwdBarriers {
+  uint64_t fixed_full;        // the tile(s) loaded once per CTA
+  uint64_t full[2], empty[2]; // the two-stage ring of streamed tiles
+  uint64_t mma_s, mma_done;   // S / dP ready; accumulators final
+  uint32_t tmem_base;
+  uint32_t pad_[3];
+};
+
+FA_DEVICE uint32_t bwd_pack(float a, float b, bool f16) {
+  if (f16) { __half2 v = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&v); }
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// ----------------------------------------------------------------------------- preprocess: D = rowsum(dO o O)
+template <typename T>
+__global__ void __launch_bounds__(256) fa100_bwd_dot_kernel(const T* __restrict__ dout, const T* __restrict__ out, float* __restrict__ dsum,
+                                                            int64_t do_b, int64_t do_r, int64_t do_h, int64_t o_b, int64_t o_r, int64_t o_h,
+                                                            int b, int h, int sq, int sq_rounded, int d) {
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+  const int lane = threadIdx.x & 31;
+  const int64_t rows = int64_t(b) * h * sq_rounded;
+  for (int64_t r = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; r < rows; r += (int64_t(gridDim.x) * blockDim.x) >> 5) {
+    const int i = int(r % sq_rounded), hh = int((r / sq_rounded) % h), bb = int(r / (int64_t(sq_rounded) * h));
+    float acc = 0.f;
+    if (i < sq) {
+      const T* pd = dout + bb * do_b + int64_t(i) * do_r + hh * do_h;
+      const T* po = out + bb * o_b + int64_t(i) * o_r + hh * o_h;
+      for (int c = lane; c < d; c += 32) acc += float(pd[c]) * float(po[c]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) dsum[r] = acc;  // rows past seqlen_q read as 0
+  }
+}
+
+// one [128 rows][d] tile = `boxes` TMA boxes of 64 columns; rows / columns past the tensor come back as zeros
+FA_DEVICE void bwd_load_tile(uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int boxes, int row0, int head, int batch) {
+  for (int hb = 0; hb < boxes; ++hb) tma_load_4d(dst + hb * kBwdBoxBytes, tm, bar, hb * 64, row0, head, batch);
+}
+
+// ----------------------------------------------------------------------------- dQ
+// TMEM: S @0 (128 fp32 columns; dS, 16 bit, is written over its columns [0, 64)), dP @128, dQ @256.
+__global__ void __launch_bounds__(kBwdThreads, 1)
+fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
+                    const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sQ = smem;                          // Q tile
+  uint8_t* sdO = smem + kBwdTileBytes;         // dO tile
+  uint8_t* sK = smem + 2 * kBwdTileBytes;      // K stages 0, 1
+  uint8_t* sV = smem + 4 * kBwdTileBytes;      // V stages 0, 1
+  BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 6 * kBwdTileBytes);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int m_blk = blockIdx.x, hq = blockIdx.y, bi = blockIdx.z;
+  const int hk = hq / (p.h / p.h_k);
+  if (tid == 0) {
+    mbar_init(&bar->fixed_full, 1); mbar_init(&bar->mma_s, 1); mbar_init(&bar->mma_done, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
+    fence_mbar_init();
+  }
+  if (warp == 0) { tmem_alloc(&bar->tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int row0 = m_blk * kBwdTile;
+  const int shift = p.seqlen_k - p.seqlen_q;
+  int n_blocks = (p.seqlen_k + kBwdTile - 1) / kBwdTile;
+  if (p.is_causal) n_blocks = min(n_blocks, max(0, (min(row0 + kBwdTile, p.seqlen_q) + shift + kBwdTile - 1) / kBwdTile));
+  const uint32_t tile_tx = uint32_t(p.boxes) * kBwdBoxBytes;
+
+  const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);   // S = Q K^T, dP = dO V^T
+  const uint32_t idesc_dq = make_idesc(fmt, fmt, kBwdTile, p.n16, 0, 1);     // dQ += dS K (B = K tile, MN-major)
+  constexpr uint32_t kHi = sdesc_hi(1024);
+  constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboMN = sdesc_lo_lbo(kBwdBoxBytes);
+
+  if (tid == 0 && n_blocks > 0) {
+    mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
+    bwd_load_tile(sQ, &tmQ, &bar->fixed_full, p.boxes, row0, hq, bi);
+    bwd_load_tile(sdO, &tmdO, &bar->fixed_full, p.boxes, row0, hq, bi);
+    mbar_arrive_expect_tx(&bar->full[0], 2 * tile_tx);
+    bwd_load_tile(sK, &tmK, &bar->full[0], p.boxes, 0, hk, bi);
+    bwd_load_tile(sV, &tmV, &bar->full[0], p.boxes, 0, hk, bi);
+  }
+  // this thread's query row
+  const int i = row0 + tid;
+  const bool row_ok = i < p.seqlen_q;
+  float lse2 = INFINITY, dsum = 0.f;  // rows past the end and rows without keys (LSE = -inf) get P = 0
+  if (row_ok) {
+    const float l = p.lse[(int64_t(bi) * p.h + hq) * p.seqlen_q + i];
+    lse2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
+    dsum = p.dsum[(int64_t(bi) * p.h + hq) * p.seqlen_q_rounded + i];
+  }
+  const int col_hi = p.is_causal ? min(p.seqlen_k, i + 1 + shift) : p.seqlen_k;
+  const uint32_t tRow = tmem + (uint32_t(warp * 32) << 16);
+
+  if (n_blocks > 0) mbar_wait(&bar->fixed_full, 0, 0xB0);
+  for (int nb = 0; nb < n_blocks; ++nb) {
+    const int st = nb & 1;
+    if (tid == 0 && nb + 1 < n_blocks) {  // prefetch the next K / V tiles into the other stage
+      const int s2 = st ^ 1;
+      if (nb + 1 >= 2) mbar_wait(&bar->empty[s2], ((nb + 1) / 2 - 1) & 1, 0xB1);
+      mbar_arrive_expect_tx(&bar->full[s2], 2 * tile_tx);
+      bwd_load_tile(sK + s2 * kBwdTileBytes, &tmK, &bar->full[s2], p.boxes, (nb + 1) * kBwdTile, hk, bi);
+      bwd_load_tile(sV + s2 * kBwdTileBytes, &tmV, &bar->full[s2], p.boxes, (nb + 1) * kBwdTile, hk, bi);
+    }
+    mbar_wait(&bar->full[st], (nb / 2) & 1, 0xB2);
+    tc_fence_after();
+    if (tid == 0) {
+      const uint32_t q_lo = (smem_u32(sQ) >> 4) | kLboK, do_lo = (smem_u32(sdO) >> 4) | kLboK;
+      const uint32_t k_lo = (smem_u32(sK + st * kBwdTileBytes) >> 4) | kLboK, v_lo = (smem_u32(sV + st * kBwdTileBytes) >> 4) | kLboK;
+      for (int ks = 0; ks < p.slices; ++ks) {
+        const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+        mma_ss<false>(tmem, q_lo + off, k_lo + off, kHi, idesc_s, ks > 0);
+      }
+      for (int ks = 0; ks < p.slices; ++ks) {
+        const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+        mma_ss<false>(tmem + 128, do_lo + off, v_lo + off, kHi, idesc_s, ks > 0);
+      }
+      tc_commit(&bar->mma_s);
+    }
+    mbar_wait(&bar->mma_s, nb & 1, 0xB3);
+    tc_fence_after();
+    // dS = P o (dP - D), 64 key columns at a time; written (16 bit) over S's columns [0, 64)
+    const int n0 = nb * kBwdTile;
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      uint32_t s[2][32], dp[2][32], pk[32];
+      tmem_ld32(tRow + hf * 64, s[0]); tmem_ld32(tRow + hf * 64 + 32, s[1]);
+      tmem_ld32(tRow + 128 + hf * 64, dp[0]); tmem_ld32(tRow + 128 + hf * 64 + 32, dp[1]);
+      tmem_ld_wait();
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          float ds[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int col = n0 + hf * 64 + c * 32 + j + e;
+            const float pr = col < col_hi ? exp2f(__uint_as_float(s[c][j + e]) * p.scale_log2 - lse2) : 0.f;
+            ds[e] = pr * (__uint_as_float(dp[c][j + e]) - dsum);
+          }
+          pk[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+        }
+      // all four S loads of this half are in registers before dS lands on S's columns [32 hf, 32 hf + 32)
+      tmem_st32(tRow + hf * 32, pk);
+    }
+    tmem_st_wait();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (tid == 0) {
+      const uint32_t k_mn = (smem_u32(sK + st * kBwdTileBytes) >> 4) | kLboMN;
+      for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 keys, 16 per slice
+        mma_ts<false>(tmem + 256, tmem + ks * 8, k_mn + ks * (16 * 128 >> 4), kHi, idesc_dq, (nb > 0 || ks > 0));
+      tc_commit(&bar->empty[st]);
+      if (nb == n_blocks - 1) tc_commit(&bar->mma_done);
+    }
+  }
+  // dQ = scale * accumulator
+  if (n_blocks > 0) { mbar_wait(&bar->mma_done, 0, 0xB4); tc_fence_after(); }
+  uint16_t* dst = reinterpret_cast<uint16_t*>(p.dq) + bi * p.dq_batch_stride + int64_t(i) * p.dq_row_stride + hq * p.dq_head_stride;
+  for (int c = 0; c < 4; ++c) {
+    if (c * 32 >= p.d) break;
+    uint32_t o[32];
+    if (n_blocks > 0) { tmem_ld32(tRow + 256 + c * 32, o); tmem_ld_wait(); }
+    else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) o[j] = 0u;
+    }
+    if (row_ok) {
+#pragma unroll
+      for (int v8 = 0; v8 < 4; ++v8)
+        if (c * 32 + v8 * 8 < p.d) {
+          uint4 u;
+          uint32_t* up = reinterpret_cast<uint32_t*>(&u);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) up[e] = bwd_pack(__uint_as_float(o[v8 * 8 + 2 * e]) * p.scale, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * p.scale, p.f16);
+          *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = u;
+        }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+// ----------------------------------------------------------------------------- dK, dV
+// TMEM: S^T @0 (keys on the lanes, 128 query columns; P^T, 16 bit, is written over its columns [0, 64)), dP^T @128 (dS^T over its
+// columns [0, 64)), dK @256, dV @384.  One CTA per (key block, KV head, batch); the steps run over (query head of the group,
+// query block) and all accumulate into the same dK / dV, which is the GQA reduction.
+__global__ void __launch_bounds__(kBwdThreads, 1)
+fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
+                      const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sK = smem;                          // K tile
+  uint8_t* sV = smem + kBwdTileBytes;          // V tile
+  uint8_t* sQ = smem + 2 * kBwdTileBytes;      // Q stages 0, 1
+  uint8_t* sdO = smem + 4 * kBwdTileBytes;     // dO stages 0, 1
+  float* sL = reinterpret_cast<float*>(smem + 6 * kBwdTileBytes);  // LSE * log2(e) of the step's 128 query rows
+  float* sD = sL + kBwdTile;                                        // D of the same rows
+  BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 6 * kBwdTileBytes + 2 * kBwdTile * 4);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int n_blk = blockIdx.x, hk = blockIdx.y, bi = blockIdx.z;
+  const int G = p.h / p.h_k;
+  if (tid == 0) {
+    mbar_init(&bar->fixed_full, 1); mbar_init(&bar->mma_s, 1); mbar_init(&bar->mma_done, 1);
+    for (int s_ = 0; s_ < 2; ++s_) { mbar_init(&bar->full[s_], 1); mbar_init(&bar->empty[s_], 1); }
+    fence_mbar_init();
+  }
+  if (warp == 0) { tmem_alloc(&bar->tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int n0 = n_blk * kBwdTile;
+  const int shift = p.seqlen_k - p.seqlen_q;
+  const int m_blocks = (p.seqlen_q + kBwdTile - 1) / kBwdTile;
+  // causal: the first query block with a row that sees key n0 (row i sees keys <= i + shift)
+  const int m_lo = p.is_causal ? min(m_blocks, max(0, (n0 - shift) / kBwdTile)) : 0;
+  const int per_head = m_blocks - m_lo;
+  const int steps = per_head * G;
+  const uint32_t tile_tx = uint32_t(p.boxes) * kBwdBoxBytes;
+  const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);
+  const uint32_t idesc_acc = make_idesc(fmt, fmt, kBwdTile, p.n16, 0, 1);
+  constexpr uint32_t kHi = sdesc_hi(1024);
+  constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboMN = sdesc_lo_lbo(kBwdBoxBytes);
+
+  auto load_step = [&](int t, int st) {
+    const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
+    mbar_arrive_expect_tx(&bar->full[st], 2 * tile_tx);
+    bwd_load_tile(sQ + st * kBwdTileBytes, &tmQ, &bar->full[st], p.boxes, m * kBwdTile, hq, bi);
+    bwd_load_tile(sdO + st * kBwdTileBytes, &tmdO, &bar->full[st], p.boxes, m * kBwdTile, hq, bi);
+  };
+  if (tid == 0 && steps > 0) {
+    mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
+    bwd_load_tile(sK, &tmK, &bar->fixed_full, p.boxes, n0, hk, bi);
+    bwd_load_tile(sV, &tmV, &bar->fixed_full, p.boxes, n0, hk, bi);
+    load_step(0, 0);
+  }
+  const int kj = n0 + tid;  // this thread's key row
+  const uint32_t tRow = tmem + (uint32_t(warp * 32) << 16);
+
+  if (steps > 0) mbar_wait(&bar->fixed_full, 0, 0xC0);
+  for (int t = 0; t < steps; ++t) {
+    const int st = t & 1;
+    const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
+    if (tid == 0 && t + 1 < steps) {
+      const int s2 = st ^ 1;
+      if (t + 1 >= 2) mbar_wait(&bar->empty[s2], ((t + 1) / 2 - 1) & 1, 0xC1);
+      load_step(t + 1, s2);
+    }
+    {  // the step's per-query-row constants (the previous step's readers are past its __syncthreads)
+      const int i = m * kBwdTile + tid;
+      float l2 = INFINITY, ds_ = 0.f;
+      if (i < p.seqlen_q) {
+        const float l = p.lse[(int64_t(bi) * p.h + hq) * p.seqlen_q + i];
+        l2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
+        ds_ = p.dsum[(int64_t(bi) * p.h + hq) * p.seqlen_q_rounded + i];
+      }
+      sL[tid] = l2; sD[tid] = ds_;
+    }
+    mbar_wait(&bar->full[st], (t / 2) & 1, 0xC2);
+    tc_fence_after();
+    if (tid == 0) {
+      const uint32_t k_lo = (smem_u32(sK) >> 4) | kLboK, v_lo = (smem_u32(sV) >> 4) | kLboK;
+      const uint32_t q_lo = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboK, do_lo = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboK;
+      for (int ks = 0; ks < p.slices; ++ks) {
+        const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+        mma_ss<false>(tmem, k_lo + off, q_lo + off, kHi, idesc_s, ks > 0);           // S^T = K Q^T
+      }
+      for (int ks = 0; ks < p.slices; ++ks) {
+        const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+        mma_ss<false>(tmem + 128, v_lo + off, do_lo + off, kHi, idesc_s, ks > 0);    // dP^T = V dO^T
+      }
+      tc_commit(&bar->mma_s);
+    }
+    __syncthreads();  // sL / sD visible
+    mbar_wait(&bar->mma_s, t & 1, 0xC3);
+    tc_fence_after();
+    const int i0 = m * kBwdTile;
+#pragma unroll
+    for (int qt = 0; qt < 4; ++qt) {  // 32 query columns at a time
+      uint32_t s[32], dp[32], pkp[16], pks[16];
+      tmem_ld32(tRow + qt * 32, s);
+      tmem_ld32(tRow + 128 + qt * 32, dp);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        float pr[2], ds[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int col = qt * 32 + j + e;
+          const bool vis = !p.is_causal || kj <= i0 + col + shift;
+          pr[e] = vis ? exp2f(__uint_as_float(s[j + e]) * p.scale_log2 - sL[col]) : 0.f;
+          ds[e] = pr[e] * (__uint_as_float(dp[j + e]) - sD[col]);
+        }
+        pkp[j / 2] = bwd_pack(pr[0], pr[1], p.f16);
+        pks[j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+      }
+      tmem_st16(tRow + qt * 16, pkp);        // P^T over S^T's consumed columns
+      tmem_st16(tRow + 128 + qt * 16, pks);  // dS^T over dP^T's consumed columns
+    }
+    tmem_st_wait();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (tid == 0) {
+      const uint32_t do_mn = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboMN, q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
+      for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step
+        mma_ts<false>(tmem + 384, tmem + ks * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));        // dV += P^T dO
+      for (int ks = 0; ks < 8; ++ks)
+        mma_ts<false>(tmem + 256, tmem + 128 + ks * 8, q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));   // dK += dS^T Q
+      tc_commit(&bar->empty[st]);
+      if (t == steps - 1) tc_commit(&bar->mma_done);
+    }
+  }
+  if (steps > 0) { mbar_wait(&bar->mma_done, 0, 0xC4); tc_fence_after(); }
+  const bool row_ok = kj < p.seqlen_k;
+  uint16_t* dk_dst = reinterpret_cast<uint16_t*>(p.dk) + bi * p.dk_batch_stride + int64_t(kj) * p.dk_row_stride + hk * p.dk_head_stride;
+  uint16_t* dv_dst = reinterpret_cast<uint16_t*>(p.dv) + bi * p.dv_batch_stride + int64_t(kj) * p.dv_row_stride + hk * p.dv_head_stride;
+  for (int which = 0; which < 2; ++which) {
+    uint16_t* dst = which == 0 ? dk_dst : dv_dst;
+    const float sc = which == 0 ? p.scale : 1.0f;
+    for (int c = 0; c < 4; ++c) {
+      if (c * 32 >= p.d) break;
+      uint32_t o[32];
+      if (steps > 0) { tmem_ld32(tRow + 256 + which * 128 + c * 32, o); tmem_ld_wait(); }
+      else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[j] = 0u;
+      }
+      if (row_ok) {
+#pragma unroll
+        for (int v8 = 0; v8 < 4; ++v8)
+          if (c * 32 + v8 * 8 < p.d) {
+            uint4 u;
+            uint32_t* up = reinterpret_cast<uint32_t*>(&u);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) up[e] = bwd_pack(__uint_as_float(o[v8 * 8 + 2 * e]) * sc, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * sc, p.f16);
+            *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = u;
+          }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+// ----------------------------------------------------------------------------- host
+static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
+  FA_CHECK_ARG(p->dout && p->q && p->k && p->v && p->out && p->lse && p->dq && p->dk && p->dv && p->softmax_d, "null tensor");
+  FA_CHECK_ARG(p->dtype == FA100_BF16 || p->dtype == FA100_FP16, "FlashAttention backward only supports fp16 and bf16 data type");
+  FA_CHECK_ARG(p->b > 0 && p->h > 0 && p->h_k > 0 && p->h % p->h_k == 0, "bad batch/head counts b=%d h=%d h_k=%d", p->b, p->h, p->h_k);
+  FA_CHECK_ARG(p->seqlen_q > 0 && p->seqlen_k > 0, "empty sequences");
+  FA_CHECK_ARG(p->d > 0 && p->d % 8 == 0, "head dim must be a multiple of 8 (d=%d)", p->d);
+  FA_UNSUPPORTED(p->d > 128 || p->dv_dim != p->d, "backward: head dim > 128 or d_v != d is not supported yet (d=%d dv=%d)", p->d, p->dv_dim);
+  FA_UNSUPPORTED(p->softcap > 0.f, "backward: softcap is not supported yet");
+  int wl = p->window_left, wr = p->is_causal ? 0 : p->window_right;
+  if (wl >= p->seqlen_k - 1) wl = -1;
+  if (wr >= p->seqlen_q - 1 && !p->is_causal) wr = -1;
+  const bool causal = wl < 0 && wr == 0;
+  FA_UNSUPPORTED(!causal && (wl >= 0 || wr >= 0), "backward: local (sliding-window) attention is not supported yet");
+  for (const int64_t* st : {&p->dq_row_stride, &p->dq_head_stride, &p->dq_batch_stride, &p->dk_row_stride, &p->dk_head_stride, &p->dk_batch_stride,
+                            &p->dv_row_stride, &p->dv_head_stride, &p->dv_batch_stride})
+    FA_CHECK_ARG(*st % 8 == 0, "dq / dk / dv strides must be multiples of 8 elements");
+  FA_CHECK_ARG(reinterpret_cast<uintptr_t>(p->dq) % 16 == 0 && reinterpret_cast<uintptr_t>(p->dk) % 16 == 0 && reinterpret_cast<uintptr_t>(p->dv) % 16 == 0,
+               "dq / dk / dv must be 16-byte aligned");
+
+  BwdKernelParams kp;
+  std::memset(&kp, 0, sizeof(kp));
+  kp.dq = p->dq; kp.dk = p->dk; kp.dv = p->dv; kp.lse = p->lse; kp.dsum = p->softmax_d;
+  kp.dq_batch_stride = p->dq_batch_stride; kp.dq_row_stride = p->dq_row_stride; kp.dq_head_stride = p->dq_head_stride;
+  kp.dk_batch_stride = p->dk_batch_stride; kp.dk_row_stride = p->dk_row_stride; kp.dk_head_stride = p->dk_head_stride;
+  kp.dv_batch_stride = p->dv_batch_stride; kp.dv_row_stride = p->dv_row_stride; kp.dv_head_stride = p->dv_head_stride;
+  kp.b = p->b; kp.h = p->h; kp.h_k = p->h_k; kp.seqlen_q = p->seqlen_q; kp.seqlen_k = p->seqlen_k; kp.d = p->d;
+  kp.seqlen_q_rounded = (p->seqlen_q + kBwdTile - 1) / kBwdTile * kBwdTile;
+  kp.boxes = (p->d + 63) / 64; kp.slices = (p->d + 15) / 16; kp.n16 = (p->d + 15) / 16 * 16;
+  kp.is_causal = causal; kp.f16 = p->dtype == FA100_FP16;
+  kp.scale = p->softmax_scale; kp.scale_log2 = p->softmax_scale * kLog2e;
+
+  CUtensorMap tmQ, tmdO, tmK, tmV;
+  const uint32_t box[4] = {64, uint32_t(kBwdTile), 1, 1};
+  auto tm4 = [&](CUtensorMap* tm, const void* base, int rows, int heads, int64_t rs, int64_t hs, int64_t bs) {
+    uint64_t dims[4] = {uint64_t(p->d), uint64_t(rows), uint64_t(heads), uint64_t(p->b)};
+    uint64_t str[4] = {0, uint64_t(rs) * 2, uint64_t(hs) * 2, uint64_t(bs) * 2};
+    return encode_tensor_map(tm, p->dtype, 4, base, dims, str, box);
+  };
+  int rc;
+  if ((rc = tm4(&tmQ, p->q, p->seqlen_q, p->h, p->q_row_stride, p->q_head_stride, p->q_batch_stride))) return rc;
+  if ((rc = tm4(&tmdO, p->dout, p->seqlen_q, p->h, p->do_row_stride, p->do_head_stride, p->do_batch_stride))) return rc;
+  if ((rc = tm4(&tmK, p->k, p->seqlen_k, p->h_k, p->k_row_stride, p->k_head_stride, p->k_batch_stride))) return rc;
+  if ((rc = tm4(&tmV, p->v, p->seqlen_k, p->h_k, p->v_row_stride, p->v_head_stride, p->v_batch_stride))) return rc;
+
+  // the 192 KB of dynamic shared memory are an opt-in per device
+  constexpr int kSmemDq = 6 * kBwdTileBytes + 256, kSmemDkdv = 6 * kBwdTileBytes + 2 * kBwdTile * 4 + 256;
+  static std::atomic<uint64_t> attr_set[2] = {{0}, {0}};
+  int dev = 0;
+  FA_CUDA(cudaGetDevice(&dev));
+  const bool tracked = dev >= 0 && dev < 128;
+  if (!tracked || !((attr_set[dev >> 6].load(std::memory_order_relaxed) >> (dev & 63)) & 1)) {
+    FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDq));
+    FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDkdv));
+    if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
+  }
+  const int64_t rows = int64_t(p->b) * p->h * kp.seqlen_q_rounded;
+  const int dot_grid = int(std::min<int64_t>((rows + 7) / 8, 148 * 16));
+  if (p->dtype == FA100_FP16)
+    FA_CUDA(launch_pdl(fa100_bwd_dot_kernel<__half>, dim3(dot_grid), dim3(256), size_t(0), stream, 1, static_cast<const __half*>(p->dout),
+                       static_cast<const __half*>(p->out), p->softmax_d, p->do_batch_stride, p->do_row_stride, p->do_head_stride, p->o_batch_stride,
+                       p->o_row_stride, p->o_head_stride, p->b, p->h, p->seqlen_q, kp.seqlen_q_rounded, p->d));
+  else
+    FA_CUDA(launch_pdl(fa100_bwd_dot_kernel<__nv_bfloat16>, dim3(dot_grid), dim3(256), size_t(0), stream, 1, static_cast<const __nv_bfloat16*>(p->dout),
+                       static_cast<const __nv_bfloat16*>(p->out), p->softmax_d, p->do_batch_stride, p->do_row_stride, p->do_head_stride, p->o_batch_stride,
+                       p->o_row_stride, p->o_head_stride, p->b, p->h, p->seqlen_q, kp.seqlen_q_rounded, p->d));
+  const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : kFmtF16;
+  const int m_blocks = kp.seqlen_q_rounded / kBwdTile, n_blocks = (p->seqlen_k + kBwdTile - 1) / kBwdTile;
+  FA_CUDA(launch_pdl(fa100_bwd_dq_kernel, dim3(m_blocks, p->h, p->b), dim3(kBwdThreads), size_t(kSmemDq), stream, 1, kp, tmQ, tmdO, tmK, tmV, fmt));
+  FA_CUDA(launch_pdl(fa100_bwd_dkdv_kernel, dim3(n_blocks, p->h_k, p->b), dim3(kBwdThreads), size_t(kSmemDkdv), stream, 1, kp, tmQ, tmdO, tmK, tmV, fmt));
+  FA_CUDA(cudaGetLastError());
+  return FA100_OK;
+}
+
+}  // namespace fa100
+
+extern "C" int fa100_bwd(const Fa100BwdParams* p, fa100_stream_t stream) {
+  if (!p) return fa100::set_error(FA100_ERR_INVALID, "null params");
+  return fa100::launch_bwd(p, static_cast<cudaStream_t>(stream));
+}

@@ -46,6 +46,15 @@ class FwdParams(C.Structure):
     )
 
 
+class BwdParams(C.Structure):
+    _fields_ = (
+        [(n, vp) for n in ("dout", "q", "k", "v", "out", "lse", "dq", "dk", "dv", "softmax_d")]
+        + [(f"{t}_{k}_stride", i64) for t in ("q", "k", "v", "o", "do", "dq", "dk", "dv") for k in ("batch", "row", "head")]
+        + [(n, i32) for n in ("b", "seqlen_q", "seqlen_k", "h", "h_k", "d", "dv_dim", "dtype", "is_causal", "window_left", "window_right")]
+        + [("softmax_scale", f32), ("softcap", f32), ("deterministic", i32), ("num_sm", i32), ("reserved", i32 * 8)]
+    )
+
+
 class CombineParams(C.Structure):
     _fields_ = (
         [("o_partial", vp), ("lse_partial", vp), ("o", vp), ("lse", vp)]
@@ -70,7 +79,7 @@ class Plan(C.Structure):
                                    "dual_stream")] + [("reserved", i32 * 8)]
 
 
-EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_append_kv", "fa100_prepare_scheduler",
+EXPORTS = ("fa100_abi_version", "fa100_last_error", "fa100_plan", "fa100_fwd", "fa100_combine", "fa100_bwd", "fa100_append_kv", "fa100_prepare_scheduler",
            "fa100_scheduler_metadata_words", "fa100_fwd_splitkv_noalloc", "fa100_noalloc_scratch_bytes", "fa100_debug_hang_info",
            "fa100_debug_trace", "fa100_debug_prof")
 
@@ -99,6 +108,8 @@ def lib() -> C.CDLL:
         l.fa100_plan.argtypes = [C.POINTER(Shape), C.POINTER(Plan)]
         l.fa100_fwd.argtypes = [C.POINTER(FwdParams), vp]
         l.fa100_combine.argtypes = [C.POINTER(CombineParams), vp]
+        l.fa100_bwd.argtypes = [C.POINTER(BwdParams), vp]
+        l.fa100_bwd.restype = C.c_int
         l.fa100_append_kv.argtypes = [C.POINTER(FwdParams), vp, i64, i64, i64, vp, vp]
         l.fa100_prepare_scheduler.argtypes = [C.POINTER(FwdParams), vp, i64, vp]
         l.fa100_scheduler_metadata_words.argtypes = [i32]

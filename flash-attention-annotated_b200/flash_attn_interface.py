@@ -41,8 +41,15 @@ def _flash_attn_forward(q, k, v, k_new, v_new, qv, out, cu_seqlens_q, cu_seqlens
     return out, softmax_lse, *rest
 
 
-def _no_backward(*_):
-    raise NotImplementedError("fa100 is a forward-only build of FlashAttention (backward is out of scope)")
+def _flash_attn_backward(dout, q, k, v, out, softmax_lse, cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k, max_seqlen_q,
+                         max_seqlen_k, dq, dk, dv, softmax_scale, causal, window_size=(-1, -1), softcap=0.0, deterministic=False,
+                         sm_margin=0):
+    """hopper/flash_attn_interface.py:119-168."""
+    dout, q, k, v, out = [maybe_contiguous(x) for x in (dout, q, k, v, out)]
+    dq, dk, dv, softmax_d, *rest = torch.ops.flash_attn_3.bwd(
+        dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k, max_seqlen_q, max_seqlen_k,
+        softmax_scale, causal, window_size[0], window_size[1], softcap, deterministic, sm_margin)
+    return dq, dk, dv, softmax_d
 
 
 class FlashAttnFunc(torch.autograd.Function):
@@ -57,12 +64,23 @@ class FlashAttnFunc(torch.autograd.Function):
             None, q_descale, k_descale, v_descale, softmax_scale, causal=causal, window_size=window_size,
             attention_chunk=attention_chunk, softcap=softcap, num_splits=num_splits, pack_gqa=pack_gqa,
             sm_margin=sm_margin)
+        ctx.save_for_backward(q, k, v, out, softmax_lse)
+        ctx.softmax_scale, ctx.causal, ctx.window_size, ctx.attention_chunk = softmax_scale, causal, window_size, attention_chunk
+        ctx.softcap, ctx.deterministic, ctx.sm_margin, ctx.has_qv = softcap, deterministic, sm_margin, qv is not None
         ctx.mark_non_differentiable(softmax_lse)
         return (out, softmax_lse) if return_softmax else out
 
     @staticmethod
     def backward(ctx, dout, *args):
-        _no_backward()
+        """hopper/flash_attn_interface.py:236-264."""
+        q, k, v, out, softmax_lse = ctx.saved_tensors
+        assert ctx.attention_chunk == 0, "FA3 backward does not support attention_chunk"
+        if ctx.has_qv or q.dtype == torch.float8_e4m3fn:
+            raise NotImplementedError("fa100: the backward does not support qv or FP8 (neither does the reference's)")
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        _flash_attn_backward(dout, q, k, v, out, softmax_lse, None, None, None, None, None, None, dq, dk, dv, ctx.softmax_scale,
+                             ctx.causal, ctx.window_size, ctx.softcap, ctx.deterministic, ctx.sm_margin)
+        return (dq, dk, dv) + (None,) * 14
 
 
 class FlashAttnVarlenFunc(torch.autograd.Function):
@@ -83,7 +101,7 @@ class FlashAttnVarlenFunc(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dout, *args):
-        _no_backward()
+        raise NotImplementedError("fa100: the backward does not support variable-length batches yet (SURVEY.md 8(f) rank 2)")
 
 
 def flash_attn_qkvpacked_func(qkv, softmax_scale=None, causal=False, q_descale=None, k_descale=None, v_descale=None,

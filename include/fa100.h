@@ -154,6 +154,30 @@ typedef struct Fa100FwdParams {
   int64_t qv_batch_stride, qv_row_stride, qv_head_stride;
 } Fa100FwdParams;
 
+/* Backward pass (hopper/flash_api.cpp:1267-1567 mha_bwd -> run_mha_bwd).  First version, scope:
+ * fixed-length batches (b, s, h, d), bf16 / fp16, d == dv <= 128 (multiple of 8), MHA / GQA / MQA, causal (bottom-right
+ * aligned) or full attention, softcap 0, no local window; everything else returns FA100_ERR_UNSUPPORTED.  Deterministic:
+ * no atomics (dQ and dK/dV come from two kernels that each recompute the scores).  All strides in elements. */
+typedef struct Fa100BwdParams {
+  const void* dout; const void* q; const void* k; const void* v; const void* out;
+  const float* lse;      /* (b, h, seqlen_q) fp32, natural-log units, as the forward returns it */
+  void* dq; void* dk; void* dv;
+  float* softmax_d;      /* workspace / output (b, h, seqlen_q_rounded) fp32: rowsum(dout * out); seqlen_q rounded up to 128 */
+  int64_t q_batch_stride, q_row_stride, q_head_stride;
+  int64_t k_batch_stride, k_row_stride, k_head_stride;
+  int64_t v_batch_stride, v_row_stride, v_head_stride;
+  int64_t o_batch_stride, o_row_stride, o_head_stride;
+  int64_t do_batch_stride, do_row_stride, do_head_stride;
+  int64_t dq_batch_stride, dq_row_stride, dq_head_stride;
+  int64_t dk_batch_stride, dk_row_stride, dk_head_stride;
+  int64_t dv_batch_stride, dv_row_stride, dv_head_stride;
+  int32_t b, seqlen_q, seqlen_k, h, h_k, d, dv_dim, dtype;
+  int32_t is_causal, window_left, window_right;
+  float softmax_scale, softcap;
+  int32_t deterministic, num_sm;
+  int32_t reserved[8];
+} Fa100BwdParams;
+
 /* LSE-weighted merge of split partials (hopper/flash_fwd_combine_kernel.h:200-483,
  * mha_combine hopper/flash_api.cpp:1569-1670).  Element strides; d stride is 1. */
 /* `o` / `lse` may alias split 0 of `o_partial` / `lse_partial` (same strides): every row is read completely before it is
@@ -202,6 +226,9 @@ const char* fa100_last_error(void);
 int fa100_plan(const Fa100Shape* shape, Fa100Plan* out);
 int fa100_fwd(const Fa100FwdParams* p, fa100_stream_t stream);
 int fa100_combine(const Fa100CombineParams* p, fa100_stream_t stream);
+/* replaces run_mha_bwd (hopper/flash_api.cpp:1267-1567, flash_bwd_launch_template.h): three launches, preprocess (softmax_d),
+ * dQ, dK/dV; allocates nothing (softmax_d is the caller's). */
+int fa100_bwd(const Fa100BwdParams* p, fa100_stream_t stream);
 
 /* Split-KV forward + combine with NO memory allocation anywhere: the fp32 partials (the only scratch memory the forward
  * uses) live in a static device array inside the library instead of caller-supplied o_accum / lse_accum.

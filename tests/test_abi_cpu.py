@@ -34,12 +34,12 @@ def test_exports_match_header(native):
 
 def test_struct_sizes_match_c(native, tmp_path):
     src = tmp_path / "sz.c"
-    src.write_text('#include <stdio.h>\n#include "fa100.h"\nint main(){printf("%zu %zu %zu %zu\\n", sizeof(Fa100FwdParams),'
-                   'sizeof(Fa100CombineParams), sizeof(Fa100Shape), sizeof(Fa100Plan));return 0;}\n')
+    src.write_text('#include <stdio.h>\n#include "fa100.h"\nint main(){printf("%zu %zu %zu %zu %zu\\n", sizeof(Fa100FwdParams),'
+                   'sizeof(Fa100CombineParams), sizeof(Fa100Shape), sizeof(Fa100Plan), sizeof(Fa100BwdParams));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
     sizes = [int(x) for x in subprocess.check_output([str(exe)]).split()]
-    assert sizes == [C.sizeof(native.FwdParams), C.sizeof(native.CombineParams), C.sizeof(native.Shape), C.sizeof(native.Plan)]
+    assert sizes == [C.sizeof(native.FwdParams), C.sizeof(native.CombineParams), C.sizeof(native.Shape), C.sizeof(native.Plan), C.sizeof(native.BwdParams)]
 
 
 def _plan(native, **kw):
