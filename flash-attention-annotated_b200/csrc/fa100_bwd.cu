@@ -40,13 +40,41 @@ struct BwdKernelParams {
   int64_t dq_batch_stride, dq_row_stride, dq_head_stride;
   int64_t dk_batch_stride, dk_row_stride, dk_head_stride;
   int64_t dv_batch_stride, dv_row_stride, dv_head_stride;
-  int32_t b, h, h_k, seqlen_q, seqlen_k, seqlen_q_rounded, d;
+  int32_t b, h, h_k, seqlen_q, seqlen_k, d;
   int32_t boxes;       // 64-column boxes per tile actually loaded: ceil(d / 64)
   int32_t slices;      // MMA k-slices over the head dim: ceil(d / 16)
   int32_t n16;         // d rounded up to 16: N of the products whose result has d columns
-  int32_t is_causal, f16;
+  int32_t f16;
+  int32_t window_left, window_right;   // keys [i + shift - window_left, i + shift + window_right] are visible; < 0 = unbounded (causal: right = 0)
   float scale, scale_log2;
+  float softcap_pre, softcap_log2;     // softcap: scale / softcap and softcap * log2(e); 0 = off
+  const int32_t* cu_seqlens_q; const int32_t* cu_seqlens_k; const int32_t* seqused_q; const int32_t* seqused_k;
+  int64_t lse_batch_stride, lse_head_stride, dsum_batch_stride, dsum_head_stride;  // fp32 elements; row stride 1
 };
+
+// per-batch lengths and offsets (hopper/seqlen.h:13-29); packed tensors use batch coordinate 0 and a row offset
+struct BwdSeq { int sq, sk, q_off, k_off, bq, bk; };
+FA_DEVICE BwdSeq bwd_seq(const BwdKernelParams& p, int bi) {
+  BwdSeq s;
+  s.q_off = p.cu_seqlens_q ? p.cu_seqlens_q[bi] : 0;
+  s.k_off = p.cu_seqlens_k ? p.cu_seqlens_k[bi] : 0;
+  s.sq = p.seqused_q ? p.seqused_q[bi] : (p.cu_seqlens_q ? p.cu_seqlens_q[bi + 1] - s.q_off : p.seqlen_q);
+  s.sk = p.seqused_k ? p.seqused_k[bi] : (p.cu_seqlens_k ? p.cu_seqlens_k[bi + 1] - s.k_off : p.seqlen_k);
+  s.bq = p.cu_seqlens_q ? 0 : bi;
+  s.bk = p.cu_seqlens_k ? 0 : bi;
+  return s;
+}
+// P and the softcap derivative factor for one score: P = exp(score - LSE), score = s * scale or softcap * tanh(s * scale / softcap)
+FA_DEVICE float bwd_prob(const BwdKernelParams& p, float s, float lse2, float& dfac) {
+  if (p.softcap_pre != 0.f) {
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(s * p.softcap_pre));
+    dfac = 1.f - t * t;
+    return exp2f(t * p.softcap_log2 - lse2);
+  }
+  dfac = 1.f;
+  return exp2f(s * p.scale_log2 - lse2);
+}
 
 struct BwdBarriers {
   uint64_t fixed_full;        // the tile(s) loaded once per CTA
@@ -117,10 +145,15 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
   pdl_wait();
   pdl_launch_dependents();
 
+  const BwdSeq sq_ = bwd_seq(p, bi);
   const int row0 = m_blk * kBwdTile;
-  const int shift = p.seqlen_k - p.seqlen_q;
-  int n_blocks = (p.seqlen_k + kBwdTile - 1) / kBwdTile;
-  if (p.is_causal) n_blocks = min(n_blocks, max(0, (min(row0 + kBwdTile, p.seqlen_q) + shift + kBwdTile - 1) / kBwdTile));
+  const int shift = sq_.sk - sq_.sq;
+  // key blocks [n_min, n_max) any row of this tile can see (hopper/block.h:14-60 with 128-row tiles)
+  int n_max = (sq_.sk + kBwdTile - 1) / kBwdTile, n_min = 0;
+  if (p.window_right >= 0) n_max = min(n_max, max(0, (min(row0 + kBwdTile, sq_.sq) + shift + p.window_right + kBwdTile - 1) / kBwdTile));
+  if (p.window_left >= 0) n_min = max(0, (row0 + shift - p.window_left) / kBwdTile);
+  if (row0 >= sq_.sq) n_max = n_min;
+  const int n_blocks = max(0, n_max - n_min);
   const uint32_t tile_tx = uint32_t(p.boxes) * kBwdBoxBytes;
 
   const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);   // S = Q K^T, dP = dO V^T
@@ -130,22 +163,23 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
 
   if (tid == 0 && n_blocks > 0) {
     mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
-    bwd_load_tile(sQ, &tmQ, &bar->fixed_full, p.boxes, row0, hq, bi);
-    bwd_load_tile(sdO, &tmdO, &bar->fixed_full, p.boxes, row0, hq, bi);
+    bwd_load_tile(sQ, &tmQ, &bar->fixed_full, p.boxes, sq_.q_off + row0, hq, sq_.bq);
+    bwd_load_tile(sdO, &tmdO, &bar->fixed_full, p.boxes, sq_.q_off + row0, hq, sq_.bq);
     mbar_arrive_expect_tx(&bar->full[0], 2 * tile_tx);
-    bwd_load_tile(sK, &tmK, &bar->full[0], p.boxes, 0, hk, bi);
-    bwd_load_tile(sV, &tmV, &bar->full[0], p.boxes, 0, hk, bi);
+    bwd_load_tile(sK, &tmK, &bar->full[0], p.boxes, sq_.k_off + n_min * kBwdTile, hk, sq_.bk);
+    bwd_load_tile(sV, &tmV, &bar->full[0], p.boxes, sq_.k_off + n_min * kBwdTile, hk, sq_.bk);
   }
   // this thread's query row
   const int i = row0 + tid;
-  const bool row_ok = i < p.seqlen_q;
+  const bool row_ok = i < sq_.sq;
   float lse2 = INFINITY, dsum = 0.f;  // rows past the end and rows without keys (LSE = -inf) get P = 0
   if (row_ok) {
-    const float l = p.lse[(int64_t(bi) * p.h + hq) * p.seqlen_q + i];
+    const float l = p.lse[bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off + i];
     lse2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
-    dsum = p.dsum[(int64_t(bi) * p.h + hq) * p.seqlen_q_rounded + i];
+    dsum = p.dsum[bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off + i];
   }
-  const int col_hi = p.is_causal ? min(p.seqlen_k, i + 1 + shift) : p.seqlen_k;
+  const int col_hi = p.window_right >= 0 ? min(sq_.sk, i + 1 + shift + p.window_right) : sq_.sk;
+  const int col_lo = p.window_left >= 0 ? max(0, i + shift - p.window_left) : 0;
   const uint32_t tRow = tmem + (uint32_t(warp * 32) << 16);
 
   if (n_blocks > 0) mbar_wait(&bar->fixed_full, 0, 0xB0);
@@ -155,8 +189,8 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
       const int s2 = st ^ 1;
       if (nb + 1 >= 2) mbar_wait(&bar->empty[s2], ((nb + 1) / 2 - 1) & 1, 0xB1);
       mbar_arrive_expect_tx(&bar->full[s2], 2 * tile_tx);
-      bwd_load_tile(sK + s2 * kBwdTileBytes, &tmK, &bar->full[s2], p.boxes, (nb + 1) * kBwdTile, hk, bi);
-      bwd_load_tile(sV + s2 * kBwdTileBytes, &tmV, &bar->full[s2], p.boxes, (nb + 1) * kBwdTile, hk, bi);
+      bwd_load_tile(sK + s2 * kBwdTileBytes, &tmK, &bar->full[s2], p.boxes, sq_.k_off + (n_min + nb + 1) * kBwdTile, hk, sq_.bk);
+      bwd_load_tile(sV + s2 * kBwdTileBytes, &tmV, &bar->full[s2], p.boxes, sq_.k_off + (n_min + nb + 1) * kBwdTile, hk, sq_.bk);
     }
     mbar_wait(&bar->full[st], (nb / 2) & 1, 0xB2);
     tc_fence_after();
@@ -176,7 +210,7 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
     mbar_wait(&bar->mma_s, nb & 1, 0xB3);
     tc_fence_after();
     // dS = P o (dP - D), 64 key columns at a time; written (16 bit) over S's columns [0, 64)
-    const int n0 = nb * kBwdTile;
+    const int n0 = (n_min + nb) * kBwdTile;
 #pragma unroll
     for (int hf = 0; hf < 2; ++hf) {
       uint32_t s[2][32], dp[2][32], pk[32];
@@ -191,8 +225,9 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int col = n0 + hf * 64 + c * 32 + j + e;
-            const float pr = col < col_hi ? exp2f(__uint_as_float(s[c][j + e]) * p.scale_log2 - lse2) : 0.f;
-            ds[e] = pr * (__uint_as_float(dp[c][j + e]) - dsum);
+            float dfac = 0.f;
+            const float pr = (col < col_hi && col >= col_lo) ? bwd_prob(p, __uint_as_float(s[c][j + e]), lse2, dfac) : 0.f;
+            ds[e] = pr * (__uint_as_float(dp[c][j + e]) - dsum) * dfac;
           }
           pk[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
         }
@@ -213,7 +248,7 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
   }
   // dQ = scale * accumulator
   if (n_blocks > 0) { mbar_wait(&bar->mma_done, 0, 0xB4); tc_fence_after(); }
-  uint16_t* dst = reinterpret_cast<uint16_t*>(p.dq) + bi * p.dq_batch_stride + int64_t(i) * p.dq_row_stride + hq * p.dq_head_stride;
+  uint16_t* dst = reinterpret_cast<uint16_t*>(p.dq) + sq_.bq * p.dq_batch_stride + int64_t(sq_.q_off + i) * p.dq_row_stride + hq * p.dq_head_stride;
   for (int c = 0; c < 4; ++c) {
     if (c * 32 >= p.d) break;
     uint32_t o[32];
@@ -270,12 +305,19 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   pdl_wait();
   pdl_launch_dependents();
 
+  const BwdSeq sq_ = bwd_seq(p, bi);
   const int n0 = n_blk * kBwdTile;
-  const int shift = p.seqlen_k - p.seqlen_q;
-  const int m_blocks = (p.seqlen_q + kBwdTile - 1) / kBwdTile;
-  // causal: the first query block with a row that sees key n0 (row i sees keys <= i + shift)
-  const int m_lo = p.is_causal ? min(m_blocks, max(0, (n0 - shift) / kBwdTile)) : 0;
-  const int per_head = m_blocks - m_lo;
+  const int shift = sq_.sk - sq_.sq;
+  const int m_blocks = (sq_.sq + kBwdTile - 1) / kBwdTile;
+  // query blocks [m_lo, m_hi) with a row that sees a key of this tile: row i sees keys [i + shift - wl, i + shift + wr]
+  int m_lo = 0, m_hi = m_blocks;
+  if (p.window_right >= 0) m_lo = min(m_blocks, max(0, (n0 - shift - p.window_right) / kBwdTile));
+  if (p.window_left >= 0) {
+    const int last_row = min(n0 + kBwdTile, sq_.sk) - 1 - shift + p.window_left;  // the last row that sees a key of this tile
+    m_hi = last_row < 0 ? 0 : min(m_blocks, last_row / kBwdTile + 1);
+  }
+  if (n0 >= sq_.sk) m_hi = m_lo;
+  const int per_head = max(0, m_hi - m_lo);
   const int steps = per_head * G;
   const uint32_t tile_tx = uint32_t(p.boxes) * kBwdBoxBytes;
   const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);
@@ -286,13 +328,13 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   auto load_step = [&](int t, int st) {
     const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
     mbar_arrive_expect_tx(&bar->full[st], 2 * tile_tx);
-    bwd_load_tile(sQ + st * kBwdTileBytes, &tmQ, &bar->full[st], p.boxes, m * kBwdTile, hq, bi);
-    bwd_load_tile(sdO + st * kBwdTileBytes, &tmdO, &bar->full[st], p.boxes, m * kBwdTile, hq, bi);
+    bwd_load_tile(sQ + st * kBwdTileBytes, &tmQ, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
+    bwd_load_tile(sdO + st * kBwdTileBytes, &tmdO, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
   };
   if (tid == 0 && steps > 0) {
     mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
-    bwd_load_tile(sK, &tmK, &bar->fixed_full, p.boxes, n0, hk, bi);
-    bwd_load_tile(sV, &tmV, &bar->fixed_full, p.boxes, n0, hk, bi);
+    bwd_load_tile(sK, &tmK, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
+    bwd_load_tile(sV, &tmV, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
     load_step(0, 0);
   }
   const int kj = n0 + tid;  // this thread's key row
@@ -310,10 +352,10 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
     {  // the step's per-query-row constants (the previous step's readers are past its __syncthreads)
       const int i = m * kBwdTile + tid;
       float l2 = INFINITY, ds_ = 0.f;
-      if (i < p.seqlen_q) {
-        const float l = p.lse[(int64_t(bi) * p.h + hq) * p.seqlen_q + i];
+      if (i < sq_.sq) {
+        const float l = p.lse[bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off + i];
         l2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
-        ds_ = p.dsum[(int64_t(bi) * p.h + hq) * p.seqlen_q_rounded + i];
+        ds_ = p.dsum[bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off + i];
       }
       sL[tid] = l2; sD[tid] = ds_;
     }
@@ -348,9 +390,11 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const int col = qt * 32 + j + e;
-          const bool vis = !p.is_causal || kj <= i0 + col + shift;
-          pr[e] = vis ? exp2f(__uint_as_float(s[j + e]) * p.scale_log2 - sL[col]) : 0.f;
-          ds[e] = pr[e] * (__uint_as_float(dp[j + e]) - sD[col]);
+          const int pos = i0 + col + shift;  // the key on this row's diagonal
+          const bool vis = (p.window_right < 0 || kj <= pos + p.window_right) && (p.window_left < 0 || kj >= pos - p.window_left);
+          float dfac = 0.f;
+          pr[e] = vis ? bwd_prob(p, __uint_as_float(s[j + e]), sL[col], dfac) : 0.f;
+          ds[e] = pr[e] * (__uint_as_float(dp[j + e]) - sD[col]) * dfac;
         }
         pkp[j / 2] = bwd_pack(pr[0], pr[1], p.f16);
         pks[j / 2] = bwd_pack(ds[0], ds[1], p.f16);
@@ -373,9 +417,9 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
     }
   }
   if (steps > 0) { mbar_wait(&bar->mma_done, 0, 0xC4); tc_fence_after(); }
-  const bool row_ok = kj < p.seqlen_k;
-  uint16_t* dk_dst = reinterpret_cast<uint16_t*>(p.dk) + bi * p.dk_batch_stride + int64_t(kj) * p.dk_row_stride + hk * p.dk_head_stride;
-  uint16_t* dv_dst = reinterpret_cast<uint16_t*>(p.dv) + bi * p.dv_batch_stride + int64_t(kj) * p.dv_row_stride + hk * p.dv_head_stride;
+  const bool row_ok = kj < sq_.sk;
+  uint16_t* dk_dst = reinterpret_cast<uint16_t*>(p.dk) + sq_.bk * p.dk_batch_stride + int64_t(sq_.k_off + kj) * p.dk_row_stride + hk * p.dk_head_stride;
+  uint16_t* dv_dst = reinterpret_cast<uint16_t*>(p.dv) + sq_.bk * p.dv_batch_stride + int64_t(sq_.k_off + kj) * p.dv_row_stride + hk * p.dv_head_stride;
   for (int which = 0; which < 2; ++which) {
     uint16_t* dst = which == 0 ? dk_dst : dv_dst;
     const float sc = which == 0 ? p.scale : 1.0f;
@@ -413,12 +457,14 @@ static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
   FA_CHECK_ARG(p->seqlen_q > 0 && p->seqlen_k > 0, "empty sequences");
   FA_CHECK_ARG(p->d > 0 && p->d % 8 == 0, "head dim must be a multiple of 8 (d=%d)", p->d);
   FA_UNSUPPORTED(p->d > 128 || p->dv_dim != p->d, "backward: head dim > 128 or d_v != d is not supported yet (d=%d dv=%d)", p->d, p->dv_dim);
-  FA_UNSUPPORTED(p->softcap > 0.f, "backward: softcap is not supported yet");
-  int wl = p->window_left, wr = p->is_causal ? 0 : p->window_right;
+  const bool varlen_q = p->cu_seqlens_q != nullptr, varlen_k = p->cu_seqlens_k != nullptr;
+  if (varlen_q) FA_CHECK_ARG(p->total_q > 0, "cu_seqlens_q needs total_q");
+  if (varlen_k) FA_CHECK_ARG(p->total_k > 0, "cu_seqlens_k needs total_k");
+  // window normalisation of the reference (hopper/flash_api.cpp:1356-1361): a window that covers everything is no window
+  int wl = p->window_left, wr = p->window_right;
   if (wl >= p->seqlen_k - 1) wl = -1;
-  if (wr >= p->seqlen_q - 1 && !p->is_causal) wr = -1;
-  const bool causal = wl < 0 && wr == 0;
-  FA_UNSUPPORTED(!causal && (wl >= 0 || wr >= 0), "backward: local (sliding-window) attention is not supported yet");
+  if (wr >= p->seqlen_q - 1) wr = -1;
+  if (p->is_causal) wr = 0;
   for (const int64_t* st : {&p->dq_row_stride, &p->dq_head_stride, &p->dq_batch_stride, &p->dk_row_stride, &p->dk_head_stride, &p->dk_batch_stride,
                             &p->dv_row_stride, &p->dv_head_stride, &p->dv_batch_stride})
     FA_CHECK_ARG(*st % 8 == 0, "dq / dk / dv strides must be multiples of 8 elements");
@@ -432,23 +478,30 @@ static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
   kp.dk_batch_stride = p->dk_batch_stride; kp.dk_row_stride = p->dk_row_stride; kp.dk_head_stride = p->dk_head_stride;
   kp.dv_batch_stride = p->dv_batch_stride; kp.dv_row_stride = p->dv_row_stride; kp.dv_head_stride = p->dv_head_stride;
   kp.b = p->b; kp.h = p->h; kp.h_k = p->h_k; kp.seqlen_q = p->seqlen_q; kp.seqlen_k = p->seqlen_k; kp.d = p->d;
-  kp.seqlen_q_rounded = (p->seqlen_q + kBwdTile - 1) / kBwdTile * kBwdTile;
   kp.boxes = (p->d + 63) / 64; kp.slices = (p->d + 15) / 16; kp.n16 = (p->d + 15) / 16 * 16;
-  kp.is_causal = causal; kp.f16 = p->dtype == FA100_FP16;
+  kp.f16 = p->dtype == FA100_FP16;
+  kp.window_left = wl; kp.window_right = wr;
   kp.scale = p->softmax_scale; kp.scale_log2 = p->softmax_scale * kLog2e;
+  if (p->softcap > 0.f) { kp.softcap_pre = p->softmax_scale / p->softcap; kp.softcap_log2 = p->softcap * kLog2e; }
+  kp.cu_seqlens_q = p->cu_seqlens_q; kp.cu_seqlens_k = p->cu_seqlens_k; kp.seqused_q = p->seqused_q; kp.seqused_k = p->seqused_k;
+  const int64_t rows_q = varlen_q ? p->total_q : p->seqlen_q;
+  const int64_t rows_q_rounded = (rows_q + kBwdTile - 1) / kBwdTile * kBwdTile;
+  kp.lse_head_stride = rows_q; kp.lse_batch_stride = varlen_q ? 0 : int64_t(p->h) * rows_q;
+  kp.dsum_head_stride = rows_q_rounded; kp.dsum_batch_stride = varlen_q ? 0 : int64_t(p->h) * rows_q_rounded;
 
   CUtensorMap tmQ, tmdO, tmK, tmV;
   const uint32_t box[4] = {64, uint32_t(kBwdTile), 1, 1};
-  auto tm4 = [&](CUtensorMap* tm, const void* base, int rows, int heads, int64_t rs, int64_t hs, int64_t bs) {
-    uint64_t dims[4] = {uint64_t(p->d), uint64_t(rows), uint64_t(heads), uint64_t(p->b)};
+  auto tm4 = [&](CUtensorMap* tm, const void* base, int64_t rows, int heads, int64_t rs, int64_t hs, int64_t bs, bool packed) {
+    uint64_t dims[4] = {uint64_t(p->d), uint64_t(rows), uint64_t(heads), uint64_t(packed ? 1 : p->b)};
     uint64_t str[4] = {0, uint64_t(rs) * 2, uint64_t(hs) * 2, uint64_t(bs) * 2};
     return encode_tensor_map(tm, p->dtype, 4, base, dims, str, box);
   };
   int rc;
-  if ((rc = tm4(&tmQ, p->q, p->seqlen_q, p->h, p->q_row_stride, p->q_head_stride, p->q_batch_stride))) return rc;
-  if ((rc = tm4(&tmdO, p->dout, p->seqlen_q, p->h, p->do_row_stride, p->do_head_stride, p->do_batch_stride))) return rc;
-  if ((rc = tm4(&tmK, p->k, p->seqlen_k, p->h_k, p->k_row_stride, p->k_head_stride, p->k_batch_stride))) return rc;
-  if ((rc = tm4(&tmV, p->v, p->seqlen_k, p->h_k, p->v_row_stride, p->v_head_stride, p->v_batch_stride))) return rc;
+  const int64_t rows_k = varlen_k ? p->total_k : p->seqlen_k;
+  if ((rc = tm4(&tmQ, p->q, rows_q, p->h, p->q_row_stride, p->q_head_stride, p->q_batch_stride, varlen_q))) return rc;
+  if ((rc = tm4(&tmdO, p->dout, rows_q, p->h, p->do_row_stride, p->do_head_stride, p->do_batch_stride, varlen_q))) return rc;
+  if ((rc = tm4(&tmK, p->k, rows_k, p->h_k, p->k_row_stride, p->k_head_stride, p->k_batch_stride, varlen_k))) return rc;
+  if ((rc = tm4(&tmV, p->v, rows_k, p->h_k, p->v_row_stride, p->v_head_stride, p->v_batch_stride, varlen_k))) return rc;
 
   // the 192 KB of dynamic shared memory are an opt-in per device
   constexpr int kSmemDq = 6 * kBwdTileBytes + 256, kSmemDkdv = 6 * kBwdTileBytes + 2 * kBwdTile * 4 + 256;
@@ -461,18 +514,20 @@ static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
     FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDkdv));
     if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
   }
-  const int64_t rows = int64_t(p->b) * p->h * kp.seqlen_q_rounded;
+  // D: a packed batch is one "sequence" of total_q rows for this kernel (rows no sequence uses are computed and never read)
+  const int dot_b = varlen_q ? 1 : p->b, dot_sq = int(rows_q), dot_sqr = int(rows_q_rounded);
+  const int64_t rows = int64_t(dot_b) * p->h * dot_sqr;
   const int dot_grid = int(std::min<int64_t>((rows + 7) / 8, 148 * 16));
   if (p->dtype == FA100_FP16)
     FA_CUDA(launch_pdl(fa100_bwd_dot_kernel<__half>, dim3(dot_grid), dim3(256), size_t(0), stream, 1, static_cast<const __half*>(p->dout),
                        static_cast<const __half*>(p->out), p->softmax_d, p->do_batch_stride, p->do_row_stride, p->do_head_stride, p->o_batch_stride,
-                       p->o_row_stride, p->o_head_stride, p->b, p->h, p->seqlen_q, kp.seqlen_q_rounded, p->d));
+                       p->o_row_stride, p->o_head_stride, dot_b, p->h, dot_sq, dot_sqr, p->d));
   else
     FA_CUDA(launch_pdl(fa100_bwd_dot_kernel<__nv_bfloat16>, dim3(dot_grid), dim3(256), size_t(0), stream, 1, static_cast<const __nv_bfloat16*>(p->dout),
                        static_cast<const __nv_bfloat16*>(p->out), p->softmax_d, p->do_batch_stride, p->do_row_stride, p->do_head_stride, p->o_batch_stride,
-                       p->o_row_stride, p->o_head_stride, p->b, p->h, p->seqlen_q, kp.seqlen_q_rounded, p->d));
+                       p->o_row_stride, p->o_head_stride, dot_b, p->h, dot_sq, dot_sqr, p->d));
   const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : kFmtF16;
-  const int m_blocks = kp.seqlen_q_rounded / kBwdTile, n_blocks = (p->seqlen_k + kBwdTile - 1) / kBwdTile;
+  const int m_blocks = (p->seqlen_q + kBwdTile - 1) / kBwdTile, n_blocks = (p->seqlen_k + kBwdTile - 1) / kBwdTile;  // of the longest sequence
   FA_CUDA(launch_pdl(fa100_bwd_dq_kernel, dim3(m_blocks, p->h, p->b), dim3(kBwdThreads), size_t(kSmemDq), stream, 1, kp, tmQ, tmdO, tmK, tmV, fmt));
   FA_CUDA(launch_pdl(fa100_bwd_dkdv_kernel, dim3(n_blocks, p->h_k, p->b), dim3(kBwdThreads), size_t(kSmemDkdv), stream, 1, kp, tmQ, tmdO, tmK, tmV, fmt));
   FA_CUDA(cudaGetLastError());

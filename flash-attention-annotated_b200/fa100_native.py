@@ -51,7 +51,9 @@ class BwdParams(C.Structure):
         [(n, vp) for n in ("dout", "q", "k", "v", "out", "lse", "dq", "dk", "dv", "softmax_d")]
         + [(f"{t}_{k}_stride", i64) for t in ("q", "k", "v", "o", "do", "dq", "dk", "dv") for k in ("batch", "row", "head")]
         + [(n, i32) for n in ("b", "seqlen_q", "seqlen_k", "h", "h_k", "d", "dv_dim", "dtype", "is_causal", "window_left", "window_right")]
-        + [("softmax_scale", f32), ("softcap", f32), ("deterministic", i32), ("num_sm", i32), ("reserved", i32 * 8)]
+        + [("softmax_scale", f32), ("softcap", f32), ("deterministic", i32), ("num_sm", i32)]
+        + [(n, vp) for n in ("cu_seqlens_q", "cu_seqlens_k", "seqused_q", "seqused_k")]
+        + [("total_q", i32), ("total_k", i32), ("reserved", i32 * 6)]
     )
 
 

@@ -433,51 +433,74 @@ def mha_fwd_get_scheduler_metadata(batch_size, max_seqlen_q, max_seqlen_k, num_h
 def mha_bwd(dout, q, k, v, out, softmax_lse, dq=None, dk=None, dv=None, cu_seqlens_q=None, cu_seqlens_k=None, seqused_q=None,
             seqused_k=None, max_seqlen_q=None, max_seqlen_k=None, softmax_scale=None, is_causal=False, window_size_left=-1,
             window_size_right=-1, softcap=0.0, deterministic=False, sm_margin=0):
-    """torch.ops.flash_attn_3.bwd (hopper/flash_api.cpp:1267-1567).  First version: fixed-length batches,
-    bf16 / fp16, d == dv <= 128, MHA / GQA / MQA, causal or full; varlen, local windows, softcap, larger head dims raise
-    NotImplementedError.  Returns (dq, dk, dv, softmax_d, softmax_lse_log2, dq_accum, dk_accum, dv_accum) like the reference;
-    the last three are empty (no fp32 accumulators: dQ and dK/dV each come from one deterministic kernel)."""
+    """torch.ops.flash_attn_3.bwd (hopper/flash_api.cpp:1267-1567): bf16 / fp16, d == dv <= 128, MHA / GQA / MQA, fixed-length or
+    variable-length (cu_seqlens / seqused) batches, causal, local windows, softcap; larger head dims raise NotImplementedError.
+    Returns (dq, dk, dv, softmax_d, softmax_lse_log2, dq_accum, dk_accum, dv_accum) like the reference; the last four are
+    empty (no fp32 accumulators: dQ and dK/dV each come from one deterministic kernel that folds log2(e) itself)."""
     _chk(q.is_cuda and k.is_cuda and v.is_cuda and dout.is_cuda and out.is_cuda and softmax_lse.is_cuda, "all tensors must be CUDA tensors")
     qt = q.dtype
     _chk(qt in (torch.float16, torch.bfloat16), "FlashAttention only support fp16 and bf16 data type")
     _chk(k.dtype == qt and v.dtype == qt and out.dtype == qt and dout.dtype == qt, "query, key, value, out and dout must have the same dtype")
     for t, nm in ((q, "q"), (k, "k"), (v, "v"), (out, "out"), (dout, "dout")):
         _chk(t.stride(-1) == 1, f"{nm} tensor must have contiguous last dimension")
-    if any(t is not None for t in (cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k)):
-        raise NotImplementedError("fa100: the backward does not support variable-length batches yet (cu_seqlens / seqused)")
-    _chk(q.dim() == 4 and k.dim() == 4 and v.dim() == 4, "q, k, v must be (batch, seqlen, nheads, headdim)")
-    b, sq, h, d = q.shape
-    _, sk, h_k, dv_dim = v.shape
-    _chk(tuple(k.shape) == (b, sk, h_k, d), "k has the wrong shape")
-    _chk(tuple(out.shape) == (b, sq, h, dv_dim) and tuple(dout.shape) == (b, sq, h, dv_dim), "out / dout have the wrong shape")
+    varlen_q, varlen_k = cu_seqlens_q is not None, cu_seqlens_k is not None
+    if varlen_q:
+        _i32(cu_seqlens_q, "cu_seqlens_q")
+        _chk(max_seqlen_q is not None, "max_seqlen_q must be provided if cu_seqlens_q is provided")
+        _chk(q.dim() == 3, "q must be (total_q, nheads, headdim) when cu_seqlens_q is given")
+    if varlen_k:
+        _i32(cu_seqlens_k, "cu_seqlens_k")
+        _chk(max_seqlen_k is not None, "max_seqlen_k must be provided if cu_seqlens_k is provided")
+        _chk(k.dim() == 3, "k must be (total_k, nheads_k, headdim) when cu_seqlens_k is given")
+    b = (cu_seqlens_q.numel() - 1) if varlen_q else q.shape[0]
+    sq = max_seqlen_q if varlen_q else q.shape[1]
+    sk = max_seqlen_k if varlen_k else k.shape[1]
+    total_q, total_k = (q.shape[0] if varlen_q else 0), (k.shape[0] if varlen_k else 0)
+    h, d = q.shape[-2], q.shape[-1]
+    h_k, dv_dim = v.shape[-2], v.shape[-1]
+    _chk(tuple(k.shape) == ((total_k, h_k, d) if varlen_k else (b, sk, h_k, d)), "k has the wrong shape")
+    _chk(tuple(v.shape) == ((total_k, h_k, dv_dim) if varlen_k else (b, sk, h_k, dv_dim)), "v has the wrong shape")
+    oshape = (total_q, h, dv_dim) if varlen_q else (b, sq, h, dv_dim)
+    _chk(tuple(out.shape) == oshape and tuple(dout.shape) == oshape, "out / dout have the wrong shape")
     _chk(h % h_k == 0, "Number of heads in key/value must divide number of heads in query")
-    _chk(softmax_lse.dtype == torch.float32 and tuple(softmax_lse.shape) == (b, h, sq), "softmax_lse must be fp32 (batch, nheads, seqlen_q)")
+    _chk(softmax_lse.dtype == torch.float32 and tuple(softmax_lse.shape) == ((h, total_q) if varlen_q else (b, h, sq)),
+         "softmax_lse must be fp32 (batch, nheads, seqlen_q) or (nheads, total_q)")
     _chk(d % 8 == 0 and dv_dim % 8 == 0, "head_size should be a multiple of 8")
+    for t, nm in ((seqused_q, "seqused_q"), (seqused_k, "seqused_k")):
+        if t is not None:
+            _i32(t, nm, b)
     if softmax_scale is None:
         softmax_scale = d ** -0.5
-    mk = lambda ref, t, nm: (torch.empty_like(ref) if t is None else t)  # noqa: E731
-    dq, dk, dv = mk(q, dq, "dq"), mk(k, dk, "dk"), mk(v, dv, "dv")
+    mk = lambda ref, t: (torch.empty_like(ref) if t is None else t)  # noqa: E731
+    dq, dk, dv = mk(q, dq), mk(k, dk), mk(v, dv)
     for t, ref, nm in ((dq, q, "dq"), (dk, k, "dk"), (dv, v, "dv")):
         _chk(t.dtype == qt and tuple(t.shape) == tuple(ref.shape) and t.stride(-1) == 1 and t.is_cuda, f"{nm} must have the dtype, shape and layout of its input")
+    if seqused_q is not None or seqused_k is not None:
+        # rows past seqused are never visited: the reference zero-fills them too (dq / dk / dv are defined for every slot)
+        dq.zero_(), dk.zero_(), dv.zero_()
     lse = softmax_lse.contiguous()
-    sq_rounded = (sq + 127) // 128 * 128
-    softmax_d = torch.empty((b, h, sq_rounded), dtype=torch.float32, device=q.device)
+    rows_q = total_q if varlen_q else sq
+    rows_q_rounded = (rows_q + 127) // 128 * 128
+    softmax_d = torch.empty((h, rows_q_rounded) if varlen_q else (b, h, rows_q_rounded), dtype=torch.float32, device=q.device)
     p = N.BwdParams()
     p.dout, p.q, p.k, p.v, p.out, p.lse = _ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(lse)
     p.dq, p.dk, p.dv, p.softmax_d = _ptr(dq), _ptr(dk), _ptr(dv), _ptr(softmax_d)
-    for nm, t in (("q", q), ("k", k), ("v", v), ("o", out), ("do", dout), ("dq", dq), ("dk", dk), ("dv", dv)):
-        setattr(p, f"{nm}_batch_stride", t.stride(0))
-        setattr(p, f"{nm}_row_stride", t.stride(1))
-        setattr(p, f"{nm}_head_stride", t.stride(2))
+    for nm, t, packed in (("q", q, varlen_q), ("k", k, varlen_k), ("v", v, varlen_k), ("o", out, varlen_q), ("do", dout, varlen_q),
+                          ("dq", dq, varlen_q), ("dk", dk, varlen_k), ("dv", dv, varlen_k)):
+        st = (0, t.stride(0), t.stride(1)) if packed else (t.stride(0), t.stride(1), t.stride(2))
+        setattr(p, f"{nm}_batch_stride", st[0])
+        setattr(p, f"{nm}_row_stride", st[1])
+        setattr(p, f"{nm}_head_stride", st[2])
     p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d, p.dv_dim, p.dtype = b, sq, sk, h, h_k, d, dv_dim, _DT[qt]
+    p.cu_seqlens_q, p.cu_seqlens_k, p.seqused_q, p.seqused_k = _ptr(cu_seqlens_q), _ptr(cu_seqlens_k), _ptr(seqused_q), _ptr(seqused_k)
+    p.total_q, p.total_k = total_q, total_k
     p.is_causal, p.window_left, p.window_right = int(is_causal), window_size_left, window_size_right
     p.softmax_scale, p.softcap, p.deterministic = float(softmax_scale), float(softcap), int(deterministic)
     p.num_sm = max(1, _sm_count(q.device) - sm_margin)
     with _on_device(q.device):
         N.check(N.lib().fa100_bwd(C.byref(p), _stream()))
     empty = torch.empty(0, dtype=torch.float32, device=q.device)
-    lse_log2 = torch.empty(0, dtype=torch.float32, device=q.device)  # the kernels fold log2(e) themselves
-    return dq, dk, dv, softmax_d, lse_log2, empty, empty, empty
+    return dq, dk, dv, softmax_d, empty, empty, empty, empty
 
 
 # ----------------------------------------------------------------------------- shape-only (Meta) kernels for tracing

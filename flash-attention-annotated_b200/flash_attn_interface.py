@@ -96,12 +96,25 @@ class FlashAttnVarlenFunc(torch.autograd.Function):
             max_seqlen_k, None, None, None, None, None, None, q_descale, k_descale, v_descale, softmax_scale,
             causal=causal, window_size=window_size, attention_chunk=attention_chunk, softcap=softcap,
             num_splits=num_splits, pack_gqa=pack_gqa, sm_margin=sm_margin)
+        ctx.save_for_backward(q, k, v, out, softmax_lse, cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k)
+        ctx.max_seqlen_q, ctx.max_seqlen_k = max_seqlen_q, max_seqlen_k
+        ctx.softmax_scale, ctx.causal, ctx.window_size, ctx.attention_chunk = softmax_scale, causal, window_size, attention_chunk
+        ctx.softcap, ctx.deterministic, ctx.sm_margin, ctx.has_qv = softcap, deterministic, sm_margin, qv is not None
         ctx.mark_non_differentiable(softmax_lse)
         return (out, softmax_lse) if return_softmax else out
 
     @staticmethod
     def backward(ctx, dout, *args):
-        raise NotImplementedError("fa100: the backward does not support variable-length batches yet (SURVEY.md 8(f) rank 2)")
+        """hopper/flash_attn_interface.py:335-367."""
+        q, k, v, out, softmax_lse, cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k = ctx.saved_tensors
+        assert ctx.attention_chunk == 0, "FA3 backward does not support attention_chunk"
+        if ctx.has_qv or q.dtype == torch.float8_e4m3fn:
+            raise NotImplementedError("fa100: the backward does not support qv or FP8 (neither does the reference's)")
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        _flash_attn_backward(dout, q, k, v, out, softmax_lse, cu_seqlens_q, cu_seqlens_k, seqused_q, seqused_k, ctx.max_seqlen_q,
+                             ctx.max_seqlen_k, dq, dk, dv, ctx.softmax_scale, ctx.causal, ctx.window_size, ctx.softcap, ctx.deterministic,
+                             ctx.sm_margin)
+        return (dq, dk, dv) + (None,) * 20
 
 
 def flash_attn_qkvpacked_func(qkv, softmax_scale=None, causal=False, q_descale=None, k_descale=None, v_descale=None,

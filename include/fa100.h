@@ -155,8 +155,8 @@ typedef struct Fa100FwdParams {
 } Fa100FwdParams;
 
 /* Backward pass (hopper/flash_api.cpp:1267-1567 mha_bwd -> run_mha_bwd).  First version, scope:
- * fixed-length batches (b, s, h, d), bf16 / fp16, d == dv <= 128 (multiple of 8), MHA / GQA / MQA, causal (bottom-right
- * aligned) or full attention, softcap 0, no local window; everything else returns FA100_ERR_UNSUPPORTED.  Deterministic:
+ * bf16 / fp16, d == dv <= 128 (multiple of 8), MHA / GQA / MQA, fixed-length or variable-length (cu_seqlens / seqused) batches,
+ * causal (bottom-right aligned), local windows, softcap; larger head dims return FA100_ERR_UNSUPPORTED.  Deterministic:
  * no atomics (dQ and dK/dV come from two kernels that each recompute the scores).  All strides in elements. */
 typedef struct Fa100BwdParams {
   const void* dout; const void* q; const void* k; const void* v; const void* out;
@@ -175,7 +175,11 @@ typedef struct Fa100BwdParams {
   int32_t is_causal, window_left, window_right;
   float softmax_scale, softcap;
   int32_t deterministic, num_sm;
-  int32_t reserved[8];
+  /* variable-length batches (packed (total, h, d) tensors, batch strides unused): cu_seqlens (b + 1) and / or seqused (b);
+   * seqlen_q / seqlen_k are then the maxima; lse is (h, total_q) and softmax_d (h, total_q rounded up to 128) */
+  const int32_t* cu_seqlens_q; const int32_t* cu_seqlens_k; const int32_t* seqused_q; const int32_t* seqused_k;
+  int32_t total_q, total_k;
+  int32_t reserved[6];
 } Fa100BwdParams;
 
 /* LSE-weighted merge of split partials (hopper/flash_fwd_combine_kernel.h:200-483,

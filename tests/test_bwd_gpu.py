@@ -3,7 +3,8 @@
 Rule of hopper/test_flash_attn.py:225-286: for g in (dq, dk, dv)
     max|g - g_ref| <= 2 * max|g_pt - g_ref| + 2 * max|(g_ref + 0.3 - 0.3) - g_ref|
 with g_ref from the fp32 oracle and g_pt from its low-precision arm (upcast=False, reorder_ops=True), all by torch autograd
-on the CPU.  Scope of this first version: fixed-length batches, bf16 / fp16, d == dv <= 128, causal or full, MHA / GQA / MQA."""
+on the CPU.  Scope: bf16 / fp16, d == dv <= 128, MHA / GQA / MQA, fixed-length and variable-length batches, causal, local windows,
+softcap."""
 import pytest
 import torch
 
@@ -91,15 +92,69 @@ def test_backward_op_outputs_and_determinism():
     _check_grads((dq, dk, dv), ref, pt)
 
 
+@pytest.mark.parametrize("kw", [dict(window_size=(100, 50)), dict(window_size=(300, 0)), dict(window_size=(0, 0)), dict(window_size=(-1, 30)),
+                                dict(window_size=(20, -1)), dict(softcap=15.0), dict(softcap=15.0, causal=True), dict(softcap=30.0, window_size=(64, 16))])
+@pytest.mark.parametrize("sq,sk", [(500, 700), (700, 500), (64, 1500), (1, 333), (256, 256)])
+def test_backward_local_and_softcap(sq, sk, kw):
+    """Sliding windows and softcap in the backward (hopper/test_flash_attn.py:63,62 x :225-286; rtol 3 with softcap, :195)."""
+    import flash_attn_interface as F
+
+    gen = torch.Generator().manual_seed(104)
+    q, k, v = (torch.randn(2, s_, h_, 128, generator=gen).to(torch.bfloat16) for s_, h_ in ((sq, 4), (sk, 2), (sk, 2)))
+    g = torch.randn(2, sq, 4, 128, generator=gen).to(torch.bfloat16)
+    ref = _grads(q.float(), k.float(), v.float(), g.float(), **kw)
+    pt = _grads(q, k, v, g, upcast=False, reorder_ops=True, **kw)
+    qd, kd, vd = (x.to(DEV).requires_grad_() for x in (q, k, v))
+    dq, dk, dv = torch.autograd.grad(F.flash_attn_func(qd, kd, vd, **kw), (qd, kd, vd), g.to(DEV))
+    torch.cuda.synchronize()
+    rt = 3.0 if kw.get("softcap") else 2.0
+    for a_, r, p_, nm in zip((dq, dk, dv), ref, pt, ("dq", "dk", "dv")):
+        atol = 2 * (r + 0.3 - 0.3 - r).abs().max().item() + (3e-4 if kw.get("softcap") else 0)
+        err = (a_.float().cpu() - r.float()).abs().max().item()
+        assert torch.isfinite(a_.float()).all() and err <= rt * (p_.float() - r.float()).abs().max().item() + atol + 1e-4, (nm, err)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("use_seqused", [False, True])
+@pytest.mark.parametrize("lens_q,lens_k", [([100, 257, 31], [100, 300, 77]), ([128, 5, 300, 1], [128, 64, 511, 1000]),
+                                           ([1, 1, 1, 1, 1], [7, 130, 250, 1, 600])])
+def test_backward_varlen(lens_q, lens_k, use_seqused, causal):
+    """Packed variable-length batches (cu_seqlens), optionally with seqused shorter than the slots (hopper/test_flash_attn.py:290-598)."""
+    import flash_attn_interface as F
+
+    gen = torch.Generator().manual_seed(105)
+    h, hk, d = 4, 2, 128
+    b = len(lens_q)
+    slot_q = [n + (17 if use_seqused else 0) for n in lens_q]   # with seqused every slot holds unused rows after the sequence
+    slot_k = [n + (40 if use_seqused else 0) for n in lens_k]
+    cq = torch.tensor([0] + torch.tensor(slot_q).cumsum(0).tolist(), dtype=torch.int32)
+    ck = torch.tensor([0] + torch.tensor(slot_k).cumsum(0).tolist(), dtype=torch.int32)
+    q = torch.randn(int(cq[-1]), h, d, generator=gen).to(torch.bfloat16)
+    k = torch.randn(int(ck[-1]), hk, d, generator=gen).to(torch.bfloat16)
+    v = torch.randn(int(ck[-1]), hk, d, generator=gen).to(torch.bfloat16)
+    g = torch.randn(int(cq[-1]), h, d, generator=gen).to(torch.bfloat16)
+    qd, kd, vd = (x.to(DEV).requires_grad_() for x in (q, k, v))
+    extra = dict(seqused_q=torch.tensor(lens_q, dtype=torch.int32, device=DEV), seqused_k=torch.tensor(lens_k, dtype=torch.int32, device=DEV)) if use_seqused else {}
+    out = F.flash_attn_varlen_func(qd, kd, vd, cq.to(DEV), ck.to(DEV), max(slot_q), max(slot_k), causal=causal, **extra)
+    dq, dk, dv = torch.autograd.grad(out, (qd, kd, vd), g.to(DEV))
+    torch.cuda.synchronize()
+    for i in range(b):
+        qs, ks = slice(int(cq[i]), int(cq[i]) + lens_q[i]), slice(int(ck[i]), int(ck[i]) + lens_k[i])
+        ref = _grads(q[qs][None].float(), k[ks][None].float(), v[ks][None].float(), g[qs][None].float(), causal=causal)
+        pt = _grads(q[qs][None], k[ks][None], v[ks][None], g[qs][None], causal=causal, upcast=False, reorder_ops=True)
+        _check_grads((dq[qs][None], dk[ks][None], dv[ks][None]), ref, pt)
+        if use_seqused:  # the unused tail of every slot gets zero gradients
+            assert dq[int(cq[i]) + lens_q[i]:int(cq[i + 1])].abs().max().item() == 0
+            assert dk[int(ck[i]) + lens_k[i]:int(ck[i + 1])].abs().max().item() == 0 and dv[int(ck[i]) + lens_k[i]:int(ck[i + 1])].abs().max().item() == 0
+
+
 def test_backward_unsupported_raises():
     import flash_attn_interface as F
 
     mk = lambda *s: torch.zeros(*s, dtype=torch.bfloat16, device=DEV, requires_grad=True)  # noqa: E731
-    q, k, v = mk(1, 64, 2, 128), mk(1, 64, 2, 128), mk(1, 64, 2, 128)
-    with pytest.raises(NotImplementedError):
-        F.flash_attn_func(q, k, v, window_size=(8, 0)).sum().backward()
-    with pytest.raises(NotImplementedError):
-        F.flash_attn_func(q, k, v, softcap=10.0).sum().backward()
     q2, k2, v2 = mk(1, 64, 2, 256), mk(1, 64, 2, 256), mk(1, 64, 2, 256)
     with pytest.raises(NotImplementedError):
-        F.flash_attn_func(q2, k2, v2).sum().backward()
+        F.flash_attn_func(q2, k2, v2).sum().backward()  # head dim > 128: not in this version
+    q, k, v = mk(1, 64, 2, 128), mk(1, 64, 2, 128), mk(1, 64, 2, 128)
+    with pytest.raises(AssertionError):
+        F.flash_attn_func(q, k, v, attention_chunk=16, causal=True).sum().backward()  # as in the reference (flash_attn_interface.py:238)
