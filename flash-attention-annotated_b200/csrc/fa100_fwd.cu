@@ -3,6 +3,7 @@
 // hopper/flash_fwd_launch_template.h:30-198) for the sm_100a kernel in fa100_fwd_softmax.cuh.
 #include "fa100_host.h"
 #include "fa100_fwd2.cuh"
+#include "fa100_fwd_split.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -49,6 +50,25 @@ static int launch_instance2(const FwdKernelParams& kp, const CUtensorMap& tmQ, c
     if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
   }
   FA_CUDA(launch_pdl(kernel, dim3(grid), dim3(kThreads2), size_t(L2::kTotalBytes), stream, 1, kp, tmQ, tmK, tmV, tmO, fmt));
+  FA_CUDA(cudaGetLastError());
+  return FA100_OK;
+}
+
+// The split-row prefill kernel of fa100_fwd_split.cuh (two softmax threads per query row; 640 threads).
+template <int HD, int ELT, bool FP8, bool F16>
+static int launch_instance_split(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                                 const CUtensorMap& tmO, const CUtensorMap& tmQv, uint32_t fmt, int grid, cudaStream_t stream) {
+  using LS = FwdSmemSplit<HD, ELT>;
+  auto kernel = fa100_fwd_split_kernel<HD, ELT, FP8, F16>;
+  static std::atomic<uint64_t> attr_set[2] = {{0}, {0}};
+  int dev = 0;
+  FA_CUDA(cudaGetDevice(&dev));
+  const bool tracked = dev >= 0 && dev < 128;
+  if (!tracked || !((attr_set[dev >> 6].load(std::memory_order_relaxed) >> (dev & 63)) & 1)) {
+    FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LS::kTotalBytes));
+    if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
+  }
+  FA_CUDA(launch_pdl(kernel, dim3(grid), dim3(kSplitThreads), size_t(LS::kTotalBytes), stream, 1, kp, tmQ, tmK, tmV, tmO, tmQv, fmt));
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
@@ -366,6 +386,13 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
                              : launch_instance2<64, 2, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
     return f16 ? launch_instance2<128, 2, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
                : launch_instance2<128, 2, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+  }
+  if (!dual && !solo && !pair && (p->variant & FA100_VARIANT_SPLIT_ROWS)) {
+    if (fp8) return launch_instance_split<128, 1, true, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);
+    if (hd == 64) return f16 ? launch_instance_split<64, 2, false, true>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream)
+                             : launch_instance_split<64, 2, false, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);
+    return f16 ? launch_instance_split<128, 2, false, true>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream)
+               : launch_instance_split<128, 2, false, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);
   }
   if (fp8) return FA_LAUNCH(128, 1, true, false);
   if (hd == 256)

@@ -132,7 +132,7 @@ static __device__ volatile unsigned int g_fa100_abort;
 #ifndef FA100_TRACE_BLOCK
 #define FA100_TRACE_BLOCK 0
 #endif
-constexpr int kTraceWarps = 16, kTracePerWarp = 4096;
+constexpr int kTraceWarps = 20, kTracePerWarp = 4096;
 static __device__ unsigned int g_fa100_trace[kTraceWarps * kTracePerWarp * 3];
 static __device__ unsigned int g_fa100_trace_cnt[kTraceWarps];
 #ifndef FA100_TRACE_MAXWARP

@@ -281,6 +281,8 @@ def _variant() -> int:
         v |= 16
     if os.environ.get("FA100_FOUR_ROLE") == "1":  # the four-role prefill mainloop (csrc/fa100_fwd2.cuh)
         v |= 32
+    if os.environ.get("FA100_SPLIT_ROWS") == "1":  # two softmax threads per query row (csrc/fa100_fwd_split.cuh)
+        v |= 64
     return v
 
 

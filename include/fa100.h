@@ -44,6 +44,7 @@ typedef void* fa100_stream_t; /* cudaStream_t */
  * o like q with dv; lse fp32 (b, h, sq) or (h, total_q). */
 #define FA100_VARIANT_NO_TMA_STORE 16
 #define FA100_VARIANT_FOUR_ROLE 32
+#define FA100_VARIANT_SPLIT_ROWS 64
 
 typedef struct Fa100FwdParams {
   /* tensors */

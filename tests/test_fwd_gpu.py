@@ -725,3 +725,29 @@ def test_four_role_variant(sq, sk, d, kw, dtype, monkeypatch):
     for pack_gqa, num_splits in ((False, 1), (True, 1), (False, 3)):
         out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), pack_gqa=pack_gqa, num_splits=num_splits, return_attn_probs=True, **kw)
         _check(out, lse, ref, low, lse_ref, rtol=4.0 if fp8 else (3.0 if kw.get("softcap") else 2.0))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float8_e4m3fn])
+@pytest.mark.parametrize("kw", [dict(), dict(causal=True), dict(window_size=(100, 20)), dict(softcap=15.0, causal=True)])
+@pytest.mark.parametrize("sq,sk,d", [(256, 512, 128), (1024, 1024, 128), (700, 500, 64), (1500, 3000, 128), (113, 203, 96)])
+def test_split_rows_variant(sq, sk, d, kw, dtype, monkeypatch):
+    """The split-row prefill kernel of csrc/fa100_fwd_split.cuh (FA100_SPLIT_ROWS=1 -> Fa100FwdParams.variant bit 64): two
+    softmax threads per query row, each on 64 of a block's 128 key columns and half of the O columns, identical running
+    maxima without a hand-shake, row sums joined once per work item.  Same oracle and tolerance as the default kernel,
+    every epilogue form (TMA store, pack-GQA vector stores, fp32 partials + combine)."""
+    F = _iface()
+    fp8 = dtype == torch.float8_e4m3fn
+    if fp8 and d == 96:
+        d = 64
+    g = torch.Generator().manual_seed(10)
+    mk = lambda *s: torch.randn(*s, generator=g).to(torch.bfloat16).to(dtype)  # noqa: E731
+    q, k, v = mk(2, sq, 8, d), mk(2, sk, 2, d), mk(2, sk, 2, d)
+    qr, kr, vr = (x.to(torch.bfloat16) if fp8 else x for x in (q, k, v))
+    ref, lse_ref = A.attention_oracle(qr, kr, vr, **kw)
+    low, _ = A.attention_oracle(qr, kr, vr, upcast=False, reorder_ops=True, intermediate_dtype=dtype if fp8 else None, **kw)
+    monkeypatch.setenv("FA100_SPLIT_ROWS", "1")
+    for pack_gqa, num_splits in ((False, 1), (True, 1), (False, 3)):
+        out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), pack_gqa=pack_gqa, num_splits=num_splits, return_attn_probs=True, **kw)
+        _check(out, lse, ref, low, lse_ref, rtol=4.0 if fp8 else (3.0 if kw.get("softcap") else 2.0))
+        again, _ = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), pack_gqa=pack_gqa, num_splits=num_splits, return_attn_probs=True, **kw)
+        assert torch.equal(out, again)  # the halves of a row agree on every rescale decision: bitwise repeatable
