@@ -5,11 +5,12 @@
 // whose instruction streams are in order, and the MUFU (128 exponentials per row and key block, 8 clk per warp
 // instruction) idles whenever both are in a non-exponential phase: 73 % busy at C2.  Here warp
 // w and warp w + 8 share the TMEM lanes (= rows) of one quarter of a tile and each takes 64 of the 128 key columns, so a
-// scheduler hosts four shorter streams.  The halves of a row never talk inside the key loop: each thread reads the OTHER
-// half's scores as well, only to reduce them to a row max (tensor-memory reads are cheap, a hand-shake between two warps
-// per key block is not), so both threads derive bit-identical running maxima and rescale decisions from identical
-// inputs.  Each keeps the row sum of its own columns and rescales / stores its own half of the O columns; the two
-// partial sums meet once per work item through shared memory.
+// scheduler hosts four shorter streams.  Per key block the two threads of a row swap the maxima of their halves through
+// shared memory (one fp32 slot each, a 64-thread named barrier), so both derive bit-identical running maxima and rescale
+// decisions; each keeps the row sum of its own columns and rescales / stores its own half of the O columns, and the two
+// partial sums meet once per work item the same way.  (First version: no swap, every thread read the other half's scores
+// too and reduced them to a max -- S was handed to the other tile's QK ~350 clk late and the S ping-pong became the critical
+// loop, profiles/r02g_c2_split_rows_phase_samples.txt.)
 #pragma once
 #include "fa100_fwd_softmax.cuh"
 
@@ -18,13 +19,17 @@ namespace fa100 {
 constexpr int kSplitSoftmaxWarps = 16;
 constexpr int kSplitMmaWarp = 16, kSplitLoadWarp = 17, kSplitPvWarp = 18;
 constexpr int kSplitThreads = 20 * 32;
-constexpr int kSplitExchangeBytes = kQTiles * 2 * kBlockM * 4;  // one fp32 row-sum slot per (tile, half, row)
+constexpr int kSplitExchangeBytes = kQTiles * 2 * kBlockM * 4;  // one fp32 slot per (tile, half, row)
 
 template <int HD, int ELT>
 struct FwdSmemSplit {
   using L = FwdSmem<HD, ELT, false>;
-  static constexpr int kExchangeOffset = L::kTotalBytes;
-  static constexpr int kTotalBytes = L::kTotalBytes + kSplitExchangeBytes;
+  // two sets of slots used alternately let a swap get by with ONE barrier (a thread's next write goes to the other set; by
+  // the time it returns to this one the peer has passed a later barrier, hence read it).  bf16 / fp16 at head dim 128 has
+  // 2 KB left in the 227 KB: one set, and a second barrier after the read.
+  static constexpr bool kDouble = L::kTotalBytes + 2 * kSplitExchangeBytes <= 227 * 1024;
+  static constexpr int kXchBytes = (kDouble ? 2 : 1) * kSplitExchangeBytes;
+  static constexpr int kTotalBytes = L::kTotalBytes + kXchBytes;
   static_assert(kTotalBytes <= 227 * 1024, "split kernel outgrew shared memory");
 };
 
@@ -54,15 +59,24 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
   const int half = warp >> 3, t = (warp >> 2) & 1, q = warp & 3;
   const int row = q * 32 + lane;
   const uint32_t tS = tmem + (uint32_t(q * 32) << 16);
-  const uint32_t tSown = tS + half * 64, tSoth = tS + (1 - half) * 64;
+  const uint32_t tSown = tS + half * 64;
   const uint32_t tP = tS + 128 + t * 64 + half * (FP8 ? 16 : 32);  // this thread's half of P_t (operand dtype)
   const uint32_t tO = tS + 256 + t * 128;
   constexpr int kOChunks = HD / 64;       // 32-column chunks of O per thread
   const int c0 = half * kOChunks;         // first of them
-  float* const my_slot = xch + (t * 2 + half) * kBlockM + row;
-  const float* const peer_slot = xch + (t * 2 + (1 - half)) * kBlockM + row;
+  constexpr bool kDouble = FwdSmemSplit<HD, ELT>::kDouble;
+  const int my_slot = (t * 2 + half) * kBlockM + row, peer_slot = (t * 2 + (1 - half)) * kBlockM + row;
   const int pair_bar = 3 + t * 4 + q;     // named barrier of the two warps that share these rows (ids 1, 2: the tiles' epilogues)
-  uint32_t s_it = 0, o_it = 0, pv_n = 0;
+  uint32_t s_it = 0, o_it = 0, pv_n = 0, xset = 0;
+  // hand v to the row's other thread and get its value (see FwdSmemSplit::kDouble for the one- / two-barrier forms)
+  auto pair_swap = [&](float v) -> float {
+    float* slots = xch + (kDouble ? xset * (kSplitExchangeBytes / 4) : 0);
+    slots[my_slot] = v;
+    named_bar_sync(pair_bar, 64);
+    const float o = slots[peer_slot];
+    if (kDouble) xset ^= 1; else named_bar_sync(pair_bar, 64);
+    return o;
+  };
   FA_PROF_DECL();
 
   const int n_work = total_work(p);
@@ -80,17 +94,6 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
       tc_fence_after();
       const int n0 = nb * kBlockN;
       const bool boundary = __any_sync(0xffffffffu, softcap || n0 + kBlockN > rg.col_hi || n0 < rg.col_lo);
-      // the other half's 64 scores: only their (raw, masked) maximum is kept
-      float m_raw;
-      {
-        uint32_t x[2][32];
-        tmem_ld32(tSoth, x[0]);
-        tmem_ld32(tSoth + 32, x[1]);
-        tmem_ld_wait();
-        const int oc = n0 + (1 - half) * 64;
-        m_raw = boundary ? fmaxf(chunk_max<true>(x[0], oc, rg.col_lo, rg.col_hi), chunk_max<true>(x[1], oc + 32, rg.col_lo, rg.col_hi))
-                         : fmaxf(chunk_max<false>(x[0], 0, 0, 0), chunk_max<false>(x[1], 0, 0, 0));
-      }
       uint32_t s[2][32];
       tmem_ld32(tSown, s[0]);
       tmem_ld32(tSown + 32, s[1]);
@@ -102,8 +105,9 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
       if (lane == 0) mbar_arrive(&bar->s_free);
       bool pv_drained = pv_n == 0;
       const int own0 = n0 + half * 64;
+      float m_raw;  // raw (pre-softcap), masked maximum: of this half, then of the row
       if (boundary) {
-        m_raw = fmaxf(m_raw, fmaxf(chunk_max<true>(s[0], own0, rg.col_lo, rg.col_hi), chunk_max<true>(s[1], own0 + 32, rg.col_lo, rg.col_hi)));
+        m_raw = fmaxf(chunk_max<true>(s[0], own0, rg.col_lo, rg.col_hi), chunk_max<true>(s[1], own0 + 32, rg.col_lo, rg.col_hi));
         // softcap first, then the mask (hopper/mainloop...:1073-1077)
         if (softcap) {
 #pragma unroll
@@ -119,10 +123,11 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
             if (col >= rg.col_hi || col < rg.col_lo) s[c][i] = 0xff800000u;  // -inf
           }
       } else {
-        m_raw = fmaxf(m_raw, fmaxf(chunk_max<false>(s[0], 0, 0, 0), chunk_max<false>(s[1], 0, 0, 0)));
+        m_raw = fmaxf(chunk_max<false>(s[0], 0, 0, 0), chunk_max<false>(s[1], 0, 0, 0));
       }
-      // Both threads of the row hold the same m_raw (a max over the same 128 values in any order is the same number) and
-      // apply the same function to it.  With softcap the reference point is tanh of the raw max: tanh.approx may differ
+      m_raw = fmaxf(m_raw, pair_swap(m_raw));
+      // Both threads of the row now hold the same m_raw (max of the same two numbers) and apply the same function to it.
+      // With softcap the reference point is tanh of the raw max: tanh.approx may differ
       // from the largest capped score by an ulp, which the lazy rescale (stale max, P up to 2^8) tolerates by design.
       const float m_blk = (softcap && m_raw != -INFINITY) ? fast_tanh(m_raw * rg.softcap_pre) : m_raw;
       FA_PROF(2);
@@ -202,9 +207,7 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
       if (FP8) out_scale = p.v_descale ? p.v_descale[g.it.bi * p.v_descale_batch_stride + g.hk * p.v_descale_head_stride] : 1.f;
       // the row sum is the sum of the halves' sums (same stale max in both, so they add without a rescale); a + b == b + a
       // exactly, so both threads normalise by the same number
-      *my_slot = l_run;
-      named_bar_sync(pair_bar, 64);
-      float l_tot = l_run + *peer_slot;
+      float l_tot = l_run + pair_swap(l_run);
       const bool dead_row = (l_tot == 0.f) || (l_tot != l_tot);
       const float inv = dead_row ? 0.f : out_scale / l_tot;
       if (FP8) l_tot *= exp2f(-kFp8Offset);
@@ -225,9 +228,8 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
           w_cur = __expf(lse_val - lse_new) * inv;
         } else w_cur = 0.f;
       }
-      // second meeting of the pair: the peer has read this thread's slot (it is rewritten at the next work item) and, when
-      // merging in place, the stored LSE that half 0 is about to replace
-      named_bar_sync(pair_bar, 64);
+      // when merging in place the peer must have read the stored LSE before half 0 replaces it
+      if (merging) named_bar_sync(pair_bar, 64);
       if (half == 0 && row_valid) {
         if (merging) { if (to_out) p.lse[li] = lse_new; else p.lse_accum[li] = lse_new; }
         else if (!split) p.lse[li] = lse_val;
@@ -358,7 +360,7 @@ fa100_fwd_split_kernel(const __grid_constant__ FwdKernelParams p, const __grid_c
   uint8_t* sKV = smem + L::kQSlots * L::kQBytes;
   uint8_t* sO = sKV + L::kStages * L::kKVBytes;
   float* xch = reinterpret_cast<float*>(smem + L::kDataBytes);
-  FwdBarriers* bar = reinterpret_cast<FwdBarriers*>(smem + L::kDataBytes + kSplitExchangeBytes);
+  FwdBarriers* bar = reinterpret_cast<FwdBarriers*>(smem + L::kDataBytes + FwdSmemSplit<HD, ELT>::kXchBytes);
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   FA_TRACE_BEGIN();
   if (smem_u32(smem) & 1023u) __trap();
