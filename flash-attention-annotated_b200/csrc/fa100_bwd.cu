@@ -29,7 +29,9 @@
 namespace fa100 {
 
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr int kBwdThreads = 128;
+constexpr int kBwdWorkerWarps = 8;                        // two threads per TMEM lane
+constexpr int kBwdProducerWarp = 8, kBwdMmaWarp = 9;
+constexpr int kBwdThreads = (kBwdWorkerWarps + 2) * 32;
 constexpr int kBwdTile = 128;                 // query rows / keys per tile
 constexpr int kBwdTileBytes = 128 * 128 * 2;  // one [128][128] 16-bit tile (two 64-column boxes)
 constexpr int kBwdBoxBytes = 128 * 128;       // one [128 rows][128 B] box
@@ -79,7 +81,10 @@ FA_DEVICE float bwd_prob(const BwdKernelParams& p, float s, float lse2, float& d
 struct BwdBarriers {
   uint64_t fixed_full;        // the tile(s) loaded once per CTA
   uint64_t full[2], empty[2]; // the two-stage ring of streamed tiles
-  uint64_t mma_s, mma_done;   // S / dP ready; accumulators final
+  uint64_t s_ready;           // S / dP of a step are in tensor memory (tcgen05.commit)
+  uint64_t regs_loaded;       // every worker warp holds the step's S / dP in registers (dQ kernel)
+  uint64_t ops_ready;         // every worker warp has stored the step's 16-bit operands (dS; P^T and dS^T)
+  uint64_t mma_done;          // accumulators final
   uint32_t tmem_base;
   uint32_t pad_[3];
 };
@@ -118,8 +123,21 @@ FA_DEVICE void bwd_load_tile(uint8_t* dst, const CUtensorMap* tm, uint64_t* bar,
   for (int hb = 0; hb < boxes; ++hb) tma_load_4d(dst + hb * kBwdBoxBytes, tm, bar, hb * 64, row0, head, batch);
 }
 
+// ----------------------------------------------------------------------------- roles shared by the two main kernels
+// 8 worker warps (two threads per TMEM lane: warp w and w + 4 own the same 32 rows and 64 of a step's 128 columns each), a
+// TMA warp and an MMA-issuing warp.  Hand-offs are mbarriers as in the forward kernel: s_ready (tcgen05.commit), regs_loaded
+// and ops_ready (one arrive per worker warp), full / empty for the two shared-memory stages.
+FA_DEVICE void bwd_warp_arrive(uint64_t* bar, int lane) {
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar);
+}
+FA_DEVICE float bwd_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
 // ----------------------------------------------------------------------------- dQ
-// TMEM: S @0 (128 fp32 columns; dS, 16 bit, is written over its columns [0, 64)), dP @128, dQ @256.
+// TMEM: S @0, dP @128 (fp32, 128 columns each), dQ @256, dS (16 bit, 64 columns) double-buffered @384 / @448.  With dS in its
+// own columns S and dP are free as soon as the workers hold them in registers, so the MMA warp computes the next block's S
+// and dP while the workers turn this block's into dS; the order in the tensor pipe is S,dP(n+1) | dQ(n) | S,dP(n+2) | ...
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                     const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
@@ -129,11 +147,12 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
   uint8_t* sK = smem + 2 * kBwdTileBytes;      // K stages 0, 1
   uint8_t* sV = smem + 4 * kBwdTileBytes;      // V stages 0, 1
   BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 6 * kBwdTileBytes);
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m_blk = blockIdx.x, hq = blockIdx.y, bi = blockIdx.z;
   const int hk = hq / (p.h / p.h_k);
   if (tid == 0) {
-    mbar_init(&bar->fixed_full, 1); mbar_init(&bar->mma_s, 1); mbar_init(&bar->mma_done, 1);
+    mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->mma_done, 1);
+    mbar_init(&bar->regs_loaded, kBwdWorkerWarps); mbar_init(&bar->ops_ready, kBwdWorkerWarps);
     for (int s = 0; s < 2; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
     fence_mbar_init();
   }
@@ -156,117 +175,142 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
   const int n_blocks = max(0, n_max - n_min);
   const uint32_t tile_tx = uint32_t(p.boxes) * kBwdBoxBytes;
 
-  const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);   // S = Q K^T, dP = dO V^T
-  const uint32_t idesc_dq = make_idesc(fmt, fmt, kBwdTile, p.n16, 0, 1);     // dQ += dS K (B = K tile, MN-major)
-  constexpr uint32_t kHi = sdesc_hi(1024);
-  constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboMN = sdesc_lo_lbo(kBwdBoxBytes);
-
-  if (tid == 0 && n_blocks > 0) {
-    mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
-    bwd_load_tile(sQ, &tmQ, &bar->fixed_full, p.boxes, sq_.q_off + row0, hq, sq_.bq);
-    bwd_load_tile(sdO, &tmdO, &bar->fixed_full, p.boxes, sq_.q_off + row0, hq, sq_.bq);
-    mbar_arrive_expect_tx(&bar->full[0], 2 * tile_tx);
-    bwd_load_tile(sK, &tmK, &bar->full[0], p.boxes, sq_.k_off + n_min * kBwdTile, hk, sq_.bk);
-    bwd_load_tile(sV, &tmV, &bar->full[0], p.boxes, sq_.k_off + n_min * kBwdTile, hk, sq_.bk);
-  }
-  // this thread's query row
-  const int i = row0 + tid;
-  const bool row_ok = i < sq_.sq;
-  float lse2 = INFINITY, dsum = 0.f;  // rows past the end and rows without keys (LSE = -inf) get P = 0
-  if (row_ok) {
-    const float l = p.lse[bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off + i];
-    lse2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
-    dsum = p.dsum[bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off + i];
-  }
-  const int col_hi = p.window_right >= 0 ? min(sq_.sk, i + 1 + shift + p.window_right) : sq_.sk;
-  const int col_lo = p.window_left >= 0 ? max(0, i + shift - p.window_left) : 0;
-  const uint32_t tRow = tmem + (uint32_t(warp * 32) << 16);
-
-  if (n_blocks > 0) mbar_wait(&bar->fixed_full, 0, 0xB0);
-  for (int nb = 0; nb < n_blocks; ++nb) {
-    const int st = nb & 1;
-    if (tid == 0 && nb + 1 < n_blocks) {  // prefetch the next K / V tiles into the other stage
-      const int s2 = st ^ 1;
-      if (nb + 1 >= 2) mbar_wait(&bar->empty[s2], ((nb + 1) / 2 - 1) & 1, 0xB1);
-      mbar_arrive_expect_tx(&bar->full[s2], 2 * tile_tx);
-      bwd_load_tile(sK + s2 * kBwdTileBytes, &tmK, &bar->full[s2], p.boxes, sq_.k_off + (n_min + nb + 1) * kBwdTile, hk, sq_.bk);
-      bwd_load_tile(sV + s2 * kBwdTileBytes, &tmV, &bar->full[s2], p.boxes, sq_.k_off + (n_min + nb + 1) * kBwdTile, hk, sq_.bk);
+  if (warp == kBwdProducerWarp) {
+    // ---- TMA: Q and dO once, K / V blocks through the two stages
+    if (lane == 0 && n_blocks > 0) {
+      mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
+      bwd_load_tile(sQ, &tmQ, &bar->fixed_full, p.boxes, sq_.q_off + row0, hq, sq_.bq);
+      bwd_load_tile(sdO, &tmdO, &bar->fixed_full, p.boxes, sq_.q_off + row0, hq, sq_.bq);
+      for (int nb = 0; nb < n_blocks; ++nb) {
+        const int st = nb & 1;
+        if (nb >= 2) mbar_wait(&bar->empty[st], (nb / 2 - 1) & 1, 0xB1);
+        mbar_arrive_expect_tx(&bar->full[st], 2 * tile_tx);
+        bwd_load_tile(sK + st * kBwdTileBytes, &tmK, &bar->full[st], p.boxes, sq_.k_off + (n_min + nb) * kBwdTile, hk, sq_.bk);
+        bwd_load_tile(sV + st * kBwdTileBytes, &tmV, &bar->full[st], p.boxes, sq_.k_off + (n_min + nb) * kBwdTile, hk, sq_.bk);
+      }
     }
-    mbar_wait(&bar->full[st], (nb / 2) & 1, 0xB2);
-    tc_fence_after();
-    if (tid == 0) {
+  } else if (warp == kBwdMmaWarp) {
+    // ---- MMA issue
+    if (lane == 0 && n_blocks > 0) {
+      const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);   // S = Q K^T, dP = dO V^T
+      const uint32_t idesc_dq = make_idesc(fmt, fmt, kBwdTile, p.n16, 0, 1);     // dQ += dS K (B = K tile, MN-major)
+      constexpr uint32_t kHi = sdesc_hi(1024);
+      constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboMN = sdesc_lo_lbo(kBwdBoxBytes);
       const uint32_t q_lo = (smem_u32(sQ) >> 4) | kLboK, do_lo = (smem_u32(sdO) >> 4) | kLboK;
-      const uint32_t k_lo = (smem_u32(sK + st * kBwdTileBytes) >> 4) | kLboK, v_lo = (smem_u32(sV + st * kBwdTileBytes) >> 4) | kLboK;
-      for (int ks = 0; ks < p.slices; ++ks) {
-        const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-        mma_ss<false>(tmem, q_lo + off, k_lo + off, kHi, idesc_s, ks > 0);
-      }
-      for (int ks = 0; ks < p.slices; ++ks) {
-        const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-        mma_ss<false>(tmem + 128, do_lo + off, v_lo + off, kHi, idesc_s, ks > 0);
-      }
-      tc_commit(&bar->mma_s);
-    }
-    mbar_wait(&bar->mma_s, nb & 1, 0xB3);
-    tc_fence_after();
-    // dS = P o (dP - D), 64 key columns at a time; written (16 bit) over S's columns [0, 64)
-    const int n0 = (n_min + nb) * kBwdTile;
-#pragma unroll
-    for (int hf = 0; hf < 2; ++hf) {
-      uint32_t s[2][32], dp[2][32], pk[32];
-      tmem_ld32(tRow + hf * 64, s[0]); tmem_ld32(tRow + hf * 64 + 32, s[1]);
-      tmem_ld32(tRow + 128 + hf * 64, dp[0]); tmem_ld32(tRow + 128 + hf * 64 + 32, dp[1]);
-      tmem_ld_wait();
-#pragma unroll
-      for (int c = 0; c < 2; ++c)
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          float ds[2];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int col = n0 + hf * 64 + c * 32 + j + e;
-            float dfac = 0.f;
-            const float pr = (col < col_hi && col >= col_lo) ? bwd_prob(p, __uint_as_float(s[c][j + e]), lse2, dfac) : 0.f;
-            ds[e] = pr * (__uint_as_float(dp[c][j + e]) - dsum) * dfac;
-          }
-          pk[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+      auto issue_s_dp = [&](int nb) {
+        const int st = nb & 1;
+        mbar_wait(&bar->full[st], (nb / 2) & 1, 0xB2);
+        tc_fence_after();
+        const uint32_t k_lo = (smem_u32(sK + st * kBwdTileBytes) >> 4) | kLboK, v_lo = (smem_u32(sV + st * kBwdTileBytes) >> 4) | kLboK;
+        for (int ks = 0; ks < p.slices; ++ks) {
+          const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+          mma_ss<false>(tmem, q_lo + off, k_lo + off, kHi, idesc_s, ks > 0);
         }
-      // all four S loads of this half are in registers before dS lands on S's columns [32 hf, 32 hf + 32)
-      tmem_st32(tRow + hf * 32, pk);
+        for (int ks = 0; ks < p.slices; ++ks) {
+          const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+          mma_ss<false>(tmem + 128, do_lo + off, v_lo + off, kHi, idesc_s, ks > 0);
+        }
+        tc_commit(&bar->s_ready);
+      };
+      mbar_wait(&bar->fixed_full, 0, 0xB0);
+      issue_s_dp(0);
+      for (int nb = 0; nb < n_blocks; ++nb) {
+        const int st = nb & 1;
+        if (nb + 1 < n_blocks) {
+          mbar_wait(&bar->regs_loaded, nb & 1, 0xB5);  // S / dP of block nb are in the workers' registers
+          issue_s_dp(nb + 1);
+        }
+        mbar_wait(&bar->ops_ready, nb & 1, 0xB6);      // dS of block nb is in its buffer
+        tc_fence_after();
+        const uint32_t k_mn = (smem_u32(sK + st * kBwdTileBytes) >> 4) | kLboMN;
+        const uint32_t t_ds = tmem + 384 + st * 64;
+        for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 keys, 16 per slice
+          mma_ts<false>(tmem + 256, t_ds + ks * 8, k_mn + ks * (16 * 128 >> 4), kHi, idesc_dq, (nb > 0 || ks > 0));
+        tc_commit(&bar->empty[st]);
+        if (nb == n_blocks - 1) tc_commit(&bar->mma_done);
+      }
     }
-    tmem_st_wait();
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    if (tid == 0) {
-      const uint32_t k_mn = (smem_u32(sK + st * kBwdTileBytes) >> 4) | kLboMN;
-      for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 keys, 16 per slice
-        mma_ts<false>(tmem + 256, tmem + ks * 8, k_mn + ks * (16 * 128 >> 4), kHi, idesc_dq, (nb > 0 || ks > 0));
-      tc_commit(&bar->empty[st]);
-      if (nb == n_blocks - 1) tc_commit(&bar->mma_done);
-    }
-  }
-  // dQ = scale * accumulator
-  if (n_blocks > 0) { mbar_wait(&bar->mma_done, 0, 0xB4); tc_fence_after(); }
-  uint16_t* dst = reinterpret_cast<uint16_t*>(p.dq) + sq_.bq * p.dq_batch_stride + int64_t(sq_.q_off + i) * p.dq_row_stride + hq * p.dq_head_stride;
-  for (int c = 0; c < 4; ++c) {
-    if (c * 32 >= p.d) break;
-    uint32_t o[32];
-    if (n_blocks > 0) { tmem_ld32(tRow + 256 + c * 32, o); tmem_ld_wait(); }
-    else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) o[j] = 0u;
-    }
+  } else {
+    // ---- workers: this thread's query row and its 64 of a block's 128 key columns
+    const int q4 = warp & 3, half = warp >> 2;
+    const int i = row0 + q4 * 32 + lane;
+    const bool row_ok = i < sq_.sq;
+    float lse2 = INFINITY, dsum = 0.f;  // rows past the end and rows without keys (LSE = -inf) get P = 0
     if (row_ok) {
+      const float l = p.lse[bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off + i];
+      lse2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
+      dsum = p.dsum[bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off + i];
+    }
+    const int col_hi = p.window_right >= 0 ? min(sq_.sk, i + 1 + shift + p.window_right) : sq_.sk;
+    const int col_lo = p.window_left >= 0 ? max(0, i + shift - p.window_left) : 0;
+    const uint32_t tRow = tmem + (uint32_t(q4 * 32) << 16);
+    const float neg_lse2 = -lse2;
+
+    for (int nb = 0; nb < n_blocks; ++nb) {
+      mbar_wait(&bar->s_ready, nb & 1, 0xB3);
+      tc_fence_after();
+      uint32_t s[2][32], dp[2][32], pk[32];
+      tmem_ld32(tRow + half * 64, s[0]); tmem_ld32(tRow + half * 64 + 32, s[1]);
+      tmem_ld32(tRow + 128 + half * 64, dp[0]); tmem_ld32(tRow + 128 + half * 64 + 32, dp[1]);
+      tmem_ld_wait();
+      bwd_warp_arrive(&bar->regs_loaded, lane);
+      const int n0 = (n_min + nb) * kBwdTile;
+      // every row of the tile sees every key of the block and there is no softcap: the lean path (CTA-uniform test)
+      const bool lean = p.softcap_pre == 0.f && n0 + kBwdTile <= sq_.sk &&
+                        (p.window_right < 0 || n0 + kBwdTile <= row0 + 1 + shift + p.window_right) &&
+                        (p.window_left < 0 || n0 >= row0 + kBwdTile - 1 + shift - p.window_left);
+      if (lean) {
 #pragma unroll
-      for (int v8 = 0; v8 < 4; ++v8)
-        if (c * 32 + v8 * 8 < p.d) {
-          uint4 u;
-          uint32_t* up = reinterpret_cast<uint32_t*>(&u);
+        for (int c = 0; c < 2; ++c)
 #pragma unroll
-          for (int e = 0; e < 4; ++e) up[e] = bwd_pack(__uint_as_float(o[v8 * 8 + 2 * e]) * p.scale, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * p.scale, p.f16);
-          *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = u;
-        }
+          for (int j = 0; j < 32; j += 2) {
+            const float p0 = bwd_ex2(fmaf(__uint_as_float(s[c][j]), p.scale_log2, neg_lse2));
+            const float p1 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 1]), p.scale_log2, neg_lse2));
+            pk[c * 16 + j / 2] = bwd_pack(p0 * (__uint_as_float(dp[c][j]) - dsum), p1 * (__uint_as_float(dp[c][j + 1]) - dsum), p.f16);
+          }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            float ds[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int col = n0 + half * 64 + c * 32 + j + e;
+              float dfac = 0.f;
+              const float pr = (col < col_hi && col >= col_lo) ? bwd_prob(p, __uint_as_float(s[c][j + e]), lse2, dfac) : 0.f;
+              ds[e] = pr * (__uint_as_float(dp[c][j + e]) - dsum) * dfac;
+            }
+            pk[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+          }
+      }
+      // keys [64 half, +64) of the block are columns [32 half, +32) of the 16-bit dS buffer
+      tmem_st32(tRow + 384 + (nb & 1) * 64 + half * 32, pk);
+      tmem_st_wait();
+      bwd_warp_arrive(&bar->ops_ready, lane);
+    }
+    // dQ = scale * accumulator; each thread stores its half of the columns
+    if (n_blocks > 0) { mbar_wait(&bar->mma_done, 0, 0xB4); tc_fence_after(); }
+    uint16_t* dst = reinterpret_cast<uint16_t*>(p.dq) + sq_.bq * p.dq_batch_stride + int64_t(sq_.q_off + i) * p.dq_row_stride + hq * p.dq_head_stride;
+    for (int c = half * 2; c < half * 2 + 2; ++c) {
+      if (c * 32 >= p.d) break;
+      uint32_t o[32];
+      if (n_blocks > 0) { tmem_ld32(tRow + 256 + c * 32, o); tmem_ld_wait(); }
+      else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[j] = 0u;
+      }
+      if (row_ok) {
+#pragma unroll
+        for (int v8 = 0; v8 < 4; ++v8)
+          if (c * 32 + v8 * 8 < p.d) {
+            uint4 u;
+            uint32_t* up = reinterpret_cast<uint32_t*>(&u);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) up[e] = bwd_pack(__uint_as_float(o[v8 * 8 + 2 * e]) * p.scale, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * p.scale, p.f16);
+            *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = u;
+          }
+      }
     }
   }
   tc_fence_before();
@@ -276,7 +320,8 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
 
 // ----------------------------------------------------------------------------- dK, dV
 // TMEM: S^T @0 (keys on the lanes, 128 query columns; P^T, 16 bit, is written over its columns [0, 64)), dP^T @128 (dS^T over its
-// columns [0, 64)), dK @256, dV @384.  One CTA per (key block, KV head, batch); the steps run over (query head of the group,
+// columns [0, 64)), dK @256, dV @384 -- all 512 columns, so S^T / dP^T cannot be double-buffered and a step is tensor work,
+// elementwise work, tensor work in turn.  One CTA per (key block, KV head, batch); the steps run over (query head of the group,
 // query block) and all accumulate into the same dK / dV, which is the GQA reduction.
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
@@ -286,14 +331,15 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   uint8_t* sV = smem + kBwdTileBytes;          // V tile
   uint8_t* sQ = smem + 2 * kBwdTileBytes;      // Q stages 0, 1
   uint8_t* sdO = smem + 4 * kBwdTileBytes;     // dO stages 0, 1
-  float* sL = reinterpret_cast<float*>(smem + 6 * kBwdTileBytes);  // LSE * log2(e) of the step's 128 query rows
-  float* sD = sL + kBwdTile;                                        // D of the same rows
-  BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 6 * kBwdTileBytes + 2 * kBwdTile * 4);
-  const int tid = threadIdx.x, warp = tid >> 5;
+  float* sL = reinterpret_cast<float*>(smem + 6 * kBwdTileBytes);  // [2][128] -LSE * log2(e) of a step's query rows (two steps in flight)
+  float* sD = sL + 2 * kBwdTile;                                    // [2][128] D of the same rows
+  BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 6 * kBwdTileBytes + 4 * kBwdTile * 4);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n_blk = blockIdx.x, hk = blockIdx.y, bi = blockIdx.z;
   const int G = p.h / p.h_k;
   if (tid == 0) {
-    mbar_init(&bar->fixed_full, 1); mbar_init(&bar->mma_s, 1); mbar_init(&bar->mma_done, 1);
+    mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->mma_done, 1);
+    mbar_init(&bar->regs_loaded, kBwdWorkerWarps); mbar_init(&bar->ops_ready, kBwdWorkerWarps);
     for (int s_ = 0; s_ < 2; ++s_) { mbar_init(&bar->full[s_], 1); mbar_init(&bar->empty[s_], 1); }
     fence_mbar_init();
   }
@@ -320,127 +366,157 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   const int per_head = max(0, m_hi - m_lo);
   const int steps = per_head * G;
   const uint32_t tile_tx = uint32_t(p.boxes) * kBwdBoxBytes;
-  const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);
-  const uint32_t idesc_acc = make_idesc(fmt, fmt, kBwdTile, p.n16, 0, 1);
-  constexpr uint32_t kHi = sdesc_hi(1024);
-  constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboMN = sdesc_lo_lbo(kBwdBoxBytes);
 
-  auto load_step = [&](int t, int st) {
-    const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
-    mbar_arrive_expect_tx(&bar->full[st], 2 * tile_tx);
-    bwd_load_tile(sQ + st * kBwdTileBytes, &tmQ, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
-    bwd_load_tile(sdO + st * kBwdTileBytes, &tmdO, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
-  };
-  if (tid == 0 && steps > 0) {
-    mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
-    bwd_load_tile(sK, &tmK, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
-    bwd_load_tile(sV, &tmV, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
-    load_step(0, 0);
-  }
-  const int kj = n0 + tid;  // this thread's key row
-  const uint32_t tRow = tmem + (uint32_t(warp * 32) << 16);
-
-  if (steps > 0) mbar_wait(&bar->fixed_full, 0, 0xC0);
-  for (int t = 0; t < steps; ++t) {
-    const int st = t & 1;
-    const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
-    if (tid == 0 && t + 1 < steps) {
-      const int s2 = st ^ 1;
-      if (t + 1 >= 2) mbar_wait(&bar->empty[s2], ((t + 1) / 2 - 1) & 1, 0xC1);
-      load_step(t + 1, s2);
+  if (warp == kBwdProducerWarp) {
+    if (lane == 0 && steps > 0) {
+      mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
+      bwd_load_tile(sK, &tmK, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
+      bwd_load_tile(sV, &tmV, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
+      for (int t = 0; t < steps; ++t) {
+        const int st = t & 1;
+        const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
+        if (t >= 2) mbar_wait(&bar->empty[st], (t / 2 - 1) & 1, 0xC1);
+        mbar_arrive_expect_tx(&bar->full[st], 2 * tile_tx);
+        bwd_load_tile(sQ + st * kBwdTileBytes, &tmQ, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
+        bwd_load_tile(sdO + st * kBwdTileBytes, &tmdO, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
+      }
     }
-    {  // the step's per-query-row constants (the previous step's readers are past its __syncthreads)
+  } else if (warp == kBwdMmaWarp) {
+    if (lane == 0 && steps > 0) {
+      const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);
+      const uint32_t idesc_acc = make_idesc(fmt, fmt, kBwdTile, p.n16, 0, 1);
+      constexpr uint32_t kHi = sdesc_hi(1024);
+      constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboMN = sdesc_lo_lbo(kBwdBoxBytes);
+      const uint32_t k_lo = (smem_u32(sK) >> 4) | kLboK, v_lo = (smem_u32(sV) >> 4) | kLboK;
+      mbar_wait(&bar->fixed_full, 0, 0xC0);
+      for (int t = 0; t < steps; ++t) {
+        const int st = t & 1;
+        mbar_wait(&bar->full[st], (t / 2) & 1, 0xC2);
+        tc_fence_after();
+        const uint32_t q_lo = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboK, do_lo = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboK;
+        // behind dV / dK of the previous step in the in-order tensor pipe, so P^T / dS^T of that step are read before S^T lands on them
+        for (int ks = 0; ks < p.slices; ++ks) {
+          const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+          mma_ss<false>(tmem, k_lo + off, q_lo + off, kHi, idesc_s, ks > 0);           // S^T = K Q^T
+        }
+        for (int ks = 0; ks < p.slices; ++ks) {
+          const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+          mma_ss<false>(tmem + 128, v_lo + off, do_lo + off, kHi, idesc_s, ks > 0);    // dP^T = V dO^T
+        }
+        tc_commit(&bar->s_ready);
+        mbar_wait(&bar->ops_ready, t & 1, 0xC5);
+        tc_fence_after();
+        const uint32_t do_mn = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboMN, q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
+        for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step
+          mma_ts<false>(tmem + 384, tmem + ks * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));        // dV += P^T dO
+        for (int ks = 0; ks < 8; ++ks)
+          mma_ts<false>(tmem + 256, tmem + 128 + ks * 8, q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));   // dK += dS^T Q
+        tc_commit(&bar->empty[st]);
+        if (t == steps - 1) tc_commit(&bar->mma_done);
+      }
+    }
+  } else {
+    // ---- workers: this thread's key row and its 64 of a step's 128 query columns
+    const int q4 = warp & 3, half = warp >> 2;
+    const int kj = n0 + q4 * 32 + lane;
+    const uint32_t tRow = tmem + (uint32_t(q4 * 32) << 16);
+    // -LSE * log2(e) and D of a step's query rows, fetched one step ahead by the first four worker warps
+    auto fetch_rows = [&](int t, float& l2, float& ds_) {
+      const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
       const int i = m * kBwdTile + tid;
-      float l2 = INFINITY, ds_ = 0.f;
+      l2 = -INFINITY; ds_ = 0.f;   // rows past the end and rows without keys (LSE = -inf): P = exp2(-inf) = 0
       if (i < sq_.sq) {
         const float l = p.lse[bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off + i];
-        l2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
+        l2 = (l == -INFINITY) ? -INFINITY : -l * kLog2e;
         ds_ = p.dsum[bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off + i];
       }
-      sL[tid] = l2; sD[tid] = ds_;
-    }
-    mbar_wait(&bar->full[st], (t / 2) & 1, 0xC2);
-    tc_fence_after();
-    if (tid == 0) {
-      const uint32_t k_lo = (smem_u32(sK) >> 4) | kLboK, v_lo = (smem_u32(sV) >> 4) | kLboK;
-      const uint32_t q_lo = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboK, do_lo = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboK;
-      for (int ks = 0; ks < p.slices; ++ks) {
-        const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-        mma_ss<false>(tmem, k_lo + off, q_lo + off, kHi, idesc_s, ks > 0);           // S^T = K Q^T
-      }
-      for (int ks = 0; ks < p.slices; ++ks) {
-        const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-        mma_ss<false>(tmem + 128, v_lo + off, do_lo + off, kHi, idesc_s, ks > 0);    // dP^T = V dO^T
-      }
-      tc_commit(&bar->mma_s);
-    }
-    __syncthreads();  // sL / sD visible
-    mbar_wait(&bar->mma_s, t & 1, 0xC3);
-    tc_fence_after();
-    const int i0 = m * kBwdTile;
-#pragma unroll
-    for (int qt = 0; qt < 4; ++qt) {  // 32 query columns at a time
-      uint32_t s[32], dp[32], pkp[16], pks[16];
-      tmem_ld32(tRow + qt * 32, s);
-      tmem_ld32(tRow + 128 + qt * 32, dp);
+    };
+    if (tid < kBwdTile && steps > 0) { float l2, ds_; fetch_rows(0, l2, ds_); sL[tid] = l2; sD[tid] = ds_; }
+    for (int t = 0; t < steps; ++t) {
+      const int m = m_lo + t % per_head;
+      const float* nl = sL + (t & 1) * kBwdTile + half * 64;
+      const float* dd = sD + (t & 1) * kBwdTile + half * 64;
+      float nl2 = 0.f, nds = 0.f;
+      const bool fetch = tid < kBwdTile && t + 1 < steps;
+      if (fetch) fetch_rows(t + 1, nl2, nds);   // in flight during this step's arithmetic
+      mbar_wait(&bar->s_ready, t & 1, 0xC3);
+      tc_fence_after();
+      uint32_t s[2][32], dp[2][32];
+      tmem_ld32(tRow + half * 64, s[0]); tmem_ld32(tRow + half * 64 + 32, s[1]);
+      tmem_ld32(tRow + 128 + half * 64, dp[0]); tmem_ld32(tRow + 128 + half * 64 + 32, dp[1]);
       tmem_ld_wait();
+      // every worker holds its scores (P^T / dS^T may now land on them) and this step's row constants are visible
+      named_bar_sync(1, kBwdWorkerWarps * 32);
+      const int i0 = m * kBwdTile;
+      // every key of the tile is visible from every query row of the step, no softcap: the lean path (CTA-uniform)
+      const bool lean = p.softcap_pre == 0.f && (p.window_right < 0 || n0 + kBwdTile - 1 <= i0 + shift + p.window_right) &&
+                        (p.window_left < 0 || n0 >= i0 + kBwdTile - 1 + shift - p.window_left);
+      uint32_t pkp[32], pks[32];
+      if (lean) {
 #pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        float pr[2], ds[2];
+        for (int c = 0; c < 2; ++c)
 #pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int col = qt * 32 + j + e;
-          const int pos = i0 + col + shift;  // the key on this row's diagonal
-          const bool vis = (p.window_right < 0 || kj <= pos + p.window_right) && (p.window_left < 0 || kj >= pos - p.window_left);
-          float dfac = 0.f;
-          pr[e] = vis ? bwd_prob(p, __uint_as_float(s[j + e]), sL[col], dfac) : 0.f;
-          ds[e] = pr[e] * (__uint_as_float(dp[j + e]) - sD[col]) * dfac;
-        }
-        pkp[j / 2] = bwd_pack(pr[0], pr[1], p.f16);
-        pks[j / 2] = bwd_pack(ds[0], ds[1], p.f16);
-      }
-      tmem_st16(tRow + qt * 16, pkp);        // P^T over S^T's consumed columns
-      tmem_st16(tRow + 128 + qt * 16, pks);  // dS^T over dP^T's consumed columns
-    }
-    tmem_st_wait();
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    if (tid == 0) {
-      const uint32_t do_mn = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboMN, q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
-      for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step
-        mma_ts<false>(tmem + 384, tmem + ks * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));        // dV += P^T dO
-      for (int ks = 0; ks < 8; ++ks)
-        mma_ts<false>(tmem + 256, tmem + 128 + ks * 8, q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));   // dK += dS^T Q
-      tc_commit(&bar->empty[st]);
-      if (t == steps - 1) tc_commit(&bar->mma_done);
-    }
-  }
-  if (steps > 0) { mbar_wait(&bar->mma_done, 0, 0xC4); tc_fence_after(); }
-  const bool row_ok = kj < sq_.sk;
-  uint16_t* dk_dst = reinterpret_cast<uint16_t*>(p.dk) + sq_.bk * p.dk_batch_stride + int64_t(sq_.k_off + kj) * p.dk_row_stride + hk * p.dk_head_stride;
-  uint16_t* dv_dst = reinterpret_cast<uint16_t*>(p.dv) + sq_.bk * p.dv_batch_stride + int64_t(sq_.k_off + kj) * p.dv_row_stride + hk * p.dv_head_stride;
-  for (int which = 0; which < 2; ++which) {
-    uint16_t* dst = which == 0 ? dk_dst : dv_dst;
-    const float sc = which == 0 ? p.scale : 1.0f;
-    for (int c = 0; c < 4; ++c) {
-      if (c * 32 >= p.d) break;
-      uint32_t o[32];
-      if (steps > 0) { tmem_ld32(tRow + 256 + which * 128 + c * 32, o); tmem_ld_wait(); }
-      else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) o[j] = 0u;
-      }
-      if (row_ok) {
-#pragma unroll
-        for (int v8 = 0; v8 < 4; ++v8)
-          if (c * 32 + v8 * 8 < p.d) {
-            uint4 u;
-            uint32_t* up = reinterpret_cast<uint32_t*>(&u);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) up[e] = bwd_pack(__uint_as_float(o[v8 * 8 + 2 * e]) * sc, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * sc, p.f16);
-            *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = u;
+          for (int j = 0; j < 32; j += 4) {
+            const float4 l4 = *reinterpret_cast<const float4*>(nl + c * 32 + j), d4 = *reinterpret_cast<const float4*>(dd + c * 32 + j);
+            const float p0 = bwd_ex2(fmaf(__uint_as_float(s[c][j]), p.scale_log2, l4.x)), p1 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 1]), p.scale_log2, l4.y));
+            const float p2 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 2]), p.scale_log2, l4.z)), p3 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 3]), p.scale_log2, l4.w));
+            pkp[c * 16 + j / 2] = bwd_pack(p0, p1, p.f16);
+            pkp[c * 16 + j / 2 + 1] = bwd_pack(p2, p3, p.f16);
+            pks[c * 16 + j / 2] = bwd_pack(p0 * (__uint_as_float(dp[c][j]) - d4.x), p1 * (__uint_as_float(dp[c][j + 1]) - d4.y), p.f16);
+            pks[c * 16 + j / 2 + 1] = bwd_pack(p2 * (__uint_as_float(dp[c][j + 2]) - d4.z), p3 * (__uint_as_float(dp[c][j + 3]) - d4.w), p.f16);
           }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            float pr[2], ds[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int col = c * 32 + j + e;
+              const int pos = i0 + half * 64 + col + shift;  // the key on this query row's diagonal
+              const bool vis = (p.window_right < 0 || kj <= pos + p.window_right) && (p.window_left < 0 || kj >= pos - p.window_left);
+              float dfac = 0.f;
+              pr[e] = vis ? bwd_prob(p, __uint_as_float(s[c][j + e]), -nl[col], dfac) : 0.f;
+              ds[e] = pr[e] * (__uint_as_float(dp[c][j + e]) - dd[col]) * dfac;
+            }
+            pkp[c * 16 + j / 2] = bwd_pack(pr[0], pr[1], p.f16);
+            pks[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+          }
+      }
+      // query columns [64 half, +64) are columns [32 half, +32) of the 16-bit operands
+      tmem_st32(tRow + half * 32, pkp);        // P^T over S^T's consumed columns
+      tmem_st32(tRow + 128 + half * 32, pks);  // dS^T over dP^T's consumed columns
+      if (fetch) { sL[((t + 1) & 1) * kBwdTile + tid] = nl2; sD[((t + 1) & 1) * kBwdTile + tid] = nds; }  // read after the next step's barrier
+      tmem_st_wait();
+      bwd_warp_arrive(&bar->ops_ready, lane);
+    }
+    if (steps > 0) { mbar_wait(&bar->mma_done, 0, 0xC4); tc_fence_after(); }
+    const bool row_ok = kj < sq_.sk;
+    uint16_t* dk_dst = reinterpret_cast<uint16_t*>(p.dk) + sq_.bk * p.dk_batch_stride + int64_t(sq_.k_off + kj) * p.dk_row_stride + hk * p.dk_head_stride;
+    uint16_t* dv_dst = reinterpret_cast<uint16_t*>(p.dv) + sq_.bk * p.dv_batch_stride + int64_t(sq_.k_off + kj) * p.dv_row_stride + hk * p.dv_head_stride;
+    for (int which = 0; which < 2; ++which) {
+      uint16_t* dst = which == 0 ? dk_dst : dv_dst;
+      const float sc = which == 0 ? p.scale : 1.0f;
+      for (int c = half * 2; c < half * 2 + 2; ++c) {
+        if (c * 32 >= p.d) break;
+        uint32_t o[32];
+        if (steps > 0) { tmem_ld32(tRow + 256 + which * 128 + c * 32, o); tmem_ld_wait(); }
+        else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) o[j] = 0u;
+        }
+        if (row_ok) {
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8)
+            if (c * 32 + v8 * 8 < p.d) {
+              uint4 u;
+              uint32_t* up = reinterpret_cast<uint32_t*>(&u);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) up[e] = bwd_pack(__uint_as_float(o[v8 * 8 + 2 * e]) * sc, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * sc, p.f16);
+              *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = u;
+            }
+        }
       }
     }
   }
@@ -504,7 +580,7 @@ static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
   if ((rc = tm4(&tmV, p->v, rows_k, p->h_k, p->v_row_stride, p->v_head_stride, p->v_batch_stride, varlen_k))) return rc;
 
   // the 192 KB of dynamic shared memory are an opt-in per device
-  constexpr int kSmemDq = 6 * kBwdTileBytes + 256, kSmemDkdv = 6 * kBwdTileBytes + 2 * kBwdTile * 4 + 256;
+  constexpr int kSmemDq = 6 * kBwdTileBytes + 256, kSmemDkdv = 6 * kBwdTileBytes + 4 * kBwdTile * 4 + 256;
   static std::atomic<uint64_t> attr_set[2] = {{0}, {0}};
   int dev = 0;
   FA_CUDA(cudaGetDevice(&dev));
