@@ -80,7 +80,8 @@ FA_DEVICE float bwd_prob(const BwdKernelParams& p, float s, float lse2, float& d
 
 struct BwdBarriers {
   uint64_t fixed_full;        // the tile(s) loaded once per CTA
-  uint64_t full[2], empty[2]; // the two-stage ring of streamed tiles
+  uint64_t full[3], empty[3]; // ring of streamed tiles (dQ kernel: three K stages; dK/dV kernel: two Q + dO stages)
+  uint64_t v_full[2], v_empty[2];  // dQ kernel: the V ring
   uint64_t s_ready;           // S / dP of a step are in tensor memory (tcgen05.commit)
   uint64_t regs_loaded;       // every worker warp holds the step's S / dP in registers (dQ kernel)
   uint64_t ops_ready;         // every worker warp has stored the step's 16-bit operands (dS; P^T and dS^T)
@@ -144,16 +145,17 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sQ = smem;                          // Q tile
   uint8_t* sdO = smem + kBwdTileBytes;         // dO tile
-  uint8_t* sK = smem + 2 * kBwdTileBytes;      // K stages 0, 1
-  uint8_t* sV = smem + 4 * kBwdTileBytes;      // V stages 0, 1
-  BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 6 * kBwdTileBytes);
+  uint8_t* sK = smem + 2 * kBwdTileBytes;      // K stages 0, 1, 2: a K block is read twice, by S (early) and by dQ (one block later)
+  uint8_t* sV = smem + 5 * kBwdTileBytes;      // V stages 0, 1: released as soon as dP is computed
+  BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 7 * kBwdTileBytes);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m_blk = blockIdx.x, hq = blockIdx.y, bi = blockIdx.z;
   const int hk = hq / (p.h / p.h_k);
   if (tid == 0) {
     mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->mma_done, 1);
     mbar_init(&bar->regs_loaded, kBwdWorkerWarps); mbar_init(&bar->ops_ready, kBwdWorkerWarps);
-    for (int s = 0; s < 2; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
+    for (int s = 0; s < 3; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bar->v_full[s], 1); mbar_init(&bar->v_empty[s], 1); }
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc(&bar->tmem_base, 512); tmem_relinquish(); }
@@ -182,52 +184,66 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
       bwd_load_tile(sQ, &tmQ, &bar->fixed_full, p.boxes, sq_.q_off + row0, hq, sq_.bq);
       bwd_load_tile(sdO, &tmdO, &bar->fixed_full, p.boxes, sq_.q_off + row0, hq, sq_.bq);
       for (int nb = 0; nb < n_blocks; ++nb) {
-        const int st = nb & 1;
-        if (nb >= 2) mbar_wait(&bar->empty[st], (nb / 2 - 1) & 1, 0xB1);
-        mbar_arrive_expect_tx(&bar->full[st], 2 * tile_tx);
-        bwd_load_tile(sK + st * kBwdTileBytes, &tmK, &bar->full[st], p.boxes, sq_.k_off + (n_min + nb) * kBwdTile, hk, sq_.bk);
-        bwd_load_tile(sV + st * kBwdTileBytes, &tmV, &bar->full[st], p.boxes, sq_.k_off + (n_min + nb) * kBwdTile, hk, sq_.bk);
+        const int ks = nb % 3, vs = nb & 1;
+        if (nb >= 3) mbar_wait(&bar->empty[ks], (nb / 3 - 1) & 1, 0xB1);
+        mbar_arrive_expect_tx(&bar->full[ks], tile_tx);
+        bwd_load_tile(sK + ks * kBwdTileBytes, &tmK, &bar->full[ks], p.boxes, sq_.k_off + (n_min + nb) * kBwdTile, hk, sq_.bk);
+        if (nb >= 2) mbar_wait(&bar->v_empty[vs], (nb / 2 - 1) & 1, 0xB7);
+        mbar_arrive_expect_tx(&bar->v_full[vs], tile_tx);
+        bwd_load_tile(sV + vs * kBwdTileBytes, &tmV, &bar->v_full[vs], p.boxes, sq_.k_off + (n_min + nb) * kBwdTile, hk, sq_.bk);
       }
     }
   } else if (warp == kBwdMmaWarp) {
-    // ---- MMA issue
-    if (lane == 0 && n_blocks > 0) {
+    // ---- MMA issue: the whole warp runs the control flow and the waits, one elected lane issues (descriptors stay in
+    // uniform registers, no divergence code around the MMAs -- the forward kernel's idiom)
+    if (n_blocks > 0) {
       const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);   // S = Q K^T, dP = dO V^T
       const uint32_t idesc_dq = make_idesc(fmt, fmt, kBwdTile, p.n16, 0, 1);     // dQ += dS K (B = K tile, MN-major)
       constexpr uint32_t kHi = sdesc_hi(1024);
       constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboMN = sdesc_lo_lbo(kBwdBoxBytes);
       const uint32_t q_lo = (smem_u32(sQ) >> 4) | kLboK, do_lo = (smem_u32(sdO) >> 4) | kLboK;
       auto issue_s_dp = [&](int nb) {
-        const int st = nb & 1;
-        mbar_wait(&bar->full[st], (nb / 2) & 1, 0xB2);
+        const int kst = nb % 3, vst = nb & 1;
+        mbar_wait(&bar->full[kst], (nb / 3) & 1, 0xB2);
+        mbar_wait(&bar->v_full[vst], (nb / 2) & 1, 0xB8);
         tc_fence_after();
-        const uint32_t k_lo = (smem_u32(sK + st * kBwdTileBytes) >> 4) | kLboK, v_lo = (smem_u32(sV + st * kBwdTileBytes) >> 4) | kLboK;
-        for (int ks = 0; ks < p.slices; ++ks) {
-          const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-          mma_ss<false>(tmem, q_lo + off, k_lo + off, kHi, idesc_s, ks > 0);
+        if (elect_one()) {
+          const uint32_t k_lo = (smem_u32(sK + kst * kBwdTileBytes) >> 4) | kLboK, v_lo = (smem_u32(sV + vst * kBwdTileBytes) >> 4) | kLboK;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+            if (ks < p.slices) mma_ss<false>(tmem, q_lo + off, k_lo + off, kHi, idesc_s, ks > 0);
+          }
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+            if (ks < p.slices) mma_ss<false>(tmem + 128, do_lo + off, v_lo + off, kHi, idesc_s, ks > 0);
+          }
+          tc_commit(&bar->s_ready);
+          tc_commit(&bar->v_empty[vst]);
         }
-        for (int ks = 0; ks < p.slices; ++ks) {
-          const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-          mma_ss<false>(tmem + 128, do_lo + off, v_lo + off, kHi, idesc_s, ks > 0);
-        }
-        tc_commit(&bar->s_ready);
+        __syncwarp();
       };
       mbar_wait(&bar->fixed_full, 0, 0xB0);
       issue_s_dp(0);
       for (int nb = 0; nb < n_blocks; ++nb) {
-        const int st = nb & 1;
+        const int st = nb & 1, kst = nb % 3;
         if (nb + 1 < n_blocks) {
           mbar_wait(&bar->regs_loaded, nb & 1, 0xB5);  // S / dP of block nb are in the workers' registers
           issue_s_dp(nb + 1);
         }
         mbar_wait(&bar->ops_ready, nb & 1, 0xB6);      // dS of block nb is in its buffer
         tc_fence_after();
-        const uint32_t k_mn = (smem_u32(sK + st * kBwdTileBytes) >> 4) | kLboMN;
-        const uint32_t t_ds = tmem + 384 + st * 64;
-        for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 keys, 16 per slice
-          mma_ts<false>(tmem + 256, t_ds + ks * 8, k_mn + ks * (16 * 128 >> 4), kHi, idesc_dq, (nb > 0 || ks > 0));
-        tc_commit(&bar->empty[st]);
-        if (nb == n_blocks - 1) tc_commit(&bar->mma_done);
+        if (elect_one()) {
+          const uint32_t k_mn = (smem_u32(sK + kst * kBwdTileBytes) >> 4) | kLboMN;
+          const uint32_t t_ds = tmem + 384 + st * 64;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 keys, 16 per slice
+            mma_ts<false>(tmem + 256, t_ds + ks * 8, k_mn + ks * (16 * 128 >> 4), kHi, idesc_dq, (nb > 0 || ks > 0));
+          tc_commit(&bar->empty[kst]);
+          if (nb == n_blocks - 1) tc_commit(&bar->mma_done);
+        }
+        __syncwarp();
       }
     }
   } else {
@@ -382,7 +398,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
       }
     }
   } else if (warp == kBwdMmaWarp) {
-    if (lane == 0 && steps > 0) {
+    if (steps > 0) {
       const uint32_t idesc_s = make_idesc(fmt, fmt, kBwdTile, kBwdTile, 0, 0);
       const uint32_t idesc_acc = make_idesc(fmt, fmt, kBwdTile, p.n16, 0, 1);
       constexpr uint32_t kHi = sdesc_hi(1024);
@@ -393,26 +409,36 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
         const int st = t & 1;
         mbar_wait(&bar->full[st], (t / 2) & 1, 0xC2);
         tc_fence_after();
-        const uint32_t q_lo = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboK, do_lo = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboK;
         // behind dV / dK of the previous step in the in-order tensor pipe, so P^T / dS^T of that step are read before S^T lands on them
-        for (int ks = 0; ks < p.slices; ++ks) {
-          const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-          mma_ss<false>(tmem, k_lo + off, q_lo + off, kHi, idesc_s, ks > 0);           // S^T = K Q^T
+        if (elect_one()) {
+          const uint32_t q_lo = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboK, do_lo = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboK;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+            if (ks < p.slices) mma_ss<false>(tmem, k_lo + off, q_lo + off, kHi, idesc_s, ks > 0);           // S^T = K Q^T
+          }
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+            if (ks < p.slices) mma_ss<false>(tmem + 128, v_lo + off, do_lo + off, kHi, idesc_s, ks > 0);    // dP^T = V dO^T
+          }
+          tc_commit(&bar->s_ready);
         }
-        for (int ks = 0; ks < p.slices; ++ks) {
-          const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-          mma_ss<false>(tmem + 128, v_lo + off, do_lo + off, kHi, idesc_s, ks > 0);    // dP^T = V dO^T
-        }
-        tc_commit(&bar->s_ready);
+        __syncwarp();
         mbar_wait(&bar->ops_ready, t & 1, 0xC5);
         tc_fence_after();
-        const uint32_t do_mn = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboMN, q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
-        for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step
-          mma_ts<false>(tmem + 384, tmem + ks * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));        // dV += P^T dO
-        for (int ks = 0; ks < 8; ++ks)
-          mma_ts<false>(tmem + 256, tmem + 128 + ks * 8, q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));   // dK += dS^T Q
-        tc_commit(&bar->empty[st]);
-        if (t == steps - 1) tc_commit(&bar->mma_done);
+        if (elect_one()) {
+          const uint32_t do_mn = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboMN, q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step
+            mma_ts<false>(tmem + 384, tmem + ks * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));        // dV += P^T dO
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            mma_ts<false>(tmem + 256, tmem + 128 + ks * 8, q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));   // dK += dS^T Q
+          tc_commit(&bar->empty[st]);
+          if (t == steps - 1) tc_commit(&bar->mma_done);
+        }
+        __syncwarp();
       }
     }
   } else {
@@ -580,7 +606,7 @@ static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
   if ((rc = tm4(&tmV, p->v, rows_k, p->h_k, p->v_row_stride, p->v_head_stride, p->v_batch_stride, varlen_k))) return rc;
 
   // the 192 KB of dynamic shared memory are an opt-in per device
-  constexpr int kSmemDq = 6 * kBwdTileBytes + 256, kSmemDkdv = 6 * kBwdTileBytes + 4 * kBwdTile * 4 + 256;
+  constexpr int kSmemDq = 7 * kBwdTileBytes + 256, kSmemDkdv = 6 * kBwdTileBytes + 4 * kBwdTile * 4 + 256;
   static std::atomic<uint64_t> attr_set[2] = {{0}, {0}};
   int dev = 0;
   FA_CUDA(cudaGetDevice(&dev));
