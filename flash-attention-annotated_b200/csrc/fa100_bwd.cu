@@ -86,6 +86,8 @@ struct BwdBarriers {
   uint64_t regs_loaded;       // every worker warp holds the step's S / dP in registers (dQ kernel)
   uint64_t ops_ready;         // every worker warp has stored the step's 16-bit operands (dS; P^T and dS^T)
   uint64_t mma_done;          // accumulators final
+  uint64_t dp_ready, p_ready; // dK/dV kernel: dP^T in tensor memory (commit); P^T stored by every worker warp
+  uint64_t rows_full[2], rows_empty[2];  // dK/dV kernel: the step's per-query-row constants in shared memory
   uint32_t tmem_base;
   uint32_t pad_[3];
 };
@@ -335,10 +337,15 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
 }
 
 // ----------------------------------------------------------------------------- dK, dV
-// TMEM: S^T @0 (keys on the lanes, 128 query columns; P^T, 16 bit, is written over its columns [0, 64)), dP^T @128 (dS^T over its
-// columns [0, 64)), dK @256, dV @384 -- all 512 columns, so S^T / dP^T cannot be double-buffered and a step is tensor work,
-// elementwise work, tensor work in turn.  One CTA per (key block, KV head, batch); the steps run over (query head of the group,
-// query block) and all accumulate into the same dK / dV, which is the GQA reduction.
+// TMEM: A @0 and B @128 (128 fp32 columns each), dK @256, dV @384 -- all 512 columns.  S^T = K Q^T lands in A (keys on the lanes,
+// the step's 128 query rows on the columns), dP^T = V dO^T in B; a worker turns its 64 columns of S^T into P^T (16 bit) and writes
+// it over the first 32 of THOSE columns (nobody else reads them), likewise dS^T over dP^T, so no thread waits for another before it
+// stores.  A step is split in two so that tensor work and arithmetic overlap:
+//   tensor pipe:  ... dV(t) | S^T(t+1) | dK(t) | dP^T(t+1) | dV(t+1) | ...
+//   workers:      ... P phase(t): exp  ->  dS phase(t): P o (dP - D)  ->  P phase(t+1) ...
+// S^T(t+1) may overwrite A once dV(t) has read P^T(t) (in-order pipe), dP^T(t+1) may overwrite B once dK(t) has read dS^T(t).
+// One CTA per (key block, KV head, batch); the steps run over (query head of the group, query block) and all accumulate into the
+// same dK / dV, which is the GQA reduction.
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                       const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
@@ -354,9 +361,12 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   const int n_blk = blockIdx.x, hk = blockIdx.y, bi = blockIdx.z;
   const int G = p.h / p.h_k;
   if (tid == 0) {
-    mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->mma_done, 1);
-    mbar_init(&bar->regs_loaded, kBwdWorkerWarps); mbar_init(&bar->ops_ready, kBwdWorkerWarps);
-    for (int s_ = 0; s_ < 2; ++s_) { mbar_init(&bar->full[s_], 1); mbar_init(&bar->empty[s_], 1); }
+    mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->dp_ready, 1); mbar_init(&bar->mma_done, 1);
+    mbar_init(&bar->p_ready, kBwdWorkerWarps); mbar_init(&bar->ops_ready, kBwdWorkerWarps);
+    for (int s_ = 0; s_ < 2; ++s_) {
+      mbar_init(&bar->full[s_], 1); mbar_init(&bar->empty[s_], 1);
+      mbar_init(&bar->rows_full[s_], 1); mbar_init(&bar->rows_empty[s_], kBwdWorkerWarps);
+    }
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc(&bar->tmem_base, 512); tmem_relinquish(); }
@@ -384,18 +394,36 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   const uint32_t tile_tx = uint32_t(p.boxes) * kBwdBoxBytes;
 
   if (warp == kBwdProducerWarp) {
+    // ---- TMA (one lane) and the per-row constants of every step (all lanes, four query rows each)
     if (lane == 0 && steps > 0) {
       mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
       bwd_load_tile(sK, &tmK, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
       bwd_load_tile(sV, &tmV, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
-      for (int t = 0; t < steps; ++t) {
-        const int st = t & 1;
-        const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
+    }
+    for (int t = 0; t < steps; ++t) {
+      const int st = t & 1;
+      const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
+      if (lane == 0) {
         if (t >= 2) mbar_wait(&bar->empty[st], (t / 2 - 1) & 1, 0xC1);
         mbar_arrive_expect_tx(&bar->full[st], 2 * tile_tx);
         bwd_load_tile(sQ + st * kBwdTileBytes, &tmQ, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
         bwd_load_tile(sdO + st * kBwdTileBytes, &tmdO, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
       }
+      __syncwarp();
+      if (t >= 2) mbar_wait(&bar->rows_empty[st], (t / 2 - 1) & 1, 0xC6);
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int i = m * kBwdTile + r * 32 + lane;
+        float l2 = -INFINITY, ds_ = 0.f;   // rows past the end and rows without keys (LSE = -inf): P = exp2(-inf) = 0
+        if (i < sq_.sq) {
+          const float l = p.lse[bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off + i];
+          l2 = (l == -INFINITY) ? -INFINITY : -l * kLog2e;
+          ds_ = p.dsum[bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off + i];
+        }
+        sL[st * kBwdTile + r * 32 + lane] = l2; sD[st * kBwdTile + r * 32 + lane] = ds_;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar->rows_full[st]);
     }
   } else if (warp == kBwdMmaWarp) {
     if (steps > 0) {
@@ -404,99 +432,101 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
       constexpr uint32_t kHi = sdesc_hi(1024);
       constexpr uint32_t kLboK = sdesc_lo_lbo(16), kLboMN = sdesc_lo_lbo(kBwdBoxBytes);
       const uint32_t k_lo = (smem_u32(sK) >> 4) | kLboK, v_lo = (smem_u32(sV) >> 4) | kLboK;
-      mbar_wait(&bar->fixed_full, 0, 0xC0);
-      for (int t = 0; t < steps; ++t) {
+      auto issue_s = [&](int t) {   // S^T(t) = K Q(t)^T -> A
         const int st = t & 1;
         mbar_wait(&bar->full[st], (t / 2) & 1, 0xC2);
         tc_fence_after();
-        // behind dV / dK of the previous step in the in-order tensor pipe, so P^T / dS^T of that step are read before S^T lands on them
         if (elect_one()) {
-          const uint32_t q_lo = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboK, do_lo = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboK;
+          const uint32_t q_lo = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboK;
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-            if (ks < p.slices) mma_ss<false>(tmem, k_lo + off, q_lo + off, kHi, idesc_s, ks > 0);           // S^T = K Q^T
-          }
-#pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
-            if (ks < p.slices) mma_ss<false>(tmem + 128, v_lo + off, do_lo + off, kHi, idesc_s, ks > 0);    // dP^T = V dO^T
+            if (ks < p.slices) mma_ss<false>(tmem, k_lo + off, q_lo + off, kHi, idesc_s, ks > 0);
           }
           tc_commit(&bar->s_ready);
         }
         __syncwarp();
-        mbar_wait(&bar->ops_ready, t & 1, 0xC5);
+      };
+      auto issue_dp = [&](int t) {  // dP^T(t) = V dO(t)^T -> B (the stage is full: S^T(t) was issued before)
+        const int st = t & 1;
+        if (elect_one()) {
+          const uint32_t do_lo = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboK;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks / 4) * (kBwdBoxBytes >> 4) + (ks % 4) * 2;
+            if (ks < p.slices) mma_ss<false>(tmem + 128, v_lo + off, do_lo + off, kHi, idesc_s, ks > 0);
+          }
+          tc_commit(&bar->dp_ready);
+        }
+        __syncwarp();
+      };
+      mbar_wait(&bar->fixed_full, 0, 0xC0);
+      issue_s(0);
+      issue_dp(0);
+      for (int t = 0; t < steps; ++t) {
+        const int st = t & 1;
+        mbar_wait(&bar->p_ready, t & 1, 0xC7);      // P^T(t) is in A
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t do_mn = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboMN, q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
+          const uint32_t do_mn = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboMN;
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step
-            mma_ts<false>(tmem + 384, tmem + ks * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));        // dV += P^T dO
+          for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step; rows [64 h, +64) sit in columns [64 h, +32)
+            mma_ts<false>(tmem + 384, tmem + (ks >> 2) * 64 + (ks & 3) * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));  // dV += P^T dO
+        }
+        __syncwarp();
+        if (t + 1 < steps) issue_s(t + 1);
+        mbar_wait(&bar->ops_ready, t & 1, 0xC5);    // dS^T(t) is in B
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
-            mma_ts<false>(tmem + 256, tmem + 128 + ks * 8, q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));   // dK += dS^T Q
+            mma_ts<false>(tmem + 256, tmem + 128 + (ks >> 2) * 64 + (ks & 3) * 8, q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));  // dK += dS^T Q
           tc_commit(&bar->empty[st]);
           if (t == steps - 1) tc_commit(&bar->mma_done);
         }
         __syncwarp();
+        if (t + 1 < steps) issue_dp(t + 1);
       }
     }
   } else {
     // ---- workers: this thread's key row and its 64 of a step's 128 query columns
     const int q4 = warp & 3, half = warp >> 2;
     const int kj = n0 + q4 * 32 + lane;
-    const uint32_t tRow = tmem + (uint32_t(q4 * 32) << 16);
-    // -LSE * log2(e) and D of a step's query rows, fetched one step ahead by the first four worker warps
-    auto fetch_rows = [&](int t, float& l2, float& ds_) {
-      const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
-      const int i = m * kBwdTile + tid;
-      l2 = -INFINITY; ds_ = 0.f;   // rows past the end and rows without keys (LSE = -inf): P = exp2(-inf) = 0
-      if (i < sq_.sq) {
-        const float l = p.lse[bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off + i];
-        l2 = (l == -INFINITY) ? -INFINITY : -l * kLog2e;
-        ds_ = p.dsum[bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off + i];
-      }
-    };
-    if (tid < kBwdTile && steps > 0) { float l2, ds_; fetch_rows(0, l2, ds_); sL[tid] = l2; sD[tid] = ds_; }
+    const uint32_t tA = tmem + (uint32_t(q4 * 32) << 16) + half * 64, tB = tA + 128;
     for (int t = 0; t < steps; ++t) {
       const int m = m_lo + t % per_head;
       const float* nl = sL + (t & 1) * kBwdTile + half * 64;
       const float* dd = sD + (t & 1) * kBwdTile + half * 64;
-      float nl2 = 0.f, nds = 0.f;
-      const bool fetch = tid < kBwdTile && t + 1 < steps;
-      if (fetch) fetch_rows(t + 1, nl2, nds);   // in flight during this step's arithmetic
-      mbar_wait(&bar->s_ready, t & 1, 0xC3);
-      tc_fence_after();
-      uint32_t s[2][32], dp[2][32];
-      tmem_ld32(tRow + half * 64, s[0]); tmem_ld32(tRow + half * 64 + 32, s[1]);
-      tmem_ld32(tRow + 128 + half * 64, dp[0]); tmem_ld32(tRow + 128 + half * 64 + 32, dp[1]);
-      tmem_ld_wait();
-      // every worker holds its scores (P^T / dS^T may now land on them) and this step's row constants are visible
-      named_bar_sync(1, kBwdWorkerWarps * 32);
       const int i0 = m * kBwdTile;
       // every key of the tile is visible from every query row of the step, no softcap: the lean path (CTA-uniform)
       const bool lean = p.softcap_pre == 0.f && (p.window_right < 0 || n0 + kBwdTile - 1 <= i0 + shift + p.window_right) &&
                         (p.window_left < 0 || n0 >= i0 + kBwdTile - 1 + shift - p.window_left);
-      uint32_t pkp[32], pks[32];
+      mbar_wait(&bar->rows_full[t & 1], (t / 2) & 1, 0xC8);
+      mbar_wait(&bar->s_ready, t & 1, 0xC3);
+      tc_fence_after();
+      uint32_t s[2][32], pk[32];
+      tmem_ld32(tA, s[0]); tmem_ld32(tA + 32, s[1]);
+      tmem_ld_wait();
+      // ---- P phase: lean: s becomes P (fp32, kept for the dS phase); general: s stays raw and P is recomputed there
       if (lean) {
 #pragma unroll
         for (int c = 0; c < 2; ++c)
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            const float4 l4 = *reinterpret_cast<const float4*>(nl + c * 32 + j), d4 = *reinterpret_cast<const float4*>(dd + c * 32 + j);
+            const float4 l4 = *reinterpret_cast<const float4*>(nl + c * 32 + j);
             const float p0 = bwd_ex2(fmaf(__uint_as_float(s[c][j]), p.scale_log2, l4.x)), p1 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 1]), p.scale_log2, l4.y));
             const float p2 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 2]), p.scale_log2, l4.z)), p3 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 3]), p.scale_log2, l4.w));
-            pkp[c * 16 + j / 2] = bwd_pack(p0, p1, p.f16);
-            pkp[c * 16 + j / 2 + 1] = bwd_pack(p2, p3, p.f16);
-            pks[c * 16 + j / 2] = bwd_pack(p0 * (__uint_as_float(dp[c][j]) - d4.x), p1 * (__uint_as_float(dp[c][j + 1]) - d4.y), p.f16);
-            pks[c * 16 + j / 2 + 1] = bwd_pack(p2 * (__uint_as_float(dp[c][j + 2]) - d4.z), p3 * (__uint_as_float(dp[c][j + 3]) - d4.w), p.f16);
+            s[c][j] = __float_as_uint(p0); s[c][j + 1] = __float_as_uint(p1); s[c][j + 2] = __float_as_uint(p2); s[c][j + 3] = __float_as_uint(p3);
+            pk[c * 16 + j / 2] = bwd_pack(p0, p1, p.f16);
+            pk[c * 16 + j / 2 + 1] = bwd_pack(p2, p3, p.f16);
           }
       } else {
 #pragma unroll
         for (int c = 0; c < 2; ++c)
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
-            float pr[2], ds[2];
+            float pr[2];
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
               const int col = c * 32 + j + e;
@@ -504,21 +534,55 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
               const bool vis = (p.window_right < 0 || kj <= pos + p.window_right) && (p.window_left < 0 || kj >= pos - p.window_left);
               float dfac = 0.f;
               pr[e] = vis ? bwd_prob(p, __uint_as_float(s[c][j + e]), -nl[col], dfac) : 0.f;
-              ds[e] = pr[e] * (__uint_as_float(dp[c][j + e]) - dd[col]) * dfac;
             }
-            pkp[c * 16 + j / 2] = bwd_pack(pr[0], pr[1], p.f16);
-            pks[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+            pk[c * 16 + j / 2] = bwd_pack(pr[0], pr[1], p.f16);
           }
       }
-      // query columns [64 half, +64) are columns [32 half, +32) of the 16-bit operands
-      tmem_st32(tRow + half * 32, pkp);        // P^T over S^T's consumed columns
-      tmem_st32(tRow + 128 + half * 32, pks);  // dS^T over dP^T's consumed columns
-      if (fetch) { sL[((t + 1) & 1) * kBwdTile + tid] = nl2; sD[((t + 1) & 1) * kBwdTile + tid] = nds; }  // read after the next step's barrier
+      tmem_st32(tA, pk);   // P^T over the first 32 of this thread's own S^T columns
+      tmem_st_wait();
+      bwd_warp_arrive(&bar->p_ready, lane);
+      // ---- dS phase
+      mbar_wait(&bar->dp_ready, t & 1, 0xC9);
+      tc_fence_after();
+      uint32_t dp[2][32];
+      tmem_ld32(tB, dp[0]); tmem_ld32(tB + 32, dp[1]);
+      tmem_ld_wait();
+      if (lean) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 d4 = *reinterpret_cast<const float4*>(dd + c * 32 + j);
+            pk[c * 16 + j / 2] = bwd_pack(__uint_as_float(s[c][j]) * (__uint_as_float(dp[c][j]) - d4.x), __uint_as_float(s[c][j + 1]) * (__uint_as_float(dp[c][j + 1]) - d4.y), p.f16);
+            pk[c * 16 + j / 2 + 1] = bwd_pack(__uint_as_float(s[c][j + 2]) * (__uint_as_float(dp[c][j + 2]) - d4.z), __uint_as_float(s[c][j + 3]) * (__uint_as_float(dp[c][j + 3]) - d4.w), p.f16);
+          }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            float ds[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int col = c * 32 + j + e;
+              const int pos = i0 + half * 64 + col + shift;
+              const bool vis = (p.window_right < 0 || kj <= pos + p.window_right) && (p.window_left < 0 || kj >= pos - p.window_left);
+              float dfac = 0.f;
+              const float pr = vis ? bwd_prob(p, __uint_as_float(s[c][j + e]), -nl[col], dfac) : 0.f;
+              ds[e] = pr * (__uint_as_float(dp[c][j + e]) - dd[col]) * dfac;
+            }
+            pk[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+          }
+      }
+      tmem_st32(tB, pk);   // dS^T over the first 32 of this thread's own dP^T columns
       tmem_st_wait();
       bwd_warp_arrive(&bar->ops_ready, lane);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar->rows_empty[t & 1]);  // this warp is done with the step's row constants
     }
     if (steps > 0) { mbar_wait(&bar->mma_done, 0, 0xC4); tc_fence_after(); }
     const bool row_ok = kj < sq_.sk;
+    const uint32_t tRow = tmem + (uint32_t(q4 * 32) << 16);
     uint16_t* dk_dst = reinterpret_cast<uint16_t*>(p.dk) + sq_.bk * p.dk_batch_stride + int64_t(sq_.k_off + kj) * p.dk_row_stride + hk * p.dk_head_stride;
     uint16_t* dv_dst = reinterpret_cast<uint16_t*>(p.dv) + sq_.bk * p.dv_batch_stride + int64_t(sq_.k_off + kj) * p.dv_row_stride + hk * p.dv_head_stride;
     for (int which = 0; which < 2; ++which) {
