@@ -31,6 +31,7 @@ namespace fa100 {
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr int kBwdWorkerWarps = 8;                        // two threads per TMEM lane
 constexpr int kBwdProducerWarp = 8, kBwdMmaWarp = 9;
+constexpr int kBwdRowSlots = 4;                           // dK/dV kernel: steps whose per-row constants sit in shared memory
 constexpr int kBwdThreads = (kBwdWorkerWarps + 2) * 32;
 constexpr int kBwdTile = 128;                 // query rows / keys per tile
 constexpr int kBwdTileBytes = 128 * 128 * 2;  // one [128][128] 16-bit tile (two 64-column boxes)
@@ -87,10 +88,12 @@ struct BwdBarriers {
   uint64_t ops_ready;         // every worker warp has stored the step's 16-bit operands (dS; P^T and dS^T)
   uint64_t mma_done;          // accumulators final
   uint64_t dp_ready, p_ready; // dK/dV kernel: dP^T in tensor memory (commit); P^T stored by every worker warp
-  uint64_t rows_full[2], rows_empty[2];  // dK/dV kernel: the step's per-query-row constants in shared memory
+  uint64_t rows_full[4], rows_empty[4];  // dK/dV kernel: the step's per-query-row constants in shared memory
   uint32_t tmem_base;
   uint32_t pad_[3];
 };
+
+static_assert(sizeof(BwdBarriers) <= 256, "barrier block outgrew its slot");
 
 FA_DEVICE uint32_t bwd_pack(float a, float b, bool f16) {
   if (f16) { __half2 v = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&v); }
@@ -354,9 +357,9 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   uint8_t* sV = smem + kBwdTileBytes;          // V tile
   uint8_t* sQ = smem + 2 * kBwdTileBytes;      // Q stages 0, 1
   uint8_t* sdO = smem + 4 * kBwdTileBytes;     // dO stages 0, 1
-  float* sL = reinterpret_cast<float*>(smem + 6 * kBwdTileBytes);  // [2][128] -LSE * log2(e) of a step's query rows (two steps in flight)
-  float* sD = sL + 2 * kBwdTile;                                    // [2][128] D of the same rows
-  BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 6 * kBwdTileBytes + 4 * kBwdTile * 4);
+  float* sL = reinterpret_cast<float*>(smem + 6 * kBwdTileBytes);  // [4][128] -LSE * log2(e) of a step's query rows, fetched two steps ahead
+  float* sD = sL + kBwdRowSlots * kBwdTile;                         // [4][128] D of the same rows
+  BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 6 * kBwdTileBytes + 2 * kBwdRowSlots * kBwdTile * 4);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n_blk = blockIdx.x, hk = blockIdx.y, bi = blockIdx.z;
   const int G = p.h / p.h_k;
@@ -364,9 +367,10 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
     mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->dp_ready, 1); mbar_init(&bar->mma_done, 1);
     mbar_init(&bar->p_ready, kBwdWorkerWarps); mbar_init(&bar->ops_ready, kBwdWorkerWarps);
     for (int s_ = 0; s_ < 2; ++s_) {
-      mbar_init(&bar->full[s_], 1); mbar_init(&bar->empty[s_], 1);
-      mbar_init(&bar->rows_full[s_], 1); mbar_init(&bar->rows_empty[s_], kBwdWorkerWarps);
+      mbar_init(&bar->full[s_], 1); mbar_init(&bar->empty[s_], 1);       // Q stages
+      mbar_init(&bar->v_full[s_], 1); mbar_init(&bar->v_empty[s_], 1);   // dO stages (free one product earlier than Q)
     }
+    for (int s_ = 0; s_ < kBwdRowSlots; ++s_) { mbar_init(&bar->rows_full[s_], 1); mbar_init(&bar->rows_empty[s_], kBwdWorkerWarps); }
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc(&bar->tmem_base, 512); tmem_relinquish(); }
@@ -394,36 +398,49 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   const uint32_t tile_tx = uint32_t(p.boxes) * kBwdBoxBytes;
 
   if (warp == kBwdProducerWarp) {
-    // ---- TMA (one lane) and the per-row constants of every step (all lanes, four query rows each)
+    // ---- TMA (one lane) and the per-row constants of every step (all lanes, four query rows each, two steps ahead)
     if (lane == 0 && steps > 0) {
       mbar_arrive_expect_tx(&bar->fixed_full, 2 * tile_tx);
       bwd_load_tile(sK, &tmK, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
       bwd_load_tile(sV, &tmV, &bar->fixed_full, p.boxes, sq_.k_off + n0, hk, sq_.bk);
     }
+    auto fetch_rows = [&](int t) {
+      const int slot = t % kBwdRowSlots;
+      const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
+      if (t >= kBwdRowSlots) mbar_wait(&bar->rows_empty[slot], (t / kBwdRowSlots - 1) & 1, 0xC6);
+      const float* lse = p.lse + bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off;
+      const float* dsm = p.dsum + bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off;
+      float l[4], d_[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {  // eight independent loads (clamped index: rows past the end are masked below)
+        const int i = min(m * kBwdTile + r * 32 + lane, sq_.sq - 1);
+        l[r] = lse[i]; d_[r] = dsm[i];
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const bool ok = m * kBwdTile + r * 32 + lane < sq_.sq;
+        // rows past the end and rows without keys (LSE = -inf): P = exp2(-inf) = 0
+        sL[slot * kBwdTile + r * 32 + lane] = (ok && l[r] != -INFINITY) ? -l[r] * kLog2e : -INFINITY;
+        sD[slot * kBwdTile + r * 32 + lane] = ok ? d_[r] : 0.f;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar->rows_full[slot]);
+    };
+    if (steps > 0) fetch_rows(0);
+    if (steps > 1) fetch_rows(1);
     for (int t = 0; t < steps; ++t) {
       const int st = t & 1;
       const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
       if (lane == 0) {
+        if (t >= 2) mbar_wait(&bar->v_empty[st], (t / 2 - 1) & 1, 0xCA);
+        mbar_arrive_expect_tx(&bar->v_full[st], tile_tx);
+        bwd_load_tile(sdO + st * kBwdTileBytes, &tmdO, &bar->v_full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
         if (t >= 2) mbar_wait(&bar->empty[st], (t / 2 - 1) & 1, 0xC1);
-        mbar_arrive_expect_tx(&bar->full[st], 2 * tile_tx);
+        mbar_arrive_expect_tx(&bar->full[st], tile_tx);
         bwd_load_tile(sQ + st * kBwdTileBytes, &tmQ, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
-        bwd_load_tile(sdO + st * kBwdTileBytes, &tmdO, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
       }
       __syncwarp();
-      if (t >= 2) mbar_wait(&bar->rows_empty[st], (t / 2 - 1) & 1, 0xC6);
-#pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int i = m * kBwdTile + r * 32 + lane;
-        float l2 = -INFINITY, ds_ = 0.f;   // rows past the end and rows without keys (LSE = -inf): P = exp2(-inf) = 0
-        if (i < sq_.sq) {
-          const float l = p.lse[bi * p.lse_batch_stride + hq * p.lse_head_stride + sq_.q_off + i];
-          l2 = (l == -INFINITY) ? -INFINITY : -l * kLog2e;
-          ds_ = p.dsum[bi * p.dsum_batch_stride + hq * p.dsum_head_stride + sq_.q_off + i];
-        }
-        sL[st * kBwdTile + r * 32 + lane] = l2; sD[st * kBwdTile + r * 32 + lane] = ds_;
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->rows_full[st]);
+      if (t + 2 < steps) fetch_rows(t + 2);
     }
   } else if (warp == kBwdMmaWarp) {
     if (steps > 0) {
@@ -447,8 +464,10 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
         }
         __syncwarp();
       };
-      auto issue_dp = [&](int t) {  // dP^T(t) = V dO(t)^T -> B (the stage is full: S^T(t) was issued before)
+      auto issue_dp = [&](int t) {  // dP^T(t) = V dO(t)^T -> B
         const int st = t & 1;
+        mbar_wait(&bar->v_full[st], (t / 2) & 1, 0xCB);
+        tc_fence_after();
         if (elect_one()) {
           const uint32_t do_lo = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboK;
 #pragma unroll
@@ -472,6 +491,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step; rows [64 h, +64) sit in columns [64 h, +32)
             mma_ts<false>(tmem + 384, tmem + (ks >> 2) * 64 + (ks & 3) * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));  // dV += P^T dO
+          tc_commit(&bar->v_empty[st]);  // last reader of dO(t)
         }
         __syncwarp();
         if (t + 1 < steps) issue_s(t + 1);
@@ -496,13 +516,14 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
     const uint32_t tA = tmem + (uint32_t(q4 * 32) << 16) + half * 64, tB = tA + 128;
     for (int t = 0; t < steps; ++t) {
       const int m = m_lo + t % per_head;
-      const float* nl = sL + (t & 1) * kBwdTile + half * 64;
-      const float* dd = sD + (t & 1) * kBwdTile + half * 64;
+      const int slot = t % kBwdRowSlots;
+      const float* nl = sL + slot * kBwdTile + half * 64;
+      const float* dd = sD + slot * kBwdTile + half * 64;
       const int i0 = m * kBwdTile;
       // every key of the tile is visible from every query row of the step, no softcap: the lean path (CTA-uniform)
       const bool lean = p.softcap_pre == 0.f && (p.window_right < 0 || n0 + kBwdTile - 1 <= i0 + shift + p.window_right) &&
                         (p.window_left < 0 || n0 >= i0 + kBwdTile - 1 + shift - p.window_left);
-      mbar_wait(&bar->rows_full[t & 1], (t / 2) & 1, 0xC8);
+      mbar_wait(&bar->rows_full[slot], (t / kBwdRowSlots) & 1, 0xC8);
       mbar_wait(&bar->s_ready, t & 1, 0xC3);
       tc_fence_after();
       uint32_t s[2][32], pk[32];
@@ -578,7 +599,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
       tmem_st_wait();
       bwd_warp_arrive(&bar->ops_ready, lane);
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->rows_empty[t & 1]);  // this warp is done with the step's row constants
+      if (lane == 0) mbar_arrive(&bar->rows_empty[slot]);  // this warp is done with the step's row constants
     }
     if (steps > 0) { mbar_wait(&bar->mma_done, 0, 0xC4); tc_fence_after(); }
     const bool row_ok = kj < sq_.sk;
@@ -670,7 +691,7 @@ static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
   if ((rc = tm4(&tmV, p->v, rows_k, p->h_k, p->v_row_stride, p->v_head_stride, p->v_batch_stride, varlen_k))) return rc;
 
   // the 192 KB of dynamic shared memory are an opt-in per device
-  constexpr int kSmemDq = 7 * kBwdTileBytes + 256, kSmemDkdv = 6 * kBwdTileBytes + 4 * kBwdTile * 4 + 256;
+  constexpr int kSmemDq = 7 * kBwdTileBytes + 256, kSmemDkdv = 6 * kBwdTileBytes + 2 * kBwdRowSlots * kBwdTile * 4 + 256;
   static std::atomic<uint64_t> attr_set[2] = {{0}, {0}};
   int dev = 0;
   FA_CUDA(cudaGetDevice(&dev));
