@@ -29,8 +29,14 @@
 namespace fa100 {
 
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr int kBwdWorkerWarps = 8;                        // two threads per TMEM lane
-constexpr int kBwdProducerWarp = 8, kBwdMmaWarp = 9;
+#ifndef FA100_BWD_PARTS
+#define FA100_BWD_PARTS 4
+#endif
+constexpr int kBwdParts = FA100_BWD_PARTS;                // worker threads per TMEM lane (row): 2 or 4
+constexpr int kBwdCols = 128 / kBwdParts;                 // columns of a step each of them owns
+constexpr int kBwdC = kBwdCols / 32;                      // ... in 32-column register chunks
+constexpr int kBwdWorkerWarps = 4 * kBwdParts;
+constexpr int kBwdProducerWarp = kBwdWorkerWarps, kBwdMmaWarp = kBwdWorkerWarps + 1;
 constexpr int kBwdRowSlots = 4;                           // dK/dV kernel: steps whose per-row constants sit in shared memory
 constexpr int kBwdThreads = (kBwdWorkerWarps + 2) * 32;
 constexpr int kBwdTile = 128;                 // query rows / keys per tile
@@ -95,10 +101,20 @@ struct BwdBarriers {
 
 static_assert(sizeof(BwdBarriers) <= 256, "barrier block outgrew its slot");
 
-FA_DEVICE uint32_t bwd_pack(float a, float b, bool f16) {
-  if (f16) { __half2 v = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&v); }
+template <bool F16> FA_DEVICE uint32_t bwd_pack(float a, float b) {
+  if (F16) { __half2 v = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&v); }
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+// packed f32x2 arithmetic for the lean paths (one issue slot for two columns)
+FA_DEVICE void bwd_fma2(float& a, float& b, float sc, float c0, float c1) {   // (a, b) = (a, b) * sc + (c0, c1)
+  asm("{\n\t.reg .b64 x, s2, c2;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 s2, {%2, %2};\n\tmov.b64 c2, {%3, %4};\n\t"
+      "fma.rn.ftz.f32x2 x, x, s2, c2;\n\tmov.b64 {%0, %1}, x;\n\t}" : "+f"(a), "+f"(b) : "f"(sc), "f"(c0), "f"(c1));
+}
+FA_DEVICE void bwd_dsv2(float& o0, float& o1, float p0, float p1, float dp0, float dp1, float d0, float d1) {  // (o0, o1) = (p0, p1) * ((dp0, dp1) - (d0, d1))
+  asm("{\n\t.reg .b64 x, y, z;\n\tmov.b64 x, {%2, %3};\n\tmov.b64 y, {%4, %5};\n\tmov.b64 z, {%6, %7};\n\t"
+      "sub.rn.ftz.f32x2 y, y, z;\n\tmul.rn.ftz.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
+      : "=f"(o0), "=f"(o1) : "f"(p0), "f"(p1), "f"(dp0), "f"(dp1), "f"(d0), "f"(d1));
 }
 
 // ----------------------------------------------------------------------------- preprocess: D = rowsum(dO o O)
@@ -138,12 +154,19 @@ FA_DEVICE void bwd_warp_arrive(uint64_t* bar, int lane) {
   __syncwarp();
   if (lane == 0) mbar_arrive(bar);
 }
+// the 16-bit operand a worker leaves in tensor memory: kBwdCols / 2 columns
+FA_DEVICE void bwd_tmem_st(uint32_t addr, const uint32_t (&r)[32]) { tmem_st32(addr, r); }
+FA_DEVICE void bwd_tmem_st(uint32_t addr, const uint32_t (&r)[16]) { tmem_st16(addr, r); }
+// TMEM column offset of MMA k-slice ks (16 consecutive columns of the step) inside a 128-column region whose owners wrote
+// their kBwdCols / 2 operand columns over the start of their own kBwdCols columns
+FA_DEVICE constexpr uint32_t bwd_slice_col(int ks) { return uint32_t((ks * 16 / kBwdCols) * kBwdCols + (ks * 16 % kBwdCols) / 2); }
 FA_DEVICE float bwd_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 // ----------------------------------------------------------------------------- dQ
 // TMEM: S @0, dP @128 (fp32, 128 columns each), dQ @256, dS (16 bit, 64 columns) double-buffered @384 / @448.  With dS in its
 // own columns S and dP are free as soon as the workers hold them in registers, so the MMA warp computes the next block's S
 // and dP while the workers turn this block's into dS; the order in the tensor pipe is S,dP(n+1) | dQ(n) | S,dP(n+2) | ...
+template <bool F16>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                     const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
@@ -252,8 +275,8 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
       }
     }
   } else {
-    // ---- workers: this thread's query row and its 64 of a block's 128 key columns
-    const int q4 = warp & 3, half = warp >> 2;
+    // ---- workers: this thread's query row and its kBwdCols of a block's 128 key columns
+    const int q4 = warp & 3, part = warp >> 2;
     const int i = row0 + q4 * 32 + lane;
     const bool row_ok = i < sq_.sq;
     float lse2 = INFINITY, dsum = 0.f;  // rows past the end and rows without keys (LSE = -inf) get P = 0
@@ -270,9 +293,9 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
     for (int nb = 0; nb < n_blocks; ++nb) {
       mbar_wait(&bar->s_ready, nb & 1, 0xB3);
       tc_fence_after();
-      uint32_t s[2][32], dp[2][32], pk[32];
-      tmem_ld32(tRow + half * 64, s[0]); tmem_ld32(tRow + half * 64 + 32, s[1]);
-      tmem_ld32(tRow + 128 + half * 64, dp[0]); tmem_ld32(tRow + 128 + half * 64 + 32, dp[1]);
+      uint32_t s[kBwdC][32], dp[kBwdC][32], pk[kBwdCols / 2];
+#pragma unroll
+      for (int c = 0; c < kBwdC; ++c) { tmem_ld32(tRow + part * kBwdCols + c * 32, s[c]); tmem_ld32(tRow + 128 + part * kBwdCols + c * 32, dp[c]); }
       tmem_ld_wait();
       bwd_warp_arrive(&bar->regs_loaded, lane);
       const int n0 = (n_min + nb) * kBwdTile;
@@ -282,38 +305,39 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
                         (p.window_left < 0 || n0 >= row0 + kBwdTile - 1 + shift - p.window_left);
       if (lean) {
 #pragma unroll
-        for (int c = 0; c < 2; ++c)
+        for (int c = 0; c < kBwdC; ++c)
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
-            const float p0 = bwd_ex2(fmaf(__uint_as_float(s[c][j]), p.scale_log2, neg_lse2));
-            const float p1 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 1]), p.scale_log2, neg_lse2));
-            pk[c * 16 + j / 2] = bwd_pack(p0 * (__uint_as_float(dp[c][j]) - dsum), p1 * (__uint_as_float(dp[c][j + 1]) - dsum), p.f16);
+            float x0 = __uint_as_float(s[c][j]), x1 = __uint_as_float(s[c][j + 1]), o0, o1;
+            bwd_fma2(x0, x1, p.scale_log2, neg_lse2, neg_lse2);
+            bwd_dsv2(o0, o1, bwd_ex2(x0), bwd_ex2(x1), __uint_as_float(dp[c][j]), __uint_as_float(dp[c][j + 1]), dsum, dsum);
+            pk[c * 16 + j / 2] = bwd_pack<F16>(o0, o1);
           }
       } else {
 #pragma unroll
-        for (int c = 0; c < 2; ++c)
+        for (int c = 0; c < kBwdC; ++c)
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
             float ds[2];
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
-              const int col = n0 + half * 64 + c * 32 + j + e;
+              const int col = n0 + part * kBwdCols + c * 32 + j + e;
               float dfac = 0.f;
               const float pr = (col < col_hi && col >= col_lo) ? bwd_prob(p, __uint_as_float(s[c][j + e]), lse2, dfac) : 0.f;
               ds[e] = pr * (__uint_as_float(dp[c][j + e]) - dsum) * dfac;
             }
-            pk[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+            pk[c * 16 + j / 2] = bwd_pack<F16>(ds[0], ds[1]);
           }
       }
-      // keys [64 half, +64) of the block are columns [32 half, +32) of the 16-bit dS buffer
-      tmem_st32(tRow + 384 + (nb & 1) * 64 + half * 32, pk);
+      // keys [kBwdCols part, +kBwdCols) of the block are columns [kBwdCols / 2 part, ...) of the 16-bit dS buffer
+      bwd_tmem_st(tRow + 384 + (nb & 1) * 64 + part * (kBwdCols / 2), pk);
       tmem_st_wait();
       bwd_warp_arrive(&bar->ops_ready, lane);
     }
-    // dQ = scale * accumulator; each thread stores its half of the columns
+    // dQ = scale * accumulator; each thread stores its share of the columns
     if (n_blocks > 0) { mbar_wait(&bar->mma_done, 0, 0xB4); tc_fence_after(); }
     uint16_t* dst = reinterpret_cast<uint16_t*>(p.dq) + sq_.bq * p.dq_batch_stride + int64_t(sq_.q_off + i) * p.dq_row_stride + hq * p.dq_head_stride;
-    for (int c = half * 2; c < half * 2 + 2; ++c) {
+    for (int c = part * kBwdC; c < (part + 1) * kBwdC; ++c) {
       if (c * 32 >= p.d) break;
       uint32_t o[32];
       if (n_blocks > 0) { tmem_ld32(tRow + 256 + c * 32, o); tmem_ld_wait(); }
@@ -328,7 +352,7 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
             uint4 u;
             uint32_t* up = reinterpret_cast<uint32_t*>(&u);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) up[e] = bwd_pack(__uint_as_float(o[v8 * 8 + 2 * e]) * p.scale, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * p.scale, p.f16);
+            for (int e = 0; e < 4; ++e) up[e] = bwd_pack<F16>(__uint_as_float(o[v8 * 8 + 2 * e]) * p.scale, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * p.scale);
             *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = u;
           }
       }
@@ -349,6 +373,7 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
 // S^T(t+1) may overwrite A once dV(t) has read P^T(t) (in-order pipe), dP^T(t+1) may overwrite B once dK(t) has read dS^T(t).
 // One CTA per (key block, KV head, batch); the steps run over (query head of the group, query block) and all accumulate into the
 // same dK / dV, which is the GQA reduction.
+template <bool F16>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                       const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, uint32_t fmt) {
@@ -489,8 +514,8 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
         if (elect_one()) {
           const uint32_t do_mn = (smem_u32(sdO + st * kBwdTileBytes) >> 4) | kLboMN;
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step; rows [64 h, +64) sit in columns [64 h, +32)
-            mma_ts<false>(tmem + 384, tmem + (ks >> 2) * 64 + (ks & 3) * 8, do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));  // dV += P^T dO
+          for (int ks = 0; ks < 8; ++ks)  // contraction over the 128 query rows of the step (bwd_slice_col: where a slice's P^T sits)
+            mma_ts<false>(tmem + 384, tmem + bwd_slice_col(ks), do_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));  // dV += P^T dO
           tc_commit(&bar->v_empty[st]);  // last reader of dO(t)
         }
         __syncwarp();
@@ -501,7 +526,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
           const uint32_t q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
-            mma_ts<false>(tmem + 256, tmem + 128 + (ks >> 2) * 64 + (ks & 3) * 8, q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));  // dK += dS^T Q
+            mma_ts<false>(tmem + 256, tmem + 128 + bwd_slice_col(ks), q_mn + ks * (16 * 128 >> 4), kHi, idesc_acc, (t > 0 || ks > 0));  // dK += dS^T Q
           tc_commit(&bar->empty[st]);
           if (t == steps - 1) tc_commit(&bar->mma_done);
         }
@@ -510,15 +535,15 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
       }
     }
   } else {
-    // ---- workers: this thread's key row and its 64 of a step's 128 query columns
-    const int q4 = warp & 3, half = warp >> 2;
+    // ---- workers: this thread's key row and its kBwdCols of a step's 128 query columns
+    const int q4 = warp & 3, part = warp >> 2;
     const int kj = n0 + q4 * 32 + lane;
-    const uint32_t tA = tmem + (uint32_t(q4 * 32) << 16) + half * 64, tB = tA + 128;
+    const uint32_t tA = tmem + (uint32_t(q4 * 32) << 16) + part * kBwdCols, tB = tA + 128;
     for (int t = 0; t < steps; ++t) {
       const int m = m_lo + t % per_head;
       const int slot = t % kBwdRowSlots;
-      const float* nl = sL + slot * kBwdTile + half * 64;
-      const float* dd = sD + slot * kBwdTile + half * 64;
+      const float* nl = sL + slot * kBwdTile + part * kBwdCols;
+      const float* dd = sD + slot * kBwdTile + part * kBwdCols;
       const int i0 = m * kBwdTile;
       // every key of the tile is visible from every query row of the step, no softcap: the lean path (CTA-uniform)
       const bool lean = p.softcap_pre == 0.f && (p.window_right < 0 || n0 + kBwdTile - 1 <= i0 + shift + p.window_right) &&
@@ -526,76 +551,83 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
       mbar_wait(&bar->rows_full[slot], (t / kBwdRowSlots) & 1, 0xC8);
       mbar_wait(&bar->s_ready, t & 1, 0xC3);
       tc_fence_after();
-      uint32_t s[2][32], pk[32];
-      tmem_ld32(tA, s[0]); tmem_ld32(tA + 32, s[1]);
+      uint32_t s[kBwdC][32], pk[kBwdCols / 2];
+#pragma unroll
+      for (int c = 0; c < kBwdC; ++c) tmem_ld32(tA + c * 32, s[c]);
       tmem_ld_wait();
       // ---- P phase: lean: s becomes P (fp32, kept for the dS phase); general: s stays raw and P is recomputed there
       if (lean) {
 #pragma unroll
-        for (int c = 0; c < 2; ++c)
+        for (int c = 0; c < kBwdC; ++c)
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             const float4 l4 = *reinterpret_cast<const float4*>(nl + c * 32 + j);
-            const float p0 = bwd_ex2(fmaf(__uint_as_float(s[c][j]), p.scale_log2, l4.x)), p1 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 1]), p.scale_log2, l4.y));
-            const float p2 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 2]), p.scale_log2, l4.z)), p3 = bwd_ex2(fmaf(__uint_as_float(s[c][j + 3]), p.scale_log2, l4.w));
+            float x0 = __uint_as_float(s[c][j]), x1 = __uint_as_float(s[c][j + 1]), x2 = __uint_as_float(s[c][j + 2]), x3 = __uint_as_float(s[c][j + 3]);
+            bwd_fma2(x0, x1, p.scale_log2, l4.x, l4.y);
+            bwd_fma2(x2, x3, p.scale_log2, l4.z, l4.w);
+            const float p0 = bwd_ex2(x0), p1 = bwd_ex2(x1), p2 = bwd_ex2(x2), p3 = bwd_ex2(x3);
             s[c][j] = __float_as_uint(p0); s[c][j + 1] = __float_as_uint(p1); s[c][j + 2] = __float_as_uint(p2); s[c][j + 3] = __float_as_uint(p3);
-            pk[c * 16 + j / 2] = bwd_pack(p0, p1, p.f16);
-            pk[c * 16 + j / 2 + 1] = bwd_pack(p2, p3, p.f16);
+            pk[c * 16 + j / 2] = bwd_pack<F16>(p0, p1);
+            pk[c * 16 + j / 2 + 1] = bwd_pack<F16>(p2, p3);
           }
       } else {
 #pragma unroll
-        for (int c = 0; c < 2; ++c)
+        for (int c = 0; c < kBwdC; ++c)
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
             float pr[2];
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
               const int col = c * 32 + j + e;
-              const int pos = i0 + half * 64 + col + shift;  // the key on this query row's diagonal
+              const int pos = i0 + part * kBwdCols + col + shift;  // the key on this query row's diagonal
               const bool vis = (p.window_right < 0 || kj <= pos + p.window_right) && (p.window_left < 0 || kj >= pos - p.window_left);
               float dfac = 0.f;
               pr[e] = vis ? bwd_prob(p, __uint_as_float(s[c][j + e]), -nl[col], dfac) : 0.f;
             }
-            pk[c * 16 + j / 2] = bwd_pack(pr[0], pr[1], p.f16);
+            pk[c * 16 + j / 2] = bwd_pack<F16>(pr[0], pr[1]);
           }
       }
-      tmem_st32(tA, pk);   // P^T over the first 32 of this thread's own S^T columns
+      bwd_tmem_st(tA, pk);   // P^T over the first half of this thread's own S^T columns
       tmem_st_wait();
       bwd_warp_arrive(&bar->p_ready, lane);
       // ---- dS phase
       mbar_wait(&bar->dp_ready, t & 1, 0xC9);
       tc_fence_after();
-      uint32_t dp[2][32];
-      tmem_ld32(tB, dp[0]); tmem_ld32(tB + 32, dp[1]);
+      uint32_t dp[kBwdC][32];
+#pragma unroll
+      for (int c = 0; c < kBwdC; ++c) tmem_ld32(tB + c * 32, dp[c]);
       tmem_ld_wait();
       if (lean) {
 #pragma unroll
-        for (int c = 0; c < 2; ++c)
+        for (int c = 0; c < kBwdC; ++c)
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             const float4 d4 = *reinterpret_cast<const float4*>(dd + c * 32 + j);
-            pk[c * 16 + j / 2] = bwd_pack(__uint_as_float(s[c][j]) * (__uint_as_float(dp[c][j]) - d4.x), __uint_as_float(s[c][j + 1]) * (__uint_as_float(dp[c][j + 1]) - d4.y), p.f16);
-            pk[c * 16 + j / 2 + 1] = bwd_pack(__uint_as_float(s[c][j + 2]) * (__uint_as_float(dp[c][j + 2]) - d4.z), __uint_as_float(s[c][j + 3]) * (__uint_as_float(dp[c][j + 3]) - d4.w), p.f16);
+            float o0, o1, o2, o3;
+            bwd_dsv2(o0, o1, __uint_as_float(s[c][j]), __uint_as_float(s[c][j + 1]), __uint_as_float(dp[c][j]), __uint_as_float(dp[c][j + 1]), d4.x, d4.y);
+            bwd_dsv2(o2, o3, __uint_as_float(s[c][j + 2]), __uint_as_float(s[c][j + 3]), __uint_as_float(dp[c][j + 2]), __uint_as_float(dp[c][j + 3]), d4.z, d4.w);
+            pk[c * 16 + j / 2] = bwd_pack<F16>(o0, o1);
+            pk[c * 16 + j / 2 + 1] = bwd_pack<F16>(o2, o3);
           }
       } else {
 #pragma unroll
-        for (int c = 0; c < 2; ++c)
+        for (int c = 0; c < kBwdC; ++c)
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
             float ds[2];
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
               const int col = c * 32 + j + e;
-              const int pos = i0 + half * 64 + col + shift;
+              const int pos = i0 + part * kBwdCols + col + shift;
               const bool vis = (p.window_right < 0 || kj <= pos + p.window_right) && (p.window_left < 0 || kj >= pos - p.window_left);
               float dfac = 0.f;
               const float pr = vis ? bwd_prob(p, __uint_as_float(s[c][j + e]), -nl[col], dfac) : 0.f;
               ds[e] = pr * (__uint_as_float(dp[c][j + e]) - dd[col]) * dfac;
             }
-            pk[c * 16 + j / 2] = bwd_pack(ds[0], ds[1], p.f16);
+            pk[c * 16 + j / 2] = bwd_pack<F16>(ds[0], ds[1]);
           }
       }
-      tmem_st32(tB, pk);   // dS^T over the first 32 of this thread's own dP^T columns
+      bwd_tmem_st(tB, pk);   // dS^T over the first half of this thread's own dP^T columns
       tmem_st_wait();
       bwd_warp_arrive(&bar->ops_ready, lane);
       __syncwarp();
@@ -609,7 +641,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
     for (int which = 0; which < 2; ++which) {
       uint16_t* dst = which == 0 ? dk_dst : dv_dst;
       const float sc = which == 0 ? p.scale : 1.0f;
-      for (int c = half * 2; c < half * 2 + 2; ++c) {
+      for (int c = part * kBwdC; c < (part + 1) * kBwdC; ++c) {
         if (c * 32 >= p.d) break;
         uint32_t o[32];
         if (steps > 0) { tmem_ld32(tRow + 256 + which * 128 + c * 32, o); tmem_ld_wait(); }
@@ -624,7 +656,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
               uint4 u;
               uint32_t* up = reinterpret_cast<uint32_t*>(&u);
 #pragma unroll
-              for (int e = 0; e < 4; ++e) up[e] = bwd_pack(__uint_as_float(o[v8 * 8 + 2 * e]) * sc, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * sc, p.f16);
+              for (int e = 0; e < 4; ++e) up[e] = bwd_pack<F16>(__uint_as_float(o[v8 * 8 + 2 * e]) * sc, __uint_as_float(o[v8 * 8 + 2 * e + 1]) * sc);
               *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = u;
             }
         }
@@ -697,8 +729,10 @@ static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
   FA_CUDA(cudaGetDevice(&dev));
   const bool tracked = dev >= 0 && dev < 128;
   if (!tracked || !((attr_set[dev >> 6].load(std::memory_order_relaxed) >> (dev & 63)) & 1)) {
-    FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDq));
-    FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDkdv));
+    FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDq));
+    FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDq));
+    FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dkdv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDkdv));
+    FA_CUDA(cudaFuncSetAttribute(fa100_bwd_dkdv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemDkdv));
     if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
   }
   // D: a packed batch is one "sequence" of total_q rows for this kernel (rows no sequence uses are computed and never read)
@@ -715,8 +749,11 @@ static int launch_bwd(const Fa100BwdParams* p, cudaStream_t stream) {
                        p->o_row_stride, p->o_head_stride, dot_b, p->h, dot_sq, dot_sqr, p->d));
   const uint32_t fmt = p->dtype == FA100_BF16 ? kFmtBF16 : kFmtF16;
   const int m_blocks = (p->seqlen_q + kBwdTile - 1) / kBwdTile, n_blocks = (p->seqlen_k + kBwdTile - 1) / kBwdTile;  // of the longest sequence
-  FA_CUDA(launch_pdl(fa100_bwd_dq_kernel, dim3(m_blocks, p->h, p->b), dim3(kBwdThreads), size_t(kSmemDq), stream, 1, kp, tmQ, tmdO, tmK, tmV, fmt));
-  FA_CUDA(launch_pdl(fa100_bwd_dkdv_kernel, dim3(n_blocks, p->h_k, p->b), dim3(kBwdThreads), size_t(kSmemDkdv), stream, 1, kp, tmQ, tmdO, tmK, tmV, fmt));
+  const bool f16 = p->dtype == FA100_FP16;
+  FA_CUDA(launch_pdl(f16 ? fa100_bwd_dq_kernel<true> : fa100_bwd_dq_kernel<false>, dim3(m_blocks, p->h, p->b), dim3(kBwdThreads), size_t(kSmemDq), stream, 1,
+                     kp, tmQ, tmdO, tmK, tmV, fmt));
+  FA_CUDA(launch_pdl(f16 ? fa100_bwd_dkdv_kernel<true> : fa100_bwd_dkdv_kernel<false>, dim3(n_blocks, p->h_k, p->b), dim3(kBwdThreads), size_t(kSmemDkdv), stream, 1,
+                     kp, tmQ, tmdO, tmK, tmV, fmt));
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
