@@ -382,6 +382,35 @@ def measure(ctx, w, steps, warmup, do_e2e, ring_kw=None, want_clocks=True):
     return res
 
 
+def measure_bwd(ctx, w, steps, warmup, peaks):
+    """Backward of the same workload through torch.ops.flash_attn_3.bwd (three launches per step: D = rowsum(dO o O), the dQ
+    kernel, the dK/dV kernel), counted as 2.5 x the forward's algorithmic FLOPs (hopper/benchmark_attn.py:62-73)."""
+    import flash_attn_interface  # noqa: F401  (registers torch.ops.flash_attn_3)
+
+    t = make_inputs(w, ctx.dev, seed=ctx.rank)
+    q, k, v = (t[n].to(ctx.dev) for n in ("q", "k", "v"))
+    out, lse, *_ = torch.ops.flash_attn_3.fwd(q, k, v, is_causal=w["causal"])
+    g = torch.randn_like(out)
+    step = lambda: torch.ops.flash_attn_3.bwd(g, q, k, v, out, lse, None, None, None, None, None, None, None, None, None, None, w["causal"])  # noqa: E731
+    for _ in range(max(warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = max(3, min(steps, 10))
+    e0.record()
+    for _ in range(n):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n
+    tf = 2.5 * flops(w) / ms / 1e9
+    peak = peaks["tensor"]
+    return dict(metric="bwd TFLOPS/GPU bf16 hdim128 causal (2.5 x forward FLOPs)", value=tf, unit="TFLOP/s", ms_per_step=ms, dtype="bf16",
+                gpu_launches=3 * n, workload=w["desc"] + ", backward (dq, dk, dv)",
+                roofline=dict(bound="tensor", achieved=tf * 7 / 5, peak=peak, unit="TFLOP/s", frac=tf * 7 / 5 / peak, traffic=None,
+                              note="achieved counts the 7 tile products the two kernels execute (S and dP are recomputed in both); value counts 5"))
+
+
 def roofline_of(w, per_gpu, peaks, name, fp8_tflops=None):
     decode = "page" in w
     if decode:
@@ -593,6 +622,10 @@ def main():
                         extra[name]["workload"] = WORKLOADS[name]["desc"]
                     except Exception as e:  # noqa: BLE001
                         extra[name] = "failed: " + repr(e)[:300]
+                try:
+                    extra["bwd"] = measure_bwd(ctx, w, args.steps, args.warmup, peaks)
+                except Exception as e:  # noqa: BLE001
+                    extra["bwd"] = "failed: " + repr(e)[:300]
                 line["extra"] = extra
             else:
                 line["ring_c5"] = measure_ring(ctx, max(3, min(args.steps, 10)), args.warmup)
