@@ -68,7 +68,7 @@ static int launch_instance_split(const FwdKernelParams& kp, const CUtensorMap& t
     FA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LS::kTotalBytes));
     if (tracked) attr_set[dev >> 6].fetch_or(uint64_t(1) << (dev & 63), std::memory_order_relaxed);
   }
-  FA_CUDA(launch_pdl(kernel, dim3(grid), dim3(kSplitThreads), size_t(LS::kTotalBytes), stream, 1, kp, tmQ, tmK, tmV, tmO, tmQv, fmt));
+  FA_CUDA(launch_pdl(kernel, dim3(grid), dim3(HD > 128 ? kThreads : kSplitThreads), size_t(LS::kTotalBytes), stream, 1, kp, tmQ, tmK, tmV, tmO, tmQv, fmt));
   FA_CUDA(cudaGetLastError());
   return FA100_OK;
 }
@@ -386,6 +386,11 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
                              : launch_instance2<64, 2, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
     return f16 ? launch_instance2<128, 2, false, true>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream)
                : launch_instance2<128, 2, false, false>(kp, tmQ, tmK, tmV, tmO, fmt, grid, stream);
+  }
+  if (!dual && solo && (p->variant & FA100_VARIANT_SPLIT_ROWS)) {
+    if (fp8) return launch_instance_split<256, 1, true, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);
+    return f16 ? launch_instance_split<256, 2, false, true>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream)
+               : launch_instance_split<256, 2, false, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);
   }
   if (!dual && !solo && !pair && (p->variant & FA100_VARIANT_SPLIT_ROWS)) {
     if (fp8) return launch_instance_split<128, 1, true, false>(kp, tmQ, tmK, tmV, tmO, tmQv, fmt, grid, stream);

@@ -17,7 +17,6 @@
 namespace fa100 {
 
 constexpr int kSplitSoftmaxWarps = 16;
-constexpr int kSplitMmaWarp = 16, kSplitLoadWarp = 17, kSplitPvWarp = 18;
 constexpr int kSplitThreads = 20 * 32;
 constexpr int kSplitExchangeBytes = kQTiles * 2 * kBlockM * 4;  // one fp32 slot per (tile, half, row)
 
@@ -53,10 +52,12 @@ FA_DEVICE float chunk_max(const uint32_t (&x)[32], int col0, int col_lo, int col
 }
 
 // Softmax warp w of 16: half = w / 8 (key columns [64 half, +64) of every block), tile t = (w / 4) % 2, TMEM lane quarter w % 4.
-template <int HD, int ELT, bool FP8, bool F16>
+// SOLO (head dims above 128, one Q tile per work item): the eight softmax warps the kernel has anyway -- four of them idle
+// in the one-thread-per-row kernel -- share the single tile: half = w / 4, t = 0, the 224-register budget is untouched.
+template <int HD, int ELT, bool FP8, bool F16, bool SOLO = false>
 FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* tmO, uint8_t* sO, float* xch, FwdBarriers* bar,
                                   uint32_t tmem, int warp, int lane) {
-  const int half = warp >> 3, t = (warp >> 2) & 1, q = warp & 3;
+  const int half = SOLO ? warp >> 2 : warp >> 3, t = SOLO ? 0 : (warp >> 2) & 1, q = warp & 3;
   const int row = q * 32 + lane;
   const uint32_t tS = tmem + (uint32_t(q * 32) << 16);
   const uint32_t tSown = tS + half * 64;
@@ -81,7 +82,7 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
 
   const int n_work = total_work(p);
   for (int wi = 0, w; (w = work_index<false>(wi)) < n_work; ++wi) {
-    const RowGeom rg = row_geom<FP8, false, false, false>(p, w, t, row);
+    const RowGeom rg = row_geom<FP8, false, SOLO, false>(p, w, t, row);
     if (!rg.has_rows) continue;
     const float scale_log2 = rg.scale_log2;
     const bool softcap = p.softcap_pre != 0.f;
@@ -195,12 +196,12 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
 
     // ---- epilogue (softmax_role's, with each thread on its own half of the O columns)
     {
-      const WorkGeom g = make_geom<false, false, false>(p, w, 0);
+      const WorkGeom g = make_geom<false, SOLO, false>(p, w, 0);
       const bool split = p.o_accum != nullptr;
       const int part = g.it.split;
       const bool live = rg.n_max > rg.n_min;
       const int in_tile = p.pack > 1 ? row / p.pack : row;
-      const int pos = tile_pos0<false, false>(p, g.it, t, 0) + in_tile;
+      const int pos = tile_pos0<SOLO, false>(p, g.it, t, 0) + in_tile;
       const int hq = p.pack > 1 ? g.it.head * p.qheads_per_kv + row % p.pack : g.it.head;
       const bool row_valid = in_tile < p.pos_per_tile && pos < g.seq.sq;
       float out_scale = 1.0f;
@@ -240,7 +241,7 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
                                             row_idx * p.o_row_stride + hq * p.o_head_stride);
       float4* o32 = reinterpret_cast<float4*>(p.o_accum + part * p.oacc_split_stride + g.it.bi * p.oacc_batch_stride +
                                               hq * p.oacc_head_stride + row_idx * p.dv);
-      if (p.o_tma) {
+      if (HD <= 128 && p.o_tma) {
         // per 64-column slice the two threads of a row convert 32 columns each into the tile's [128][128 B] staging box
         uint8_t* stage = sO + t * FwdSmem<HD, ELT, false>::kOStageBytes;
         const bool issuer = (half == 0 && q == 0 && lane == 0);
@@ -334,7 +335,7 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
       }
     }
   }
-  if (p.o_tma && half == 0 && q == 0 && lane == 0) tma_store_wait0();
+  if (HD <= 128 && p.o_tma && half == 0 && q == 0 && lane == 0) tma_store_wait0();
   FA_PROF(7);
   FA_PROF_FLUSH();
 }
@@ -349,12 +350,14 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
 constexpr int kSplitRegs[2] = {FA100_SPLIT_SMX_REGS, FA100_SPLIT_OTHER_REGS};
 
 template <int HD, int ELT, bool FP8, bool F16>
-__global__ void __launch_bounds__(kSplitThreads, 1)
+__global__ void __launch_bounds__(HD > 128 ? kThreads : kSplitThreads, 1)
 fa100_fwd_split_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constant__ CUtensorMap tmQ,
                        const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                        const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmQv, uint32_t fmt) {
   using L = FwdSmem<HD, ELT, false>;
-  static_assert(HD <= 128, "the split-row kernel covers head dims up to 128");
+  constexpr bool SOLO = HD > 128;  // one Q tile per work item: 8 softmax warps (the default kernel's 12-warp CTA), else 16 (20 warps)
+  constexpr int kSmxWarps = SOLO ? kSoftmaxWarps : kSplitSoftmaxWarps;
+  constexpr int kMma = kSmxWarps, kLoad = kSmxWarps + 1, kPv = kSmxWarps + 2;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sQ = smem;
   uint8_t* sKV = smem + L::kQSlots * L::kQBytes;
@@ -364,8 +367,8 @@ fa100_fwd_split_kernel(const __grid_constant__ FwdKernelParams p, const __grid_c
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   FA_TRACE_BEGIN();
   if (smem_u32(smem) & 1023u) __trap();
-  if (warp == kSplitLoadWarp && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); if (p.o_tma) tma_prefetch_desc(&tmO); }
-  if (warp == kSplitMmaWarp && lane == 0) {
+  if (warp == kLoad && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); if (p.o_tma) tma_prefetch_desc(&tmO); }
+  if (warp == kMma && lane == 0) {
     constexpr int kSmxArrivals = 8;  // eight softmax warps per Q tile
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
@@ -388,14 +391,14 @@ fa100_fwd_split_kernel(const __grid_constant__ FwdKernelParams p, const __grid_c
     if (threadIdx.x == 0 && blockIdx.x == 0) { g_fa100_hang_info[0] = 0xDEAD0000u | 0x5CEDu; g_fa100_hang_info[1] = 0; g_fa100_hang_info[2] = 0; g_fa100_hang_info[3] = 0; __threadfence(); }
     __trap();
   }
-  if (warp < kSplitSoftmaxWarps) {
-    setmaxnreg_inc<kSplitRegs[0]>();
-    softmax_split_role<HD, ELT, FP8, F16>(p, &tmO, sO, xch, bar, tmem, warp, lane);
+  if (warp < kSmxWarps) {
+    setmaxnreg_inc<SOLO ? 224 : kSplitRegs[0]>();
+    softmax_split_role<HD, ELT, FP8, F16, SOLO>(p, &tmO, sO, xch, bar, tmem, warp, lane);
   } else {
-    setmaxnreg_dec<kSplitRegs[1]>();
-    if (warp == kSplitMmaWarp) mma_role<HD, ELT, FP8, false, true, false>(p, fmt, sQ, sKV, bar, tmem);
-    if (warp == kSplitPvWarp) mma_role<HD, ELT, FP8, false, false, false>(p, fmt, sQ, sKV, bar, tmem);
-    if (warp == kSplitLoadWarp) producer_role<HD, ELT, false, false>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar, 0, &tmQv);
+    setmaxnreg_dec<SOLO ? 56 : kSplitRegs[1]>();
+    if (warp == kMma) mma_role<HD, ELT, FP8, false, true, false>(p, fmt, sQ, sKV, bar, tmem);
+    if (warp == kPv) mma_role<HD, ELT, FP8, false, false, false>(p, fmt, sQ, sKV, bar, tmem);
+    if (warp == kLoad) producer_role<HD, ELT, false, false>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar, 0, &tmQv);
   }
   FA_TRACE_END();
   tc_fence_before();

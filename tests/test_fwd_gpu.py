@@ -729,7 +729,7 @@ def test_four_role_variant(sq, sk, d, kw, dtype, monkeypatch):
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float8_e4m3fn])
 @pytest.mark.parametrize("kw", [dict(), dict(causal=True), dict(window_size=(100, 20)), dict(softcap=15.0, causal=True)])
-@pytest.mark.parametrize("sq,sk,d", [(256, 512, 128), (1024, 1024, 128), (700, 500, 64), (1500, 3000, 128), (113, 203, 96)])
+@pytest.mark.parametrize("sq,sk,d", [(256, 512, 128), (1024, 1024, 128), (700, 500, 64), (1500, 3000, 128), (113, 203, 96), (300, 700, 256)])
 def test_split_rows_variant(sq, sk, d, kw, dtype, monkeypatch):
     """The split-row prefill kernel of csrc/fa100_fwd_split.cuh (FA100_SPLIT_ROWS=1 -> Fa100FwdParams.variant bit 64): two
     softmax threads per query row, each on 64 of a block's 128 key columns and half of the O columns, identical running
@@ -739,6 +739,7 @@ def test_split_rows_variant(sq, sk, d, kw, dtype, monkeypatch):
     fp8 = dtype == torch.float8_e4m3fn
     if fp8 and d == 96:
         d = 64
+    # d = 256: the one-tile (head dim > 128) geometry, where the eight softmax warps share the single Q tile
     g = torch.Generator().manual_seed(10)
     mk = lambda *s: torch.randn(*s, generator=g).to(torch.bfloat16).to(dtype)  # noqa: E731
     q, k, v = mk(2, sq, 8, d), mk(2, sk, 2, d), mk(2, sk, 2, d)
