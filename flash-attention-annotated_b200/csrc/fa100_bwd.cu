@@ -91,7 +91,8 @@ struct BwdBarriers {
   uint64_t v_full[2], v_empty[2];  // dQ kernel: the V ring
   uint64_t s_ready;           // S / dP of a step are in tensor memory (tcgen05.commit)
   uint64_t regs_loaded;       // every worker warp holds the step's S / dP in registers (dQ kernel)
-  uint64_t ops_ready;         // every worker warp has stored the step's 16-bit operands (dS; P^T and dS^T)
+  uint64_t ops_ready[2];      // every worker warp has stored the step's 16-bit operands (dS; P^T and dS^T).  Two of them in the dQ
+                              // kernel (block n uses n & 1): the workers may finish block n + 1 before the MMA warp has looked at block n
   uint64_t mma_done;          // accumulators final
   uint64_t dp_ready, p_ready; // dK/dV kernel: dP^T in tensor memory (commit); P^T stored by every worker warp
   uint64_t rows_full[4], rows_empty[4];  // dK/dV kernel: the step's per-query-row constants in shared memory
@@ -181,7 +182,7 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
   const int hk = hq / (p.h / p.h_k);
   if (tid == 0) {
     mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->mma_done, 1);
-    mbar_init(&bar->regs_loaded, kBwdWorkerWarps); mbar_init(&bar->ops_ready, kBwdWorkerWarps);
+    mbar_init(&bar->regs_loaded, kBwdWorkerWarps); mbar_init(&bar->ops_ready[0], kBwdWorkerWarps); mbar_init(&bar->ops_ready[1], kBwdWorkerWarps);
     for (int s = 0; s < 3; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&bar->v_full[s], 1); mbar_init(&bar->v_empty[s], 1); }
     fence_mbar_init();
@@ -260,7 +261,7 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
           mbar_wait(&bar->regs_loaded, nb & 1, 0xB5);  // S / dP of block nb are in the workers' registers
           issue_s_dp(nb + 1);
         }
-        mbar_wait(&bar->ops_ready, nb & 1, 0xB6);      // dS of block nb is in its buffer
+        mbar_wait(&bar->ops_ready[nb & 1], (nb >> 1) & 1, 0xB6);      // dS of block nb is in its buffer
         tc_fence_after();
         if (elect_one()) {
           const uint32_t k_mn = (smem_u32(sK + kst * kBwdTileBytes) >> 4) | kLboMN;
@@ -332,7 +333,7 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
       // keys [kBwdCols part, +kBwdCols) of the block are columns [kBwdCols / 2 part, ...) of the 16-bit dS buffer
       bwd_tmem_st(tRow + 384 + (nb & 1) * 64 + part * (kBwdCols / 2), pk);
       tmem_st_wait();
-      bwd_warp_arrive(&bar->ops_ready, lane);
+      bwd_warp_arrive(&bar->ops_ready[nb & 1], lane);
     }
     // dQ = scale * accumulator; each thread stores its share of the columns
     if (n_blocks > 0) { mbar_wait(&bar->mma_done, 0, 0xB4); tc_fence_after(); }
@@ -390,7 +391,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
   const int G = p.h / p.h_k;
   if (tid == 0) {
     mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->dp_ready, 1); mbar_init(&bar->mma_done, 1);
-    mbar_init(&bar->p_ready, kBwdWorkerWarps); mbar_init(&bar->ops_ready, kBwdWorkerWarps);
+    mbar_init(&bar->p_ready, kBwdWorkerWarps); mbar_init(&bar->ops_ready[0], kBwdWorkerWarps);
     for (int s_ = 0; s_ < 2; ++s_) {
       mbar_init(&bar->full[s_], 1); mbar_init(&bar->empty[s_], 1);       // Q stages
       mbar_init(&bar->v_full[s_], 1); mbar_init(&bar->v_empty[s_], 1);   // dO stages (free one product earlier than Q)
@@ -520,7 +521,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
         }
         __syncwarp();
         if (t + 1 < steps) issue_s(t + 1);
-        mbar_wait(&bar->ops_ready, t & 1, 0xC5);    // dS^T(t) is in B
+        mbar_wait(&bar->ops_ready[0], t & 1, 0xC5);    // dS^T(t) is in B
         tc_fence_after();
         if (elect_one()) {
           const uint32_t q_mn = (smem_u32(sQ + st * kBwdTileBytes) >> 4) | kLboMN;
@@ -629,7 +630,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
       }
       bwd_tmem_st(tB, pk);   // dS^T over the first half of this thread's own dP^T columns
       tmem_st_wait();
-      bwd_warp_arrive(&bar->ops_ready, lane);
+      bwd_warp_arrive(&bar->ops_ready[0], lane);
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar->rows_empty[slot]);  // this warp is done with the step's row constants
     }
