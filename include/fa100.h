@@ -136,7 +136,9 @@ typedef struct Fa100FwdParams {
    * FA100_VARIANT_FOUR_ROLE = the four-role prefill mainloop of csrc/fa100_fwd2.cuh (one MMA warp issuing PV_t, QK_t in order
    * with P_t overlaid on S_t, separate softmax and correction warpgroups, P published in two pieces) instead of the default
    * (score buffer shared by the two Q tiles, QK and PV issuing warps, softmax warps own rescale + epilogue).  Parity-green on
-   * the whole suite; measured 12 % slower on C2, hence opt-in. */
+   * the whole suite; measured 12 % slower on C2, hence opt-in.  FA100_VARIANT_SPLIT_ROWS = two softmax threads per
+   * query row (csrc/fa100_fwd_split.cuh; 16 softmax warps, each thread on 64 of a block's 128 key columns): parity-green, 5-8 % slower
+   * on C2, opt-in. */
   int32_t variant;
   /* Fused merge of a running partial (ring / context-parallel attention): with o_accum / lse_accum set and
    * num_splits == 1, 1 = read the fp32 partial already in o_accum / lse_accum, merge this call's result into it with the
