@@ -221,7 +221,7 @@ FA_DEVICE void softmax2_role(const FwdKernelParams& p, float* sMsg, FwdBarriers2
 
   const int n_work = total_work(p);
   for (int wi = 0, w; (w = work_index<false>(wi)) < n_work; ++wi) {
-    const RowGeom rg = row_geom<FP8, false, false, false>(p, w, t, row, 0);
+    const RowGeom rg = row_geom<FP8, false, false, false>(p, make_geom<false, false, false>(p, w, 0), t, row, 0);
     if (!rg.has_rows || rg.n_max <= rg.n_min) continue;  // a tile without keys is written by the correction warpgroup alone
     const float scale_log2 = rg.scale_log2;
     const bool softcap = rg.softcap_pre != 0.f;

@@ -9,7 +9,8 @@
 //   warp  8     QK issuer (elected lane): S = Q_t K^T (SS form) into the score buffer the two tiles share
 //   warp  9     TMA producer (elected lane): Q tiles once per work item, K/V tiles through an mbarrier ring
 //   warp  10    PV issuer (elected lane): O_t += P_t V (TS form, P in TMEM)
-//   warp  11    idle (completes the third warpgroup for setmaxnreg: softmax warps run with 224 registers, the rest 56)
+//   warp  11    geometry: decodes the work items ahead of everybody else into a shared-memory ring (and completes the third
+//               warpgroup for setmaxnreg: softmax warps run with 224 registers, the rest 56)
 //
 // TMEM (512 columns): S @0 (fp32 scores; ONE buffer the two Q tiles take turns in), P_0 @128, P_1 @192 (operand dtype: 64
 // columns at 16 bit, 32 at e4m3), O_0 @256, O_1 @384.  Two 128-row Q tiles per CTA ping-pong through the tensor pipe: a
@@ -29,6 +30,7 @@ constexpr int kSoftmaxWarps = 8;
 constexpr int kMmaWarp = 8;
 constexpr int kLoadWarp = 9;
 constexpr int kPvWarp = 10;
+constexpr int kGeomWarp = 11;  // computes every work item's geometry ahead of the other roles (geom ring)
 constexpr int kThreads = 12 * 32;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -107,6 +109,19 @@ struct SeqInfo {
 };
 
 struct TileRange { int n_min, n_max; bool has_rows; };
+
+// Work-item geometry every role needs (make_geom in fa100_fwd_roles.cuh).  In the default kernel the otherwise idle twelfth
+// warp computes it one to four items ahead and hands it to the other roles through shared memory (geom ring below): a
+// make_geom costs ~2500-3000 clk of integer divisions and dependent loads, twice per item on every softmax warp before
+// (cycle-bucket build with -DFA100_PROF_EPI: 6500 of the 36800 clk a softmax warp spent per 1024-token causal item).
+struct WorkGeom {
+  WorkItem it;
+  SeqInfo seq;
+  TileRange tr[2];
+  int n_lo, n_hi;  // union of the tiles' key-block ranges; n_hi <= n_lo means nothing to do
+  int hk;          // kv head
+};
+constexpr int kGeomSlots = 4;
 
 // Static persistent schedule: CTA c runs list positions c, 2 grid - 1 - c, 2 grid + c, ... (boustrophedon).  Item lengths
 // fall linearly inside a K/V group, so pairing a forward pass with a reversed one evens out what plain round-robin
@@ -241,6 +256,8 @@ struct FwdBarriers {
   uint64_t s_free;
   uint64_t o_full[kQTiles], o_empty[kQTiles];
   uint64_t kv_full[8], kv_empty[8];
+  uint64_t geom_full[kGeomSlots], geom_empty[kGeomSlots];  // geometry ring: filled by the geometry warp, released by every consumer warp
+  WorkGeom geom[kGeomSlots];
   uint32_t tmem_base;
   uint32_t ts[8];  // latency-probe timestamps of the profiling build (0,1: QK_t issued; 2: s_free arrive; 4,5: p_full[t] arrive)
   uint32_t pad_[3];

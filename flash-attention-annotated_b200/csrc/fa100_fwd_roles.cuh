@@ -4,14 +4,8 @@
 
 namespace fa100 {
 
-// Work-item geometry every role derives identically (no communication needed).
-struct WorkGeom {
-  WorkItem it;
-  SeqInfo seq;
-  TileRange tr[kQTiles];
-  int n_lo, n_hi;  // union of the tiles' key-block ranges; n_hi <= n_lo means nothing to do
-  int hk;          // kv head
-};
+// Work-item geometry (struct WorkGeom, fa100_fwd_kernel.cuh): every role derives it identically with make_geom, or -- RING --
+// takes it from the shared-memory ring the geometry warp fills.
 
 // DUAL (decode, all query rows of an item fit one 128-row tile): both TMEM tile pipelines work on the SAME rows and
 // split the item's key blocks between them -- tile 0 takes blocks n_hi-1, n_hi-3, ..., tile 1 takes n_hi-2, n_hi-4, ... --
@@ -76,13 +70,45 @@ template <bool ONE_TILE, bool PAIR = false> FA_DEVICE int tile_pos0(const FwdKer
 FA_DEVICE bool tile_live(const WorkGeom& g, int t) { return g.tr[t].n_max > g.tr[t].n_min; }
 FA_DEVICE bool tile_uses(const WorkGeom& g, int t, int nb) { return nb >= g.tr[t].n_min && nb < g.tr[t].n_max; }
 
+// RING: item wi's geometry from the ring (every consumer warp takes and releases every item, in order, exactly once)
+template <bool DUAL, bool SOLO, bool PAIR, bool RING, typename Bar>
+FA_DEVICE WorkGeom item_geom(const FwdKernelParams& p, Bar* bar, int w, int wi, int rank) {
+  if constexpr (RING) {
+    const int slot = wi % kGeomSlots;
+    mbar_wait(&bar->geom_full[slot], (wi / kGeomSlots) & 1, 0x90);
+    return bar->geom[slot];
+  } else {
+    return make_geom<DUAL, SOLO, PAIR>(p, w, rank);
+  }
+}
+template <bool RING, typename Bar>
+FA_DEVICE void item_geom_release(Bar* bar, int wi) {
+  if constexpr (RING) {
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(&bar->geom_empty[wi % kGeomSlots]);
+  }
+}
+// the geometry warp: walks the CTA's work list ahead of everybody else
+template <bool DUAL, bool SOLO, bool PAIR>
+FA_DEVICE void geom_role(const FwdKernelParams& p, FwdBarriers* bar, int rank) {
+  const int lane = threadIdx.x & 31;
+  const int n_work = total_work(p);
+  for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
+    const int slot = wi % kGeomSlots;
+    if (wi >= kGeomSlots) mbar_wait(&bar->geom_empty[slot], (wi / kGeomSlots - 1) & 1, 0x91);
+    if (lane == 0) bar->geom[slot] = make_geom<DUAL, SOLO, PAIR>(p, w, rank);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bar->geom_full[slot]);
+  }
+}
+
 struct RingState { int stage = 0; uint32_t phase = 0; };
 template <int STAGES> FA_DEVICE void ring_advance(RingState& r) { if (++r.stage == STAGES) { r.stage = 0; r.phase ^= 1; } }
 
 // ----------------------------------------------------------------------------- TMA producer
 // The whole warp walks the schedule (warp-uniform control flow keeps descriptors and coordinates in uniform
 // registers); one elected lane issues the bulk copies.
-template <int HD, int ELT, bool DUAL, bool PAIR = false, typename Bar = FwdBarriers>
+template <int HD, int ELT, bool DUAL, bool PAIR = false, typename Bar = FwdBarriers, bool RING = false>
 FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, const CUtensorMap* tmK,
                              const CUtensorMap* tmV, uint8_t* sQ, uint8_t* sKV, Bar* bar, int rank = 0, const CUtensorMap* tmQv = nullptr) {
   using L = FwdSmem<HD, ELT, PAIR>;
@@ -103,7 +129,8 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   const uint32_t q_tx = uint32_t((p.qk_boxes + (with_qv ? p.v_boxes : 0)) * kRowBytes) * p.pack * p.pos_per_tile;
   const int n_work = total_work(p);
   for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
-    const WorkGeom g = make_geom<DUAL, (HD > 128), PAIR>(p, w, rank);
+    const WorkGeom g = item_geom<DUAL, (HD > 128), PAIR, RING>(p, bar, w, wi, rank);
+    item_geom_release<RING>(bar, wi);  // g is a copy
     if (g.n_hi <= g.n_lo) continue;
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
@@ -211,7 +238,7 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
 // same ring sequence (kIsQK selects which stages a warp acts on): K(first), then V(nb), K(nb-1) per key block, or in
 // DUAL mode K_0, K_1, then V_0, K_0(next), V_1, K_1(next) per step.  All 32 lanes run the control flow and the waits
 // (descriptors stay in uniform registers); one elected lane issues.
-template <int HD, int ELT, bool FP8, bool DUAL, bool kIsQK, bool PAIR = false>
+template <int HD, int ELT, bool FP8, bool DUAL, bool kIsQK, bool PAIR = false, bool RING = false>
 FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uint8_t* sKV, FwdBarriers* bar, uint32_t tmem) {
   using L = FwdSmem<HD, ELT, PAIR>;
   constexpr int kHalfBytes = kBlockN * 128;
@@ -339,11 +366,12 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
     int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi, seq_k;
     {
-      const WorkGeom g = make_geom<DUAL, (HD > 128), PAIR>(p, w, 0);
+      const WorkGeom g = item_geom<DUAL, (HD > 128), PAIR, RING>(p, bar, w, wi, 0);  // the MMA warps run in the pair's rank 0
       n_lo = g.n_lo; n_hi = g.n_hi; seq_k = g.seq.sk;
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) { n_min[t] = g.tr[t].n_min; n_max[t] = g.tr[t].n_max; }
     }
+    item_geom_release<RING>(bar, wi);
     if (n_hi <= n_lo) continue;
     if (kIsQK) {
 #pragma unroll

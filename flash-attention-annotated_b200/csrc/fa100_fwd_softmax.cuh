@@ -86,8 +86,7 @@ struct RowGeom {
 };
 
 template <bool FP8, bool DUAL, bool SOLO, bool PAIR = false>
-FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row, int rank = 0) {
-  const WorkGeom g = make_geom<DUAL, SOLO, PAIR>(p, w, rank);
+FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, const WorkGeom& g, int t, int row, int rank = 0) {
   RowGeom r;
   const TileRange tr = t == 0 ? g.tr[0] : g.tr[1];  // no dynamic indexing: that would put the struct in local memory
   r.has_rows = tr.has_rows;
@@ -123,7 +122,17 @@ FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, int w, int t, int row, int 
 // on Q tile t = w / 4 and owns TMEM lanes (= query rows) 32*(w%4)..; one thread owns one row, so the row max and the
 // row sum need no shuffles.  The step loop has two bodies: a lean one for interior key blocks (no mask, no softcap; it
 // is the instruction stream tools/ubench/ubench_softmax.cu measures in isolation) and a general one for boundary blocks.
-template <int HD, int ELT, bool FP8, bool F16, bool DUAL, bool PAIR = false>
+// -DFA100_PROF_EPI (cycle-bucket build only): the key loop's marks all go to bucket 0 and buckets 1-6 split the time between
+// key loops: 1 loop exit + geometry + LSE, 2 wait o_full, 3 O: TMEM -> registers -> convert, 4 staging barriers + stores,
+// 5 o_empty arrive + loop back, 6 next item's row_geom; 7 stays "top of the first block".
+#ifdef FA100_PROF_EPI
+#define FA_PROF_L(i) FA_PROF(0)
+#define FA_PROF_E(i) FA_PROF(i)
+#else
+#define FA_PROF_L(i) FA_PROF(i)
+#define FA_PROF_E(i) do { } while (0)
+#endif
+template <int HD, int ELT, bool FP8, bool F16, bool DUAL, bool PAIR = false, bool RING = false>
 FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, uint8_t* sO, FwdBarriers* bar, uint32_t tmem, int warp, int lane, int rank = 0) {
   const int t = warp >> 2, q = warp & 3;
   const int row = q * 32 + lane;
@@ -138,15 +147,16 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
 
   const int n_work = total_work(p);
   for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
-    const RowGeom rg = row_geom<FP8, DUAL, (HD > 128), PAIR>(p, w, t, row, rank);
-    if (!rg.has_rows) continue;
+    const RowGeom rg = row_geom<FP8, DUAL, (HD > 128), PAIR>(p, item_geom<DUAL, (HD > 128), PAIR, RING>(p, bar, w, wi, rank), t, row, rank);
+    FA_PROF_E(6);
+    if (!rg.has_rows) { item_geom_release<RING>(bar, wi); continue; }
     const float scale_log2 = rg.scale_log2;
     const bool softcap = p.softcap_pre != 0.f;
     float m_run = -INFINITY, l_run = 0.f;
     for (int nb = rg.n_max - 1; nb >= rg.n_min; nb -= (DUAL ? 2 : 1)) {
-      FA_PROF(7);
+      FA_PROF_L(7);
       mbar_wait(&bar->s_full[t], s_it & 1, 0x70 + t);
-      FA_PROF(0);
+      FA_PROF_L(0);
       FA_LAT_ACC(3, &bar->ts[t]);
       ++s_it;
       tc_fence_after();
@@ -154,7 +164,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
 #pragma unroll
       for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
       tmem_ld_wait();
-      FA_PROF(1);
+      FA_PROF_L(1);
       // the scores are in registers: hand S to the other tile's QK
       tc_fence_before();
       __syncwarp();
@@ -191,7 +201,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
           mx2 = fmaxf(mx2, __uint_as_float(s[c][i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[c][i + 3]));
         }
       const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-      FA_PROF(2);
+      FA_PROF_L(2);
       const float m_cand = fmaxf(m_run, m_blk);
       // lazy rescale: keep the stale max unless it grew by more than 2^8 (NaN from -inf - -inf compares false)
       const bool grow = (m_cand - m_run) * scale_log2 > (FP8 ? kFp8RescaleThreshold : kRescaleThreshold);
@@ -212,7 +222,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
         }
       }
       const float m_sub = (m_run == -INFINITY) ? 0.f : m_run * scale_log2 - (FP8 ? kFp8Offset : 0.0f);
-      FA_PROF(2);
+      FA_PROF_L(2);
       // P = exp2(S * scale - max), packed to the operand dtype and written over S: keys [32c, 32c + 32) of the tile go to
       // columns [16c, +16) (16-bit operands) or [8c, +8) (e4m3)
       float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
@@ -244,7 +254,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
             }
           }
         }
-        FA_PROF(4);
+        FA_PROF_L(4);
         if (!pv_drained) mbar_wait(&bar->pv_done[t], (pv_n - 1) & 1, 0x78 + t);
         tc_fence_after();
 #pragma unroll
@@ -253,7 +263,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
           else tmem_st8(tP + c * 8, pk + c * 8);
         }
       }
-      FA_PROF(5);
+      FA_PROF_L(5);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -261,13 +271,14 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
       if (q == 3) FA_LAT_STAMP(&bar->ts[4 + t]);
       FA_TRACE_POINT(0xA0 + t);
       ++pv_n;
-      FA_PROF(6);
+      FA_PROF_L(6);
       l_run = l_run * acc_scale + ((sum0 + sum1) + (sum2 + sum3));
     }
 
     // ---- epilogue: O / rowsum, LSE (hopper/softmax.h:137-155, epilogue_fwd.hpp:215-481); geometry is recomputed here
     {
-      const WorkGeom g = make_geom<DUAL, (HD > 128), PAIR>(p, w, rank);
+      // RING: the slot is still this warp's (released below); otherwise recomputed rather than carried through the key loop
+      const WorkGeom g = item_geom<DUAL, (HD > 128), PAIR, RING>(p, bar, w, wi, rank);
       const bool split = p.o_accum != nullptr;  // fp32 partials (split-KV, or one hop of ring attention)
       const int part = DUAL ? g.it.split * 2 + t : g.it.split;  // index of this partial
       const bool live = rg.n_max > rg.n_min;
@@ -305,7 +316,9 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
         if (!split) p.lse[g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + row_idx] = lse_val;
         else p.lse_accum[part * p.lseacc_split_stride + g.it.bi * p.lse_batch_stride + hq * p.lse_head_stride + row_idx] = lse_val;
       }
+      FA_PROF_E(1);
       if (live) { mbar_wait(&bar->o_full[t], o_it & 1, 0x80 + t); ++o_it; tc_fence_after(); }
+      FA_PROF_E(2);
       uint4* o16 = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.o) + g.seq.bq * p.o_batch_stride +
                                             row_idx * p.o_row_stride + hq * p.o_head_stride);
       float4* o32 = reinterpret_cast<float4*>(p.o_accum + part * p.oacc_split_stride + g.it.bi * p.oacc_batch_stride +
@@ -336,6 +349,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
               pk[hf * 16 + i] = F16 ? pack_f16(a, b2) : pack_bf16(a, b2);
             }
           }
+          FA_PROF_E(3);
           if (issuer) tma_store_wait_read0();
           named_bar_sync(1 + t, 128);
 #pragma unroll
@@ -349,6 +363,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
             tma_store_4d(tmO, stage, sl * 64, pos - in_tile, hq, g.seq.bq);
             tma_store_commit();
           }
+          FA_PROF_E(4);
         }
       } else
 #pragma unroll
@@ -406,7 +421,9 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
         __syncwarp();
         if (lane == 0) { if (PAIR) mbar_arrive_cluster(a_o_empty); else mbar_arrive(&bar->o_empty[t]); }
       }
+      FA_PROF_E(5);
     }
+    item_geom_release<RING>(bar, wi);
   }
   if (HD <= 128 && p.o_tma && q == 0 && lane == 0) tma_store_wait0();  // the staging box must outlive the last store
   FA_PROF(7);
@@ -441,6 +458,8 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
     }
     mbar_init(&bar->s_free, kSmxArrivals);
     for (int s = 0; s < 8; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
+    // geometry ring: consumers are the eight softmax warps, the producer and (rank 0 of a pair only) the two issuing warps
+    for (int s = 0; s < kGeomSlots; ++s) { mbar_init(&bar->geom_full[s], 1); mbar_init(&bar->geom_empty[s], (PAIR && rank != 0) ? 9 : 11); }
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -467,14 +486,15 @@ fa100_fwd_kernel(const __grid_constant__ FwdKernelParams p, const __grid_constan
   // register pool at launch: 384 threads x 168; warps 8-11 give 112 each to the 8 softmax warps (+56 each)
   if (warp < kSoftmaxWarps) {
     setmaxnreg_inc<224>();
-    softmax_role<HD, ELT, FP8, F16, DUAL, PAIR>(p, &tmO, sO, bar, tmem, warp, lane, rank);
+    softmax_role<HD, ELT, FP8, F16, DUAL, PAIR, true>(p, &tmO, sO, bar, tmem, warp, lane, rank);
   } else {
     setmaxnreg_dec<56>();
     if (rank == 0) {
-      if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL, true, PAIR>(p, fmt, sQ, sKV, bar, tmem);
-      if (warp == kPvWarp) mma_role<HD, ELT, FP8, DUAL, false, PAIR>(p, fmt, sQ, sKV, bar, tmem);
+      if (warp == kMmaWarp) mma_role<HD, ELT, FP8, DUAL, true, PAIR, true>(p, fmt, sQ, sKV, bar, tmem);
+      if (warp == kPvWarp) mma_role<HD, ELT, FP8, DUAL, false, PAIR, true>(p, fmt, sQ, sKV, bar, tmem);
     }
-    if (warp == kLoadWarp) producer_role<HD, ELT, DUAL, PAIR>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar, rank, &tmQv);
+    if (warp == kLoadWarp) producer_role<HD, ELT, DUAL, PAIR, FwdBarriers, true>(p, &tmQ, &tmK, &tmV, sQ, sKV, bar, rank, &tmQv);
+    if (warp == kGeomWarp) geom_role<DUAL, (HD > 128), PAIR>(p, bar, rank);
   }
   FA_TRACE_END();
   tc_fence_before();

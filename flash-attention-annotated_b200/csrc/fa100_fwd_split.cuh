@@ -82,7 +82,7 @@ FA_DEVICE void softmax_split_role(const FwdKernelParams& p, const CUtensorMap* t
 
   const int n_work = total_work(p);
   for (int wi = 0, w; (w = work_index<false>(wi)) < n_work; ++wi) {
-    const RowGeom rg = row_geom<FP8, false, SOLO, false>(p, w, t, row);
+    const RowGeom rg = row_geom<FP8, false, SOLO, false>(p, make_geom<false, SOLO, false>(p, w, 0), t, row);
     if (!rg.has_rows) continue;
     const float scale_log2 = rg.scale_log2;
     const bool softcap = p.softcap_pre != 0.f;
