@@ -128,6 +128,8 @@ FA_DEVICE RowGeom row_geom(const FwdKernelParams& p, const WorkGeom& g, int t, i
 #ifdef FA100_PROF_EPI
 #define FA_PROF_L(i) FA_PROF(0)
 #define FA_PROF_E(i) FA_PROF(i)
+#undef FA_LAT_ACC
+#define FA_LAT_ACC(i, word) do { } while (0)
 #else
 #define FA_PROF_L(i) FA_PROF(i)
 #define FA_PROF_E(i) do { } while (0)
@@ -184,13 +186,21 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
 #pragma unroll
             for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(fast_tanh(__uint_as_float(s[c][i]) * rg.softcap_pre));
         }
+        // visible columns of this row inside the block: [lo, hi) with compile-time column indices on the other side of the
+        // compare (one ISETP + one SEL per score; the left limit only when some row of the warp has one inside the block)
+        const int hi = rg.col_hi - n0, lo = rg.col_lo - n0;
 #pragma unroll
         for (int c = 0; c < 4; ++c)
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int col = n0 + c * 32 + i;
-            if (col >= rg.col_hi || col < rg.col_lo) s[c][i] = 0xff800000u;  // -inf
-          }
+          for (int i = 0; i < 32; ++i)
+            if (c * 32 + i >= hi) s[c][i] = 0xff800000u;  // -inf
+        if (__any_sync(0xffffffffu, lo > 0)) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (c * 32 + i < lo) s[c][i] = 0xff800000u;
+        }
       }
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll

@@ -18,6 +18,6 @@ items = b * h * ((s + 255) // 256); grid = min(items, 148)
 mine = len([r for r in range((items + grid - 1) // grid + 1) if (r * grid + (grid - 1 if r & 1 else 0)) < items])
 print(f"b{b} s{s} h{h} d{d} causal={causal}: {ms*1e3:.1f} us; CTA0 ~{mine} items; clk per ITEM per bucket")
 print("  buckets: 0 s_full wait, 1 S load, 2 s_free+mask+max, 3 rescale, 4 exp, 5 st issue, 6 st wait+publish, 7 loop top / geometry / epilogue")
-for w in (0, 4, 8, 9, 10):
+for w in (0, 4, 8, 9, 10, 12, 13):
     if w < len(pr) and sum(pr[w]):
         print(f"  warp {w:2d} total {sum(pr[w])/mine:8.0f} | " + " ".join(f"{i}:{x/mine:7.0f}" for i, x in enumerate(pr[w])))
