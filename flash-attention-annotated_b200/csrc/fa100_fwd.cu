@@ -151,6 +151,19 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   kp.is_local = ((wl >= 0 || wr >= 0 || p->attention_chunk > 0) && !kp.is_causal) ? 1 : 0;
   kp.window_left = wl; kp.window_right = wr; kp.attention_chunk = p->attention_chunk;
   kp.out_fp16 = p->dtype == FA100_FP16;
+  // Dynamic scheduling over a length-ordered list (decode_work, geom_role) under causal / local masks, when the caller supplies a
+  // zeroed counter: not for CTA pairs (both CTAs must agree on the item) and not on top of a device-built schedule.  The
+  // super-groups of the list are sized so that the K / V of the groups in flight stay in L2 (48 MB of its 126).
+  kp.tile_counter = nullptr;
+  kp.lpt_groups = 0;
+  if (p->tile_counter && !pair && (kp.is_causal || kp.is_local) && kp.sched == nullptr && kp.num_m_blocks > 1) {
+    const int gsz = kp.heads_work / p->h_k;
+    const int64_t kv_bytes = int64_t(p->seqlen_k) * (p->d + p->dv) * elt;
+    const int64_t by_l2 = std::max<int64_t>(1, (int64_t(48) << 20) / std::max<int64_t>(1, kv_bytes));
+    const int by_grid = std::max(1, plan->num_sm / std::max(1, gsz * cta_splits));
+    kp.lpt_groups = int(std::min<int64_t>(std::min<int64_t>(by_l2, by_grid), int64_t(p->b) * p->h_k));
+    kp.tile_counter = p->tile_counter;
+  }
   kp.softmax_scale = p->softmax_scale;
   if (p->softcap > 0.f) { kp.softcap_pre = p->softmax_scale / p->softcap; kp.scale_log2 = p->softcap * kLog2e; }
   else { kp.softcap_pre = 0.f; kp.scale_log2 = p->softmax_scale * kLog2e; }

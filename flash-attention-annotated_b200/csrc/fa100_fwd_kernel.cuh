@@ -84,10 +84,12 @@ struct FwdKernelParams {
   int32_t num_splits;
   int32_t num_work;       // static schedule: every (m block, batch, head, split); an upper bound when sched is set
   int32_t tiles_per_item; // 128-row Q tiles one work item covers: 2, or 1 in the dual-stream and head-dim-256 kernels
+  int32_t lpt_groups;     // > 0 (causal / local, static schedule): (batch, KV head) groups per super-group of the length-ordered work list
   // Device-built schedule for ragged batches (fa100_prepare_scheduler): [0] work items, [1] batches, [2 .. 2+b) batch
   // ids, most key blocks first, [2+b .. 2+2b] exclusive prefix of work items over that order, [3+2b .. 3+3b) CTA-level
   // split count of each batch element in that order (<= num_splits).  Null: static schedule.
   const int32_t* sched;
+  int32_t* tile_counter;  // dynamic scheduling (zeroed by the caller): the geometry warp takes the CTA's next item with an atomicAdd; null = static
   int32_t num_sm;         // SMs the launch may use (the schedule kernel sizes the per-batch split counts with it)
   int32_t is_causal, is_local, window_left, window_right, attention_chunk;
   int32_t out_fp16;       // 1: fp16 output, 0: bf16 output
@@ -120,6 +122,7 @@ struct WorkGeom {
   TileRange tr[2];
   int n_lo, n_hi;  // union of the tiles' key-block ranges; n_hi <= n_lo means nothing to do
   int hk;          // kv head
+  int w;           // index of the item in the work list; -1 in the geometry ring = the list is exhausted
 };
 constexpr int kGeomSlots = 4;
 
@@ -173,6 +176,23 @@ FA_DEVICE WorkItem decode_work(const FwdKernelParams& p, int w) {
   it.nsplits = p.num_splits;
   it.split = w % p.num_splits;  w /= p.num_splits;
   const int g = w % gsz;        w /= gsz;
+  if (p.lpt_groups > 0) {
+    // Causal / local masks make the row blocks of a sequence unequal (1 .. num_m_blocks key-block pairs), and the order above
+    // hands a CTA whole stretches of one group: makespan / mean 1.045 at C2, 1.11 for 4 x 16 heads x 8192 (host model,
+    // DESIGN.md 4.1).  Here the list is cut into super-groups of lpt_groups (batch, KV head) groups -- about one round of the
+    // grid -- and inside a super-group the row blocks go longest first ACROSS its groups, so the items of one round have
+    // (nearly) the same length and every CTA's sum comes out the same.  The query heads of a KV head stay adjacent (they
+    // run in the same round and share its K / V in L2).
+    const int groups = p.b * p.h_k;
+    const int per_sg = p.num_m_blocks * p.lpt_groups;
+    const int sg = w / per_sg, rem = w - sg * per_sg;
+    const int in_sg = min(p.lpt_groups, groups - sg * p.lpt_groups);  // the last super-group may be smaller
+    const int m_rev = rem / in_sg, group = sg * p.lpt_groups + (rem - m_rev * in_sg);
+    it.m_blk = p.num_m_blocks - 1 - m_rev;
+    it.bi = group / p.h_k;
+    it.head = (group - it.bi * p.h_k) * gsz + g;
+    return it;
+  }
   it.m_blk = p.num_m_blocks - 1 - w % p.num_m_blocks;  w /= p.num_m_blocks;
   it.head = (w % p.h_k) * gsz + g;
   it.bi = w / p.h_k;

@@ -19,6 +19,7 @@ namespace fa100 {
 template <bool DUAL, bool SOLO = false, bool PAIR = false>
 FA_DEVICE WorkGeom make_geom(const FwdKernelParams& p, int w, int rank = 0) {
   WorkGeom g;
+  g.w = w;
   g.it = decode_work(p, w);
   g.seq = load_seq(p, g.it.bi);
   g.hk = p.pack > 1 ? g.it.head : g.it.head / p.qheads_per_kv;
@@ -88,17 +89,29 @@ FA_DEVICE void item_geom_release(Bar* bar, int wi) {
     if ((threadIdx.x & 31) == 0) mbar_arrive(&bar->geom_empty[wi % kGeomSlots]);
   }
 }
-// the geometry warp: walks the CTA's work list ahead of everybody else
+// the geometry warp: walks the CTA's work list ahead of everybody else.  Static schedule: list positions work_index(0), (1), ...;
+// with FwdKernelParams.tile_counter (not for CTA pairs, whose two CTAs must agree on the item): the CTA's own index first, then
+// whatever an atomicAdd on the counter hands out (hopper/tile_scheduler.hpp:363-470, DynamicPersistentTileScheduler) -- the
+// round trip is hidden by the ring's depth.  A slot with w = -1 ends every consumer's loop.
 template <bool DUAL, bool SOLO, bool PAIR>
 FA_DEVICE void geom_role(const FwdKernelParams& p, FwdBarriers* bar, int rank) {
   const int lane = threadIdx.x & 31;
   const int n_work = total_work(p);
-  for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
+  const bool dynamic = !PAIR && p.tile_counter != nullptr;
+  for (int wi = 0;; ++wi) {
     const int slot = wi % kGeomSlots;
     if (wi >= kGeomSlots) mbar_wait(&bar->geom_empty[slot], (wi / kGeomSlots - 1) & 1, 0x91);
-    if (lane == 0) bar->geom[slot] = make_geom<DUAL, SOLO, PAIR>(p, w, rank);
+    int w = 0;
+    if (lane == 0) w = dynamic ? (wi == 0 ? int(blockIdx.x) : int(gridDim.x) + atomicAdd(p.tile_counter, 1)) : work_index<PAIR>(wi);
+    w = __shfl_sync(0xffffffffu, w, 0);
+    const bool done = w >= n_work;
+    if (lane == 0) {
+      if (done) bar->geom[slot].w = -1;
+      else bar->geom[slot] = make_geom<DUAL, SOLO, PAIR>(p, w, rank);
+    }
     __syncwarp();
     if (lane == 0) mbar_arrive(&bar->geom_full[slot]);
+    if (done) break;
   }
 }
 
@@ -128,9 +141,12 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
   const bool with_qv = HD > 128 && p.qv_slices > 0;
   const uint32_t q_tx = uint32_t((p.qk_boxes + (with_qv ? p.v_boxes : 0)) * kRowBytes) * p.pack * p.pos_per_tile;
   const int n_work = total_work(p);
-  for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
+  for (int wi = 0;; ++wi) {
+    const int w = RING ? 0 : work_index<PAIR>(wi);
+    if (!RING && w >= n_work) break;
     const WorkGeom g = item_geom<DUAL, (HD > 128), PAIR, RING>(p, bar, w, wi, rank);
     item_geom_release<RING>(bar, wi);  // g is a copy
+    if (RING && g.w < 0) break;
     if (g.n_hi <= g.n_lo) continue;
 #pragma unroll
     for (int t = 0; t < kQTiles; ++t) {
@@ -363,15 +379,20 @@ FA_DEVICE void mma_role(const FwdKernelParams& p, uint32_t fmt, uint8_t* sQ, uin
   };
 
   const int n_work = total_work(p);
-  for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
+  for (int wi = 0;; ++wi) {
+    const int w = RING ? 0 : work_index<PAIR>(wi);
+    if (!RING && w >= n_work) break;
     int n_min[kQTiles], n_max[kQTiles], n_lo, n_hi, seq_k;
+    bool end_of_list;
     {
       const WorkGeom g = item_geom<DUAL, (HD > 128), PAIR, RING>(p, bar, w, wi, 0);  // the MMA warps run in the pair's rank 0
+      end_of_list = RING && g.w < 0;
       n_lo = g.n_lo; n_hi = g.n_hi; seq_k = g.seq.sk;
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) { n_min[t] = g.tr[t].n_min; n_max[t] = g.tr[t].n_max; }
     }
     item_geom_release<RING>(bar, wi);
+    if (end_of_list) break;
     if (n_hi <= n_lo) continue;
     if (kIsQK) {
 #pragma unroll

@@ -148,8 +148,16 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
   FA_PROF_DECL();  // 0 s_full wait, 1 S load, 2 s_free + mask + row max, 3 rescale, 4 exp chunks 0-1, 5 exp chunks 2-3, 6 st wait + publish, 7 rest
 
   const int n_work = total_work(p);
-  for (int wi = 0, w; (w = work_index<PAIR>(wi)) < n_work; ++wi) {
-    const RowGeom rg = row_geom<FP8, DUAL, (HD > 128), PAIR>(p, item_geom<DUAL, (HD > 128), PAIR, RING>(p, bar, w, wi, rank), t, row, rank);
+  for (int wi = 0;; ++wi) {
+    int w = RING ? 0 : work_index<PAIR>(wi);
+    if (!RING && w >= n_work) break;
+    RowGeom rg;
+    {
+      const WorkGeom g0 = item_geom<DUAL, (HD > 128), PAIR, RING>(p, bar, w, wi, rank);
+      if (RING && g0.w < 0) { item_geom_release<RING>(bar, wi); break; }
+      w = g0.w;
+      rg = row_geom<FP8, DUAL, (HD > 128), PAIR>(p, g0, t, row, rank);
+    }
     FA_PROF_E(6);
     if (!rg.has_rows) { item_geom_release<RING>(bar, wi); continue; }
     const float scale_log2 = rg.scale_log2;

@@ -41,7 +41,7 @@ class FwdParams(C.Structure):
         + [("softmax_scale", f32), ("softcap", f32)]
         + [(n, i32) for n in ("is_causal", "window_left", "window_right", "attention_chunk")]
         + [(n, i32) for n in ("num_splits", "pack_gqa", "num_sm")]
-        + [("scheduler_metadata", vp), ("variant", i32), ("merge_partial", i32), ("lse_accum_prefilled", i32), ("reserved", i32 * 5)]
+        + [("scheduler_metadata", vp), ("variant", i32), ("merge_partial", i32), ("lse_accum_prefilled", i32), ("reserved0", i32), ("tile_counter", vp), ("reserved", i32 * 2)]
         + [("qv", vp), ("qv_batch_stride", i64), ("qv_row_stride", i64), ("qv_head_stride", i64)]
     )
 

@@ -257,7 +257,14 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
             N.check(N.lib().fa100_prepare_scheduler(C.byref(p), _ptr(meta), meta.numel(), _stream()))
             p.scheduler_metadata = _ptr(meta)
             p.lse_accum_prefilled = int(lse_accum is not None and splits > 1 and p.merge_partial == 0)  # filled by that launch
+        counter = None
+        if (is_causal or window_size_left >= 0 or window_size_right >= 0) and seqlen_q > 256 and not p.scheduler_metadata and _DYNAMIC:
+            # dynamic tile scheduling (the reference's tile_count_semaphore, zeroed per call): a fresh counter per launch, so calls
+            # on different streams or replays of different graphs never share one
+            counter = torch.zeros(1, dtype=torch.int32, device=q.device)
+            p.tile_counter = _ptr(counter)
         N.check(N.lib().fa100_fwd(C.byref(p), _stream()))
+        del counter  # allocated and used on the current stream: the caching allocator reuses it only for later work of that stream
         if _partial is None and splits > 1:
             if varlen_q:  # (splits, h, total_q, dv) viewed as (splits, b=1, s=total_q, h, dv)
                 op = out_accum.permute(0, 2, 1, 3).unsqueeze(1)
@@ -270,6 +277,7 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
 
 META_HEADER = 8  # host-written words in front of the device-built schedule
 DYN_SPLIT_BOUND = 8  # partials a ragged decode call is sized for when the caller leaves num_splits to the library
+_DYNAMIC = os.environ.get("FA100_STATIC_SCHEDULE") != "1"  # A/B switch: FA100_STATIC_SCHEDULE=1 = no tile counter (static round-robin)
 _NO_SCHED = bool(os.environ.get("FA100_NO_SCHED"))  # A/B switch: static schedule for ragged batches too
 
 

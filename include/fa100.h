@@ -149,7 +149,14 @@ typedef struct Fa100FwdParams {
    * "empty partial" marker, in the same launch that builds the schedule): fa100_fwd then skips its own fill launch.
    * Leave 0 with a schedule built ahead of time (get_scheduler_metadata). */
   int32_t lse_accum_prefilled;
-  int32_t reserved[5];
+  int32_t reserved0;   /* must be 0 */
+  /* Dynamic tile scheduling (role of the reference's tile_count_semaphore, hopper/tile_scheduler.hpp:363-470,
+   * flash_api.cpp:996-1025): one int32 on the device that the CALLER HAS SET TO ZERO in stream order before this call and does
+   * not share with another launch in flight.  With it, under causal / local masks (row blocks of unequal length) the CTAs take work
+   * items from one length-ordered list as they finish instead of in a fixed round-robin; results are bitwise the same either way.
+   * Null = static schedule.  Carved out of the reserved words: the struct layout and ABI version are unchanged. */
+  int32_t* tile_counter;
+  int32_t reserved[2]; /* must be 0 */
   /* ABI version 2.  qv (hopper/flash_api.cpp:1028-1050, params.qv_ptr): a second query tensor (b, sq, h, dv) or packed
    * (total_q, h, dv), same dtype and layout rules as q; the scores become (q k^T + qv v^T) * softmax_scale.  Like the
    * reference: 16-bit dtypes, d <= 64, dv >= 256 (this library: dv == 256).  Null = off. */
