@@ -558,3 +558,32 @@ def test_qv_rules():
         F.flash_attn_func(mk(1, 8, 2, 64), mk(1, 8, 2, 64), mk(1, 8, 2, 128), qv=mk(1, 8, 2, 128))
     with pytest.raises(RuntimeError, match="wrong shape"):
         F.flash_attn_func(mk(1, 8, 2, 64), mk(1, 8, 2, 64), mk(1, 8, 2, 256), qv=mk(1, 9, 2, 256))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, E4M3])
+@pytest.mark.parametrize("kw", [dict(causal=True), dict(window_size=(300, 0)), dict(window_size=(200, 100)), dict(causal=True, softcap=20.0)])
+@pytest.mark.parametrize("b,sq,sk,h,hk,d", [(3, 1500, 1500, 8, 2, 128), (2, 1100, 2300, 6, 6, 64), (5, 700, 700, 4, 1, 128), (2, 900, 900, 4, 2, 256)])
+def test_dynamic_schedule(b, sq, sk, h, hk, d, kw, dtype, monkeypatch):
+    """Dynamic tile scheduling (Fa100FwdParams.tile_counter, the reference's tile_count_semaphore): the CTAs take the items of the
+    length-ordered list as they finish.  Which CTA computes an item does not change its arithmetic: the result is bitwise the one
+    of the static schedule, it matches the oracle, and a second call (fresh counter) repeats it."""
+    import fa100_ops
+
+    F = _iface()
+    fp8 = dtype == E4M3
+    g = torch.Generator().manual_seed(21)
+    mk = lambda *s: torch.randn(*s, generator=g).to(torch.bfloat16).to(dtype)  # noqa: E731
+    q, k, v = mk(b, sq, h, d), mk(b, sk, hk, d), mk(b, sk, hk, d)
+    qr, kr, vr = (x.to(torch.bfloat16) if fp8 else x for x in (q, k, v))
+    ref, lse_ref = A.attention_oracle(qr, kr, vr, **kw)
+    low, _ = A.attention_oracle(qr, kr, vr, upcast=False, reorder_ops=True, intermediate_dtype=dtype if fp8 else None, **kw)
+    monkeypatch.setattr(fa100_ops, "_DYNAMIC", False)
+    static, _ = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), return_attn_probs=True, **kw)
+    monkeypatch.setattr(fa100_ops, "_DYNAMIC", True)
+    for num_splits in (1, 3):
+        out, lse = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), num_splits=num_splits, return_attn_probs=True, **kw)
+        _check(out, lse, ref, low, lse_ref, rtol=4.0 if fp8 else (3.0 if kw.get("softcap") else 2.0))
+        if num_splits == 1:
+            assert torch.equal(out, static)
+            again, _ = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), return_attn_probs=True, **kw)
+            assert torch.equal(out, again)
