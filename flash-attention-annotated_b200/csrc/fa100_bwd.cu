@@ -178,7 +178,8 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
   uint8_t* sV = smem + 5 * kBwdTileBytes;      // V stages 0, 1: released as soon as dP is computed
   BwdBarriers* bar = reinterpret_cast<BwdBarriers*>(smem + 7 * kBwdTileBytes);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int m_blk = blockIdx.x, hq = blockIdx.y, bi = blockIdx.z;
+  // the hardware hands out blockIdx.x in ascending order: under a causal mask the late row blocks are the long ones, so they go first
+  const int m_blk = int(gridDim.x) - 1 - int(blockIdx.x), hq = blockIdx.y, bi = blockIdx.z;
   const int hk = hq / (p.h / p.h_k);
   if (tid == 0) {
     mbar_init(&bar->fixed_full, 1); mbar_init(&bar->s_ready, 1); mbar_init(&bar->mma_done, 1);
