@@ -315,6 +315,21 @@ fa100_bwd_dq_kernel(const __grid_constant__ BwdKernelParams p, const __grid_cons
             bwd_dsv2(o0, o1, bwd_ex2(x0), bwd_ex2(x1), __uint_as_float(dp[c][j]), __uint_as_float(dp[c][j + 1]), dsum, dsum);
             pk[c * 16 + j / 2] = bwd_pack<F16>(o0, o1);
           }
+      } else if (p.softcap_pre == 0.f) {
+        // masked block without softcap (the diagonal block of every causal item): the lean arithmetic, then columns outside this
+        // row's window [lo, hi) become 0 -- compile-time column index against two per-thread limits
+        const int hi = col_hi - n0 - part * kBwdCols, lo = col_lo - n0 - part * kBwdCols;
+#pragma unroll
+        for (int c = 0; c < kBwdC; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            float x0 = __uint_as_float(s[c][j]), x1 = __uint_as_float(s[c][j + 1]), o0, o1;
+            bwd_fma2(x0, x1, p.scale_log2, neg_lse2, neg_lse2);
+            bwd_dsv2(o0, o1, bwd_ex2(x0), bwd_ex2(x1), __uint_as_float(dp[c][j]), __uint_as_float(dp[c][j + 1]), dsum, dsum);
+            if (c * 32 + j >= hi || c * 32 + j < lo) o0 = 0.f;
+            if (c * 32 + j + 1 >= hi || c * 32 + j + 1 < lo) o1 = 0.f;
+            pk[c * 16 + j / 2] = bwd_pack<F16>(o0, o1);
+          }
       } else {
 #pragma unroll
         for (int c = 0; c < kBwdC; ++c)
@@ -453,9 +468,9 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar->rows_full[slot]);
     };
-    if (steps > 0) fetch_rows(0);
-    if (steps > 1) fetch_rows(1);
-    for (int t = 0; t < steps; ++t) {
+    // the first two steps' tiles go out before anything else (no stage to wait for): fetching their row constants first cost every
+    // CTA ~3 us before its first S^T could start -- a third of a 1024-token CTA's life
+    auto load_step = [&](int t) {
       const int st = t & 1;
       const int hq = hk * G + t / per_head, m = m_lo + t % per_head;
       if (lane == 0) {
@@ -467,6 +482,13 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
         bwd_load_tile(sQ + st * kBwdTileBytes, &tmQ, &bar->full[st], p.boxes, sq_.q_off + m * kBwdTile, hq, sq_.bq);
       }
       __syncwarp();
+    };
+    if (steps > 0) load_step(0);
+    if (steps > 1) load_step(1);
+    if (steps > 0) fetch_rows(0);
+    if (steps > 1) fetch_rows(1);
+    for (int t = 0; t < steps; ++t) {
+      if (t >= 2) load_step(t);
       if (t + 2 < steps) fetch_rows(t + 2);
     }
   } else if (warp == kBwdMmaWarp) {
@@ -550,6 +572,11 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
       // every key of the tile is visible from every query row of the step, no softcap: the lean path (CTA-uniform)
       const bool lean = p.softcap_pre == 0.f && (p.window_right < 0 || n0 + kBwdTile - 1 <= i0 + shift + p.window_right) &&
                         (p.window_left < 0 || n0 >= i0 + kBwdTile - 1 + shift - p.window_left);
+      // query columns [q_lo, q_hi) of this thread's kBwdCols see its key row: row i sees keys [i + shift - wl, i + shift + wr]
+      const int q_base = i0 + part * kBwdCols + shift;
+      const int q_lo = p.window_right >= 0 ? kj - p.window_right - q_base : -(1 << 30);
+      const int q_hi = p.window_left >= 0 ? kj + p.window_left - q_base + 1 : (1 << 30);
+      const bool plain = lean || p.softcap_pre == 0.f;  // s holds P (masked where needed) after the P phase
       mbar_wait(&bar->rows_full[slot], (t / kBwdRowSlots) & 1, 0xC8);
       mbar_wait(&bar->s_ready, t & 1, 0xC3);
       tc_fence_after();
@@ -568,6 +595,26 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
             bwd_fma2(x0, x1, p.scale_log2, l4.x, l4.y);
             bwd_fma2(x2, x3, p.scale_log2, l4.z, l4.w);
             const float p0 = bwd_ex2(x0), p1 = bwd_ex2(x1), p2 = bwd_ex2(x2), p3 = bwd_ex2(x3);
+            s[c][j] = __float_as_uint(p0); s[c][j + 1] = __float_as_uint(p1); s[c][j + 2] = __float_as_uint(p2); s[c][j + 3] = __float_as_uint(p3);
+            pk[c * 16 + j / 2] = bwd_pack<F16>(p0, p1);
+            pk[c * 16 + j / 2 + 1] = bwd_pack<F16>(p2, p3);
+          }
+      } else if (p.softcap_pre == 0.f) {
+        // masked step without softcap (the diagonal step of every causal key block): the lean arithmetic, then query columns that
+        // do not see this key row become 0; s keeps the masked P for the dS phase
+#pragma unroll
+        for (int c = 0; c < kBwdC; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 l4 = *reinterpret_cast<const float4*>(nl + c * 32 + j);
+            float x0 = __uint_as_float(s[c][j]), x1 = __uint_as_float(s[c][j + 1]), x2 = __uint_as_float(s[c][j + 2]), x3 = __uint_as_float(s[c][j + 3]);
+            bwd_fma2(x0, x1, p.scale_log2, l4.x, l4.y);
+            bwd_fma2(x2, x3, p.scale_log2, l4.z, l4.w);
+            float p0 = bwd_ex2(x0), p1 = bwd_ex2(x1), p2 = bwd_ex2(x2), p3 = bwd_ex2(x3);
+            if (c * 32 + j >= q_hi || c * 32 + j < q_lo) p0 = 0.f;
+            if (c * 32 + j + 1 >= q_hi || c * 32 + j + 1 < q_lo) p1 = 0.f;
+            if (c * 32 + j + 2 >= q_hi || c * 32 + j + 2 < q_lo) p2 = 0.f;
+            if (c * 32 + j + 3 >= q_hi || c * 32 + j + 3 < q_lo) p3 = 0.f;
             s[c][j] = __float_as_uint(p0); s[c][j + 1] = __float_as_uint(p1); s[c][j + 2] = __float_as_uint(p2); s[c][j + 3] = __float_as_uint(p3);
             pk[c * 16 + j / 2] = bwd_pack<F16>(p0, p1);
             pk[c * 16 + j / 2 + 1] = bwd_pack<F16>(p2, p3);
@@ -599,7 +646,7 @@ fa100_bwd_dkdv_kernel(const __grid_constant__ BwdKernelParams p, const __grid_co
 #pragma unroll
       for (int c = 0; c < kBwdC; ++c) tmem_ld32(tB + c * 32, dp[c]);
       tmem_ld_wait();
-      if (lean) {
+      if (plain) {
 #pragma unroll
         for (int c = 0; c < kBwdC; ++c)
 #pragma unroll

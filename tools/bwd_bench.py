@@ -5,7 +5,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "flash-attention-annotated_b200")]
 import torch
 import flash_attn_interface as F  # noqa: F401
-for (b, s, h, hk, causal) in ((8, 8192, 32, 8, True), (4, 8192, 16, 16, False), (2, 16384, 16, 16, True)):
+for (b, s, h, hk, causal) in ((8, 8192, 32, 8, True), (4, 8192, 16, 16, False), (2, 16384, 16, 16, True), (32, 1024, 16, 16, True), (16, 2048, 16, 16, True),
+                            (32, 1024, 16, 16, False), (8, 4096, 16, 16, True)):
     q = torch.randn(b, s, h, 128, device="cuda", dtype=torch.bfloat16)
     k = torch.randn(b, s, hk, 128, device="cuda", dtype=torch.bfloat16)
     v = torch.randn_like(k)
