@@ -587,3 +587,28 @@ def test_dynamic_schedule(b, sq, sk, h, hk, d, kw, dtype, monkeypatch):
             assert torch.equal(out, static)
             again, _ = F.flash_attn_func(q.to(DEV), k.to(DEV), v.to(DEV), return_attn_probs=True, **kw)
             assert torch.equal(out, again)
+
+
+def test_dynamic_schedule_cuda_graph():
+    """The tile counter is allocated and zeroed inside the op (torch.zeros): under CUDA-graph capture that is a memset node in front
+    of the kernel, so every replay starts from zero and reproduces the eager result bitwise."""
+    F = _iface()
+    g = torch.Generator().manual_seed(22)
+    q = torch.randn(2, 1300, 8, 128, generator=g).to(torch.bfloat16).to(DEV)
+    k = torch.randn(2, 1300, 2, 128, generator=g).to(torch.bfloat16).to(DEV)
+    v = torch.randn(2, 1300, 2, 128, generator=g).to(torch.bfloat16).to(DEV)
+    eager = F.flash_attn_func(q, k, v, causal=True)
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        F.flash_attn_func(q, k, v, causal=True)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = F.flash_attn_func(q, k, v, causal=True)
+    torch.cuda.current_stream().wait_stream(st)
+    for _ in range(3):
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, eager)
