@@ -152,11 +152,15 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   kp.window_left = wl; kp.window_right = wr; kp.attention_chunk = p->attention_chunk;
   kp.out_fp16 = p->dtype == FA100_FP16;
   // Dynamic scheduling over a length-ordered list (decode_work, geom_role) under causal / local masks, when the caller supplies a
-  // zeroed counter: not for CTA pairs (both CTAs must agree on the item) and not on top of a device-built schedule.  The
+  // zeroed counter: not for CTA pairs (both CTAs must agree on the item).  The
   // super-groups of the list are sized so that the K / V of the groups in flight stay in L2 (48 MB of its 126).
   kp.tile_counter = nullptr;
   kp.lpt_groups = 0;
-  if (p->tile_counter && !pair && (kp.is_causal || kp.is_local) && kp.sched == nullptr && kp.num_m_blocks > 1) {
+  if (p->tile_counter && !pair && kp.sched != nullptr) {
+    // ragged batch: the device-built list is already ordered (batch elements with the most key blocks first); the CTAs take its
+    // items as they finish instead of in a fixed deal
+    kp.tile_counter = p->tile_counter;
+  } else if (p->tile_counter && !pair && (kp.is_causal || kp.is_local) && kp.num_m_blocks > 1) {
     const int gsz = kp.heads_work / p->h_k;
     const int64_t kv_bytes = int64_t(p->seqlen_k) * (p->d + p->dv) * elt;
     const int64_t by_l2 = std::max<int64_t>(1, (int64_t(48) << 20) / std::max<int64_t>(1, kv_bytes));

@@ -247,6 +247,14 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
     p.variant = _variant()
     p.merge_partial = int(_merge) if _partial is not None else 0
     with _on_device(q.device):
+        counter = None
+        use_sched = (scheduler_metadata is not None and scheduler_metadata.numel() >= META_HEADER + _sched_words(b)) or ragged
+        if _DYNAMIC and pl.num_work > pl.num_sm and (use_sched or ((is_causal or window_size_left >= 0 or window_size_right >= 0) and seqlen_q > 256)):
+            # dynamic tile scheduling (the reference's tile_count_semaphore, zeroed per call) when the items are unequal (masks, ragged
+            # batches) and there are more of them than CTAs: a fresh counter per launch, so calls on different streams or replays of
+            # different graphs never share one.  Zeroed BEFORE the schedule kernel so that kernel and the forward stay PDL-chained.
+            counter = torch.zeros(1, dtype=torch.int32, device=q.device)
+            p.tile_counter = _ptr(counter)
         if scheduler_metadata is not None and scheduler_metadata.numel() >= META_HEADER + _sched_words(b):
             # the schedule get_scheduler_metadata built ahead of time (CUDA-graphed decode): used as is
             _chk(int(scheduler_metadata.numel()) >= META_HEADER, "scheduler_metadata is too short")
@@ -257,12 +265,6 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
             N.check(N.lib().fa100_prepare_scheduler(C.byref(p), _ptr(meta), meta.numel(), _stream()))
             p.scheduler_metadata = _ptr(meta)
             p.lse_accum_prefilled = int(lse_accum is not None and splits > 1 and p.merge_partial == 0)  # filled by that launch
-        counter = None
-        if (is_causal or window_size_left >= 0 or window_size_right >= 0) and seqlen_q > 256 and not p.scheduler_metadata and _DYNAMIC:
-            # dynamic tile scheduling (the reference's tile_count_semaphore, zeroed per call): a fresh counter per launch, so calls
-            # on different streams or replays of different graphs never share one
-            counter = torch.zeros(1, dtype=torch.int32, device=q.device)
-            p.tile_counter = _ptr(counter)
         N.check(N.lib().fa100_fwd(C.byref(p), _stream()))
         del counter  # allocated and used on the current stream: the caching allocator reuses it only for later work of that stream
         if _partial is None and splits > 1:
