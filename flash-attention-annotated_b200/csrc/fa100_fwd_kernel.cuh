@@ -84,7 +84,7 @@ struct FwdKernelParams {
   int32_t num_splits;
   int32_t num_work;       // static schedule: every (m block, batch, head, split); an upper bound when sched is set
   int32_t tiles_per_item; // 128-row Q tiles one work item covers: 2, or 1 in the dual-stream and head-dim-256 kernels
-  int32_t lpt_groups;     // > 0 (causal / local, static schedule): (batch, KV head) groups per super-group of the length-ordered work list
+  int32_t lpt_groups;     // > 0 (causal / local with a tile counter): (batch, KV head) groups per super-group of the length-ordered work list
   // Device-built schedule for ragged batches (fa100_prepare_scheduler): [0] work items, [1] batches, [2 .. 2+b) batch
   // ids, most key blocks first, [2+b .. 2+2b] exclusive prefix of work items over that order, [3+2b .. 3+3b) CTA-level
   // split count of each batch element in that order (<= num_splits).  Null: static schedule.
