@@ -13,6 +13,10 @@
 
 namespace fa100 {
 
+#ifndef FA100_LPT_L2_MB
+#define FA100_LPT_L2_MB 96  // K / V of the (batch, KV head) groups in flight under the length-ordered dynamic schedule
+#endif
+
 template <int HD, int ELT, bool FP8, bool F16, bool DUAL, bool PAIR = false>
 static int launch_instance(const FwdKernelParams& kp, const CUtensorMap& tmQ, const CUtensorMap& tmK,
                            const CUtensorMap& tmV, const CUtensorMap& tmO, const CUtensorMap& tmQv, uint32_t fmt, int grid, cudaStream_t stream) {
@@ -153,7 +157,7 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   kp.out_fp16 = p->dtype == FA100_FP16;
   // Dynamic scheduling over a length-ordered list (decode_work, geom_role) under causal / local masks, when the caller supplies a
   // zeroed counter: not for CTA pairs (both CTAs must agree on the item).  The
-  // super-groups of the list are sized so that the K / V of the groups in flight stay in L2 (48 MB of its 126).
+  // super-groups of the list are sized so that the K / V of the groups in flight stay in L2 (FA100_LPT_L2_MB).
   kp.tile_counter = nullptr;
   kp.lpt_groups = 0;
   if (p->tile_counter && !pair && kp.sched != nullptr) {
@@ -163,7 +167,7 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   } else if (p->tile_counter && !pair && (kp.is_causal || kp.is_local) && kp.num_m_blocks > 1) {
     const int gsz = kp.heads_work / p->h_k;
     const int64_t kv_bytes = int64_t(p->seqlen_k) * (p->d + p->dv) * elt;
-    const int64_t by_l2 = std::max<int64_t>(1, (int64_t(48) << 20) / std::max<int64_t>(1, kv_bytes));
+    const int64_t by_l2 = std::max<int64_t>(1, (int64_t(FA100_LPT_L2_MB) << 20) / std::max<int64_t>(1, kv_bytes));
     const int by_grid = std::max(1, plan->num_sm / std::max(1, gsz * cta_splits));
     kp.lpt_groups = int(std::min<int64_t>(std::min<int64_t>(by_l2, by_grid), int64_t(p->b) * p->h_k));
     kp.tile_counter = p->tile_counter;
