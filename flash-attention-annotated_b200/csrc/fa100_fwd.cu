@@ -364,16 +364,22 @@ int launch_fwd(const Fa100FwdParams* p, const Fa100Plan* plan, cudaStream_t stre
   // into the next sequence), no seqused_q, no pack-GQA (rows interleave heads), no fp32 partials; hdim <= 128.
   CUtensorMap tmO = tmQ;
   {
-    const bool o_tma = !(p->variant & FA100_VARIANT_NO_TMA_STORE) && p->o_accum == nullptr && !varlen_q && !p->seqused_q && kp.pack == 1 &&
+    // packed / seqused_q batches take the TMA path per tile (o_tma_check); the opt-in variant kernels keep it for dense batches only
+    const bool partial_rows = varlen_q || p->seqused_q != nullptr;
+    const bool variant_kernel = (p->variant & (FA100_VARIANT_FOUR_ROLE | FA100_VARIANT_SPLIT_ROWS)) != 0;
+    const bool o_tma = !(p->variant & FA100_VARIANT_NO_TMA_STORE) && p->o_accum == nullptr && !(partial_rows && variant_kernel) && kp.pack == 1 &&
                        std::max(p->d, p->dv) <= 128 && (p->o_row_stride * 2) % 16 == 0 && (p->o_head_stride * 2) % 16 == 0 &&
-                       (p->o_batch_stride * 2) % 16 == 0 && reinterpret_cast<uintptr_t>(p->o) % 16 == 0;
+                       (varlen_q || (p->o_batch_stride * 2) % 16 == 0) && reinterpret_cast<uintptr_t>(p->o) % 16 == 0;
     if (o_tma) {
-      uint64_t dims[4] = {uint64_t(p->dv), uint64_t(p->seqlen_q), uint64_t(p->h), uint64_t(p->b)};
-      uint64_t str[4] = {0, uint64_t(p->o_row_stride) * 2, uint64_t(p->o_head_stride) * 2, uint64_t(p->o_batch_stride) * 2};
+      // packed: one "batch" of total_q rows (the kernel adds the sequence's row offset)
+      uint64_t dims[4] = {uint64_t(p->dv), uint64_t(varlen_q ? p->total_q : p->seqlen_q), uint64_t(p->h), uint64_t(varlen_q ? 1 : p->b)};
+      uint64_t str[4] = {0, uint64_t(p->o_row_stride) * 2, uint64_t(p->o_head_stride) * 2,
+                         varlen_q ? uint64_t(p->o_row_stride) * 2 * uint64_t(p->total_q) : uint64_t(p->o_batch_stride) * 2};
       uint32_t box[4] = {64, 128, 1, 1};
       int rc = encode_tensor_map(&tmO, p->dtype == FA100_FP16 ? FA100_FP16 : FA100_BF16, 4, p->o, dims, str, box);
       if (rc) return rc;
       kp.o_tma = 1;
+      kp.o_tma_check = partial_rows ? 1 : 0;
     }
   }
   if (p->o_accum == nullptr) {

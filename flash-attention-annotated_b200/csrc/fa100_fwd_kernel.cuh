@@ -93,7 +93,8 @@ struct FwdKernelParams {
   int32_t num_sm;         // SMs the launch may use (the schedule kernel sizes the per-batch split counts with it)
   int32_t is_causal, is_local, window_left, window_right, attention_chunk;
   int32_t out_fp16;       // 1: fp16 output, 0: bf16 output
-  int32_t o_tma;          // 1: O leaves through shared memory and TMA stores (dense batch, no pack-GQA, no partials)
+  int32_t o_tma;          // 1: O leaves through shared memory and TMA stores (no pack-GQA, no partials)
+  int32_t o_tma_check;    // 1 (packed or seqused_q batches): only for tiles that lie wholly inside their sequence
   int32_t merge;          // 1 / 2: merge with the fp32 partial already in o_accum / lse_accum, in place / into o and lse
   float scale_log2;       // softmax_scale * log2(e)   (softcap: softcap * log2(e))
   float softcap_pre;      // softmax_scale / softcap, 0 when softcap is off

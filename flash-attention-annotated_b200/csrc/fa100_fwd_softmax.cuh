@@ -341,7 +341,9 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
                                             row_idx * p.o_row_stride + hq * p.o_head_stride);
       float4* o32 = reinterpret_cast<float4*>(p.o_accum + part * p.oacc_split_stride + g.it.bi * p.oacc_batch_stride +
                                               hq * p.oacc_head_stride + row_idx * p.dv);
-      if (HD <= 128 && p.o_tma) {
+      // packed (cu_seqlens_q) / seqused_q batches: a box that runs past the end of its sequence would write into the next one
+      // (or into rows the caller keeps), so only tiles that lie wholly inside take the TMA path (tile-uniform test)
+      if (HD <= 128 && p.o_tma && (!p.o_tma_check || pos - in_tile + kBlockM <= g.seq.sq)) {
         // TMA-store epilogue (role of the reference's smem_o + TMA store, hopper/epilogue_fwd.hpp:262-318): per 64-column
         // slice every thread converts its row, writes it into this tile's [128][128 B] staging box in the 128-byte
         // swizzle, and one thread sends the box with a bulk tensor store; rows past seqlen_q are clipped by the tensor map.
@@ -378,7 +380,7 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
           fence_proxy_async_smem();
           named_bar_sync(1 + t, 128);
           if (issuer) {
-            tma_store_4d(tmO, stage, sl * 64, pos - in_tile, hq, g.seq.bq);
+            tma_store_4d(tmO, stage, sl * 64, g.seq.q_off + pos - in_tile, hq, g.seq.bq);
             tma_store_commit();
           }
           FA_PROF_E(4);
