@@ -612,3 +612,47 @@ def test_dynamic_schedule_cuda_graph():
         graph.replay()
         torch.cuda.synchronize()
         assert torch.equal(out, eager)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_tma_store_stays_inside_sequences(causal):
+    """Packed and seqused_q batches take the TMA-store epilogue only for tiles that lie wholly inside their sequence (o_tma_check):
+    rows past a sequence's used length keep what the caller's buffer held, and no sequence's first rows are overwritten by the box of
+    the sequence in front of it (lengths that are not multiples of the 128-row tile)."""
+    import fa100_ops
+
+    g = torch.Generator().manual_seed(31)
+    h, hk, d = 4, 2, 128
+    # dense layout + seqused_q: rows [used, seqlen_q) must keep the sentinel
+    b, sq, sk = 3, 700, 900
+    q = torch.randn(b, sq, h, d, generator=g).to(torch.bfloat16)
+    k = torch.randn(b, sk, hk, d, generator=g).to(torch.bfloat16)
+    v = torch.randn(b, sk, hk, d, generator=g).to(torch.bfloat16)
+    used = torch.tensor([300, 513, 700], dtype=torch.int32)
+    out = torch.full((b, sq, h, d), 7.0, dtype=torch.bfloat16, device=DEV)
+    # num_splits = 1: with split-KV the combine kernel rewrites every row of `out` (rows past seqused_q become zeros)
+    res = fa100_ops.mha_fwd(q.to(DEV), k.to(DEV), v.to(DEV), out=out, seqused_q=used.to(DEV), is_causal=causal, num_splits=1)
+    torch.cuda.synchronize()
+    o = res[0].cpu()
+    for i in range(b):
+        u = int(used[i])
+        assert torch.all(o[i, u:] == 7.0), "rows past seqused_q were written"
+        ref, _ = A.attention_oracle(q[i:i + 1, :u], k[i:i + 1], v[i:i + 1], causal=causal)
+        low, _ = A.attention_oracle(q[i:i + 1, :u], k[i:i + 1], v[i:i + 1], causal=causal, upcast=False, reorder_ops=True)
+        _check(o[i:i + 1, :u], None, ref, low, None)
+    # packed layout: every sequence against the oracle (a box that ran over would have replaced the next sequence's first rows)
+    F = _iface()
+    lens = [130, 257, 1, 640, 383, 128, 900]
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32)
+    tot = int(cu[-1])
+    q = torch.randn(tot, h, d, generator=g).to(torch.bfloat16)
+    k = torch.randn(tot, hk, d, generator=g).to(torch.bfloat16)
+    v = torch.randn(tot, hk, d, generator=g).to(torch.bfloat16)
+    for _ in range(3):  # the order in which the CTAs finish varies from launch to launch
+        o, lse = F.flash_attn_varlen_func(q.to(DEV), k.to(DEV), v.to(DEV), cu.to(DEV), cu.to(DEV), max(lens), max(lens), causal=causal,
+                                          return_attn_probs=True)
+        for i, n in enumerate(lens):
+            sl = slice(int(cu[i]), int(cu[i + 1]))
+            ref, lse_ref = A.attention_oracle(q[sl][None], k[sl][None], v[sl][None], causal=causal)
+            low, _ = A.attention_oracle(q[sl][None], k[sl][None], v[sl][None], causal=causal, upcast=False, reorder_ops=True)
+            _check(o[sl][None], lse[:, sl][None], ref, low, lse_ref)
