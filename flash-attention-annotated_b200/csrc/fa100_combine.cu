@@ -23,6 +23,8 @@ __global__ void __launch_bounds__(kCombineWarps * 32) fa100_combine_kernel(const
     const int hh = int(r % p.h);
     const int ss = int((r / p.h) % p.s);
     const int bb = int(r / (int64_t(p.h) * p.s));
+    // rows past the sequence's used length are left as the caller had them (hopper/flash_fwd_combine_kernel.h, Varlen)
+    if (p.seqused != nullptr && ss >= p.seqused[bb]) continue;
     const float* lp = p.lse_partial + bb * p.lp_batch_stride + ss * p.lp_row_stride + hh * p.lp_head_stride;
     // 1. max and sum over splits (lanes stride over splits)
     float mx = -INFINITY;

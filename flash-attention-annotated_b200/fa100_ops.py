@@ -273,7 +273,7 @@ def mha_fwd(q, k, v, k_new=None, v_new=None, q_v=None, out=None, cu_seqlens_q=No
                 lp = lse_accum.permute(0, 2, 1).unsqueeze(1)
                 _combine_into(op, lp, out.unsqueeze(0), lse.t().unsqueeze(0))
             else:
-                _combine_into(out_accum.permute(0, 1, 3, 2, 4), lse_accum.permute(0, 1, 3, 2), out, lse.permute(0, 2, 1))
+                _combine_into(out_accum.permute(0, 1, 3, 2, 4), lse_accum.permute(0, 1, 3, 2), out, lse.permute(0, 2, 1), seqused=seqused_q)
     return out, lse, (out_accum if out_accum is not None else empty), (lse_accum if lse_accum is not None else empty)
 
 
@@ -363,7 +363,7 @@ def _append_kv(q, k, v, k_new, v_new, cu_seqlens_q, cu_seqlens_k_new, seqused_q,
     return (q_rot if q_rot is not None else q), new_lens
 
 
-def _combine_into(op, lp, out, lse):
+def _combine_into(op, lp, out, lse, seqused=None):
     """op (splits,b,s,h,d) fp32, lp (splits,b,s,h) fp32, out (b,s,h,d), lse (b,s,h) -- any strides, d stride 1."""
     splits, b, s, h, d = op.shape
     c = N.CombineParams()
@@ -373,6 +373,8 @@ def _combine_into(op, lp, out, lse):
     c.o_batch_stride, c.o_row_stride, c.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
     c.lse_batch_stride, c.lse_row_stride, c.lse_head_stride = lse.stride(0), lse.stride(1), lse.stride(2)
     c.num_splits, c.b, c.s, c.h, c.d, c.out_dtype = splits, b, s, h, d, _DT[out.dtype]
+    if seqused is not None:  # rows past a batch element's used length keep what the caller's buffer held
+        c.seqused = _ptr(seqused)
     N.check(N.lib().fa100_combine(C.byref(c), _stream()))
 
 

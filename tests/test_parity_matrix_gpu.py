@@ -630,16 +630,17 @@ def test_tma_store_stays_inside_sequences(causal):
     v = torch.randn(b, sk, hk, d, generator=g).to(torch.bfloat16)
     used = torch.tensor([300, 513, 700], dtype=torch.int32)
     out = torch.full((b, sq, h, d), 7.0, dtype=torch.bfloat16, device=DEV)
-    # num_splits = 1: with split-KV the combine kernel rewrites every row of `out` (rows past seqused_q become zeros)
-    res = fa100_ops.mha_fwd(q.to(DEV), k.to(DEV), v.to(DEV), out=out, seqused_q=used.to(DEV), is_causal=causal, num_splits=1)
-    torch.cuda.synchronize()
-    o = res[0].cpu()
-    for i in range(b):
-        u = int(used[i])
-        assert torch.all(o[i, u:] == 7.0), "rows past seqused_q were written"
-        ref, _ = A.attention_oracle(q[i:i + 1, :u], k[i:i + 1], v[i:i + 1], causal=causal)
-        low, _ = A.attention_oracle(q[i:i + 1, :u], k[i:i + 1], v[i:i + 1], causal=causal, upcast=False, reorder_ops=True)
-        _check(o[i:i + 1, :u], None, ref, low, None)
+    for num_splits in (1, 0, 3):  # one pass; the library's choice (split-KV here: few tiles) and a forced split, both through fa100_combine
+      out.fill_(7.0)
+      res = fa100_ops.mha_fwd(q.to(DEV), k.to(DEV), v.to(DEV), out=out, seqused_q=used.to(DEV), is_causal=causal, num_splits=num_splits)
+      torch.cuda.synchronize()
+      o = res[0].cpu()
+      for i in range(b):
+          u = int(used[i])
+          assert torch.all(o[i, u:] == 7.0), "rows past seqused_q were written"
+          ref, _ = A.attention_oracle(q[i:i + 1, :u], k[i:i + 1], v[i:i + 1], causal=causal)
+          low, _ = A.attention_oracle(q[i:i + 1, :u], k[i:i + 1], v[i:i + 1], causal=causal, upcast=False, reorder_ops=True)
+          _check(o[i:i + 1, :u], None, ref, low, None)
     # packed layout: every sequence against the oracle (a box that ran over would have replaced the next sequence's first rows)
     F = _iface()
     lens = [130, 257, 1, 640, 383, 128, 900]
