@@ -117,5 +117,6 @@ extern "C" int fa100_fwd_splitkv_noalloc(const Fa100FwdParams* p, fa100_stream_t
   c.lse_batch_stride = int64_t(p->h) * p->seqlen_q; c.lse_head_stride = p->seqlen_q; c.lse_row_stride = 1;
   c.num_splits = splits; c.b = p->b; c.s = p->seqlen_q; c.h = p->h; c.d = p->dv;
   c.out_dtype = p->dtype == FA100_FP16 ? FA100_FP16 : FA100_BF16;
+  c.seqused = p->seqused_q;  // rows past a batch element's used length stay as the caller had them
   return launch_combine(&c, stream);
 }
