@@ -1,4 +1,4 @@
-// fa100_bwd.cu -- backward pass of the attention forward, first version.
+// fa100_bwd.cu -- backward pass of the attention forward.
 //
 // Role of hopper/flash_bwd_launch_template.h + mainloop_bwd_sm90_tma_gmma_ws.hpp + flash_bwd_preprocess_kernel.h (and of
 // flash_attn/cute/flash_bwd_sm100.py) re-designed around tensor memory, with the same math:
@@ -7,18 +7,18 @@
 //   dP   = dO V^T,   dS = P o (dP - D)
 //   dV   = P^T dO,   dK = scale * dS^T Q,   dQ = scale * dS K
 // Three launches, no atomics, bitwise deterministic:
-//   fa100_bwd_dot_kernel     one warp per query row: D
-//   fa100_bwd_dq_kernel      one CTA per (128-row query block, head, batch) walks the key blocks: S and dP in TMEM (fp32), one
-//                            thread per query row turns them into dS (16 bit, written over S's columns), dQ += dS K with dS as
-//                            the TMEM A operand -- the forward's P V form
+//   fa100_bwd_dot_*kernel    D, memory-bound (16-byte loads, two rows per warp pass; a scalar fallback for unaligned rows)
+//   fa100_bwd_dq_kernel      one CTA per (128-row query block, head, batch) walks the key blocks: S and dP in TMEM (fp32), the
+//                            workers turn them into dS (16 bit, in its own double-buffered TMEM columns), dQ += dS K with dS as
+//                            the TMEM A operand -- the forward's P V form; the next block's S / dP overlap this block's dS
 //   fa100_bwd_dkdv_kernel    one CTA per (128-key block, KV head, batch) walks the query blocks of every query head of the
-//                            group: S^T = K Q^T and dP^T = V dO^T (keys on the TMEM lanes), one thread per key row makes P^T
-//                            and dS^T, dV += P^T dO and dK += dS^T Q, again in the forward's P V form; the GQA sum over the
-//                            group's heads happens in the accumulators
+//                            group: S^T = K Q^T and dP^T = V dO^T (keys on the TMEM lanes), the workers make P^T, then dS^T
+//                            (two phases pipelined against the tensor pipe), dV += P^T dO and dK += dS^T Q, again in the
+//                            forward's P V form; the GQA sum over the group's heads happens in the accumulators
 // Recomputing S and dP in both kernels costs 7 instead of 5 MMAs per (query block, key block) pair and buys: no dQ atomics,
 // no transposes, only operand forms the forward kernel already uses (SS K-major x K-major, TS with an MN-major B).
-// Simple CTAs (128 threads, one issuing thread, two-stage TMA prefetch); the tensor pipe and the elementwise work of a step
-// are serialised -- this is the functional first version, not the tuned one.
+// Both main kernels have the forward's role structure: 16 worker warps (four threads per TMEM lane), a TMA warp, an MMA-issuing
+// warp, mbarrier hand-offs (DESIGN.md 4.8 has the pipelines and what the jitter build found in them).
 #include "fa100_host.h"
 #include "fa100_ptx.cuh"
 
