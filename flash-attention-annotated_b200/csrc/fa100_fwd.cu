@@ -167,7 +167,11 @@ static void fill_kernel_params(const Fa100FwdParams* p, const Fa100Plan* plan, F
   } else if (p->tile_counter && !pair && (kp.is_causal || kp.is_local) && kp.num_m_blocks > 1) {
     const int gsz = kp.heads_work / p->h_k;
     const int64_t kv_bytes = int64_t(p->seqlen_k) * (p->d + p->dv) * elt;
-    const int64_t by_l2 = std::max<int64_t>(1, (int64_t(FA100_LPT_L2_MB) << 20) / std::max<int64_t>(1, kv_bytes));
+    // MHA (one query head per K / V head and row-block level) needs more groups in flight for an even deal and gets the whole budget;
+    // with several query heads per K / V head half of it balances as well and keeps C2's DRAM traffic at the algorithmic 1.4 GB
+    // (2.7 GB with the whole budget, same speed: profiles/r02p_c2_fwd_ncu_full_lpt96.md)
+    const int64_t l2_bytes = (int64_t(FA100_LPT_L2_MB) << 20) / (gsz == 1 ? 1 : 2);
+    const int64_t by_l2 = std::max<int64_t>(1, l2_bytes / std::max<int64_t>(1, kv_bytes));
     const int by_grid = std::max(1, plan->num_sm / std::max(1, gsz * cta_splits));
     kp.lpt_groups = int(std::min<int64_t>(std::min<int64_t>(by_l2, by_grid), int64_t(p->b) * p->h_k));
     kp.tile_counter = p->tile_counter;
