@@ -40,13 +40,25 @@ FA_DEVICE uint16_t pack8_v(uint32_t lo, uint32_t hi) {
   asm volatile("cvt.rn.satfinite.e4m3x2.f32 %0, %2, %1;" : "=h"(r) : "r"(lo), "r"(hi));
   return r;
 }
-// Build-time experiment switches (default off = the product kernel): every FA100_E2E_MOD-th score pair of the first three
-// chunks of a row (FA100_E2E_MOD_FP8 for the e4m3 kernels) takes the polynomial exp2 below instead of the MUFU.
+// Polynomial exp2 on a share of the scores: every kMod-th score pair of the first kLim pairs of a row takes ex2_poly2_v (FMA
+// pipe) instead of the MUFU.  On by default for 16-bit head dim 64 only (every third pair of all 64): there the tensor work per
+// score is half that of head dim 128 and the MUFU is the one wall (+5 % causal, +8 % non-causal at 8 k tokens,
+// profiles/r02q_ab_poly_exp2_hdim64.log); at head dim 128 and for e4m3 every setting measured neutral or slower
+// (profiles/r02_ab_poly_exp2_default_kernel.log), so those stay build-time experiment switches, default off.
 #ifndef FA100_E2E_MOD
 #define FA100_E2E_MOD 0
 #endif
 #ifndef FA100_E2E_MOD_FP8
 #define FA100_E2E_MOD_FP8 FA100_E2E_MOD
+#endif
+#ifndef FA100_E2E_MOD_D64
+#define FA100_E2E_MOD_D64 3
+#endif
+#ifndef FA100_E2E_LIM
+#define FA100_E2E_LIM 48
+#endif
+#ifndef FA100_E2E_LIM_D64
+#define FA100_E2E_LIM_D64 64
 #endif
 // exp2 of two scores on the FMA pipe instead of the MUFU (Cody-Waite split + degree-3 polynomial on [0, 1), the scheme of
 // the reference's Blackwell kernel, flash_attn/cute/utils.py:601-681): x <= 0 here, clamped at -127; relative error ~1e-4,
@@ -257,8 +269,10 @@ FA_DEVICE void softmax_role(const FwdKernelParams& p, const CUtensorMap* tmO, ui
         for (int k = -kAhead; k < 64 + kBehind; ++k) {
           if (k + kAhead < 64) { const int a = k + kAhead; ffma2_v(s[a >> 4][(a & 15) * 2], s[a >> 4][(a & 15) * 2 + 1], scale_log2, neg_m); }
           if (k >= 0 && k < 64) {
-            constexpr int kMod = FP8 ? FA100_E2E_MOD_FP8 : FA100_E2E_MOD;
-            if (kMod > 0 && k < 48 && (k % (kMod > 0 ? kMod : 1)) == (kMod > 0 ? kMod : 1) - 1) ex2_poly2_v(s[k >> 4][(k & 15) * 2], s[k >> 4][(k & 15) * 2 + 1]);
+            constexpr bool kD64 = !FP8 && HD == 64;
+            constexpr int kMod = FP8 ? FA100_E2E_MOD_FP8 : (kD64 ? FA100_E2E_MOD_D64 : FA100_E2E_MOD);
+            constexpr int kLim = kD64 ? FA100_E2E_LIM_D64 : FA100_E2E_LIM;
+            if (kMod > 0 && k < kLim && (k % (kMod > 0 ? kMod : 1)) == (kMod > 0 ? kMod : 1) - 1) ex2_poly2_v(s[k >> 4][(k & 15) * 2], s[k >> 4][(k & 15) * 2 + 1]);
             else { ex2_v(s[k >> 4][(k & 15) * 2]); ex2_v(s[k >> 4][(k & 15) * 2 + 1]); }
           }
           if (k - kBehind >= 0) {

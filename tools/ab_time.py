@@ -8,10 +8,13 @@ sys.path[:0] = [os.path.join(%r, "flash-attention-annotated_b200")]
 from flash_attn_interface import flash_attn_func
 dev = "cuda"
 res = []
-for (b, s, h, hk, causal, dt) in ((8, 8192, 32, 8, True, torch.bfloat16), (4, 8192, 32, 8, False, torch.bfloat16), (4, 16384, 16, 16, True, torch.float8_e4m3fn), (4, 16384, 16, 16, False, torch.float8_e4m3fn)):
-    q = torch.randn(b, s, h, 128, device=dev, dtype=torch.bfloat16).to(dt)
-    k = torch.randn(b, s, hk, 128, device=dev, dtype=torch.bfloat16).to(dt)
-    v = torch.randn(b, s, hk, 128, device=dev, dtype=torch.bfloat16).to(dt)
+D = int(os.environ.get("AB_HEADDIM", "128"))  # AB_HEADDIM=64: the sweep's hdim-64 shapes (MHA, 32 heads) instead of C2 / C3
+shapes = ((8, 8192, 32, 8, True, torch.bfloat16), (4, 8192, 32, 8, False, torch.bfloat16), (4, 16384, 16, 16, True, torch.float8_e4m3fn), (4, 16384, 16, 16, False, torch.float8_e4m3fn))
+if D != 128: shapes = ((4, 8192, 32, 32, True, torch.bfloat16), (4, 8192, 32, 32, False, torch.bfloat16), (16, 2048, 32, 32, True, torch.bfloat16), (2, 16384, 32, 32, False, torch.bfloat16))
+for (b, s, h, hk, causal, dt) in shapes:
+    q = torch.randn(b, s, h, D, device=dev, dtype=torch.bfloat16).to(dt)
+    k = torch.randn(b, s, hk, D, device=dev, dtype=torch.bfloat16).to(dt)
+    v = torch.randn(b, s, hk, D, device=dev, dtype=torch.bfloat16).to(dt)
     for _ in range(3): flash_attn_func(q, k, v, causal=causal)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -19,7 +22,7 @@ for (b, s, h, hk, causal, dt) in ((8, 8192, 32, 8, True, torch.bfloat16), (4, 81
     for _ in range(10): flash_attn_func(q, k, v, causal=causal)
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
-    fl = b * h * 2 * s * (s / 2 if causal else s) * 256
+    fl = b * h * 2 * s * (s / 2 if causal else s) * 2 * D
     res.append(fl / ms / 1e9)
 print("RES", *[f"{x:.1f}" for x in res])
 ''' % ROOT
@@ -34,7 +37,8 @@ for r in range(rounds):
         if not line:
             print(l, "FAILED", p.stderr[-500:]); continue
         out[l].append([float(x) for x in line[0].split()[1:]])
-print(f"{'library':28s} {'bf16 causal':>22s} {'bf16 non-causal':>22s} {'fp8 causal':>22s} {'fp8 non-causal':>22s}   (TFLOPS: best / median of {rounds})")
+heads = ("bf16 causal", "bf16 non-causal", "fp8 causal", "fp8 non-causal") if os.environ.get("AB_HEADDIM", "128") == "128" else ("8k causal", "8k non-causal", "2k causal", "16k non-causal")
+print(f"{'library':28s} " + " ".join(f"{x:>22s}" for x in heads) + f"   (TFLOPS: best / median of {rounds})")
 for l in libs:
     if out[l]:
         cols = list(zip(*out[l]))

@@ -1,7 +1,7 @@
 """The reference's headline sweep (hopper/benchmark_attn.py:229-420) for fa100: dim 2048 split into heads of 64 / 128 / 256,
 (batch, seqlen) pairs with batch * seqlen = 32 k tokens, causal and non-causal, forward and backward, in TFLOP/s with the
 reference's FLOP count (`flops`, :62-73; backward = 2.5 x forward).  cuDNN (torch SDPA backend) and flash_attn 2.8 are timed
-beside it where they run.  python tools/benchmark_attn.py [--fp8] > profiles/<tag>_benchmark_attn_sweep.txt"""
+beside it where they run.  python tools/benchmark_attn.py [--fp8] [--hdim 64] [--fwd-only] > profiles/<tag>_benchmark_attn_sweep.txt"""
 import os
 import sys
 
@@ -12,6 +12,8 @@ import torch.nn.functional as F
 from flash_attn_interface import flash_attn_func
 
 FP8 = "--fp8" in sys.argv
+FWD_ONLY = "--fwd-only" in sys.argv
+HDIMS = (int(sys.argv[sys.argv.index("--hdim") + 1]),) if "--hdim" in sys.argv else (64, 128, 256)
 dev = "cuda"
 
 
@@ -52,7 +54,7 @@ def fa2_fwd(q, k, v, causal):
 
 print(f"# fa100 sweep ({'e4m3' if FP8 else 'bf16'}), dim 2048, batch x seqlen = 32768 tokens; TFLOP/s (backward counted as 2.5 x forward)")
 print(f"{'hdim':>4} {'causal':>6} {'batch':>5} {'seqlen':>6} | {'fa100 fwd':>9} {'fa100 bwd':>9} | {'cuDNN fwd':>9} {'FA2 fwd':>8}")
-for headdim in (64, 128, 256):
+for headdim in HDIMS:
     nheads = 2048 // headdim
     for causal in (False, True):
         for batch, seqlen in ((32, 1024), (16, 2048), (8, 4096), (4, 8192), (2, 16384)):
@@ -67,7 +69,7 @@ for headdim in (64, 128, 256):
             else:
                 ms_f = timeit(lambda: flash_attn_func(q, k, v, causal=causal))
                 ms_b = None
-                if headdim <= 128:
+                if headdim <= 128 and not FWD_ONLY:
                     out, lse, *_ = torch.ops.flash_attn_3.fwd(q, k, v, is_causal=causal)
                     g = torch.randn_like(out)
                     ms_b = timeit(lambda: torch.ops.flash_attn_3.bwd(g, q, k, v, out, lse, None, None, None, None, None, None, None, None, None, None, causal), iters=5)
