@@ -226,7 +226,17 @@ FA_DEVICE void producer_role(const FwdKernelParams& p, const CUtensorMap* tmQ, c
       __syncwarp();
       ring_advance<kRing>(ring);
     };
-    if (!DUAL) {
+    if (!DUAL && kRing == 1 && !with_qv) {
+      // One K and one V stage (16-bit hdim-256 instance): K(nb - 1) goes out BEFORE V(nb).  This warp waits in program order, and
+      // V(nb)'s stage is free only when P V(nb + 1) has completed -- a full key block after QK(nb) released the K stage; behind
+      // V(nb) the K load started that late and every key block paid load latency + both products in series.  The QK and PV warps
+      // watch their own stages only, so the order between the kinds is free (not with qv: there QK(nb) also reads V(nb)).
+      load_tile(0, g.n_hi - 1);
+      for (int nb = g.n_hi - 1; nb >= g.n_lo; --nb) {
+        if (nb - 1 >= g.n_lo) load_tile(0, nb - 1);
+        load_tile(1, nb);
+      }
+    } else if (!DUAL) {
       // ring order == the order the MMA warp consumes: K(first), then V(nb), K(nb-1) per key block
       for (int nb = g.n_hi - 1; nb >= g.n_lo; --nb) { load_tile(0, nb); load_tile(1, nb); }
     } else {
